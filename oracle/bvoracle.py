@@ -1,0 +1,207 @@
+"""ctypes front end of the CPU oracle (oracle/bvoracle.c).
+
+TEST INFRASTRUCTURE ONLY: imported by tests/, by __graft_entry__.smoke() and by bench.py's cpu_baseline /
+``--impl reference`` legs -- never by the product package.  See the header of bvoracle.c for the parity status.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+# CompressionFlags.java:26-46
+DELTA, GAMMA, GOLOMB, SKEWED_GOLOMB, UNARY, ZETA, NIBBLE = 1, 2, 3, 4, 5, 6, 7
+_CODING = {"DELTA": DELTA, "GAMMA": GAMMA, "GOLOMB": GOLOMB, "SKEWED_GOLOMB": SKEWED_GOLOMB,
+           "UNARY": UNARY, "ZETA": ZETA, "NIBBLE": NIBBLE}
+# bit slot of each field inside the flag mask, BVG:475-524 / setFlags BVG:1281-1289
+_SLOT = {"OUTDEGREES": 0, "BLOCKS": 4, "RESIDUALS": 8, "REFERENCES": 12, "BLOCK_COUNT": 16, "OFFSETS": 20}
+# the constants BVGraph actually declares (string2Flags resolves names by reflection, BVG:1316-1331)
+_DECLARED = {
+    "OUTDEGREES_GAMMA", "OUTDEGREES_DELTA", "BLOCKS_GAMMA", "BLOCKS_DELTA", "RESIDUALS_GAMMA", "RESIDUALS_ZETA",
+    "RESIDUALS_DELTA", "RESIDUALS_NIBBLE", "RESIDUALS_GOLOMB", "REFERENCES_GAMMA", "REFERENCES_DELTA",
+    "REFERENCES_UNARY", "BLOCK_COUNT_GAMMA", "BLOCK_COUNT_DELTA", "BLOCK_COUNT_UNARY", "OFFSETS_GAMMA",
+    "OFFSETS_DELTA",
+}
+
+
+class Params(C.Structure):
+    _fields_ = [("nodes", C.c_int64), ("arcs", C.c_int64),
+                ("window", C.c_int32), ("maxref", C.c_int32), ("minint", C.c_int32), ("zetak", C.c_int32),
+                ("outdegree_coding", C.c_int32), ("block_coding", C.c_int32), ("residual_coding", C.c_int32),
+                ("reference_coding", C.c_int32), ("blockcount_coding", C.c_int32), ("offset_coding", C.c_int32)]
+
+
+def build(force=False):
+    so = os.path.join(_HERE, "libbvoracle.so")
+    src = os.path.join(_HERE, "bvoracle.c")
+    if force or not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-C", _HERE, "-s", "-B", "libbvoracle.so"])
+    return so
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        L = C.CDLL(build())
+        u8p, u64p, i64p = C.POINTER(C.c_uint8), C.POINTER(C.c_uint64), C.POINTER(C.c_int64)
+        L.bvo_read_offsets.argtypes = [C.POINTER(Params), C.c_void_p, C.c_uint64, C.c_void_p]
+        L.bvo_read_offsets.restype = C.c_int
+        L.bvo_outdegree.argtypes = [C.POINTER(Params), C.c_void_p, C.c_uint64, C.c_void_p, C.c_int64]
+        L.bvo_outdegree.restype = C.c_int64
+        L.bvo_successors.argtypes = [C.POINTER(Params), C.c_void_p, C.c_uint64, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64]
+        L.bvo_successors.restype = C.c_int64
+        L.bvo_decode_range.argtypes = [C.POINTER(Params), C.c_void_p, C.c_uint64, C.c_void_p, C.c_int64, C.c_int64,
+                                       C.c_void_p, C.c_void_p, C.c_int64]
+        L.bvo_decode_range.restype = C.c_int64
+        L.bvo_decode_split.argtypes = [C.POINTER(Params), C.c_void_p, C.c_uint64, C.c_void_p, C.c_int64, C.c_int64,
+                                       C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.bvo_decode_split.restype = C.c_int64
+        L.bvo_read_code.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64), C.c_int, C.c_int]
+        L.bvo_read_code.restype = C.c_uint64
+        del u8p, u64p, i64p
+        _LIB = L
+    return _LIB
+
+
+def parse_properties(text):
+    """java.util.Properties subset: key=value / key:value lines, # and ! comments."""
+    props = {}
+    for line in text.splitlines():
+        line = line.strip()
+        if not line or line[0] in "#!":
+            continue
+        for i, ch in enumerate(line):
+            if ch in "=:":
+                props[line[:i].strip()] = line[i + 1:].strip()
+                break
+        else:
+            props[line] = ""
+    return props
+
+
+def string2flags(s):
+    """BVGraph.string2Flags, BVG:1316-1331."""
+    flags = 0
+    if s:
+        for name in s.split("|"):
+            name = name.strip()
+            if name not in _DECLARED:
+                raise IOError(f"Compression flag {name} unknown.")
+            field, coding = next((f, name[len(f) + 1:]) for f in _SLOT if name.startswith(f + "_"))
+            flags |= _CODING[coding] << _SLOT[field]
+    return flags
+
+
+def params_from_properties(props):
+    """The checks and assignments of BVGraph.loadInternal, BVG:1482-1503."""
+    gc = props.get("graphclass", "")
+    if gc.replace("it.unimi.dsi.webgraph", "it.unimi.dsi.big.webgraph") != "it.unimi.dsi.big.webgraph.BVGraph":
+        raise IOError(f'cannot load a graph stored using class "{gc}"')
+    if "version" not in props:
+        raise IOError("Missing format version information")
+    if int(props["version"]) > 0:
+        raise IOError("format too new")
+    flags = string2flags(props.get("compressionflags", ""))
+    p = Params(nodes=int(props["nodes"]), arcs=int(props["arcs"]), window=int(props["windowsize"]),
+               maxref=int(props["maxrefcount"]), minint=int(props["minintervallength"]),
+               zetak=int(props.get("zetak", 3)),
+               outdegree_coding=GAMMA, block_coding=GAMMA, residual_coding=ZETA, reference_coding=UNARY,
+               blockcount_coding=GAMMA, offset_coding=GAMMA)
+    for slot, field in ((0, "outdegree_coding"), (4, "block_coding"), (8, "residual_coding"),
+                        (12, "reference_coding"), (16, "blockcount_coding"), (20, "offset_coding")):
+        v = (flags >> slot) & 0xF
+        if v:
+            setattr(p, field, v)
+    return p
+
+
+class OracleGraph:
+    """A BVGraph held in host memory and decoded by the CPU oracle."""
+
+    def __init__(self, params, graph_bytes, offsets_bytes=None, offsets=None):
+        self.p = params
+        self.graph = np.frombuffer(graph_bytes, dtype=np.uint8) if not isinstance(graph_bytes, np.ndarray) else graph_bytes
+        self.graph = np.ascontiguousarray(self.graph)
+        if offsets is None and offsets_bytes is not None:
+            ob = np.ascontiguousarray(np.frombuffer(offsets_bytes, dtype=np.uint8))
+            offsets = np.zeros(params.nodes + 1, dtype=np.uint64)
+            rc = lib().bvo_read_offsets(C.byref(self.p), ob.ctypes.data, ob.size, offsets.ctypes.data)
+            if rc:
+                raise IOError(f"bvo_read_offsets failed: {rc}")
+        self.offsets = offsets
+
+    @classmethod
+    def load(cls, basename):
+        with open(basename + ".properties") as f:
+            params = params_from_properties(parse_properties(f.read()))
+        with open(basename + ".graph", "rb") as f:
+            g = f.read()
+        with open(basename + ".offsets", "rb") as f:
+            o = f.read()
+        return cls(params, g, o)
+
+    @property
+    def num_nodes(self):
+        return self.p.nodes
+
+    def _off(self):
+        return self.offsets.ctypes.data if self.offsets is not None else None
+
+    def outdegree(self, x):
+        d = lib().bvo_outdegree(C.byref(self.p), self.graph.ctypes.data, self.graph.size, self._off(), x)
+        if d < 0:
+            raise _err(d)
+        return d
+
+    def successors(self, x):
+        d = self.outdegree(x)
+        out = np.empty(max(d, 1), dtype=np.int64)
+        r = lib().bvo_successors(C.byref(self.p), self.graph.ctypes.data, self.graph.size, self._off(), x, out.ctypes.data, out.size)
+        if r < 0:
+            raise _err(r)
+        return out[:r]
+
+    def decode_range(self, lo=0, hi=None, threads=1, want_col=True):
+        """Sequential (threads == 1, nodeIterator) or split (splitNodeIterators) scan of [lo, hi): (deg, col)."""
+        hi = self.p.nodes if hi is None else hi
+        n = max(hi - lo, 0)
+        deg = np.zeros(n, dtype=np.int64)
+        L = lib()
+        g, gb = self.graph.ctypes.data, self.graph.size
+        if threads <= 1:
+            arcs = L.bvo_decode_range(C.byref(self.p), g, gb, self._off(), lo, hi, deg.ctypes.data, None, 0)
+            if arcs < 0:
+                raise _err(arcs)
+            if not want_col:
+                return deg, None
+            col = np.empty(max(arcs, 1), dtype=np.int64)
+            arcs2 = L.bvo_decode_range(C.byref(self.p), g, gb, self._off(), lo, hi, deg.ctypes.data, col.ctypes.data, col.size)
+            assert arcs2 == arcs, (arcs, arcs2)
+            return deg, col[:arcs]
+        arcs = L.bvo_decode_split(C.byref(self.p), g, gb, self._off(), lo, hi, threads, deg.ctypes.data, None, None)
+        if arcs < 0:
+            raise _err(arcs)
+        if not want_col:
+            return deg, None
+        rowptr = np.zeros(n + 1, dtype=np.int64)
+        np.cumsum(deg, out=rowptr[1:])
+        col = np.empty(max(arcs, 1), dtype=np.int64)
+        arcs2 = L.bvo_decode_split(C.byref(self.p), g, gb, self._off(), lo, hi, threads, deg.ctypes.data, col.ctypes.data, rowptr.ctypes.data)
+        assert arcs2 == arcs
+        return deg, col[:arcs]
+
+
+def read_code(buf, bitpos, coding, k=3):
+    b = np.ascontiguousarray(np.frombuffer(buf, dtype=np.uint8))
+    pos = C.c_uint64(bitpos)
+    v = lib().bvo_read_code(b.ctypes.data, b.size, C.byref(pos), coding, k)
+    return v, pos.value
+
+
+def _err(code):
+    return {-1: IndexError("Node index out of range"), -2: RuntimeError("illegal state (malformed stream / bad reference)"),
+            -3: IOError("bit stream overrun"), -4: NotImplementedError("unsupported coding"),
+            -5: MemoryError("capacity")}.get(code, RuntimeError(f"oracle error {code}"))
