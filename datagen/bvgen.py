@@ -181,6 +181,7 @@ def csr_checksum(first_node, rowptr, col):
 
 def write_codes(coding, values, k=3):
     vals = np.ascontiguousarray(values, dtype=np.uint64)
-    out = np.zeros(vals.size * 17 + 64, dtype=np.uint8)
+    per = 17 if coding not in (UNARY, GOLOMB) else int(vals.max() if vals.size else 0) // 8 + 17
+    out = np.zeros(vals.size * per + 64, dtype=np.uint8)
     bits = lib().bvg_write_codes(coding, k, vals.ctypes.data, vals.size, out.ctypes.data, out.size)
     return out[: (bits + 7) // 8].copy(), bits

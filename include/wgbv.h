@@ -1,0 +1,187 @@
+/*
+ * wgbv.h -- C ABI of libwgbv, a B200 (sm_100a) BVGraph decompression engine.
+ *
+ * This is the drop-in boundary behind webgraph-big's ImmutableGraph API for the BVGraph -> CSR decode path:
+ * every entry point names the reference interface it stands in for.  "BVG" is
+ * src/it/unimi/dsi/big/webgraph/BVGraph.java and "IG" is src/it/unimi/dsi/big/webgraph/ImmutableGraph.java of
+ * webgraph-big 3.7.1.  Plain C: opaque handles, plain pointers and sizes, integer status codes -- callable from
+ * Java (Panama FFM or JNI), Python ctypes, C and C++ (see INTEGRATION.md for the Java binding).
+ *
+ * There is no CPU fallback: every decode entry point runs hand-written CUDA kernels and fails with WGBV_ECUDA
+ * when no usable device is present.
+ *
+ * Conventions
+ *   - Every function that can fail returns 0 or one of the negative codes below; wgbv_last_error() then gives a
+ *     thread-local, human-readable message.  The codes map one to one onto the exceptions of the reference.
+ *   - A wgbv_graph is immutable after opening and may be shared by any number of threads (it is what a
+ *     BVGraph and all its copy()s share: the bit stream and the Elias-Fano offsets, BVG:553-578).
+ *   - A wgbv_stream holds the mutable per-user state (one CUDA stream plus scratch memory): the counterpart of
+ *     one flyweight copy() (IG:187-197).  One stream must not be used by two threads at once.
+ *   - Node ids are 64-bit and global (also when the handle only holds a shard of the graph).
+ *   - "device" pointers are CUDA device pointers valid on the graph's device; "host" pointers are ordinary
+ *     (preferably pinned) host memory.
+ */
+#ifndef WGBV_H
+#define WGBV_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define WGBV_API __attribute__((visibility("default")))
+#else
+#define WGBV_API
+#endif
+
+/* Status codes (reference exception in brackets). */
+#define WGBV_OK 0
+#define WGBV_EINDEX (-1)       /* IllegalArgumentException "Node index out of range" (BVG:823, 863, 1000, 1128) */
+#define WGBV_ESTATE (-2)       /* IllegalStateException: reference > window size (BVG:701), malformed stream */
+#define WGBV_EIO (-3)          /* IOException: missing file, wrong graphclass, missing/too-new version (BVG:1491-1497) */
+#define WGBV_EUNSUPPORTED (-4) /* UnsupportedOperationException: unknown coding id (BVG:631, 658, 699, 733, 763, 794) */
+#define WGBV_ECUDA (-5)        /* no usable device, CUDA failure, out of device memory */
+#define WGBV_EARG (-6)         /* IllegalArgumentException for any other bad argument (null pointer, capacity too small) */
+
+/* Coding ids of the compression flags (CompressionFlags.java:26-46). */
+#define WGBV_DELTA 1
+#define WGBV_GAMMA 2
+#define WGBV_GOLOMB 3
+#define WGBV_SKEWED_GOLOMB 4
+#define WGBV_UNARY 5
+#define WGBV_ZETA 6
+#define WGBV_NIBBLE 7
+
+/* The decoded content of a .properties file (the fields BVGraph.loadInternal reads, BVG:1495-1503, with the
+ * compression flags already unpacked as setFlags does, BVG:1281-1289). */
+typedef struct wgbv_props {
+	int64_t nodes;
+	int64_t arcs;
+	int32_t window_size;
+	int32_t max_ref_count;
+	int32_t min_interval_length;
+	int32_t zeta_k;
+	int32_t outdegree_coding;   /* GAMMA (default) | DELTA */
+	int32_t block_coding;       /* GAMMA (default) | DELTA | UNARY */
+	int32_t residual_coding;    /* ZETA (default) | GAMMA | DELTA | GOLOMB | NIBBLE */
+	int32_t reference_coding;   /* UNARY (default) | GAMMA | DELTA */
+	int32_t block_count_coding; /* GAMMA (default) | DELTA | UNARY */
+	int32_t offset_coding;      /* GAMMA (default) | DELTA */
+} wgbv_props;
+
+typedef struct wgbv_graph wgbv_graph;
+typedef struct wgbv_stream wgbv_stream;
+
+/* Thread-local message of the last failure on the calling thread ("" if none). */
+WGBV_API const char *wgbv_last_error(void);
+
+/* Parses the text of a .properties file into *out, applying the checks of BVGraph.loadInternal (BVG:1482-1503:
+ * graphclass must name BVGraph, standard or big; version present and <= 0) and string2Flags/setFlags
+ * (BVG:1316-1331, 1281-1289).  Host only. */
+WGBV_API int wgbv_parse_properties(const char *text, wgbv_props *out);
+
+/*
+ * Opening.  Replaces BVGraph.load(basename) (BVG:1345-1383 -> loadInternal BVG:1479-1574): reads
+ * <basename>.properties, <basename>.graph and <basename>.offsets, turns the gamma/delta coded offsets
+ * (OffsetsLongIterator, BVG:870-898) into an Elias-Fano list in device memory (the role of
+ * EliasFanoMonotoneLongBigList at BVG:1558) and uploads the bit stream.
+ *
+ * shard_index / shard_count select a contiguous, bit-offset-balanced shard of the node range (shard_count = 1:
+ * the whole graph).  A shard also keeps the window_size * max_ref_count predecessors of its first node (the
+ * GPU analogue of the window pre-fill of nodeIterator(from), BVG:1139-1143) so that decoding never needs
+ * another device.  Graphs whose max_ref_count makes that halo unbounded can only be opened with shard_count 1.
+ */
+WGBV_API int wgbv_open(const char *basename, int device, int shard_index, int shard_count, wgbv_graph **out);
+
+/* Same, from memory: `graph` and `offsets` are the bytes of the .graph and .offsets files. */
+WGBV_API int wgbv_open_mem(const wgbv_props *props, const uint8_t *graph, uint64_t graph_bytes, const uint8_t *offsets,
+                  uint64_t offsets_bytes, int device, int shard_index, int shard_count, wgbv_graph **out);
+
+/* Releases the device memory of a graph.  All its streams must have been destroyed. */
+WGBV_API void wgbv_close(wgbv_graph *g);
+
+/* numNodes() IG:245, numArcs() IG:263 (the value stored in .properties), and the properties themselves. */
+WGBV_API int64_t wgbv_num_nodes(const wgbv_graph *g);
+WGBV_API int64_t wgbv_num_arcs(const wgbv_graph *g);
+WGBV_API int wgbv_get_props(const wgbv_graph *g, wgbv_props *out);
+
+/* The node range [*first, *last) this handle can decode (the shard; the whole graph if unsharded), the bytes of
+ * device memory the handle holds, and the bytes the Elias-Fano offsets take (for bits-per-pointer reports, cf.
+ * BVG:1565-1566). */
+WGBV_API int wgbv_shard_range(const wgbv_graph *g, int64_t *first, int64_t *last);
+WGBV_API uint64_t wgbv_device_bytes(const wgbv_graph *g);
+WGBV_API uint64_t wgbv_offsets_bytes(const wgbv_graph *g);
+
+/* Per-user state: the counterpart of ImmutableGraph.copy() (IG:447, BVG:553-578).  `cuda_stream` is a
+ * cudaStream_t to run on (e.g. torch's current stream) or NULL for a stream owned by the library. */
+WGBV_API int wgbv_stream_create(wgbv_graph *g, void *cuda_stream, wgbv_stream **out);
+WGBV_API void wgbv_stream_destroy(wgbv_stream *s);
+/* Blocks until everything queued on the stream has finished; reports errors found by the kernels. */
+WGBV_API int wgbv_stream_sync(wgbv_stream *s);
+
+/*
+ * Bulk decode of nodes [from, to) to CSR -- the new bulk call of the GPU-backed graph.  It produces what a full
+ * sequential scan produces (nodeIterator(from) + nextLong()/outdegree()/successorBigArray() until `to`,
+ * BVG:1100-1245; per node BVGraph.successors(x, ibs, window, outd), BVG:995-1097): for every node its
+ * outdegree and its successors in increasing order.
+ *
+ * Two steps, so that the caller can size the column array:
+ *   wgbv_decode_degrees  header pass + device prefix scan: d_rowptr[i] = number of arcs of nodes [from, from+i),
+ *                        i = 0..to-from (device, int64), *arcs_out = d_rowptr[to-from] (host; forces a sync).
+ *                        Also what outdegree(x) (BVG:821-842) returns for every x in the range:
+ *                        outdegree(from+i) = d_rowptr[i+1] - d_rowptr[i].
+ *   wgbv_decode_csr      the complete decode; d_col must hold at least the arcs of [from, to) (col_capacity in
+ *                        elements); writes d_rowptr (to-from+1 int64) and d_col (int64 successors).  Asynchronous
+ *                        on the stream: call wgbv_stream_sync before reading and to collect decode errors.
+ */
+WGBV_API int wgbv_decode_degrees(wgbv_stream *s, int64_t from, int64_t to, int64_t *d_rowptr, int64_t *arcs_out);
+WGBV_API int wgbv_decode_csr(wgbv_stream *s, int64_t from, int64_t to, int64_t *d_rowptr, int64_t *d_col, uint64_t col_capacity);
+
+/* The same with HOST buffers (pinned memory recommended): uploads nothing but the request, decodes on the device and
+ * copies row pointers and successors back.  h_col may be NULL to only count (then *arcs_out is still set).
+ * Synchronous.  This is the call a host-side ImmutableGraph implementation sits on. */
+WGBV_API int wgbv_decode_csr_host(wgbv_stream *s, int64_t from, int64_t to, int64_t *h_rowptr, int64_t *h_col,
+                         uint64_t col_capacity, int64_t *arcs_out);
+
+/* outdegree(x) for a batch of arbitrary nodes (BVG:821-851): h_out[i] = outdegree(h_ids[i]).  Host buffers. */
+WGBV_API int wgbv_outdegrees(wgbv_stream *s, const int64_t *h_ids, uint64_t k, int64_t *h_out);
+
+/*
+ * Batched random access: successors(x) (BVG:860-867, with the recursive reference resolution of BVG:1084) for k
+ * arbitrary nodes.  Two steps like the bulk call:
+ *   wgbv_successors_batch_degrees  d_rowptr[i] = arcs of queries 0..i-1 (k+1 int64, device), *arcs_out on host
+ *   wgbv_successors_batch          fills d_col (capacity in elements) with the successor lists, query after query
+ * d_ids is a device array of k node ids.  Any id outside [0, numNodes) fails with WGBV_EINDEX (BVG:863) before
+ * anything is decoded; ids outside a shard's range likewise.
+ */
+WGBV_API int wgbv_successors_batch_degrees(wgbv_stream *s, const int64_t *d_ids, uint64_t k, int64_t *d_rowptr, int64_t *arcs_out);
+WGBV_API int wgbv_successors_batch(wgbv_stream *s, const int64_t *d_ids, uint64_t k, int64_t *d_rowptr, int64_t *d_col,
+                          uint64_t col_capacity);
+/* Host-buffer form (ids, row pointers and successors in host memory).  h_col may be NULL to only count. */
+WGBV_API int wgbv_successors_batch_host(wgbv_stream *s, const int64_t *h_ids, uint64_t k, int64_t *h_rowptr, int64_t *h_col,
+                               uint64_t col_capacity, int64_t *arcs_out);
+
+/* Order-sensitive checksum of a CSR held in device memory: sum over the rows of a 64-bit hash of
+ * (node id, outdegree, successors in order).  Equal CSRs give equal checksums whatever the sharding; used to
+ * verify decodes that are too large to compare element by element (the role of ImmutableGraph.equals, IG:759-779,
+ * at scale).  first_node is the id of row 0.  Synchronous. */
+WGBV_API int wgbv_csr_checksum(wgbv_stream *s, int64_t first_node, int64_t rows, const int64_t *d_rowptr, const int64_t *d_col,
+                      uint64_t *checksum_out);
+
+/* Timing of the stages of the last wgbv_decode_csr on this stream, in milliseconds (CUDA events on the stream):
+ * out[0] header pass, [1] scan, [2] depth levels, [3] successor decode, [4] total.  Synchronises the stream. */
+WGBV_API int wgbv_last_stage_ms(wgbv_stream *s, float out[5]);
+
+/* Number of kernels the library has launched on this stream since it was created (for launch accounting). */
+WGBV_API uint64_t wgbv_kernel_launches(const wgbv_stream *s);
+
+/* Algorithmic bytes of decoding [from, to) (compressed bits in + Elias-Fano bits touched + int64 row pointers
+ * out + int64 successors out), given the arc count of the range. */
+WGBV_API uint64_t wgbv_algorithmic_bytes(const wgbv_graph *g, int64_t from, int64_t to, int64_t arcs);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* WGBV_H */

@@ -1,0 +1,251 @@
+"""GPU parity tests (run with -m gpu on a B200): the CUDA decode, called through the C ABI, against the reference's
+golden fixture and against the CPU oracle on the same seeded inputs.  Bit-exact: everything is integer work."""
+import numpy as np
+import pytest
+
+import bvgen as bg
+import bvoracle as bo
+import webgraph_big_b200 as wg
+
+pytestmark = pytest.mark.gpu
+
+
+def oracle_of(e):
+    p = bo.params_from_properties(bo.parse_properties(e.properties_text()))
+    return bo.OracleGraph(p, e.graph, e.offsets_stream.tobytes())
+
+
+def gpu_of(e, **kw):
+    return wg.GpuBVGraph.load_mem(e.properties_text(), e.graph, e.offsets_stream, **kw)
+
+
+def rowptr_of(deg):
+    rp = np.zeros(deg.size + 1, dtype=np.int64)
+    np.cumsum(deg, out=rp[1:])
+    return rp
+
+
+# ------------------------------------------------------------------------------------------------ the golden fixture
+@pytest.fixture(scope="module")
+def cnr(cnr_basename):
+    g = wg.GpuBVGraph.load(cnr_basename)
+    yield g
+    g.close()
+
+
+def test_cnr2000_bulk_decode_equals_golden(cnr, cnr_golden):
+    """BVGraphTest.testLarge (BVGraphTest.java:105-123): the loaded graph equals the ASCII golden."""
+    deg, rowptr, col = cnr_golden
+    assert cnr.numNodes() == 325557 and cnr.numArcs() == 3216152
+    rp, c = cnr.decodeToCSR()
+    assert np.array_equal(rp, rowptr)
+    assert np.array_equal(c, col)
+
+
+def test_cnr2000_random_access_equals_golden(cnr, cnr_golden):
+    """BVGraphTest.java:114-121: outdegree(i) and successors(i) for every node, including the trailing -1."""
+    deg, rowptr, col = cnr_golden
+    ids = np.arange(cnr.numNodes(), dtype=np.int64)
+    assert np.array_equal(cnr.outdegrees(ids), deg)
+    rp, c = cnr.successorsBatch(ids)
+    assert np.array_equal(rp, rowptr) and np.array_equal(c, col)
+    rng = np.random.default_rng(3)
+    ids = rng.integers(0, cnr.numNodes(), 20000)
+    rp, c = cnr.successorsBatch(ids)
+    want = np.concatenate([col[rowptr[x]:rowptr[x + 1]] for x in ids])
+    assert np.array_equal(np.diff(rp), deg[ids]) and np.array_equal(c, want)
+    it = cnr.successors(5)
+    got = []
+    while (v := it.nextLong()) != -1:
+        got.append(v)
+    assert got == list(col[rowptr[5]:rowptr[6]]) and it.nextLong() == -1
+
+
+def test_cnr2000_node_iterator_from_any_start(cnr, cnr_golden):
+    """WebGraphTestCase.assertGraph (WebGraphTestCase.java:151-180): nodeIterator(s) agrees with random access."""
+    deg, rowptr, col = cnr_golden
+    n = cnr.numNodes()
+    for s in (0, 1, 6, 7, 8, 22, 1000, 123457, n - 3, n):
+        e = min(s + 3000, n)
+        rp, c = cnr.decodeToCSR(s, e)
+        assert np.array_equal(rp, rowptr[s:e + 1] - rowptr[s]), s
+        assert np.array_equal(c, col[rowptr[s]:rowptr[e]]), s
+    it = cnr.nodeIterator(n - 40)
+    with pytest.raises(wg.IllegalStateException):  # BVG:1185
+        it.outdegree()
+    seen = 0
+    while it.hasNext():
+        x = it.nextLong()
+        assert it.outdegree() == deg[x]
+        assert np.array_equal(it.successorArray(), col[rowptr[x]:rowptr[x + 1]])
+        seen += 1
+    assert seen == 40
+    with pytest.raises(wg.NoSuchElementException):  # BVG:1165
+        it.nextLong()
+
+
+def test_cnr2000_split_iterators_and_copies(cnr, cnr_golden):
+    """splitNodeIterators (IG:405-436) over flyweight copies: the parts cover the graph exactly once."""
+    deg, rowptr, col = cnr_golden
+    parts = cnr.splitNodeIterators(5)
+    assert len(parts) == 5
+    total = 0
+    nxt = 0
+    for it in parts:
+        while it.hasNext():
+            x = it.nextLong()
+            assert x == nxt
+            nxt += 1
+            total += it.outdegree()
+            if x % 997 == 0:
+                assert np.array_equal(it.successorArray(), col[rowptr[x]:rowptr[x + 1]])
+    assert nxt == cnr.numNodes() and total == cnr.numArcs()
+    c = cnr.copy()
+    assert np.array_equal(c.successorArray(12345), col[rowptr[12345]:rowptr[12346]])
+    c.close()
+
+
+def test_index_errors(cnr):
+    n = cnr.numNodes()
+    for call in (lambda: cnr.outdegree(n), lambda: cnr.successors(-1), lambda: cnr.successorArray(n), lambda: cnr.nodeIterator(n + 1),
+                 lambda: cnr.decodeToCSR(5, n + 1), lambda: cnr.successorsBatch(np.array([1, n]))):
+        with pytest.raises(wg.IllegalArgumentException):
+            call()
+    rp, c = cnr.decodeToCSR(7, 7)
+    assert rp.tolist() == [0] and c.size == 0
+
+
+def test_checksum_kernel_matches_generator_hash(cnr, cnr_golden):
+    torch = pytest.importorskip("torch")
+    deg, rowptr, col = cnr_golden
+    n = cnr.numNodes()
+    d_rp = torch.empty(n + 1, dtype=torch.int64, device="cuda")
+    arcs = cnr.decodeDegreesDevice(0, n, d_rp.data_ptr())
+    assert arcs == col.size
+    d_col = torch.empty(arcs, dtype=torch.int64, device="cuda")
+    cnr.decodeToCSRDevice(0, n, d_rp.data_ptr(), d_col.data_ptr(), arcs)
+    assert np.array_equal(d_col.cpu().numpy(), col)
+    assert cnr.csrChecksumDevice(0, n, d_rp.data_ptr(), d_col.data_ptr()) == bg.csr_checksum(0, rowptr, col)
+    ms = cnr.lastStageMs()
+    assert len(ms) == 5 and ms[4] > 0
+    assert cnr.kernelLaunches() > 0
+    assert cnr.algorithmicBytes(0, n, arcs) == (11443904 + 7) // 8 + (n * (2 + 5) + 7) // 8 + 8 * (n + 1) + 8 * arcs
+
+
+# ------------------------------------------------------------------------------------------------ synthetic inputs vs oracle
+@pytest.mark.parametrize("window,maxref,minint", [(7, 3, 4), (0, 3, 4), (1, 1, 0), (3, 0, 2), (16, 8, 1), (7, 3, 3)])
+def test_copy_model_equals_oracle(window, maxref, minint):
+    e = bg.copy_model(40000, seed=window * 100 + maxref * 10 + minint, mean_degree=15,
+                      params=bg.make_params(window=window, maxref=maxref, minint=minint), nsplits=4)
+    deg, col = oracle_of(e).decode_range()
+    with gpu_of(e) as g:
+        rp, c = g.decodeToCSR()
+        assert np.array_equal(rp, rowptr_of(deg)) and np.array_equal(c, col)
+        for s, t in ((1, 40000), (39990, 40000), (20000, 20001), (12345, 23456)):
+            rp2, c2 = g.decodeToCSR(s, t)
+            assert np.array_equal(c2, col[rp[s]:rp[t]]) and np.array_equal(rp2, rp[s:t + 1] - rp[s])
+        ids = np.random.default_rng(1).integers(0, 40000, 3000)
+        rpb, cb = g.successorsBatch(ids)
+        assert np.array_equal(cb, np.concatenate([col[rp[x]:rp[x + 1]] for x in ids]))
+
+
+@pytest.mark.parametrize("residual", [bg.ZETA, bg.GAMMA, bg.DELTA, bg.NIBBLE, bg.GOLOMB])
+@pytest.mark.parametrize("other", [bg.GAMMA, bg.DELTA])
+@pytest.mark.parametrize("zetak", [1, 3, 5])
+def test_every_compression_flag_equals_oracle(residual, other, zetak):
+    """Codings the reference's own tests never exercise (parity with the reference itself is unpinned for them;
+    here they are checked against the oracle, which reads them from the published definitions)."""
+    params = bg.make_params(window=5, maxref=4, minint=2, zetak=zetak, outdegree=other, block=other, residual=residual,
+                            reference=bg.UNARY if other == bg.GAMMA else other, blockcount=other, offset=other)
+    e = bg.copy_model(6000, seed=31 + residual + other, mean_degree=12, params=params, nsplits=3)
+    deg, col = oracle_of(e).decode_range()
+    with gpu_of(e) as g:
+        rp, c = g.decodeToCSR()
+        assert np.array_equal(rp, rowptr_of(deg)) and np.array_equal(c, col)
+
+
+def test_erdos_renyi_config1():
+    """BASELINE config 1 at reduced size: ER, w=7, maxRef=3, minInt=4, zeta3 (residual-dominated rows)."""
+    e = bg.erdos_renyi(100000, 1.6e-4, seed=1, params=bg.make_params(7, 3, 4, 3))
+    deg, col = oracle_of(e).decode_range()
+    with gpu_of(e) as g:
+        rp, c = g.decodeToCSR()
+        assert np.array_equal(rp, rowptr_of(deg)) and np.array_equal(c, col)
+
+
+def test_unbounded_reference_chains_config3():
+    """maxrefcount=2147483647 (what -m -1 writes, BVG:2654): deep level-by-level copy resolution."""
+    e = bg.copy_model(60000, seed=9, mean_degree=10, p_ref=0.95, params=bg.make_params(maxref=2147483647), nsplits=1)
+    deg, col = oracle_of(e).decode_range()
+    with gpu_of(e) as g:
+        rp, c = g.decodeToCSR()
+        assert np.array_equal(rp, rowptr_of(deg)) and np.array_equal(c, col)
+        rp2, c2 = g.decodeToCSR(50000, 60000)
+        assert np.array_equal(c2, col[rp[50000]:rp[60000]])
+        ids = np.array([59999, 1, 31234, 44444], dtype=np.int64)
+        rpb, cb = g.successorsBatch(ids)
+        assert np.array_equal(cb, np.concatenate([col[rp[x]:rp[x + 1]] for x in ids]))
+
+
+def test_giant_rows_and_zero_degree_nodes():
+    """The shape of the reference's slow test (slow/.../BVGraphSlowTest.java:30-85): a row far larger than all others."""
+    e = bg.big_graph(30000, giant_every=7000, giant_degree=200000, giant_stride=3, nsplits=2)
+    deg, col = oracle_of(e).decode_range()
+    with gpu_of(e) as g:
+        rp, c = g.decodeToCSR()
+        assert np.array_equal(rp, rowptr_of(deg)) and np.array_equal(c, col)
+    # isolated nodes only
+    rowptr = np.zeros(1001, dtype=np.int64)
+    e = bg.encode_csr(rowptr, np.zeros(0, dtype=np.int64))
+    with gpu_of(e) as g:
+        rp, c = g.decodeToCSR()
+        assert not rp.any() and c.size == 0
+
+
+def test_tree_grid():
+    """BVGraphTest.testCompression grid (BVGraphTest.java:52-103), a sample of it."""
+    from test_datagen import tree_csr
+    for n, w, r, i, inward in ((1, 0, 0, 0, False), (7, 2, 2, 3, True), (7, 1, 0, 1, False), (5, 2, 1, 2, True), (3, 0, 2, 0, False)):
+        rowptr, col = tree_csr(n, inward)
+        e = bg.encode_csr(rowptr, col, bg.make_params(window=w, maxref=r, minint=i))
+        with gpu_of(e) as g:
+            rp, c = g.decodeToCSR()
+            assert np.array_equal(rp, rowptr) and np.array_equal(c, col)
+            for s in range(n + 1):
+                rp2, c2 = g.decodeToCSR(s, n)
+                assert np.array_equal(c2, col[rowptr[s]:])
+
+
+def test_shards_concatenate_to_the_whole_graph():
+    """Bit-balanced contiguous shards with a window*maxref halo decode independently; the CSR is their concatenation."""
+    e = bg.copy_model(50000, seed=77, mean_degree=15, nsplits=8)
+    deg, col = oracle_of(e).decode_range()
+    rowptr = rowptr_of(deg)
+    for count in (2, 3, 8):
+        nxt, total, chk = 0, 0, 0
+        for k in range(count):
+            with gpu_of(e, shard_index=k, shard_count=count) as g:
+                lo, hi = g.shardRange()
+                assert lo == nxt
+                nxt = hi
+                rp, c = g.decodeToCSR()
+                assert np.array_equal(rp, rowptr[lo:hi + 1] - rowptr[lo]) and np.array_equal(c, col[rowptr[lo]:rowptr[hi]])
+                total += c.size
+                chk = (chk + bg.csr_checksum(lo, rp, c)) % (1 << 64)
+                if hi > lo:
+                    with pytest.raises(wg.IllegalArgumentException):
+                        g.decodeToCSR(lo, hi + 1) if hi < 50000 else g.decodeToCSR(lo - 1, hi) if lo > 0 else g.decodeToCSR(-1, hi)
+        assert nxt == 50000 and total == e.arcs and chk == e.checksum
+    with pytest.raises(wg.UnsupportedOperationException):
+        e2 = bg.copy_model(1000, seed=1, params=bg.make_params(maxref=2147483647), nsplits=1)
+        gpu_of(e2, shard_index=0, shard_count=2)
+
+
+def test_malformed_reference_is_reported():
+    """A reference larger than the window is the reference's IllegalStateException (BVG:701)."""
+    e = bg.copy_model(2000, seed=5, params=bg.make_params(window=7), nsplits=1)
+    text = e.properties_text().replace("windowsize=7", "windowsize=1")
+    g = wg.GpuBVGraph.load_mem(text, e.graph, e.offsets_stream)
+    with pytest.raises(wg.IllegalStateException):
+        g.decodeToCSR()
+    g.close()

@@ -1,0 +1,78 @@
+"""Pins the CPU oracle on the reference's own known-answer fixture cnr-2000 (the assertions of
+test/it/unimi/dsi/big/webgraph/BVGraphTest.java:105-123 and WebGraphTestCase.java:106-199 of the reference)."""
+import numpy as np
+import pytest
+
+import bvoracle as bo
+
+
+@pytest.fixture(scope="module")
+def og(cnr_basename):
+    return bo.OracleGraph.load(cnr_basename)
+
+
+def test_properties(og):
+    p = og.p
+    assert (p.nodes, p.arcs, p.window, p.maxref, p.minint, p.zetak) == (325557, 3216152, 7, 3, 3, 3)
+    assert (p.outdegree_coding, p.block_coding, p.residual_coding, p.reference_coding, p.blockcount_coding, p.offset_coding) == \
+        (bo.GAMMA, bo.GAMMA, bo.ZETA, bo.UNARY, bo.GAMMA, bo.GAMMA)
+
+
+def test_offsets_land_on_the_stream_length(og):
+    assert og.offsets[0] == 0
+    assert og.offsets[-1] == 11443904 <= og.graph.size * 8
+    assert (np.diff(og.offsets.astype(np.int64)) > 0).all()
+
+
+def test_sequential_scan_equals_golden(og, cnr_golden):
+    deg, rowptr, col = cnr_golden
+    d, c = og.decode_range()
+    assert np.array_equal(d, deg)
+    assert np.array_equal(c, col)
+    assert int(d.sum()) == og.p.arcs  # WebGraphTestCase.java:140
+
+
+def test_split_scan_equals_golden(og, cnr_golden):
+    deg, rowptr, col = cnr_golden
+    for k in (2, 7):
+        d, c = og.decode_range(threads=k)
+        assert np.array_equal(d, deg) and np.array_equal(c, col)
+
+
+def test_random_access_equals_golden(og, cnr_golden):
+    deg, rowptr, col = cnr_golden
+    rng = np.random.default_rng(7)
+    for x in np.concatenate([[0, 1, 7, 8, og.p.nodes - 1], rng.integers(0, og.p.nodes, 5000)]):
+        x = int(x)
+        assert og.outdegree(x) == deg[x]
+        assert np.array_equal(og.successors(x), col[rowptr[x]:rowptr[x + 1]])
+
+
+def test_node_iterator_from_every_kind_of_start(og, cnr_golden):
+    """nodeIterator(s) agrees with random access (WebGraphTestCase.java:151-180): exercises the window pre-fill."""
+    deg, rowptr, col = cnr_golden
+    n = og.p.nodes
+    for s in (1, 2, 6, 7, 8, 9, 1000, 123457, n - 3, n):
+        e = min(s + 2000, n)
+        d, c = og.decode_range(s, e)
+        assert np.array_equal(d, deg[s:e])
+        assert np.array_equal(c, col[rowptr[s]:rowptr[e]])
+
+
+def test_index_errors(og):
+    with pytest.raises(IndexError):
+        og.successors(og.p.nodes)
+    with pytest.raises(IndexError):
+        og.outdegree(-1)
+
+
+def test_flag_parsing():
+    assert bo.string2flags("") == 0
+    f = bo.string2flags("RESIDUALS_DELTA | OUTDEGREES_DELTA|REFERENCES_GAMMA")
+    assert f == (bo.DELTA << 8) | bo.DELTA | (bo.GAMMA << 12)
+    with pytest.raises(IOError):
+        bo.string2flags("RESIDUALS_UNARY")
+    with pytest.raises(IOError):
+        bo.params_from_properties({"graphclass": "it.unimi.dsi.big.webgraph.EFGraph", "version": "0"})
+    with pytest.raises(IOError):
+        bo.params_from_properties({"graphclass": "it.unimi.dsi.webgraph.BVGraph"})

@@ -1,0 +1,380 @@
+"""webgraph-big_b200 -- a B200 (sm_100a) BVGraph decompression engine behind webgraph-big's ImmutableGraph API.
+
+This module is the host-side mirror of the reference's plugin interface for the BVGraph decode path, written
+over the C ABI of libwgbv (include/wgbv.h): same method names, argument meaning and error behaviour as
+``it.unimi.dsi.big.webgraph.ImmutableGraph`` / ``NodeIterator`` / ``LazyLongIterator`` (reference files
+ImmutableGraph.java:201-447, NodeIterator.java:34-133, LazyLongIterator.java:28-43, BVGraph.java:821-1265), plus
+the bulk call ``decodeToCSR``.  Every decode runs in CUDA; nothing here decodes on the CPU.
+
+The directory name contains a hyphen: import it as ``import webgraph_big_b200`` (alias module at the repository
+root) or through ``importlib.import_module("webgraph-big_b200")``.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import (CudaError, IllegalArgumentException, IllegalStateException, IOException,  # noqa: F401
+                   NoSuchElementException, Props, UnsupportedOperationException)
+
+__all__ = ["GpuBVGraph", "NodeIterator", "LazyLongIterator", "Props", "parse_properties", "IllegalArgumentException",
+           "IllegalStateException", "IOException", "UnsupportedOperationException", "NoSuchElementException", "CudaError"]
+
+GRAPH_EXTENSION, OFFSETS_EXTENSION, PROPERTIES_EXTENSION = ".graph", ".offsets", ".properties"
+
+
+def parse_properties(text):
+    """The .properties checks of BVGraph.loadInternal (BVG:1482-1503) -> Props."""
+    p = Props()
+    _lib.check(_lib.lib().wgbv_parse_properties(text.encode("utf-8"), C.byref(p)))
+    return p
+
+
+class LazyLongIterator:
+    """The reference's lazy iterator protocol (LazyLongIterator.java:28-43): nextLong() returns -1 when exhausted."""
+
+    def __init__(self, values):
+        self._v = values
+        self._i = 0
+
+    def nextLong(self):
+        if self._i >= len(self._v):
+            return -1
+        r = int(self._v[self._i])
+        self._i += 1
+        return r
+
+    def skip(self, n):
+        k = min(int(n), len(self._v) - self._i)
+        self._i += k
+        return k
+
+    def __iter__(self):
+        while True:
+            r = self.nextLong()
+            if r == -1:
+                return
+            yield r
+
+
+class _Stream:
+    """One wgbv_stream: the mutable state behind one flyweight copy (IG:187-197)."""
+
+    def __init__(self, graph_handle, cuda_stream=None):
+        self.h = C.c_void_p()
+        _lib.check(_lib.lib().wgbv_stream_create(graph_handle, C.c_void_p(cuda_stream or 0), C.byref(self.h)))
+
+    def close(self):
+        if self.h:
+            _lib.lib().wgbv_stream_destroy(self.h)
+            self.h = C.c_void_p()
+
+
+class _Shared:
+    """The immutable part shared by a graph and all its copies (bit stream + Elias-Fano offsets on the device)."""
+
+    def __init__(self, handle, basename):
+        self.handle = handle
+        self.basename = basename
+        self.refs = 0
+
+    def release(self):
+        self.refs -= 1
+        if self.refs == 0 and self.handle:
+            _lib.lib().wgbv_close(self.handle)
+            self.handle = C.c_void_p()
+
+
+class GpuBVGraph:
+    """A BVGraph whose successor lists are decoded on a B200.
+
+    A sibling of ``it.unimi.dsi.big.webgraph.BVGraph`` (it accepts the same files, ``graphclass`` naming BVGraph,
+    standard or big), selected explicitly like ``-g GpuBVGraph`` would in the reference's tools.
+    """
+
+    CHUNK_NODES = 1 << 16  # nodes decoded per bulk call behind nodeIterator()
+
+    def __init__(self, shared, cuda_stream=None):
+        self._sh = shared
+        shared.refs += 1
+        self._st = _Stream(shared.handle, cuda_stream)
+        L = _lib.lib()
+        self._n = L.wgbv_num_nodes(shared.handle)
+        self._m = L.wgbv_num_arcs(shared.handle)
+        lo, hi = C.c_int64(), C.c_int64()
+        _lib.check(L.wgbv_shard_range(shared.handle, C.byref(lo), C.byref(hi)))
+        self._lo, self._hi = lo.value, hi.value
+
+    # -------------------------------------------------------------------------------------------- loading
+    @classmethod
+    def load(cls, basename, device=0, shard_index=0, shard_count=1, cuda_stream=None):
+        """BVGraph.load(basename) (BVG:1345-1383): reads basename.properties/.graph/.offsets onto the device."""
+        h = C.c_void_p()
+        _lib.check(_lib.lib().wgbv_open(str(basename).encode("utf-8"), device, shard_index, shard_count, C.byref(h)))
+        return cls(_Shared(h, str(basename)), cuda_stream)
+
+    # the reference's other loaders all need the whole stream in device memory here
+    loadMapped = load
+    loadOffline = load
+
+    @classmethod
+    def load_mem(cls, props, graph_bytes, offsets_bytes, device=0, shard_index=0, shard_count=1, cuda_stream=None):
+        """Same from memory: ``props`` is a Props or the text of a .properties file."""
+        if isinstance(props, str):
+            props = parse_properties(props)
+        g = np.ascontiguousarray(np.frombuffer(graph_bytes, dtype=np.uint8)) if not isinstance(graph_bytes, np.ndarray) else np.ascontiguousarray(graph_bytes)
+        o = np.ascontiguousarray(np.frombuffer(offsets_bytes, dtype=np.uint8)) if not isinstance(offsets_bytes, np.ndarray) else np.ascontiguousarray(offsets_bytes)
+        h = C.c_void_p()
+        _lib.check(_lib.lib().wgbv_open_mem(C.byref(props), g.ctypes.data, g.size, o.ctypes.data, o.size, device,
+                                            shard_index, shard_count, C.byref(h)))
+        return cls(_Shared(h, None), cuda_stream)
+
+    @classmethod
+    def loadOnce(cls, stream):
+        raise UnsupportedOperationException("GpuBVGraph needs random access to the bit stream")
+
+    def close(self):
+        if self._st is not None:
+            self._st.close()
+            self._st = None
+            self._sh.release()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    # -------------------------------------------------------------------------------------------- ImmutableGraph
+    def numNodes(self):
+        return self._n
+
+    def numArcs(self):
+        return self._m
+
+    def randomAccess(self):
+        return True
+
+    def hasCopiableIterators(self):
+        return True
+
+    def basename(self):
+        return self._sh.basename
+
+    def copy(self):
+        """Flyweight copy (IG:447, BVG:553-578): shares the device-resident graph, owns its stream and scratch."""
+        return GpuBVGraph(self._sh)
+
+    def props(self):
+        p = Props()
+        _lib.check(_lib.lib().wgbv_get_props(self._sh.handle, C.byref(p)))
+        return p
+
+    def shardRange(self):
+        return self._lo, self._hi
+
+    def _check_node(self, x):
+        if x < 0 or x >= self._n:
+            raise IllegalArgumentException(f"Node index out of range: {x}")
+
+    def outdegree(self, x):
+        """BVGraph.outdegree(x), BVG:821-842."""
+        self._check_node(x)
+        return int(self.outdegrees(np.array([x], dtype=np.int64))[0])
+
+    def outdegrees(self, ids):
+        ids = np.ascontiguousarray(ids, dtype=np.int64)
+        out = np.empty(ids.size, dtype=np.int64)
+        _lib.check(_lib.lib().wgbv_outdegrees(self._st.h, ids.ctypes.data, ids.size, out.ctypes.data))
+        return out
+
+    def successorArray(self, x):
+        """successorBigArray(x) (IG:329-333): the successors of x as an int64 array of length outdegree(x)."""
+        self._check_node(x)
+        _, col = self.successorsBatch(np.array([x], dtype=np.int64))
+        return col
+
+    successorBigArray = successorArray
+
+    def successors(self, x):
+        """BVGraph.successors(x), BVG:860-867: a lazy iterator ending with -1."""
+        return LazyLongIterator(self.successorArray(x))
+
+    def successorsBatch(self, ids):
+        """Batched random access: (rowptr[k+1], col) for k arbitrary node ids (host arrays)."""
+        ids = np.ascontiguousarray(ids, dtype=np.int64)
+        L = _lib.lib()
+        rowptr = np.empty(ids.size + 1, dtype=np.int64)
+        arcs = C.c_int64()
+        _lib.check(L.wgbv_successors_batch_host(self._st.h, ids.ctypes.data, ids.size, rowptr.ctypes.data, None, 0, C.byref(arcs)))
+        col = np.empty(arcs.value, dtype=np.int64)
+        _lib.check(L.wgbv_successors_batch_host(self._st.h, ids.ctypes.data, ids.size, rowptr.ctypes.data,
+                                                col.ctypes.data if col.size else None, col.size, C.byref(arcs)))
+        return rowptr, col
+
+    def nodeIterator(self, from_=0):
+        """BVGraph.nodeIterator(from), BVG:1257: sequential scan served from chunked bulk decodes."""
+        if from_ < 0 or from_ > self._n:
+            raise IllegalArgumentException(f"Node index out of range: {from_}")
+        return NodeIterator(self, from_, self._n)
+
+    def splitNodeIterators(self, howMany):
+        """ImmutableGraph.splitNodeIterators(howMany), IG:405-436: contiguous ranges of ceil(n / howMany) nodes."""
+        if self._n == 0 and howMany == 0:
+            return []
+        if howMany < 1:
+            raise IllegalArgumentException()
+        m = -(-self._n // howMany)
+        res = []
+        f = 0
+        while f < self._n:
+            res.append(NodeIterator(self.copy(), f, min(f + m, self._n), own_graph=True))
+            f += m
+        while len(res) < howMany:
+            res.append(NodeIterator(self, self._n, self._n))
+        return res
+
+    # -------------------------------------------------------------------------------------------- bulk call
+    def decodeToCSR(self, from_=None, to=None):
+        """Bulk decode of [from, to) into host arrays: (rowptr int64[to-from+1], col int64[arcs])."""
+        from_ = self._lo if from_ is None else from_
+        to = self._hi if to is None else to
+        L = _lib.lib()
+        rowptr = np.empty(max(to - from_, 0) + 1, dtype=np.int64)
+        arcs = C.c_int64()
+        _lib.check(L.wgbv_decode_csr_host(self._st.h, from_, to, rowptr.ctypes.data, None, 0, C.byref(arcs)))
+        col = np.empty(arcs.value, dtype=np.int64)
+        _lib.check(L.wgbv_decode_csr_host(self._st.h, from_, to, rowptr.ctypes.data, col.ctypes.data if col.size else None,
+                                          col.size, C.byref(arcs)))
+        return rowptr, col
+
+    def decodeDegreesDevice(self, from_, to, d_rowptr):
+        """Header pass + scan into a device buffer (int pointer); returns the arc count of [from, to)."""
+        arcs = C.c_int64()
+        _lib.check(_lib.lib().wgbv_decode_degrees(self._st.h, from_, to, C.c_void_p(d_rowptr), C.byref(arcs)))
+        return arcs.value
+
+    def decodeToCSRDevice(self, from_, to, d_rowptr, d_col, col_capacity, sync=True):
+        """Bulk decode into caller-provided DEVICE buffers (raw pointers, e.g. torch tensors' data_ptr())."""
+        _lib.check(_lib.lib().wgbv_decode_csr(self._st.h, from_, to, C.c_void_p(d_rowptr), C.c_void_p(d_col), col_capacity))
+        if sync:
+            self.sync()
+
+    def sync(self):
+        _lib.check(_lib.lib().wgbv_stream_sync(self._st.h))
+
+    def csrChecksumDevice(self, first_node, rows, d_rowptr, d_col):
+        out = C.c_uint64()
+        _lib.check(_lib.lib().wgbv_csr_checksum(self._st.h, first_node, rows, C.c_void_p(d_rowptr), C.c_void_p(d_col), C.byref(out)))
+        return out.value
+
+    def successorsBatchDevice(self, d_ids, k, d_rowptr, d_col=None, col_capacity=0):
+        """Batched random access on device buffers.  With d_col None only the row pointers are produced."""
+        L = _lib.lib()
+        if d_col is None:
+            arcs = C.c_int64()
+            _lib.check(L.wgbv_successors_batch_degrees(self._st.h, C.c_void_p(d_ids), k, C.c_void_p(d_rowptr), C.byref(arcs)))
+            return arcs.value
+        _lib.check(L.wgbv_successors_batch(self._st.h, C.c_void_p(d_ids), k, C.c_void_p(d_rowptr), C.c_void_p(d_col), col_capacity))
+        self.sync()
+        return None
+
+    def lastStageMs(self):
+        out = (C.c_float * 5)()
+        _lib.check(_lib.lib().wgbv_last_stage_ms(self._st.h, C.byref(out)))
+        return list(out)
+
+    def kernelLaunches(self):
+        return _lib.lib().wgbv_kernel_launches(self._st.h)
+
+    def algorithmicBytes(self, from_, to, arcs):
+        return _lib.lib().wgbv_algorithmic_bytes(self._sh.handle, from_, to, arcs)
+
+    def deviceBytes(self):
+        return _lib.lib().wgbv_device_bytes(self._sh.handle)
+
+    def offsetsBytes(self):
+        return _lib.lib().wgbv_offsets_bytes(self._sh.handle)
+
+    # ImmutableGraph.equals, IG:759-779: same n; per node same outdegree and same successors in order
+    def equals(self, other):
+        if self.numNodes() != other.numNodes():
+            return False
+        a, b = self.nodeIterator(), other.nodeIterator()
+        while a.hasNext():
+            a.nextLong()
+            b.nextLong()
+            if a.outdegree() != b.outdegree() or not np.array_equal(a.successorArray(), b.successorArray()):
+                return False
+        return True
+
+
+class NodeIterator:
+    """BVGraphNodeIterator (BVG:1100-1245) over chunked GPU decodes; arrays returned are valid until the next
+    nextLong() (the reference's window-slot rule, BVG:1171-1172)."""
+
+    def __init__(self, graph, from_, upper_bound, own_graph=False):
+        self._g = graph
+        self._own = own_graph
+        self._from = from_
+        self._curr = from_ - 1
+        self._limit = min(upper_bound, graph.numNodes()) - 1  # hasNextLimit, BVG:1147
+        self._c0 = self._c1 = from_  # chunk [c0, c1) currently held
+        self._rowptr = self._col = None
+
+    def hasNext(self):
+        return self._curr < self._limit
+
+    def nextLong(self):
+        if not self.hasNext():
+            raise NoSuchElementException()
+        self._curr += 1
+        if self._curr >= self._c1:
+            self._c0 = self._curr
+            self._c1 = min(self._c0 + GpuBVGraph.CHUNK_NODES, self._limit + 1)
+            self._rowptr, self._col = self._g.decodeToCSR(self._c0, self._c1)
+        return self._curr
+
+    __next__ = nextLong
+
+    def __iter__(self):
+        while self.hasNext():
+            yield self.nextLong()
+
+    def _row(self):
+        if self._curr == self._from - 1:
+            raise IllegalStateException()
+        i = self._curr - self._c0
+        return self._rowptr[i], self._rowptr[i + 1]
+
+    def outdegree(self):
+        a, b = self._row()
+        return int(b - a)
+
+    def successorArray(self):
+        a, b = self._row()
+        return self._col[a:b]
+
+    successorBigArray = successorArray
+
+    def successors(self):
+        return LazyLongIterator(self.successorArray())
+
+    def skip(self, n):
+        if n < 0:
+            raise IllegalArgumentException(f"Argument must be nonnegative: {n}")
+        k = 0
+        while k < n and self.hasNext():
+            self.nextLong()
+            k += 1
+        return k
+
+    def copy(self, upper_bound):
+        """NodeIterator.copy(upperBound), BVG:1223-1229: an independent iterator over [curr+1, upperBound)."""
+        return NodeIterator(self._g.copy(), self._curr + 1, upper_bound, own_graph=True)

@@ -1,0 +1,514 @@
+// bv_kernels.cu -- the CUDA kernels of the BVGraph -> CSR decoder (sm_100a).
+//
+// General ("level-synchronous") pipeline, valid for every graph including unbounded reference chains:
+//   k_header      stage 1   thread per node: Elias-Fano offset -> outdegree + reference
+//   k_scan        stage 2   single-pass decoupled look-back prefix sum -> CSR row pointers
+//   k_depth       stage 2b  reference-chain depth of every node
+//   k_extras      stage 3a  intervals + residuals of every row, merged, into the tail of the row's CSR slot
+//   k_copy_level  stage 3b  one launch per depth level: copy blocks of the reference row merged in place
+// All of it is integer/bit work bound by HBM and the integer pipes; no tensor cores are involved.
+#include <stdio.h>
+
+#include "bv_kernels.cuh"
+#include "bv_rows.cuh"
+
+namespace wgbv {
+
+static constexpr int TPB = 256;
+
+static inline unsigned grid_for(int64_t items, int per_block) {
+	int64_t b = (items + per_block - 1) / per_block;
+	if (b < 1) b = 1;
+	return (unsigned)b;
+}
+
+#define WGBV_LAUNCHED(L) do { if ((L).launches) ++*(L).launches; } while (0)
+
+// ------------------------------------------------------------------------------------------------ load-time
+__global__ void k_bswap(uint64_t *words, uint64_t nwords) {
+	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= nwords) return;
+	const uint64_t v = words[i];
+	const uint32_t lo = (uint32_t)v, hi = (uint32_t)(v >> 32);
+	words[i] = ((uint64_t)__byte_perm(lo, 0, 0x0123) << 32) | __byte_perm(hi, 0, 0x0123);
+}
+
+void launch_bswap(const Launch &L, uint64_t *words, uint64_t nwords) {
+	if (!nwords) return;
+	k_bswap<<<grid_for((int64_t)nwords, TPB), TPB, 0, L.stream>>>(words, nwords);
+	WGBV_LAUNCHED(L);
+}
+
+// ------------------------------------------------------------------------------------------------ stage 1
+// Outdegree and reference of every node: readOutdegree / readReference at the node's offset
+// (BVG:654-661, 692-703; the offset lookup is offsets.getLong(x), BVG:834).
+template <bool DEF>
+__global__ void __launch_bounds__(TPB) k_header(GraphDev g, int64_t lo, int64_t count, uint32_t *__restrict__ deg, uint8_t *__restrict__ ref) {
+	const int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
+	if (i >= count) return;
+	const int64_t x = lo + i;
+	BitReader r;
+	r.init(g, ef_get(g, x));
+	const uint64_t d = rd_outdegree<DEF>(r, g);
+	uint64_t rf = 0;
+	if (d > 0x7fffffffull) { raise(g, ERR_DEGREE); deg[i] = 0; ref[i] = 0; return; }
+	if (d && g.window > 0) {
+		rf = rd_reference<DEF>(r, g);
+		if (rf > (uint64_t)g.window || (int64_t)rf > x) { raise(g, ERR_REF_WINDOW); rf = 0; }
+	}
+	if (r.past_end()) raise(g, ERR_OVERRUN);
+	deg[i] = (uint32_t)d;
+	ref[i] = (uint8_t)rf;
+}
+
+void launch_header(const Launch &L, const GraphDev &g, bool def, int64_t lo, int64_t count, uint32_t *deg, uint8_t *ref) {
+	if (count <= 0) return;
+	if (def) k_header<true><<<grid_for(count, TPB), TPB, 0, L.stream>>>(g, lo, count, deg, ref);
+	else k_header<false><<<grid_for(count, TPB), TPB, 0, L.stream>>>(g, lo, count, deg, ref);
+	WGBV_LAUNCHED(L);
+}
+
+// ------------------------------------------------------------------------------------------------ stage 2
+// Exclusive prefix sum, one pass, decoupled look-back.  Tiles are handed out through a ticket so that a tile
+// only ever waits for tiles that are already running.  state[t] = flag (2 top bits) | value (62 bits):
+// 1 = tile aggregate available, 2 = inclusive prefix available.
+static constexpr int SCAN_ITEMS = 8;
+static constexpr int SCAN_TILE = TPB * SCAN_ITEMS;
+enum : uint64_t { FLAG_AGG = 1ull << 62, FLAG_PFX = 2ull << 62, FLAG_MASK = 3ull << 62 };
+
+template <typename T>
+__global__ void __launch_bounds__(TPB) k_scan(const T *__restrict__ in, int64_t *__restrict__ out, int64_t count,
+                                              volatile uint64_t *state, uint32_t *ticket) {
+	__shared__ uint32_t s_tile;
+	__shared__ uint64_t s_warp[TPB / 32];
+	__shared__ uint64_t s_base;
+	if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
+	__syncthreads();
+	const uint32_t tile = s_tile;
+	const int64_t base = (int64_t)tile * SCAN_TILE + (int64_t)threadIdx.x * SCAN_ITEMS;
+
+	uint64_t v[SCAN_ITEMS];
+#pragma unroll
+	for (int j = 0; j < SCAN_ITEMS; j++) v[j] = base + j < count ? (uint64_t)in[base + j] : 0;
+	uint64_t sum = 0;
+#pragma unroll
+	for (int j = 0; j < SCAN_ITEMS; j++) sum += v[j];
+
+	// block-wide exclusive scan of the per-thread sums
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	uint64_t inc = sum;
+#pragma unroll
+	for (int o = 1; o < 32; o <<= 1) {
+		const uint64_t t = __shfl_up_sync(0xffffffffu, inc, o);
+		if (lane >= o) inc += t;
+	}
+	if (lane == 31) s_warp[warp] = inc;
+	__syncthreads();
+	if (warp == 0) {
+		uint64_t w = lane < TPB / 32 ? s_warp[lane] : 0;
+#pragma unroll
+		for (int o = 1; o < TPB / 32; o <<= 1) {
+			const uint64_t t = __shfl_up_sync(0xffffffffu, w, o);
+			if (lane >= o) w += t;
+		}
+		const uint64_t tile_total = __shfl_sync(0xffffffffu, w, TPB / 32 - 1);
+		if (lane < TPB / 32) s_warp[lane] = w;  // inclusive per-warp
+		// look-back by the first warp
+		uint64_t exclusive = 0;
+		if (tile == 0) {
+			if (lane == 0) { state[0] = FLAG_PFX | tile_total; }
+		} else {
+			if (lane == 0) { state[tile] = FLAG_AGG | tile_total; }
+			int64_t look = (int64_t)tile - 1;
+			for (;;) {
+				const int64_t idx = look - lane;
+				uint64_t s = idx >= 0 ? state[idx] : FLAG_PFX;
+				// wait until every inspected predecessor has published something
+				while (__any_sync(0xffffffffu, (s & FLAG_MASK) == 0)) {
+					if ((s & FLAG_MASK) == 0) s = state[idx];
+				}
+				const unsigned pfx = __ballot_sync(0xffffffffu, (s & FLAG_MASK) == FLAG_PFX);
+				const int first = pfx ? __ffs(pfx) - 1 : 32;  // nearest predecessor holding an inclusive prefix
+				uint64_t contrib = (lane <= first && idx >= 0) ? (s & ~FLAG_MASK) : 0;
+#pragma unroll
+				for (int o = 16; o; o >>= 1) contrib += __shfl_xor_sync(0xffffffffu, contrib, o);
+				exclusive += contrib;
+				if (pfx) break;
+				look -= 32;
+			}
+			if (lane == 0) { state[tile] = FLAG_PFX | (exclusive + tile_total); }
+		}
+		if (lane == 0) s_base = exclusive;
+	}
+	__syncthreads();
+	uint64_t run = s_base + (warp ? s_warp[warp - 1] : 0) + (inc - sum);
+#pragma unroll
+	for (int j = 0; j < SCAN_ITEMS; j++) {
+		if (base + j <= count) out[base + j] = (int64_t)run;
+		run += v[j];
+	}
+}
+
+template <typename T>
+static void launch_scan_t(const Launch &L, const T *in, int64_t *out, int64_t count, uint64_t *state, uint32_t *ticket) {
+	const int64_t items = count + 1;  // out has count+1 entries
+	const unsigned tiles = grid_for(items, SCAN_TILE);
+	cudaMemsetAsync(state, 0, (size_t)tiles * sizeof(uint64_t), L.stream);
+	cudaMemsetAsync(ticket, 0, sizeof(uint32_t), L.stream);
+	k_scan<T><<<tiles, TPB, 0, L.stream>>>(in, out, count, state, ticket);
+	WGBV_LAUNCHED(L);
+}
+void launch_scan(const Launch &L, const uint32_t *deg, int64_t *rp, int64_t count, uint64_t *state, uint32_t *ticket) {
+	launch_scan_t<uint32_t>(L, deg, rp, count, state, ticket);
+}
+void launch_scan64(const Launch &L, const unsigned long long *in, int64_t *out, int64_t count, uint64_t *state, uint32_t *ticket) {
+	launch_scan_t<unsigned long long>(L, in, out, count, state, ticket);
+}
+
+__global__ void k_emit_rowptr(const int64_t *__restrict__ rp, int64_t skip, int64_t count, int64_t *__restrict__ out) {
+	const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i > count) return;
+	out[i] = rp[skip + i] - rp[skip];
+}
+void launch_emit_rowptr(const Launch &L, const int64_t *rp, int64_t skip, int64_t count, int64_t *rowptr_out) {
+	k_emit_rowptr<<<grid_for(count + 1, TPB), TPB, 0, L.stream>>>(rp, skip, count, rowptr_out);
+	WGBV_LAUNCHED(L);
+}
+
+// ------------------------------------------------------------------------------------------------ stage 2b
+// depth[x] = 0 if x has no reference, else depth[x - ref] + 1.  Each pass follows a chain for at most
+// DEPTH_HOPS hops or until it meets a node resolved by an earlier pass, so bounded graphs (maxrefcount small)
+// finish in one pass and unbounded ones in ceil(longest chain / DEPTH_HOPS) passes.  Chains that leave the
+// decodable range (possible for halo rows only) are marked invalid.
+static constexpr int DEPTH_HOPS = 64;
+
+__global__ void __launch_bounds__(TPB) k_depth(GraphDev g, const uint8_t *__restrict__ ref, uint32_t *depth, int64_t lo,
+                                               int64_t from, int64_t count, int first_pass, uint32_t *stats) {
+	const int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
+	volatile uint32_t *vdepth = depth;
+	uint32_t result = 0;
+	if (i < count) {
+		result = first_pass ? DEPTH_UNRESOLVED : vdepth[i];
+		if (result == DEPTH_UNRESOLVED) {
+			int64_t y = i;
+			uint32_t hops = 0;
+			for (int h = 0; h <= DEPTH_HOPS; h++) {
+				const uint32_t rf = ref[y];
+				if (rf == 0) { result = hops; break; }
+				if (!first_pass && hops) {
+					// resolved by an earlier pass, or earlier in this one: a 32-bit store is either seen whole or not at all
+					const uint32_t dy = vdepth[y];
+					if (dy != DEPTH_UNRESOLVED) { result = dy == DEPTH_INVALID ? DEPTH_INVALID : dy + hops; break; }
+				}
+				if (y - (int64_t)rf < 0) { result = DEPTH_INVALID; break; }
+				y -= rf;
+				hops++;
+			}
+			if (result == DEPTH_INVALID && lo + i >= from) raise(g, ERR_REF_UNRESOLVED);
+			if (first_pass || result != DEPTH_UNRESOLVED) depth[i] = result;
+		}
+	}
+	const bool unresolved = i < count && result == DEPTH_UNRESOLVED;
+	const uint32_t m = (i < count && result < DEPTH_INVALID) ? result : 0;
+	const uint32_t wm = __reduce_max_sync(0xffffffffu, m);
+	const unsigned un = __ballot_sync(0xffffffffu, unresolved);
+	if ((threadIdx.x & 31) == 0) {
+		if (un) atomicAdd(&stats[0], (uint32_t)__popc(un));
+		if (wm) atomicMax(&stats[1], wm);
+	}
+}
+
+void launch_depth(const Launch &L, const GraphDev &g, const uint8_t *ref, uint32_t *depth, int64_t lo, int64_t from,
+                  int64_t count, int first_pass, uint32_t *stats) {
+	if (count <= 0) return;
+	k_depth<<<grid_for(count, TPB), TPB, 0, L.stream>>>(g, ref, depth, lo, from, count, first_pass, stats);
+	WGBV_LAUNCHED(L);
+}
+
+// Level lists (only used when chains are deep): histogram of depths, then a scatter of node indices by level.
+__global__ void __launch_bounds__(TPB) k_level_count(const uint32_t *__restrict__ depth, int64_t count, uint32_t nlevels,
+                                                     unsigned long long *level_count) {
+	const int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
+	if (i >= count) return;
+	const uint32_t d = depth[i];
+	if (d == 0 || d >= nlevels) return;
+	atomicAdd(&level_count[d], 1ull);
+}
+__global__ void __launch_bounds__(TPB) k_level_scatter(const uint32_t *__restrict__ depth, int64_t count, uint32_t nlevels,
+                                                       unsigned long long *level_cursor, uint32_t *__restrict__ list) {
+	const int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
+	if (i >= count) return;
+	const uint32_t d = depth[i];
+	if (d == 0 || d >= nlevels) return;
+	const unsigned long long p = atomicAdd(&level_cursor[d], 1ull);
+	list[p] = (uint32_t)i;
+}
+void launch_level_count(const Launch &L, const uint32_t *depth, int64_t count, uint32_t nlevels, unsigned long long *level_count) {
+	k_level_count<<<grid_for(count, TPB), TPB, 0, L.stream>>>(depth, count, nlevels, level_count);
+	WGBV_LAUNCHED(L);
+}
+void launch_level_scatter(const Launch &L, const uint32_t *depth, int64_t count, uint32_t nlevels,
+                          unsigned long long *level_cursor, uint32_t *list) {
+	k_level_scatter<<<grid_for(count, TPB), TPB, 0, L.stream>>>(depth, count, nlevels, level_cursor, list);
+	WGBV_LAUNCHED(L);
+}
+
+// ------------------------------------------------------------------------------------------------ stage 3
+__device__ __forceinline__ int64_t *row_slot(const RangeDev &R, int64_t i, int64_t rp_from) {
+	const int64_t p = R.rp[i];
+	return (R.lo + i >= R.from) ? R.col + (p - rp_from) : R.halo + p;
+}
+
+// stage 3a: thread per node.  Rows without a reference come out complete.
+template <bool DEF>
+__global__ void __launch_bounds__(TPB) k_extras(GraphDev g, RangeDev R) {
+	const int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
+	const int64_t count = R.hi - R.lo;
+	if (i >= count) return;
+	const uint32_t d = R.deg[i];
+	if (d == 0 || R.depth[i] >= DEPTH_INVALID) return;
+	const int64_t x = R.lo + i;
+	const int64_t rp_from = R.rp[R.from - R.lo];
+	if (x >= R.from && (uint64_t)(R.rp[i + 1] - rp_from) > R.col_capacity) { raise(g, ERR_CAPACITY); return; }
+	BitReader r;
+	r.init(g, ef_get(g, x));
+	RowHead h;
+	const uint32_t rf = R.ref[i];
+	if (!row_head<DEF>(g, r, rf ? R.deg[i - rf] : 0, h)) return;
+	int64_t *dst = row_slot(R, i, rp_from);
+	row_extras<DEF>(g, r, x, h.d - h.ncopied, dst + h.ncopied);
+}
+
+void launch_extras(const Launch &L, const GraphDev &g, bool def, const RangeDev &r) {
+	const int64_t count = r.hi - r.lo;
+	if (count <= 0) return;
+	if (def) k_extras<true><<<grid_for(count, TPB), TPB, 0, L.stream>>>(g, r);
+	else k_extras<false><<<grid_for(count, TPB), TPB, 0, L.stream>>>(g, r);
+	WGBV_LAUNCHED(L);
+}
+
+// stage 3b: thread per row of one depth level.
+template <bool DEF>
+__global__ void __launch_bounds__(TPB) k_copy_level(GraphDev g, RangeDev R, uint32_t level, const uint32_t *__restrict__ list,
+                                                    uint64_t list_count) {
+	const uint64_t t = (uint64_t)blockIdx.x * TPB + threadIdx.x;
+	int64_t i;
+	if (list) {
+		if (t >= list_count) return;
+		i = list[t];
+	} else {
+		if ((int64_t)t >= R.hi - R.lo) return;
+		i = (int64_t)t;
+		if (R.depth[i] != level) return;
+	}
+	const uint32_t d = R.deg[i];
+	if (d == 0) return;
+	const int64_t x = R.lo + i;
+	const int64_t rp_from = R.rp[R.from - R.lo];
+	if (x >= R.from && (uint64_t)(R.rp[i + 1] - rp_from) > R.col_capacity) return;
+	const uint32_t rf = R.ref[i];
+	const uint32_t dref = R.deg[i - rf];
+	BitReader r;
+	r.init(g, ef_get(g, x));
+	RowHead h;
+	if (!row_head<DEF>(g, r, dref, h)) return;
+	r.seek(h.blocks_pos);
+	row_copy<DEF>(g, r, row_slot(R, i - rf, rp_from), dref, row_slot(R, i, rp_from), h.d, h.bc, h.ncopied);
+}
+
+void launch_copy_level(const Launch &L, const GraphDev &g, bool def, const RangeDev &r, uint32_t level, const uint32_t *list,
+                       uint64_t list_count) {
+	const int64_t items = list ? (int64_t)list_count : r.hi - r.lo;
+	if (items <= 0) return;
+	if (def) k_copy_level<true><<<grid_for(items, TPB), TPB, 0, L.stream>>>(g, r, level, list, list_count);
+	else k_copy_level<false><<<grid_for(items, TPB), TPB, 0, L.stream>>>(g, r, level, list, list_count);
+	WGBV_LAUNCHED(L);
+}
+
+// ------------------------------------------------------------------------------------------------ checksum
+// Same row hash as datagen/bvgen.c (row_hash) and, through it, what the generator computed before encoding.
+__device__ __forceinline__ uint64_t row_hash(int64_t x, const int64_t *a, int64_t d) {
+	uint64_t h = 0x9e3779b97f4a7c15ull ^ (uint64_t)d;
+	for (int64_t i = 0; i < d; i++) h = (h ^ (uint64_t)a[i]) * 0x100000001b3ull + 0x632be59bd9b4e019ull;
+	h ^= (uint64_t)x * 0xff51afd7ed558ccdull;
+	h ^= h >> 32;
+	h *= 0xd6e8feb86659fd93ull;
+	h ^= h >> 32;
+	return h;
+}
+
+__global__ void __launch_bounds__(TPB) k_checksum(int64_t first_node, int64_t rows, const int64_t *__restrict__ rowptr,
+                                                  const int64_t *__restrict__ col, unsigned long long *out) {
+	const int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
+	uint64_t h = 0;
+	if (i < rows) {
+		const int64_t a = rowptr[i], b = rowptr[i + 1];
+		h = row_hash(first_node + i, col + (a - rowptr[0]), b - a);
+	}
+#pragma unroll
+	for (int o = 16; o; o >>= 1) h += __shfl_xor_sync(0xffffffffu, h, o);
+	if ((threadIdx.x & 31) == 0 && h) atomicAdd(out, (unsigned long long)h);
+}
+
+void launch_checksum(const Launch &L, int64_t first_node, int64_t rows, const int64_t *rowptr, const int64_t *col,
+                     unsigned long long *out) {
+	if (rows <= 0) return;
+	k_checksum<<<grid_for(rows, TPB), TPB, 0, L.stream>>>(first_node, rows, rowptr, col, out);
+	WGBV_LAUNCHED(L);
+}
+
+// ------------------------------------------------------------------------------------------------ random access
+// outdegree(x) for arbitrary x (BVG:821-851).  Ids outside [lo, hi) raise the index error.
+template <bool DEF>
+__global__ void __launch_bounds__(TPB) k_batch_degrees(GraphDev g, const int64_t *__restrict__ ids, uint64_t k, int64_t lo,
+                                                       int64_t hi, uint32_t *__restrict__ deg) {
+	const uint64_t q = (uint64_t)blockIdx.x * TPB + threadIdx.x;
+	if (q >= k) return;
+	const int64_t x = ids[q];
+	if (x < lo || x >= hi) { raise(g, ERR_INDEX); deg[q] = 0; return; }
+	BitReader r;
+	r.init(g, ef_get(g, x));
+	const uint64_t d = rd_outdegree<DEF>(r, g);
+	if (d > 0x7fffffffull) { raise(g, ERR_DEGREE); deg[q] = 0; return; }
+	deg[q] = (uint32_t)d;
+}
+void launch_batch_degrees(const Launch &L, const GraphDev &g, bool def, const int64_t *ids, uint64_t k, int64_t lo, int64_t hi,
+                          uint32_t *deg) {
+	if (!k) return;
+	if (def) k_batch_degrees<true><<<grid_for((int64_t)k, TPB), TPB, 0, L.stream>>>(g, ids, k, lo, hi, deg);
+	else k_batch_degrees<false><<<grid_for((int64_t)k, TPB), TPB, 0, L.stream>>>(g, ids, k, lo, hi, deg);
+	WGBV_LAUNCHED(L);
+}
+
+// The reference resolves successors(x) recursively through x - ref (BVG:1084).  Here every query's chain
+// x, x - r1, x - r1 - r2, ... is laid out as explicit rows: the query row goes to the output, its ancestors to a
+// scratch store; rows are then decoded with the same two steps as the bulk path, root level first.
+template <bool DEF>
+__device__ __forceinline__ void chain_step(const GraphDev &g, int64_t y, uint32_t &d, uint32_t &rf) {
+	BitReader r;
+	r.init(g, ef_get(g, y));
+	const uint64_t dd = rd_outdegree<DEF>(r, g);
+	d = dd > 0x7fffffffull ? 0u : (uint32_t)dd;
+	rf = 0;
+	if (d && g.window > 0) {
+		const uint64_t f = rd_reference<DEF>(r, g);
+		if (f > (uint64_t)g.window || (int64_t)f > y) raise(g, ERR_REF_WINDOW);
+		else rf = (uint32_t)f;
+	}
+}
+
+template <bool DEF>
+__global__ void __launch_bounds__(TPB) k_chain_walk(GraphDev g, const int64_t *__restrict__ ids, uint64_t k, int64_t lo,
+                                                    uint32_t *__restrict__ chain_len, unsigned long long *__restrict__ chain_arcs,
+                                                    uint32_t *stats) {
+	const uint64_t q = (uint64_t)blockIdx.x * TPB + threadIdx.x;
+	if (q >= k) return;
+	int64_t y = ids[q];
+	uint32_t len = 0;
+	unsigned long long arcs = 0;
+	for (;;) {
+		uint32_t d, rf;
+		chain_step<DEF>(g, y, d, rf);
+		if (len) arcs += d;
+		len++;
+		if (!rf) break;
+		if (y - (int64_t)rf < lo) { raise(g, ERR_REF_UNRESOLVED); break; }
+		y -= rf;
+	}
+	chain_len[q] = len;
+	chain_arcs[q] = arcs;
+	atomicMax(&stats[1], len);
+}
+void launch_chain_walk(const Launch &L, const GraphDev &g, bool def, const int64_t *ids, uint64_t k, int64_t lo,
+                       uint32_t *chain_len, unsigned long long *chain_arcs, uint32_t *stats) {
+	if (!k) return;
+	if (def) k_chain_walk<true><<<grid_for((int64_t)k, TPB), TPB, 0, L.stream>>>(g, ids, k, lo, chain_len, chain_arcs, stats);
+	else k_chain_walk<false><<<grid_for((int64_t)k, TPB), TPB, 0, L.stream>>>(g, ids, k, lo, chain_len, chain_arcs, stats);
+	WGBV_LAUNCHED(L);
+}
+
+template <bool DEF>
+__global__ void __launch_bounds__(TPB) k_chain_fill(GraphDev g, const int64_t *__restrict__ ids, uint64_t k,
+                                                    const int64_t *__restrict__ chain_row0, const int64_t *__restrict__ store_off0,
+                                                    const int64_t *__restrict__ rowptr, int64_t *node, int64_t *dst_off,
+                                                    int32_t *parent, uint32_t *deg, uint8_t *is_query, uint32_t *level) {
+	const uint64_t q = (uint64_t)blockIdx.x * TPB + threadIdx.x;
+	if (q >= k) return;
+	const int64_t row0 = chain_row0[q];
+	const uint32_t len = (uint32_t)(chain_row0[q + 1] - row0);
+	int64_t y = ids[q];
+	int64_t soff = store_off0[q];
+	for (uint32_t j = 0; j < len; j++) {
+		uint32_t d, rf;
+		chain_step<DEF>(g, y, d, rf);
+		const int64_t row = row0 + j;
+		node[row] = y;
+		deg[row] = d;
+		is_query[row] = j == 0;
+		level[row] = len - 1 - j;
+		parent[row] = (j + 1 < len) ? (int32_t)(row + 1) : -1;
+		if (j == 0) dst_off[row] = rowptr[q];
+		else { dst_off[row] = soff; soff += d; }
+		y -= rf;
+	}
+}
+void launch_chain_fill(const Launch &L, const GraphDev &g, bool def, const int64_t *ids, uint64_t k, const int64_t *chain_row0,
+                       const int64_t *store_off0, const int64_t *rowptr, int64_t *node, int64_t *dst_off, int32_t *parent,
+                       uint32_t *deg, uint8_t *is_query, uint32_t *level) {
+	if (!k) return;
+	if (def) k_chain_fill<true><<<grid_for((int64_t)k, TPB), TPB, 0, L.stream>>>(g, ids, k, chain_row0, store_off0, rowptr, node, dst_off, parent, deg, is_query, level);
+	else k_chain_fill<false><<<grid_for((int64_t)k, TPB), TPB, 0, L.stream>>>(g, ids, k, chain_row0, store_off0, rowptr, node, dst_off, parent, deg, is_query, level);
+	WGBV_LAUNCHED(L);
+}
+
+__device__ __forceinline__ int64_t *chain_slot(const ChainDev &c, uint64_t row) {
+	return (c.is_query[row] ? c.col : c.store) + c.dst_off[row];
+}
+
+template <bool DEF>
+__global__ void __launch_bounds__(TPB) k_chain_extras(GraphDev g, ChainDev c, uint64_t rows) {
+	const uint64_t row = (uint64_t)blockIdx.x * TPB + threadIdx.x;
+	if (row >= rows) return;
+	const uint32_t d = c.deg[row];
+	if (d == 0) return;
+	const int64_t x = c.node[row];
+	const int32_t p = c.parent[row];
+	BitReader r;
+	r.init(g, ef_get(g, x));
+	RowHead h;
+	if (!row_head<DEF>(g, r, p >= 0 ? c.deg[p] : 0, h)) return;
+	row_extras<DEF>(g, r, x, h.d - h.ncopied, chain_slot(c, row) + h.ncopied);
+}
+void launch_chain_extras(const Launch &L, const GraphDev &g, bool def, const ChainDev &c, uint64_t rows) {
+	if (!rows) return;
+	if (def) k_chain_extras<true><<<grid_for((int64_t)rows, TPB), TPB, 0, L.stream>>>(g, c, rows);
+	else k_chain_extras<false><<<grid_for((int64_t)rows, TPB), TPB, 0, L.stream>>>(g, c, rows);
+	WGBV_LAUNCHED(L);
+}
+
+template <bool DEF>
+__global__ void __launch_bounds__(TPB) k_chain_copy(GraphDev g, ChainDev c, uint64_t rows, const uint32_t *__restrict__ level,
+                                                    uint32_t this_level) {
+	const uint64_t row = (uint64_t)blockIdx.x * TPB + threadIdx.x;
+	if (row >= rows || level[row] != this_level) return;
+	const uint32_t d = c.deg[row];
+	const int32_t p = c.parent[row];
+	if (d == 0 || p < 0) return;
+	const int64_t x = c.node[row];
+	const uint32_t dref = c.deg[p];
+	BitReader r;
+	r.init(g, ef_get(g, x));
+	RowHead h;
+	if (!row_head<DEF>(g, r, dref, h)) return;
+	r.seek(h.blocks_pos);
+	row_copy<DEF>(g, r, chain_slot(c, (uint64_t)p), dref, chain_slot(c, row), h.d, h.bc, h.ncopied);
+}
+void launch_chain_copy(const Launch &L, const GraphDev &g, bool def, const ChainDev &c, uint64_t rows, const uint32_t *level,
+                       uint32_t this_level) {
+	if (!rows) return;
+	if (def) k_chain_copy<true><<<grid_for((int64_t)rows, TPB), TPB, 0, L.stream>>>(g, c, rows, level, this_level);
+	else k_chain_copy<false><<<grid_for((int64_t)rows, TPB), TPB, 0, L.stream>>>(g, c, rows, level, this_level);
+	WGBV_LAUNCHED(L);
+}
+
+}  // namespace wgbv

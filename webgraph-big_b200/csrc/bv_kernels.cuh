@@ -1,0 +1,81 @@
+// bv_kernels.cuh -- launch interface between the C ABI (wgbv_api.cu) and the kernels (bv_kernels.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "bv_device.cuh"
+
+namespace wgbv {
+
+enum : uint32_t {
+	DEPTH_UNRESOLVED = 0xffffffffu,  // chain not followed to its root yet
+	DEPTH_INVALID = 0xfffffffeu,     // chain leaves the decodable range (halo rows only)
+};
+
+// One bulk decode job: nodes [lo, hi) are decoded, of which [from, hi) were requested; [lo, from) is the halo.
+struct RangeDev {
+	int64_t lo, from, hi;
+	const uint32_t *deg;    // outdegrees of [lo, hi)
+	const uint8_t *ref;     // references of [lo, hi) (0: none)
+	const uint32_t *depth;  // reference-chain depth of [lo, hi)
+	const int64_t *rp;      // exclusive prefix sum of deg, hi-lo+1 entries, rp[0] = 0
+	int64_t *col;           // successors of [from, hi): row x starts at col + rp[x-lo] - rp[from-lo]
+	int64_t *halo;          // successors of [lo, from): row x starts at halo + rp[x-lo]
+	uint64_t col_capacity;  // elements available at col
+};
+
+// One random-access job list: `rows` chain rows, each decoded into its own slot.
+struct ChainDev {
+	const int64_t *node;     // node id of each chain row
+	const int64_t *dst_off;  // element offset of the row's slot (in `store` for ancestors, in `col` for the query row)
+	const int32_t *parent;   // index of the row holding the reference list (-1: none)
+	const uint32_t *deg;     // outdegree of each chain row
+	const uint8_t *is_query; // 1: the row is a query's own list (goes to col), 0: ancestor (goes to store)
+	int64_t *col;
+	int64_t *store;
+};
+
+struct Launch {
+	cudaStream_t stream;
+	uint64_t *launches;  // incremented once per kernel launched
+};
+
+// stage 1: outdegree and reference of every node of [lo, lo+count)
+void launch_header(const Launch &L, const GraphDev &g, bool def, int64_t lo, int64_t count, uint32_t *deg, uint8_t *ref);
+// stage 2: exclusive prefix sum (single pass, decoupled look-back).  state: count/2048+2 words, ticket: 1 word
+void launch_scan(const Launch &L, const uint32_t *deg, int64_t *rp, int64_t count, uint64_t *state, uint32_t *ticket);
+// rowptr_out[i] = rp[skip + i] - rp[skip] (+ base), i = 0..count
+void launch_emit_rowptr(const Launch &L, const int64_t *rp, int64_t skip, int64_t count, int64_t *rowptr_out);
+// stage 2b: reference-chain depths.  stats[0] = nodes still unresolved after this pass, stats[1] = max depth seen
+void launch_depth(const Launch &L, const GraphDev &g, const uint8_t *ref, uint32_t *depth, int64_t lo, int64_t from,
+                  int64_t count, int first_pass, uint32_t *stats);
+// level lists for deep chains: count per level, then scatter node indices (relative to lo) by level
+void launch_level_count(const Launch &L, const uint32_t *depth, int64_t count, uint32_t nlevels, unsigned long long *level_count);
+void launch_level_scatter(const Launch &L, const uint32_t *depth, int64_t count, uint32_t nlevels,
+                          unsigned long long *level_cursor, uint32_t *list);
+// stage 3a: intervals + residuals of every row (whole row when it has no reference)
+void launch_extras(const Launch &L, const GraphDev &g, bool def, const RangeDev &r);
+// stage 3b: copy-block resolution of the rows at one depth level; list == nullptr: every node is inspected
+void launch_copy_level(const Launch &L, const GraphDev &g, bool def, const RangeDev &r, uint32_t level,
+                       const uint32_t *list, uint64_t list_count);
+// checksum of a CSR
+void launch_checksum(const Launch &L, int64_t first_node, int64_t rows, const int64_t *rowptr, const int64_t *col,
+                     unsigned long long *out);
+
+// random access
+void launch_batch_degrees(const Launch &L, const GraphDev &g, bool def, const int64_t *ids, uint64_t k, int64_t lo,
+                          int64_t hi, uint32_t *deg);
+// walks the reference chain of every query: chain_len[q] rows, chain_arcs[q] successors in ancestor rows
+void launch_chain_walk(const Launch &L, const GraphDev &g, bool def, const int64_t *ids, uint64_t k, int64_t lo,
+                       uint32_t *chain_len, unsigned long long *chain_arcs, uint32_t *stats);
+void launch_chain_fill(const Launch &L, const GraphDev &g, bool def, const int64_t *ids, uint64_t k,
+                       const int64_t *chain_row0, const int64_t *store_off0, const int64_t *rowptr, int64_t *node,
+                       int64_t *dst_off, int32_t *parent, uint32_t *deg, uint8_t *is_query, uint32_t *level);
+void launch_chain_extras(const Launch &L, const GraphDev &g, bool def, const ChainDev &c, uint64_t rows);
+void launch_chain_copy(const Launch &L, const GraphDev &g, bool def, const ChainDev &c, uint64_t rows,
+                       const uint32_t *level, uint32_t this_level);
+void launch_scan64(const Launch &L, const unsigned long long *in, int64_t *out, int64_t count, uint64_t *state, uint32_t *ticket);
+// byte-swap the uploaded stream into big-endian 64-bit words, in place
+void launch_bswap(const Launch &L, uint64_t *words, uint64_t nwords);
+
+}  // namespace wgbv

@@ -1,0 +1,638 @@
+// wgbv_api.cu -- the C ABI of libwgbv (include/wgbv.h): handles, device memory, and the orchestration of the
+// decode pipeline.  Host code only; the kernels live in bv_kernels.cu.
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "bv_kernels.cuh"
+#include "bv_loader.h"
+
+using namespace wgbv;
+
+#define CU(call)                                                                                                  \
+	do {                                                                                                          \
+		const cudaError_t e_ = (call);                                                                            \
+		if (e_ != cudaSuccess) return fail(WGBV_ECUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+	} while (0)
+
+// ------------------------------------------------------------------------------------------------ handles
+struct wgbv_graph {
+	wgbv_props props{};
+	int device = 0;
+	bool def_codes = true;
+	int64_t shard_lo = 0, shard_hi = 0;  // nodes this handle decodes
+	int64_t avail_lo = 0;                // first node whose record is held (shard_lo minus the halo)
+	int64_t halo_nodes = 0;              // window_size * max_ref_count, or -1 if unbounded
+	GraphDev dev{};
+	uint64_t *d_words = nullptr, *d_lower = nullptr, *d_upper = nullptr, *d_hints = nullptr, *d_sparse = nullptr;
+	uint64_t device_bytes = 0;
+	EliasFano ef;  // host copy, for accounting
+	int streams = 0;
+};
+
+// A grow-only device buffer.
+struct DevBuf {
+	void *p = nullptr;
+	size_t cap = 0;
+	int ensure(size_t bytes) {
+		if (bytes <= cap) return WGBV_OK;
+		if (p) cudaFree(p);
+		p = nullptr;
+		cap = 0;
+		size_t want = bytes + bytes / 8 + 256;
+		cudaError_t e = cudaMalloc(&p, want);
+		if (e != cudaSuccess) {
+			want = bytes;
+			e = cudaMalloc(&p, want);
+		}
+		if (e != cudaSuccess) { p = nullptr; return fail(WGBV_ECUDA, "cudaMalloc of %zu bytes failed: %s", want, cudaGetErrorString(e)); }
+		cap = want;
+		return WGBV_OK;
+	}
+	void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+	template <typename T> T *as() const { return (T *)p; }
+};
+
+struct wgbv_stream {
+	wgbv_graph *g = nullptr;
+	cudaStream_t stream = nullptr;
+	bool own_stream = false;
+	GraphDev dev{};            // the graph's view with this stream's error word
+	uint32_t *d_err = nullptr;  // [0] sticky error bits, [1..3] spare
+	uint32_t *d_stats = nullptr;  // [0] unresolved, [1] max depth, [2..3] spare
+	uint64_t *h_pin = nullptr;  // pinned host scratch for read-backs (16 words)
+	uint64_t launches = 0;
+	DevBuf deg, ref, depth, rp, scan_state, ticket, halo, levels, list, col, rowptr, ids, batch;
+	DevBuf c_node, c_dst, c_parent, c_deg, c_isq, c_level, c_len, c_arcs, c_row0, c_soff, c_store;
+	cudaEvent_t ev[6]{};
+	bool ev_valid = false;
+	Launch launch() { return Launch{stream, &launches}; }
+};
+
+// ------------------------------------------------------------------------------------------------ misc
+extern "C" const char *wgbv_last_error(void) { return last_error_message(); }
+
+extern "C" int wgbv_parse_properties(const char *text, wgbv_props *out) {
+	clear_error();
+	return parse_properties_text(text, out);
+}
+
+static int check_codings(const wgbv_props &p) {
+	auto gd = [](int c) { return c == WGBV_GAMMA || c == WGBV_DELTA; };
+	auto gdu = [](int c) { return c == WGBV_GAMMA || c == WGBV_DELTA || c == WGBV_UNARY; };
+	if (!gd(p.outdegree_coding)) return fail(WGBV_EUNSUPPORTED, "The required outdegree coding (%d) is not supported.", p.outdegree_coding);
+	if (!gdu(p.reference_coding)) return fail(WGBV_EUNSUPPORTED, "The required reference coding (%d) is not supported.", p.reference_coding);
+	if (!gdu(p.block_count_coding)) return fail(WGBV_EUNSUPPORTED, "The required block count coding (%d) is not supported.", p.block_count_coding);
+	if (!gdu(p.block_coding)) return fail(WGBV_EUNSUPPORTED, "The required block coding (%d) is not supported.", p.block_coding);
+	const int r = p.residual_coding;
+	if (r != WGBV_GAMMA && r != WGBV_ZETA && r != WGBV_DELTA && r != WGBV_GOLOMB && r != WGBV_NIBBLE)
+		return fail(WGBV_EUNSUPPORTED, "The required residuals coding (%d) is not supported.", r);
+	if (!gd(p.offset_coding)) return fail(WGBV_EUNSUPPORTED, "The required offset coding (%d) is not supported.", p.offset_coding);
+	if (p.window_size < 0 || p.window_size > 255) return fail(WGBV_EUNSUPPORTED, "window sizes above 255 are not supported");
+	if (p.zeta_k < 1 || p.zeta_k > 32) return fail(WGBV_EUNSUPPORTED, "zeta_k out of range");
+	return WGBV_OK;
+}
+
+static int select_device(int device) {
+	int n = 0;
+	const cudaError_t e = cudaGetDeviceCount(&n);
+	if (e != cudaSuccess || n == 0) return fail(WGBV_ECUDA, "no usable CUDA device (%s); libwgbv has no CPU fallback", e != cudaSuccess ? cudaGetErrorString(e) : "0 devices");
+	if (device < 0 || device >= n) return fail(WGBV_ECUDA, "device %d out of range (%d devices)", device, n);
+	CU(cudaSetDevice(device));
+	return WGBV_OK;
+}
+
+static int upload(uint64_t **dst, const std::vector<uint64_t> &v, uint64_t *total) {
+	const size_t bytes = std::max<size_t>(v.size(), 1) * 8;
+	CU(cudaMalloc((void **)dst, bytes));
+	if (!v.empty()) CU(cudaMemcpy(*dst, v.data(), v.size() * 8, cudaMemcpyHostToDevice));
+	*total += bytes;
+	return WGBV_OK;
+}
+
+extern "C" void wgbv_close(wgbv_graph *g) {
+	if (!g) return;
+	cudaSetDevice(g->device);
+	cudaFree(g->d_words);
+	cudaFree(g->d_lower);
+	cudaFree(g->d_upper);
+	cudaFree(g->d_hints);
+	cudaFree(g->d_sparse);
+	delete g;
+}
+
+extern "C" int wgbv_open_mem(const wgbv_props *props, const uint8_t *graph, uint64_t graph_bytes, const uint8_t *offsets,
+                             uint64_t offsets_bytes, int device, int shard_index, int shard_count, wgbv_graph **out) {
+	clear_error();
+	if (!props || !out || (!graph && graph_bytes) || !offsets) return fail(WGBV_EARG, "null argument");
+	*out = nullptr;
+	if (shard_count < 1 || shard_index < 0 || shard_index >= shard_count) return fail(WGBV_EARG, "bad shard %d of %d", shard_index, shard_count);
+	int rc = check_codings(*props);
+	if (rc) return rc;
+	if ((rc = select_device(device))) return rc;
+
+	std::vector<uint64_t> off;
+	if ((rc = decode_offsets(*props, offsets, offsets_bytes, off))) return rc;
+	const int64_t n = props->nodes;
+	if (off[(size_t)n] > graph_bytes * 8) return fail(WGBV_EIO, "the last offset (%llu) lies beyond the end of the bit stream (%llu bits)", (unsigned long long)off[(size_t)n], (unsigned long long)graph_bytes * 8);
+	for (int64_t i = 0; i < n; i++)
+		if (off[(size_t)i + 1] < off[(size_t)i]) return fail(WGBV_EIO, "offsets are not monotone at node %lld", (long long)i);
+
+	wgbv_graph *g = new (std::nothrow) wgbv_graph();
+	if (!g) return fail(WGBV_EARG, "out of host memory");
+	g->props = *props;
+	g->device = device;
+	g->def_codes = props->outdegree_coding == WGBV_GAMMA && props->block_coding == WGBV_GAMMA && props->residual_coding == WGBV_ZETA &&
+	               props->reference_coding == WGBV_UNARY && props->block_count_coding == WGBV_GAMMA;
+	// halo: a reference chain has at most max_ref_count hops of at most window_size nodes each (BVG:701, 2258)
+	const int64_t halo = (int64_t)props->window_size * (int64_t)props->max_ref_count;
+	g->halo_nodes = (props->window_size == 0 || props->max_ref_count <= 0) ? 0 : (props->max_ref_count > (1 << 20) ? -1 : halo);
+	if (g->halo_nodes < 0 && shard_count > 1) {
+		delete g;
+		return fail(WGBV_EUNSUPPORTED, "maxrefcount=%d makes reference chains unbounded: the graph cannot be sharded", props->max_ref_count);
+	}
+	std::vector<int64_t> bounds;
+	plan_shards(off, shard_count, bounds);
+	g->shard_lo = bounds[(size_t)shard_index];
+	g->shard_hi = bounds[(size_t)shard_index + 1];
+	g->avail_lo = g->halo_nodes < 0 ? 0 : std::max<int64_t>(0, g->shard_lo - g->halo_nodes);
+
+	// the slice of the bit stream that holds [avail_lo, shard_hi), starting on a 64-bit word of the file
+	const uint64_t bit0 = off[(size_t)g->avail_lo] & ~63ull;
+	const uint64_t bit1 = off[(size_t)g->shard_hi];
+	const uint64_t byte0 = bit0 >> 3;
+	const uint64_t byte1 = std::min<uint64_t>((bit1 + 7) >> 3, graph_bytes);
+	const uint64_t data_words = (byte1 > byte0 ? byte1 - byte0 + 7 : 0) / 8;
+	const uint64_t nwords = data_words + 2;
+	auto cleanup = [&](int code) { wgbv_close(g); return code; };
+	if (cudaMalloc((void **)&g->d_words, nwords * 8) != cudaSuccess) return cleanup(fail(WGBV_ECUDA, "cudaMalloc of the bit stream (%llu bytes) failed", (unsigned long long)nwords * 8));
+	g->device_bytes += nwords * 8;
+	if (cudaMemset(g->d_words, 0, nwords * 8) != cudaSuccess) return cleanup(fail(WGBV_ECUDA, "cudaMemset failed"));
+	if (byte1 > byte0 && cudaMemcpy(g->d_words, graph + byte0, byte1 - byte0, cudaMemcpyHostToDevice) != cudaSuccess)
+		return cleanup(fail(WGBV_ECUDA, "upload of the bit stream failed"));
+	Launch L{nullptr, nullptr};
+	launch_bswap(L, g->d_words, data_words);
+
+	// Elias-Fano list of the offsets of [avail_lo, shard_hi] relative to bit0
+	g->ef.build(off.data() + g->avail_lo, (uint64_t)(g->shard_hi - g->avail_lo + 1), bit0);
+	if ((rc = upload(&g->d_lower, g->ef.lower, &g->device_bytes))) return cleanup(rc);
+	if ((rc = upload(&g->d_upper, g->ef.upper, &g->device_bytes))) return cleanup(rc);
+	if ((rc = upload(&g->d_hints, g->ef.hints, &g->device_bytes))) return cleanup(rc);
+	if ((rc = upload(&g->d_sparse, g->ef.sparse, &g->device_bytes))) return cleanup(rc);
+	if (cudaDeviceSynchronize() != cudaSuccess) return cleanup(fail(WGBV_ECUDA, "device error while loading: %s", cudaGetErrorString(cudaGetLastError())));
+
+	GraphDev &d = g->dev;
+	d.words = g->d_words;
+	d.nwords = nwords;
+	d.bit_base = bit0;
+	d.bit_end = bit1;
+	d.ef_lower = g->d_lower;
+	d.ef_upper = g->d_upper;
+	d.ef_hints = g->d_hints;
+	d.ef_sparse = g->d_sparse;
+	d.ef_first = g->avail_lo;
+	d.ef_count = g->shard_hi - g->avail_lo + 1;
+	d.ef_l = g->ef.l;
+	d.nodes = n;
+	d.window = props->window_size;
+	d.min_interval = props->min_interval_length;
+	d.zeta_k = props->zeta_k;
+	d.outdegree_coding = props->outdegree_coding;
+	d.block_coding = props->block_coding;
+	d.residual_coding = props->residual_coding;
+	d.reference_coding = props->reference_coding;
+	d.block_count_coding = props->block_count_coding;
+	d.err = nullptr;
+	*out = g;
+	return WGBV_OK;
+}
+
+extern "C" int wgbv_open(const char *basename, int device, int shard_index, int shard_count, wgbv_graph **out) {
+	clear_error();
+	if (!basename || !out) return fail(WGBV_EARG, "null argument");
+	std::vector<uint8_t> ptxt, graph, offs;
+	int rc;
+	const std::string base(basename);
+	if ((rc = read_file(base + ".properties", ptxt))) return rc;
+	ptxt.push_back(0);
+	wgbv_props p;
+	if ((rc = parse_properties_text((const char *)ptxt.data(), &p))) return rc;
+	if ((rc = read_file(base + ".graph", graph))) return rc;
+	if ((rc = read_file(base + ".offsets", offs))) return rc;
+	return wgbv_open_mem(&p, graph.data(), graph.size(), offs.data(), offs.size(), device, shard_index, shard_count, out);
+}
+
+extern "C" int64_t wgbv_num_nodes(const wgbv_graph *g) { return g ? g->props.nodes : 0; }
+extern "C" int64_t wgbv_num_arcs(const wgbv_graph *g) { return g ? g->props.arcs : 0; }
+extern "C" int wgbv_get_props(const wgbv_graph *g, wgbv_props *out) {
+	if (!g || !out) return fail(WGBV_EARG, "null argument");
+	*out = g->props;
+	return WGBV_OK;
+}
+extern "C" int wgbv_shard_range(const wgbv_graph *g, int64_t *first, int64_t *last) {
+	if (!g || !first || !last) return fail(WGBV_EARG, "null argument");
+	*first = g->shard_lo;
+	*last = g->shard_hi;
+	return WGBV_OK;
+}
+extern "C" uint64_t wgbv_device_bytes(const wgbv_graph *g) { return g ? g->device_bytes : 0; }
+extern "C" uint64_t wgbv_offsets_bytes(const wgbv_graph *g) { return g ? g->ef.bytes() : 0; }
+
+extern "C" uint64_t wgbv_algorithmic_bytes(const wgbv_graph *g, int64_t from, int64_t to, int64_t arcs) {
+	if (!g || from < g->avail_lo || to > g->shard_hi || to < from) return 0;
+	const uint64_t bits = g->ef.get((uint64_t)(to - g->avail_lo)) - g->ef.get((uint64_t)(from - g->avail_lo));
+	const uint64_t nodes = (uint64_t)(to - from);
+	const uint64_t ef_bits = nodes * (2 + (uint64_t)g->ef.l);
+	return (bits + 7) / 8 + (ef_bits + 7) / 8 + 8 * (nodes + 1) + 8 * (uint64_t)arcs;
+}
+
+// ------------------------------------------------------------------------------------------------ streams
+extern "C" int wgbv_stream_create(wgbv_graph *g, void *cuda_stream, wgbv_stream **out) {
+	clear_error();
+	if (!g || !out) return fail(WGBV_EARG, "null argument");
+	*out = nullptr;
+	CU(cudaSetDevice(g->device));
+	wgbv_stream *s = new (std::nothrow) wgbv_stream();
+	if (!s) return fail(WGBV_EARG, "out of host memory");
+	s->g = g;
+	if (cuda_stream) s->stream = (cudaStream_t)cuda_stream;
+	else {
+		if (cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking) != cudaSuccess) { delete s; return fail(WGBV_ECUDA, "cudaStreamCreate failed"); }
+		s->own_stream = true;
+	}
+	if (cudaMalloc((void **)&s->d_err, 32) != cudaSuccess || cudaMemset(s->d_err, 0, 32) != cudaSuccess ||
+	    cudaMallocHost((void **)&s->h_pin, 16 * 8) != cudaSuccess) {
+		wgbv_stream_destroy(s);
+		return fail(WGBV_ECUDA, "allocation of the stream state failed");
+	}
+	s->d_stats = s->d_err + 4;
+	for (auto &e : s->ev) cudaEventCreate(&e);
+	s->dev = g->dev;
+	s->dev.err = s->d_err;
+	g->streams++;
+	*out = s;
+	return WGBV_OK;
+}
+
+extern "C" void wgbv_stream_destroy(wgbv_stream *s) {
+	if (!s) return;
+	cudaSetDevice(s->g->device);
+	if (s->stream) cudaStreamSynchronize(s->stream);
+	for (DevBuf *b : {&s->deg, &s->ref, &s->depth, &s->rp, &s->scan_state, &s->ticket, &s->halo, &s->levels, &s->list, &s->col,
+	                  &s->rowptr, &s->ids, &s->batch, &s->c_node, &s->c_dst, &s->c_parent, &s->c_deg, &s->c_isq, &s->c_level,
+	                  &s->c_len, &s->c_arcs, &s->c_row0, &s->c_soff, &s->c_store})
+		b->release();
+	if (s->d_err) cudaFree(s->d_err);
+	if (s->h_pin) cudaFreeHost(s->h_pin);
+	for (auto &e : s->ev) if (e) cudaEventDestroy(e);
+	if (s->own_stream && s->stream) cudaStreamDestroy(s->stream);
+	s->g->streams--;
+	delete s;
+}
+
+// Reads and clears the sticky error word; maps it onto a status code.
+static int collect_errors(wgbv_stream *s) {
+	uint32_t *h = (uint32_t *)(s->h_pin + 8);
+	CU(cudaMemcpyAsync(h, s->d_err, 4, cudaMemcpyDeviceToHost, s->stream));
+	CU(cudaStreamSynchronize(s->stream));
+	const uint32_t e = h[0];
+	if (!e) return WGBV_OK;
+	CU(cudaMemsetAsync(s->d_err, 0, 4, s->stream));
+	if (e & ERR_INDEX) return fail(WGBV_EINDEX, "Node index out of range");
+	if (e & ERR_REF_WINDOW) return fail(WGBV_ESTATE, "The required reference is incompatible with the window size (%d)", s->g->props.window_size);
+	if (e & ERR_OVERRUN) return fail(WGBV_EIO, "a code runs past the end of the bit stream");
+	if (e & ERR_REF_UNRESOLVED) return fail(WGBV_ESTATE, "a reference chain is longer than maxrefcount allows and leaves the loaded range");
+	if (e & ERR_NOT_SORTED) return fail(WGBV_ESTATE, "malformed successor list: copied successors and extras overlap");
+	if (e & ERR_CAPACITY) return fail(WGBV_EARG, "output capacity exceeded");
+	return fail(WGBV_ESTATE, "malformed bit stream (inconsistent counts, error bits 0x%x)", e);
+}
+
+extern "C" int wgbv_stream_sync(wgbv_stream *s) {
+	clear_error();
+	if (!s) return fail(WGBV_EARG, "null argument");
+	CU(cudaSetDevice(s->g->device));
+	CU(cudaStreamSynchronize(s->stream));
+	const cudaError_t e = cudaGetLastError();
+	if (e != cudaSuccess) return fail(WGBV_ECUDA, "CUDA error: %s", cudaGetErrorString(e));
+	return collect_errors(s);
+}
+
+extern "C" uint64_t wgbv_kernel_launches(const wgbv_stream *s) { return s ? s->launches : 0; }
+
+// ------------------------------------------------------------------------------------------------ bulk decode
+static int check_range(const wgbv_graph *g, int64_t from, int64_t to) {
+	if (from < 0 || from > g->props.nodes || to < from || to > g->props.nodes) return fail(WGBV_EINDEX, "Node index out of range: [%lld, %lld)", (long long)from, (long long)to);
+	if (from < g->shard_lo || to > g->shard_hi) return fail(WGBV_EINDEX, "Node index out of range for this shard [%lld, %lld): [%lld, %lld)", (long long)g->shard_lo, (long long)g->shard_hi, (long long)from, (long long)to);
+	return WGBV_OK;
+}
+
+// First node that has to be decoded so that every row of [from, ...) finds its reference chain.
+static int64_t halo_start(const wgbv_graph *g, int64_t from) {
+	if (g->halo_nodes < 0) return g->avail_lo;
+	return std::max<int64_t>(g->avail_lo, from - g->halo_nodes);
+}
+
+struct Prepared {
+	int64_t lo = 0, cnt = 0, halo_n = 0;
+	int64_t halo_arcs = 0, arcs = 0;
+	uint32_t max_depth = 0;
+	const int64_t *rp = nullptr;
+};
+
+// Stages 1, 2 and 2b for [from, to): degrees, row pointers and depth levels.  Leaves the row pointers of
+// [lo, to) in s->rp and writes those of [from, to) to d_rowptr.  Synchronises once to learn the arc counts.
+static int prepare(wgbv_stream *s, int64_t from, int64_t to, int64_t *d_rowptr, bool want_depth, Prepared &P) {
+	wgbv_graph *g = s->g;
+	const Launch L = s->launch();
+	P.lo = halo_start(g, from);
+	P.cnt = to - P.lo;
+	P.halo_n = from - P.lo;
+	if (P.cnt >= (int64_t)0xfffffff0ll) return fail(WGBV_EARG, "a single decode call is limited to 2^32-16 nodes; split the range");
+	int rc;
+	const size_t c = (size_t)std::max<int64_t>(P.cnt, 1);
+	if ((rc = s->deg.ensure(c * 4)) || (rc = s->ref.ensure(c)) || (rc = s->rp.ensure((c + 1) * 8)) ||
+	    (rc = s->scan_state.ensure(((c + 1) / 2048 + 2) * 8)) || (rc = s->ticket.ensure(64)))
+		return rc;
+	if (want_depth && (rc = s->depth.ensure(c * 4))) return rc;
+	cudaEventRecord(s->ev[0], s->stream);
+	launch_header(L, s->dev, g->def_codes, P.lo, P.cnt, s->deg.as<uint32_t>(), s->ref.as<uint8_t>());
+	cudaEventRecord(s->ev[1], s->stream);
+	int64_t *rp = (P.halo_n == 0 && d_rowptr) ? d_rowptr : s->rp.as<int64_t>();
+	launch_scan(L, s->deg.as<uint32_t>(), rp, P.cnt, s->scan_state.as<uint64_t>(), s->ticket.as<uint32_t>());
+	if (rp != d_rowptr && d_rowptr) launch_emit_rowptr(L, rp, P.halo_n, to - from, d_rowptr);
+	P.rp = rp;
+	cudaEventRecord(s->ev[2], s->stream);
+	uint32_t *hs = (uint32_t *)(s->h_pin + 4);
+	if (want_depth) {
+		for (int pass = 0;; pass++) {
+			CU(cudaMemsetAsync(s->d_stats, 0, 8, s->stream));
+			launch_depth(L, s->dev, s->ref.as<uint8_t>(), s->depth.as<uint32_t>(), P.lo, from, P.cnt, pass == 0, s->d_stats);
+			CU(cudaMemcpyAsync(hs, s->d_stats, 8, cudaMemcpyDeviceToHost, s->stream));
+			if (pass == 0) {
+				CU(cudaMemcpyAsync(s->h_pin, rp + P.halo_n, 8, cudaMemcpyDeviceToHost, s->stream));
+				CU(cudaMemcpyAsync(s->h_pin + 1, rp + P.cnt, 8, cudaMemcpyDeviceToHost, s->stream));
+			}
+			CU(cudaStreamSynchronize(s->stream));
+			if (hs[0] == 0) break;
+			if (pass > (1 << 26)) return fail(WGBV_ESTATE, "reference chains do not resolve");
+		}
+		P.max_depth = hs[1];
+	} else {
+		CU(cudaMemcpyAsync(s->h_pin, rp + P.halo_n, 8, cudaMemcpyDeviceToHost, s->stream));
+		CU(cudaMemcpyAsync(s->h_pin + 1, rp + P.cnt, 8, cudaMemcpyDeviceToHost, s->stream));
+		CU(cudaStreamSynchronize(s->stream));
+	}
+	P.halo_arcs = (int64_t)s->h_pin[0];
+	P.arcs = (int64_t)s->h_pin[1] - P.halo_arcs;
+	cudaEventRecord(s->ev[3], s->stream);
+	return WGBV_OK;
+}
+
+extern "C" int wgbv_decode_degrees(wgbv_stream *s, int64_t from, int64_t to, int64_t *d_rowptr, int64_t *arcs_out) {
+	clear_error();
+	if (!s || !d_rowptr) return fail(WGBV_EARG, "null argument");
+	CU(cudaSetDevice(s->g->device));
+	int rc = check_range(s->g, from, to);
+	if (rc) return rc;
+	Prepared P;
+	// no halo is needed for degrees alone
+	wgbv_graph *g = s->g;
+	const Launch L = s->launch();
+	const int64_t cnt = to - from;
+	const size_t c = (size_t)std::max<int64_t>(cnt, 1);
+	if (cnt >= (int64_t)0xfffffff0ll) return fail(WGBV_EARG, "a single decode call is limited to 2^32-16 nodes; split the range");
+	if ((rc = s->deg.ensure(c * 4)) || (rc = s->ref.ensure(c)) || (rc = s->scan_state.ensure(((c + 1) / 2048 + 2) * 8)) || (rc = s->ticket.ensure(64))) return rc;
+	launch_header(L, s->dev, g->def_codes, from, cnt, s->deg.as<uint32_t>(), s->ref.as<uint8_t>());
+	launch_scan(L, s->deg.as<uint32_t>(), d_rowptr, cnt, s->scan_state.as<uint64_t>(), s->ticket.as<uint32_t>());
+	CU(cudaMemcpyAsync(s->h_pin, d_rowptr + cnt, 8, cudaMemcpyDeviceToHost, s->stream));
+	if ((rc = collect_errors(s))) return rc;
+	if (arcs_out) *arcs_out = (int64_t)s->h_pin[0];
+	(void)P;
+	return WGBV_OK;
+}
+
+// Stage 3 on a prepared range.
+static int decode_rows(wgbv_stream *s, int64_t from, int64_t to, const Prepared &P, int64_t *d_col, uint64_t col_capacity) {
+	wgbv_graph *g = s->g;
+	const Launch L = s->launch();
+	int rc;
+	if ((uint64_t)P.arcs > col_capacity) return fail(WGBV_EARG, "col_capacity (%llu) is smaller than the %lld arcs of [%lld, %lld)", (unsigned long long)col_capacity, (long long)P.arcs, (long long)from, (long long)to);
+	if ((rc = s->halo.ensure((size_t)std::max<int64_t>(P.halo_arcs, 1) * 8))) return rc;
+	RangeDev R;
+	R.lo = P.lo;
+	R.from = from;
+	R.hi = to;
+	R.deg = s->deg.as<uint32_t>();
+	R.ref = s->ref.as<uint8_t>();
+	R.depth = s->depth.as<uint32_t>();
+	R.rp = P.rp;
+	R.col = d_col;
+	R.halo = s->halo.as<int64_t>();
+	R.col_capacity = col_capacity;
+	launch_extras(L, s->dev, g->def_codes, R);
+	if (P.max_depth <= 8) {
+		for (uint32_t lev = 1; lev <= P.max_depth; lev++) launch_copy_level(L, s->dev, g->def_codes, R, lev, nullptr, 0);
+	} else {
+		// deep chains: one compacted list of rows per level
+		const uint32_t nlev = P.max_depth + 1;
+		if ((rc = s->levels.ensure((size_t)(nlev + 1) * 8 * 2)) || (rc = s->list.ensure((size_t)std::max<int64_t>(P.cnt, 1) * 4))) return rc;
+		unsigned long long *counts = s->levels.as<unsigned long long>();
+		unsigned long long *cursor = counts + nlev + 1;
+		CU(cudaMemsetAsync(counts, 0, (size_t)(nlev + 1) * 8, s->stream));
+		launch_level_count(L, R.depth, P.cnt, nlev, counts);
+		std::vector<unsigned long long> h(nlev + 1), start(nlev + 1);
+		CU(cudaMemcpyAsync(h.data(), counts, (size_t)(nlev + 1) * 8, cudaMemcpyDeviceToHost, s->stream));
+		CU(cudaStreamSynchronize(s->stream));
+		unsigned long long acc = 0;
+		for (uint32_t i = 0; i <= nlev; i++) { start[i] = acc; acc += h[i]; }
+		CU(cudaMemcpyAsync(cursor, start.data(), (size_t)(nlev + 1) * 8, cudaMemcpyHostToDevice, s->stream));
+		launch_level_scatter(L, R.depth, P.cnt, nlev, cursor, s->list.as<uint32_t>());
+		CU(cudaStreamSynchronize(s->stream));  // `start` must outlive the copy above
+		for (uint32_t lev = 1; lev <= P.max_depth; lev++)
+			if (h[lev]) launch_copy_level(L, s->dev, g->def_codes, R, lev, s->list.as<uint32_t>() + start[lev], h[lev]);
+	}
+	cudaEventRecord(s->ev[4], s->stream);
+	s->ev_valid = true;
+	const cudaError_t e = cudaGetLastError();
+	if (e != cudaSuccess) return fail(WGBV_ECUDA, "kernel launch failed: %s", cudaGetErrorString(e));
+	return WGBV_OK;
+}
+
+extern "C" int wgbv_decode_csr(wgbv_stream *s, int64_t from, int64_t to, int64_t *d_rowptr, int64_t *d_col, uint64_t col_capacity) {
+	clear_error();
+	if (!s || !d_rowptr || (!d_col && col_capacity)) return fail(WGBV_EARG, "null argument");
+	CU(cudaSetDevice(s->g->device));
+	int rc = check_range(s->g, from, to);
+	if (rc) return rc;
+	Prepared P;
+	if ((rc = prepare(s, from, to, d_rowptr, true, P))) return rc;
+	return decode_rows(s, from, to, P, d_col, col_capacity);
+}
+
+extern "C" int wgbv_last_stage_ms(wgbv_stream *s, float out[5]) {
+	clear_error();
+	if (!s || !out) return fail(WGBV_EARG, "null argument");
+	if (!s->ev_valid) return fail(WGBV_ESTATE, "no decode has run on this stream");
+	CU(cudaStreamSynchronize(s->stream));
+	for (int i = 0; i < 4; i++) CU(cudaEventElapsedTime(&out[i], s->ev[i], s->ev[i + 1]));
+	CU(cudaEventElapsedTime(&out[4], s->ev[0], s->ev[4]));
+	return WGBV_OK;
+}
+
+extern "C" int wgbv_decode_csr_host(wgbv_stream *s, int64_t from, int64_t to, int64_t *h_rowptr, int64_t *h_col, uint64_t col_capacity,
+                                    int64_t *arcs_out) {
+	clear_error();
+	if (!s || !h_rowptr) return fail(WGBV_EARG, "null argument");
+	CU(cudaSetDevice(s->g->device));
+	int rc = check_range(s->g, from, to);
+	if (rc) return rc;
+	const int64_t cnt = to - from;
+	if ((rc = s->rowptr.ensure((size_t)(cnt + 1) * 8))) return rc;
+	Prepared P;
+	if ((rc = prepare(s, from, to, s->rowptr.as<int64_t>(), h_col != nullptr, P))) return rc;
+	if (arcs_out) *arcs_out = P.arcs;
+	CU(cudaMemcpyAsync(h_rowptr, s->rowptr.as<int64_t>(), (size_t)(cnt + 1) * 8, cudaMemcpyDeviceToHost, s->stream));
+	if (h_col) {
+		if ((uint64_t)P.arcs > col_capacity) return fail(WGBV_EARG, "col_capacity (%llu) is smaller than the %lld arcs of the range", (unsigned long long)col_capacity, (long long)P.arcs);
+		if ((rc = s->col.ensure((size_t)std::max<int64_t>(P.arcs, 1) * 8))) return rc;
+		if ((rc = decode_rows(s, from, to, P, s->col.as<int64_t>(), (uint64_t)P.arcs))) return rc;
+		if (P.arcs) CU(cudaMemcpyAsync(h_col, s->col.as<int64_t>(), (size_t)P.arcs * 8, cudaMemcpyDeviceToHost, s->stream));
+	}
+	return collect_errors(s);
+}
+
+// ------------------------------------------------------------------------------------------------ random access
+static int batch_degrees(wgbv_stream *s, const int64_t *d_ids, uint64_t k, int64_t *d_rowptr, int64_t *arcs_out) {
+	wgbv_graph *g = s->g;
+	const Launch L = s->launch();
+	int rc;
+	const size_t c = (size_t)std::max<uint64_t>(k, 1);
+	if (k >= 0x7ffffff0ull) return fail(WGBV_EARG, "a batch is limited to 2^31-16 queries");
+	if ((rc = s->deg.ensure(c * 4)) || (rc = s->scan_state.ensure(((c + 1) / 2048 + 2) * 8)) || (rc = s->ticket.ensure(64))) return rc;
+	launch_batch_degrees(L, s->dev, g->def_codes, d_ids, k, g->shard_lo, g->shard_hi, s->deg.as<uint32_t>());
+	launch_scan(L, s->deg.as<uint32_t>(), d_rowptr, (int64_t)k, s->scan_state.as<uint64_t>(), s->ticket.as<uint32_t>());
+	CU(cudaMemcpyAsync(s->h_pin, d_rowptr + k, 8, cudaMemcpyDeviceToHost, s->stream));
+	if ((rc = collect_errors(s))) return rc;
+	if (arcs_out) *arcs_out = (int64_t)s->h_pin[0];
+	return WGBV_OK;
+}
+
+extern "C" int wgbv_successors_batch_degrees(wgbv_stream *s, const int64_t *d_ids, uint64_t k, int64_t *d_rowptr, int64_t *arcs_out) {
+	clear_error();
+	if (!s || (!d_ids && k) || !d_rowptr) return fail(WGBV_EARG, "null argument");
+	CU(cudaSetDevice(s->g->device));
+	return batch_degrees(s, d_ids, k, d_rowptr, arcs_out);
+}
+
+extern "C" int wgbv_successors_batch(wgbv_stream *s, const int64_t *d_ids, uint64_t k, int64_t *d_rowptr, int64_t *d_col,
+                                     uint64_t col_capacity) {
+	clear_error();
+	if (!s || (!d_ids && k) || !d_rowptr || (!d_col && col_capacity)) return fail(WGBV_EARG, "null argument");
+	CU(cudaSetDevice(s->g->device));
+	wgbv_graph *g = s->g;
+	const Launch L = s->launch();
+	int rc;
+	int64_t arcs = 0;
+	if ((rc = batch_degrees(s, d_ids, k, d_rowptr, &arcs))) return rc;
+	if ((uint64_t)arcs > col_capacity) return fail(WGBV_EARG, "col_capacity (%llu) is smaller than the %lld arcs of the batch", (unsigned long long)col_capacity, (long long)arcs);
+	if (k == 0) return WGBV_OK;
+	// chains
+	const size_t c = (size_t)k;
+	if ((rc = s->c_len.ensure(c * 4)) || (rc = s->c_arcs.ensure(c * 8)) || (rc = s->c_row0.ensure((c + 1) * 8)) || (rc = s->c_soff.ensure((c + 1) * 8))) return rc;
+	CU(cudaMemsetAsync(s->d_stats, 0, 8, s->stream));
+	launch_chain_walk(L, s->dev, g->def_codes, d_ids, k, g->avail_lo, s->c_len.as<uint32_t>(), s->c_arcs.as<unsigned long long>(), s->d_stats);
+	launch_scan(L, s->c_len.as<uint32_t>(), s->c_row0.as<int64_t>(), (int64_t)k, s->scan_state.as<uint64_t>(), s->ticket.as<uint32_t>());
+	launch_scan64(L, s->c_arcs.as<unsigned long long>(), s->c_soff.as<int64_t>(), (int64_t)k, s->scan_state.as<uint64_t>(), s->ticket.as<uint32_t>());
+	uint32_t *hs = (uint32_t *)(s->h_pin + 4);
+	CU(cudaMemcpyAsync(hs, s->d_stats, 8, cudaMemcpyDeviceToHost, s->stream));
+	CU(cudaMemcpyAsync(s->h_pin, s->c_row0.as<int64_t>() + k, 8, cudaMemcpyDeviceToHost, s->stream));
+	CU(cudaMemcpyAsync(s->h_pin + 1, s->c_soff.as<int64_t>() + k, 8, cudaMemcpyDeviceToHost, s->stream));
+	if ((rc = collect_errors(s))) return rc;
+	const uint64_t rows = s->h_pin[0], store = s->h_pin[1];
+	const uint32_t max_len = hs[1];
+	if (rows >= 0x7ffffff0ull) return fail(WGBV_EARG, "the batch expands to too many chain rows; split it");
+	const size_t r = (size_t)std::max<uint64_t>(rows, 1);
+	if ((rc = s->c_node.ensure(r * 8)) || (rc = s->c_dst.ensure(r * 8)) || (rc = s->c_parent.ensure(r * 4)) || (rc = s->c_deg.ensure(r * 4)) ||
+	    (rc = s->c_isq.ensure(r)) || (rc = s->c_level.ensure(r * 4)) || (rc = s->c_store.ensure((size_t)std::max<uint64_t>(store, 1) * 8)))
+		return rc;
+	launch_chain_fill(L, s->dev, g->def_codes, d_ids, k, s->c_row0.as<int64_t>(), s->c_soff.as<int64_t>(), d_rowptr, s->c_node.as<int64_t>(),
+	                  s->c_dst.as<int64_t>(), s->c_parent.as<int32_t>(), s->c_deg.as<uint32_t>(), s->c_isq.as<uint8_t>(), s->c_level.as<uint32_t>());
+	ChainDev C;
+	C.node = s->c_node.as<int64_t>();
+	C.dst_off = s->c_dst.as<int64_t>();
+	C.parent = s->c_parent.as<int32_t>();
+	C.deg = s->c_deg.as<uint32_t>();
+	C.is_query = s->c_isq.as<uint8_t>();
+	C.col = d_col;
+	C.store = s->c_store.as<int64_t>();
+	launch_chain_extras(L, s->dev, g->def_codes, C, rows);
+	for (uint32_t lev = 1; lev < max_len; lev++) launch_chain_copy(L, s->dev, g->def_codes, C, rows, s->c_level.as<uint32_t>(), lev);
+	const cudaError_t e = cudaGetLastError();
+	if (e != cudaSuccess) return fail(WGBV_ECUDA, "kernel launch failed: %s", cudaGetErrorString(e));
+	return WGBV_OK;
+}
+
+extern "C" int wgbv_successors_batch_host(wgbv_stream *s, const int64_t *h_ids, uint64_t k, int64_t *h_rowptr, int64_t *h_col,
+                                          uint64_t col_capacity, int64_t *arcs_out) {
+	clear_error();
+	if (!s || (!h_ids && k) || !h_rowptr) return fail(WGBV_EARG, "null argument");
+	CU(cudaSetDevice(s->g->device));
+	// BVG:863: an id outside [0, n) is an error before anything is decoded
+	for (uint64_t i = 0; i < k; i++)
+		if (h_ids[i] < 0 || h_ids[i] >= s->g->props.nodes) return fail(WGBV_EINDEX, "Node index out of range: %lld", (long long)h_ids[i]);
+	int rc;
+	if ((rc = s->ids.ensure((size_t)std::max<uint64_t>(k, 1) * 8)) || (rc = s->rowptr.ensure((size_t)(k + 1) * 8))) return rc;
+	if (k) CU(cudaMemcpyAsync(s->ids.as<int64_t>(), h_ids, (size_t)k * 8, cudaMemcpyHostToDevice, s->stream));
+	int64_t arcs = 0;
+	if ((rc = batch_degrees(s, s->ids.as<int64_t>(), k, s->rowptr.as<int64_t>(), &arcs))) return rc;
+	if (arcs_out) *arcs_out = arcs;
+	CU(cudaMemcpyAsync(h_rowptr, s->rowptr.as<int64_t>(), (size_t)(k + 1) * 8, cudaMemcpyDeviceToHost, s->stream));
+	if (h_col) {
+		if ((uint64_t)arcs > col_capacity) return fail(WGBV_EARG, "col_capacity (%llu) is smaller than the %lld arcs of the batch", (unsigned long long)col_capacity, (long long)arcs);
+		if ((rc = s->col.ensure((size_t)std::max<int64_t>(arcs, 1) * 8))) return rc;
+		if ((rc = wgbv_successors_batch(s, s->ids.as<int64_t>(), k, s->rowptr.as<int64_t>(), s->col.as<int64_t>(), (uint64_t)arcs))) return rc;
+		if (arcs) CU(cudaMemcpyAsync(h_col, s->col.as<int64_t>(), (size_t)arcs * 8, cudaMemcpyDeviceToHost, s->stream));
+	}
+	return collect_errors(s);
+}
+
+extern "C" int wgbv_outdegrees(wgbv_stream *s, const int64_t *h_ids, uint64_t k, int64_t *h_out) {
+	clear_error();
+	if (!s || (!h_ids && k) || (!h_out && k)) return fail(WGBV_EARG, "null argument");
+	CU(cudaSetDevice(s->g->device));
+	for (uint64_t i = 0; i < k; i++)
+		if (h_ids[i] < 0 || h_ids[i] >= s->g->props.nodes) return fail(WGBV_EINDEX, "Node index out of range: %lld", (long long)h_ids[i]);
+	if (k == 0) return WGBV_OK;
+	int rc;
+	if ((rc = s->ids.ensure((size_t)k * 8)) || (rc = s->deg.ensure((size_t)k * 4))) return rc;
+	CU(cudaMemcpyAsync(s->ids.as<int64_t>(), h_ids, (size_t)k * 8, cudaMemcpyHostToDevice, s->stream));
+	launch_batch_degrees(s->launch(), s->dev, s->g->def_codes, s->ids.as<int64_t>(), k, s->g->shard_lo, s->g->shard_hi, s->deg.as<uint32_t>());
+	std::vector<uint32_t> tmp((size_t)k);
+	CU(cudaMemcpyAsync(tmp.data(), s->deg.as<uint32_t>(), (size_t)k * 4, cudaMemcpyDeviceToHost, s->stream));
+	if ((rc = collect_errors(s))) return rc;
+	for (uint64_t i = 0; i < k; i++) h_out[i] = tmp[(size_t)i];
+	return WGBV_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ checksum
+extern "C" int wgbv_csr_checksum(wgbv_stream *s, int64_t first_node, int64_t rows, const int64_t *d_rowptr, const int64_t *d_col,
+                                 uint64_t *checksum_out) {
+	clear_error();
+	if (!s || !d_rowptr || !checksum_out) return fail(WGBV_EARG, "null argument");
+	CU(cudaSetDevice(s->g->device));
+	int rc;
+	if ((rc = s->ticket.ensure(64))) return rc;
+	unsigned long long *acc = s->ticket.as<unsigned long long>() + 1;
+	CU(cudaMemsetAsync(acc, 0, 8, s->stream));
+	launch_checksum(s->launch(), first_node, rows, d_rowptr, d_col, acc);
+	CU(cudaMemcpyAsync(s->h_pin + 2, acc, 8, cudaMemcpyDeviceToHost, s->stream));
+	CU(cudaStreamSynchronize(s->stream));
+	const cudaError_t e = cudaGetLastError();
+	if (e != cudaSuccess) return fail(WGBV_ECUDA, "CUDA error: %s", cudaGetErrorString(e));
+	*checksum_out = s->h_pin[2];
+	return WGBV_OK;
+}
