@@ -33,7 +33,9 @@ enum { BVG_MODEL_CSR = 0, BVG_MODEL_ER = 1, BVG_MODEL_COPY = 2, BVG_MODEL_BIG = 
 
 typedef struct {
 	int32_t model;
-	int64_t n;
+	int64_t n;            /* nodes generated: ids [first_node, first_node + n) */
+	int64_t first_node;   /* id of the first node (parts of a larger graph are generated independently) */
+	int64_t global_n;     /* nodes of the whole graph: successors lie in [0, global_n) */
 	uint64_t seed;
 	/* ER: p = arc probability.  COPY: mean_degree, p_ref, p_keep, p_run, far_frac, near_scale, max_degree.
 	 * BIG: giant_every = one giant row every that many nodes (0: only node 0), giant_degree, giant_stride. */
@@ -315,7 +317,7 @@ static void gen_er(const bvg_model *m, int64_t x, lvec *out) {
 	for (;;) {
 		const double u = 1.0 - u01(&s);
 		y += 1 + (int64_t)floor(log(u) / lq);
-		if (y >= m->n || y < 0) break;
+		if (y >= m->global_n || y < 0) break;
 		lv_push(out, y);
 	}
 }
@@ -355,19 +357,19 @@ static void gen_copy(const bvg_model *m, int64_t x, int64_t split_start, lvec *c
 		if (len > rest) len = rest;
 		int64_t a = x + (int64_t)(splitmix64(&s) % 2001) - 1000;
 		if (a < 0) a = 0;
-		for (int64_t j = 0; j < len && a + j < m->n; j++) lv_push(out, a + j);
+		for (int64_t j = 0; j < len && a + j < m->global_n; j++) lv_push(out, a + j);
 		rest -= len;
 	}
 	const double lq = log1p(-1.0 / m->near_scale);
 	for (; rest > 0; rest--) {
 		int64_t y;
-		if (u01(&s) < m->far_frac) y = (int64_t)(splitmix64(&s) % (uint64_t)m->n);
+		if (u01(&s) < m->far_frac) y = (int64_t)(splitmix64(&s) % (uint64_t)m->global_n);
 		else {
 			const int64_t mag = (int64_t)floor(log(1.0 - u01(&s)) / lq);
 			y = (splitmix64(&s) & 1) ? x + mag : x - mag;
 			if (y < 0) y = -y;
-			if (y >= m->n) y = 2 * (m->n - 1) - y;
-			if (y < 0 || y >= m->n) y = (int64_t)(splitmix64(&s) % (uint64_t)m->n);
+			if (y >= m->global_n) y = 2 * (m->global_n - 1) - y;
+			if (y < 0 || y >= m->global_n) y = (int64_t)(splitmix64(&s) % (uint64_t)m->global_n);
 		}
 		lv_push(out, y);
 	}
@@ -384,7 +386,7 @@ static void gen_big(const bvg_model *m, int64_t x, lvec *out) {
 		lv_need(out, m->giant_degree);
 		for (int64_t i = 0; i < m->giant_degree; i++) {
 			const int64_t y = i * m->giant_stride;
-			if (y >= m->n) break;
+			if (y >= m->global_n) break;
 			out->a[out->n++] = y;
 		}
 		return;
@@ -448,7 +450,7 @@ static void encode_split(bvg_job *J, split_t *sp) {
 		case BVG_MODEL_COPY: gen_copy(&J->m, x, sp->from, ring, cyc, cur); break;
 		case BVG_MODEL_BIG: gen_big(&J->m, x, cur); break;
 		default: {
-			const int64_t a = J->m.rowptr[x], b = J->m.rowptr[x + 1];
+			const int64_t a = J->m.rowptr[x - J->m.first_node], b = J->m.rowptr[x - J->m.first_node + 1];
 			lv_need(cur, b - a); memcpy(cur->a, J->m.col + a, (size_t)(b - a) * 8); cur->n = b - a;
 		}
 		}
@@ -475,7 +477,7 @@ static void encode_split(bvg_job *J, split_t *sp) {
 		{
 			const uint64_t h = row_hash(x, cur->a, d);
 			sp->checksum += h;
-			if (J->seg_checksum) __atomic_fetch_add(&J->seg_checksum[x / J->seg_nodes], h, __ATOMIC_RELAXED);
+			if (J->seg_checksum) __atomic_fetch_add(&J->seg_checksum[(x - J->m.first_node) / J->seg_nodes], h, __ATOMIC_RELAXED);
 		}
 	}
 	obs_finish(o);
@@ -525,7 +527,7 @@ static void *worker_concat(void *p) {
 		}
 		/* absolute offsets of this split's nodes */
 		uint64_t acc = D;
-		for (int64_t x = sp->from; x < sp->to; x++) { J->offsets[x] = acc; acc += sp->bitlen[x - sp->from]; }
+		for (int64_t x = sp->from; x < sp->to; x++) { J->offsets[x - J->m.first_node] = acc; acc += sp->bitlen[x - sp->from]; }
 		free(sp->obs.buf); sp->obs.buf = NULL;
 		free(sp->bitlen); sp->bitlen = NULL;
 	}
@@ -544,6 +546,8 @@ static void run_threads(void *(*fn)(void *), void *arg, int threads) {
 bvg_job *bvg_run(const bvg_params *g, const bvg_model *m, int nsplits, int threads, int64_t seg_nodes) {
 	bvg_job *J = (bvg_job *)calloc(1, sizeof(bvg_job));
 	J->g = *g; J->m = *m;
+	if (J->m.global_n <= 0) J->m.global_n = J->m.first_node + J->m.n;
+	m = &J->m;
 	const int64_t n = m->n;
 	if (nsplits < 1) nsplits = 1;
 	if ((int64_t)nsplits > n && n > 0) nsplits = (int)n;
@@ -553,8 +557,8 @@ bvg_job *bvg_run(const bvg_params *g, const bvg_model *m, int nsplits, int threa
 	J->splits = (split_t *)calloc((size_t)nsplits, sizeof(split_t));
 	const int64_t per = (n + nsplits - 1) / nsplits;
 	for (int k = 0; k < nsplits; k++) {
-		J->splits[k].from = per * k < n ? per * k : n;
-		J->splits[k].to = per * (k + 1) < n ? per * (k + 1) : n;
+		J->splits[k].from = m->first_node + (per * k < n ? per * k : n);
+		J->splits[k].to = m->first_node + (per * (k + 1) < n ? per * (k + 1) : n);
 	}
 	if (seg_nodes > 0) {
 		J->seg_nodes = seg_nodes; J->nseg = (n + seg_nodes - 1) / seg_nodes;

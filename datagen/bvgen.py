@@ -25,7 +25,8 @@ class Params(C.Structure):
 
 
 class Model(C.Structure):
-    _fields_ = [("model", C.c_int32), ("n", C.c_int64), ("seed", C.c_uint64), ("p", C.c_double),
+    _fields_ = [("model", C.c_int32), ("n", C.c_int64), ("first_node", C.c_int64), ("global_n", C.c_int64),
+                ("seed", C.c_uint64), ("p", C.c_double),
                 ("mean_degree", C.c_double), ("p_ref", C.c_double), ("p_keep", C.c_double), ("p_run", C.c_double),
                 ("far_frac", C.c_double), ("near_scale", C.c_double), ("max_degree", C.c_int64),
                 ("giant_every", C.c_int64), ("giant_degree", C.c_int64), ("giant_stride", C.c_int64),
@@ -160,9 +161,10 @@ def erdos_renyi(n, p, seed=1, params=None, nsplits=64, threads=0, seg_nodes=0):
 
 
 def copy_model(n, seed=2, mean_degree=20.0, p_ref=0.7, p_keep=0.8, p_run=0.3, far_frac=0.05, near_scale=1e4,
-               max_degree=10000, params=None, nsplits=256, threads=0, seg_nodes=0):
+               max_degree=10000, params=None, nsplits=256, threads=0, seg_nodes=0, first_node=0, global_n=0):
+    """Copy-model web-like graph; with first_node/global_n one part [first_node, first_node+n) of a larger graph."""
     params = params or make_params()
-    m = Model(model=MODEL_COPY, n=n, seed=seed, mean_degree=mean_degree, p_ref=p_ref, p_keep=p_keep, p_run=p_run,
+    m = Model(model=MODEL_COPY, n=n, first_node=first_node, global_n=global_n, seed=seed, mean_degree=mean_degree, p_ref=p_ref, p_keep=p_keep, p_run=p_run,
               far_frac=far_frac, near_scale=near_scale, max_degree=max_degree)
     return _collect(lib().bvg_run(C.byref(params), C.byref(m), nsplits, _threads(threads), seg_nodes), params, n, seg_nodes)
 

@@ -99,6 +99,19 @@ WGBV_API int wgbv_open(const char *basename, int device, int shard_index, int sh
 WGBV_API int wgbv_open_mem(const wgbv_props *props, const uint8_t *graph, uint64_t graph_bytes, const uint8_t *offsets,
                   uint64_t offsets_bytes, int device, int shard_index, int shard_count, wgbv_graph **out);
 
+/*
+ * Opening from a pre-cut slice, for callers that read only their own byte range of a large file (one process per
+ * GPU, each holding one shard).  `bits` is a piece of the .graph bit stream and `offsets` a gamma/delta coded stream
+ * of node_count + 1 differences in the .offsets format (BVG:870-898) whose running sums are the bit positions, inside
+ * `bits`, of the records of nodes first_node .. first_node + node_count (the last one being the end of the slice).
+ * The first halo_nodes nodes of the slice are only kept as reference material: the handle decodes
+ * [first_node + halo_nodes, first_node + node_count).  props describes the whole graph (props->nodes is global).
+ * The loader counterpart is the same loadInternal (BVG:1479-1574) restricted to a node range.
+ */
+WGBV_API int wgbv_open_slice(const wgbv_props *props, int64_t first_node, int64_t node_count, int64_t halo_nodes,
+                             const uint8_t *bits, uint64_t nbytes, const uint8_t *offsets, uint64_t offsets_bytes, int device,
+                             wgbv_graph **out);
+
 /* Releases the device memory of a graph.  All its streams must have been destroyed. */
 WGBV_API void wgbv_close(wgbv_graph *g);
 
@@ -120,6 +133,12 @@ WGBV_API int wgbv_stream_create(wgbv_graph *g, void *cuda_stream, wgbv_stream **
 WGBV_API void wgbv_stream_destroy(wgbv_stream *s);
 /* Blocks until everything queued on the stream has finished; reports errors found by the kernels. */
 WGBV_API int wgbv_stream_sync(wgbv_stream *s);
+
+/* Copies the bit stream from host memory to the device again, asynchronously on the stream (the upload half of
+ * loadInternal's "read the whole graph into memory", BVG:1520-1528, for callers that keep the compressed graph in
+ * pinned host memory and stream it in per pass).  `graph` must be the buffer (or an identical copy) the handle was
+ * opened from. */
+WGBV_API int wgbv_upload_stream(wgbv_stream *s, const uint8_t *graph, uint64_t graph_bytes);
 
 /*
  * Bulk decode of nodes [from, to) to CSR -- the new bulk call of the GPU-backed graph.  It produces what a full

@@ -130,6 +130,18 @@ class GpuBVGraph:
         return cls(_Shared(h, None), cuda_stream)
 
     @classmethod
+    def load_slice(cls, props, first_node, node_count, bits, offsets_bytes, halo_nodes=0, device=0, cuda_stream=None):
+        """Opens a pre-cut slice of a larger graph (one shard per process): see wgbv_open_slice in include/wgbv.h."""
+        if isinstance(props, str):
+            props = parse_properties(props)
+        b = np.ascontiguousarray(bits)
+        o = np.ascontiguousarray(offsets_bytes)
+        h = C.c_void_p()
+        _lib.check(_lib.lib().wgbv_open_slice(C.byref(props), first_node, node_count, halo_nodes, b.ctypes.data, b.size,
+                                              o.ctypes.data, o.size, device, C.byref(h)))
+        return cls(_Shared(h, None), cuda_stream)
+
+    @classmethod
     def loadOnce(cls, stream):
         raise UnsupportedOperationException("GpuBVGraph needs random access to the bit stream")
 
@@ -268,6 +280,17 @@ class GpuBVGraph:
 
     def sync(self):
         _lib.check(_lib.lib().wgbv_stream_sync(self._st.h))
+
+    def uploadStream(self, host_ptr, nbytes):
+        """Re-uploads the compressed bit stream from (pinned) host memory, asynchronously on this copy's stream."""
+        _lib.check(_lib.lib().wgbv_upload_stream(self._st.h, C.c_void_p(host_ptr), nbytes))
+
+    def decodeToCSRHostInto(self, from_, to, h_rowptr, h_col, col_capacity):
+        """Bulk decode of [from, to) into caller-provided HOST buffers (raw pointers); returns the arc count."""
+        arcs = C.c_int64()
+        _lib.check(_lib.lib().wgbv_decode_csr_host(self._st.h, from_, to, C.c_void_p(h_rowptr), C.c_void_p(h_col),
+                                                   col_capacity, C.byref(arcs)))
+        return arcs.value
 
     def csrChecksumDevice(self, first_node, rows, d_rowptr, d_col):
         out = C.c_uint64()

@@ -200,18 +200,18 @@ struct HostBits {
 };
 }  // namespace
 
-int decode_offsets(const wgbv_props &p, const uint8_t *bytes, uint64_t nbytes, std::vector<uint64_t> &out) {
+int decode_offsets(const wgbv_props &p, const uint8_t *bytes, uint64_t nbytes, int64_t count, std::vector<uint64_t> &out) {
 	if (p.offset_coding != WGBV_GAMMA && p.offset_coding != WGBV_DELTA)
 		return fail(WGBV_EUNSUPPORTED, "The required offset coding (%d) is not supported.", p.offset_coding);
 	HostBits s{bytes, nbytes * 8, 0};
-	out.resize((size_t)p.nodes + 1);
+	out.resize((size_t)count);
 	uint64_t acc = 0;
 	const bool g = p.offset_coding == WGBV_GAMMA;
-	for (int64_t i = 0; i <= p.nodes; i++) {
+	for (int64_t i = 0; i < count; i++) {
 		acc += g ? s.gamma() : s.delta();
 		out[(size_t)i] = acc;
 	}
-	if (s.overrun) return fail(WGBV_EIO, "the offsets stream ends before %lld offsets were read", (long long)p.nodes + 1);
+	if (s.overrun) return fail(WGBV_EIO, "the offsets stream ends before %lld offsets were read", (long long)count);
 	return WGBV_OK;
 }
 

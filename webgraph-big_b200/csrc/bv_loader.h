@@ -18,8 +18,8 @@ void clear_error();
 int parse_properties_text(const char *text, wgbv_props *out);
 int read_file(const std::string &path, std::vector<uint8_t> &out);
 
-// n+1 absolute bit offsets from the gamma/delta coded differences (OffsetsLongIterator, BVG:870-898).
-int decode_offsets(const wgbv_props &p, const uint8_t *bytes, uint64_t nbytes, std::vector<uint64_t> &out);
+// `count` absolute bit offsets from the gamma/delta coded differences (OffsetsLongIterator, BVG:870-898).
+int decode_offsets(const wgbv_props &p, const uint8_t *bytes, uint64_t nbytes, int64_t count, std::vector<uint64_t> &out);
 
 // Elias-Fano representation of a monotone list, laid out for the device (see bv_device.cuh: ef_get).
 struct EliasFano {

@@ -30,6 +30,7 @@ struct wgbv_graph {
 	GraphDev dev{};
 	uint64_t *d_words = nullptr, *d_lower = nullptr, *d_upper = nullptr, *d_hints = nullptr, *d_sparse = nullptr;
 	uint64_t device_bytes = 0;
+	uint64_t byte0 = 0, byte1 = 0, data_words = 0;  // the byte range of the caller's buffer that is resident
 	EliasFano ef;  // host copy, for accounting
 	int streams = 0;
 };
@@ -125,49 +126,33 @@ extern "C" void wgbv_close(wgbv_graph *g) {
 	delete g;
 }
 
-extern "C" int wgbv_open_mem(const wgbv_props *props, const uint8_t *graph, uint64_t graph_bytes, const uint8_t *offsets,
-                             uint64_t offsets_bytes, int device, int shard_index, int shard_count, wgbv_graph **out) {
-	clear_error();
-	if (!props || !out || (!graph && graph_bytes) || !offsets) return fail(WGBV_EARG, "null argument");
-	*out = nullptr;
-	if (shard_count < 1 || shard_index < 0 || shard_index >= shard_count) return fail(WGBV_EARG, "bad shard %d of %d", shard_index, shard_count);
-	int rc = check_codings(*props);
-	if (rc) return rc;
-	if ((rc = select_device(device))) return rc;
-
-	std::vector<uint64_t> off;
-	if ((rc = decode_offsets(*props, offsets, offsets_bytes, off))) return rc;
-	const int64_t n = props->nodes;
-	if (off[(size_t)n] > graph_bytes * 8) return fail(WGBV_EIO, "the last offset (%llu) lies beyond the end of the bit stream (%llu bits)", (unsigned long long)off[(size_t)n], (unsigned long long)graph_bytes * 8);
-	for (int64_t i = 0; i < n; i++)
-		if (off[(size_t)i + 1] < off[(size_t)i]) return fail(WGBV_EIO, "offsets are not monotone at node %lld", (long long)i);
-
+// Builds the device-resident graph for nodes [avail_lo, shard_hi) from `off`, the absolute bit offsets (inside
+// `graph`) of nodes [off_first, off_first + off.size() - 1].
+static int build_graph(const wgbv_props *props, const uint8_t *graph, uint64_t graph_bytes, const std::vector<uint64_t> &off,
+                       int64_t off_first, int64_t avail_lo, int64_t shard_lo, int64_t shard_hi, int64_t halo_nodes, int device,
+                       wgbv_graph **out) {
 	wgbv_graph *g = new (std::nothrow) wgbv_graph();
 	if (!g) return fail(WGBV_EARG, "out of host memory");
 	g->props = *props;
 	g->device = device;
 	g->def_codes = props->outdegree_coding == WGBV_GAMMA && props->block_coding == WGBV_GAMMA && props->residual_coding == WGBV_ZETA &&
 	               props->reference_coding == WGBV_UNARY && props->block_count_coding == WGBV_GAMMA;
-	// halo: a reference chain has at most max_ref_count hops of at most window_size nodes each (BVG:701, 2258)
-	const int64_t halo = (int64_t)props->window_size * (int64_t)props->max_ref_count;
-	g->halo_nodes = (props->window_size == 0 || props->max_ref_count <= 0) ? 0 : (props->max_ref_count > (1 << 20) ? -1 : halo);
-	if (g->halo_nodes < 0 && shard_count > 1) {
-		delete g;
-		return fail(WGBV_EUNSUPPORTED, "maxrefcount=%d makes reference chains unbounded: the graph cannot be sharded", props->max_ref_count);
-	}
-	std::vector<int64_t> bounds;
-	plan_shards(off, shard_count, bounds);
-	g->shard_lo = bounds[(size_t)shard_index];
-	g->shard_hi = bounds[(size_t)shard_index + 1];
-	g->avail_lo = g->halo_nodes < 0 ? 0 : std::max<int64_t>(0, g->shard_lo - g->halo_nodes);
+	g->halo_nodes = halo_nodes;
+	g->shard_lo = shard_lo;
+	g->shard_hi = shard_hi;
+	g->avail_lo = avail_lo;
+	int rc;
 
 	// the slice of the bit stream that holds [avail_lo, shard_hi), starting on a 64-bit word of the file
-	const uint64_t bit0 = off[(size_t)g->avail_lo] & ~63ull;
-	const uint64_t bit1 = off[(size_t)g->shard_hi];
+	const uint64_t bit0 = off[(size_t)(avail_lo - off_first)] & ~63ull;
+	const uint64_t bit1 = off[(size_t)(shard_hi - off_first)];
 	const uint64_t byte0 = bit0 >> 3;
 	const uint64_t byte1 = std::min<uint64_t>((bit1 + 7) >> 3, graph_bytes);
 	const uint64_t data_words = (byte1 > byte0 ? byte1 - byte0 + 7 : 0) / 8;
 	const uint64_t nwords = data_words + 2;
+	g->byte0 = byte0;
+	g->byte1 = byte1;
+	g->data_words = data_words;
 	auto cleanup = [&](int code) { wgbv_close(g); return code; };
 	if (cudaMalloc((void **)&g->d_words, nwords * 8) != cudaSuccess) return cleanup(fail(WGBV_ECUDA, "cudaMalloc of the bit stream (%llu bytes) failed", (unsigned long long)nwords * 8));
 	g->device_bytes += nwords * 8;
@@ -178,7 +163,7 @@ extern "C" int wgbv_open_mem(const wgbv_props *props, const uint8_t *graph, uint
 	launch_bswap(L, g->d_words, data_words);
 
 	// Elias-Fano list of the offsets of [avail_lo, shard_hi] relative to bit0
-	g->ef.build(off.data() + g->avail_lo, (uint64_t)(g->shard_hi - g->avail_lo + 1), bit0);
+	g->ef.build(off.data() + (avail_lo - off_first), (uint64_t)(shard_hi - avail_lo + 1), bit0);
 	if ((rc = upload(&g->d_lower, g->ef.lower, &g->device_bytes))) return cleanup(rc);
 	if ((rc = upload(&g->d_upper, g->ef.upper, &g->device_bytes))) return cleanup(rc);
 	if ((rc = upload(&g->d_hints, g->ef.hints, &g->device_bytes))) return cleanup(rc);
@@ -194,10 +179,10 @@ extern "C" int wgbv_open_mem(const wgbv_props *props, const uint8_t *graph, uint
 	d.ef_upper = g->d_upper;
 	d.ef_hints = g->d_hints;
 	d.ef_sparse = g->d_sparse;
-	d.ef_first = g->avail_lo;
-	d.ef_count = g->shard_hi - g->avail_lo + 1;
+	d.ef_first = avail_lo;
+	d.ef_count = shard_hi - avail_lo + 1;
 	d.ef_l = g->ef.l;
-	d.nodes = n;
+	d.nodes = props->nodes;
 	d.window = props->window_size;
 	d.min_interval = props->min_interval_length;
 	d.zeta_k = props->zeta_k;
@@ -208,6 +193,73 @@ extern "C" int wgbv_open_mem(const wgbv_props *props, const uint8_t *graph, uint
 	d.block_count_coding = props->block_count_coding;
 	d.err = nullptr;
 	*out = g;
+	return WGBV_OK;
+}
+
+// halo: a reference chain has at most max_ref_count hops of at most window_size nodes each (BVG:701, 2258); -1 = unbounded
+static int64_t halo_of(const wgbv_props *props) {
+	if (props->window_size == 0 || props->max_ref_count <= 0) return 0;
+	if (props->max_ref_count > (1 << 20)) return -1;
+	return (int64_t)props->window_size * (int64_t)props->max_ref_count;
+}
+
+static int check_offsets(const std::vector<uint64_t> &off, uint64_t graph_bytes) {
+	if (off.back() > graph_bytes * 8) return fail(WGBV_EIO, "the last offset (%llu) lies beyond the end of the bit stream (%llu bits)", (unsigned long long)off.back(), (unsigned long long)graph_bytes * 8);
+	for (size_t i = 0; i + 1 < off.size(); i++)
+		if (off[i + 1] < off[i]) return fail(WGBV_EIO, "offsets are not monotone at entry %zu", i);
+	return WGBV_OK;
+}
+
+extern "C" int wgbv_open_mem(const wgbv_props *props, const uint8_t *graph, uint64_t graph_bytes, const uint8_t *offsets,
+                             uint64_t offsets_bytes, int device, int shard_index, int shard_count, wgbv_graph **out) {
+	clear_error();
+	if (!props || !out || (!graph && graph_bytes) || !offsets) return fail(WGBV_EARG, "null argument");
+	*out = nullptr;
+	if (shard_count < 1 || shard_index < 0 || shard_index >= shard_count) return fail(WGBV_EARG, "bad shard %d of %d", shard_index, shard_count);
+	int rc = check_codings(*props);
+	if (rc) return rc;
+	if ((rc = select_device(device))) return rc;
+	std::vector<uint64_t> off;
+	if ((rc = decode_offsets(*props, offsets, offsets_bytes, props->nodes + 1, off))) return rc;
+	if ((rc = check_offsets(off, graph_bytes))) return rc;
+	const int64_t halo = halo_of(props);
+	if (halo < 0 && shard_count > 1)
+		return fail(WGBV_EUNSUPPORTED, "maxrefcount=%d makes reference chains unbounded: the graph cannot be sharded", props->max_ref_count);
+	std::vector<int64_t> bounds;
+	plan_shards(off, shard_count, bounds);
+	const int64_t lo = bounds[(size_t)shard_index], hi = bounds[(size_t)shard_index + 1];
+	const int64_t avail_lo = halo < 0 ? 0 : std::max<int64_t>(0, lo - halo);
+	return build_graph(props, graph, graph_bytes, off, 0, avail_lo, lo, hi, halo, device, out);
+}
+
+extern "C" int wgbv_open_slice(const wgbv_props *props, int64_t first_node, int64_t node_count, int64_t halo_nodes,
+                               const uint8_t *bits, uint64_t nbytes, const uint8_t *offsets, uint64_t offsets_bytes, int device,
+                               wgbv_graph **out) {
+	clear_error();
+	if (!props || !out || (!bits && nbytes) || !offsets) return fail(WGBV_EARG, "null argument");
+	*out = nullptr;
+	if (first_node < 0 || node_count < 0 || halo_nodes < 0 || halo_nodes > node_count || first_node + node_count > props->nodes)
+		return fail(WGBV_EINDEX, "Node index out of range: slice [%lld, %lld) of %lld nodes", (long long)first_node, (long long)(first_node + node_count), (long long)props->nodes);
+	int rc = check_codings(*props);
+	if (rc) return rc;
+	if ((rc = select_device(device))) return rc;
+	std::vector<uint64_t> off;
+	if ((rc = decode_offsets(*props, offsets, offsets_bytes, node_count + 1, off))) return rc;
+	if ((rc = check_offsets(off, nbytes))) return rc;
+	return build_graph(props, bits, nbytes, off, first_node, first_node, first_node + halo_nodes, first_node + node_count, halo_of(props), device, out);
+}
+
+extern "C" int wgbv_upload_stream(wgbv_stream *s, const uint8_t *graph, uint64_t graph_bytes) {
+	clear_error();
+	if (!s || (!graph && graph_bytes)) return fail(WGBV_EARG, "null argument");
+	wgbv_graph *g = s->g;
+	CU(cudaSetDevice(g->device));
+	if (graph_bytes < g->byte1) return fail(WGBV_EARG, "the buffer (%llu bytes) is shorter than the stream that was opened (%llu bytes)", (unsigned long long)graph_bytes, (unsigned long long)g->byte1);
+	if (g->data_words) {
+		CU(cudaMemsetAsync(g->d_words + g->data_words - 1, 0, 8, s->stream));
+		CU(cudaMemcpyAsync(g->d_words, graph + g->byte0, g->byte1 - g->byte0, cudaMemcpyHostToDevice, s->stream));
+		launch_bswap(s->launch(), g->d_words, g->data_words);
+	}
 	return WGBV_OK;
 }
 
