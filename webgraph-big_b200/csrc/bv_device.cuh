@@ -47,77 +47,92 @@ struct GraphDev {
 __device__ __forceinline__ void raise(const GraphDev &g, uint32_t bit) { atomicOr(g.err, bit); }
 
 // ------------------------------------------------------------------------------------------------ bit reader
-// Position-based reader with the current and the next word cached in registers: one 8-byte load per 64 bits
-// consumed.  All positions are relative to g.bit_base.
+// The reader keeps a 64-bit, left-aligned bit buffer plus the next 32-bit word of the stream in registers.  After
+// refill() at least 33 bits are valid, so every code of up to 32 bits -- all but a vanishing fraction in practice
+// -- is decoded from the top half of the buffer with 32-bit arithmetic: one count-leading-zeros, a few shifts and
+// one funnel shift to consume it.  The refill is a handful of predicated instructions (no divergent branch) and the
+// load it issues is for the word AFTER the one it consumes, so its latency is off the critical path.
+// Longer codes take a slow path built from unary() and bits().  All positions are relative to g.bit_base.
 struct BitReader {
-	const uint64_t *__restrict__ w;
-	uint64_t nwords;
-	uint64_t pos;   // relative bit position
-	uint64_t widx;  // index of `cur`
-	uint64_t cur, nxt;
+	const uint32_t *__restrict__ w;  // the stream as 32-bit words; stream word j lives at index j ^ 1 (big-endian 64-bit storage)
+	uint64_t nw;                     // number of 32-bit words that may be loaded
+	uint64_t wi;                     // index of the stream word held in `nxt`
+	uint64_t buf;                    // next bits of the stream, first bit in the most significant position
+	uint32_t nb;                     // valid bits in buf
+	uint32_t nxt;                    // stream word wi, not yet in buf
 
-	__device__ __forceinline__ uint64_t load(uint64_t i) const { return i < nwords ? __ldg(w + i) : 0ull; }
+	__device__ __forceinline__ uint32_t load(uint64_t j) const { return j < nw ? __ldg(w + (j ^ 1)) : 0u; }
 
 	__device__ __forceinline__ void seek(uint64_t p) {
-		pos = p;
-		widx = p >> 6;
-		cur = load(widx);
-		nxt = load(widx + 1);
+		const uint64_t j = p >> 5;
+		const unsigned sh = (unsigned)p & 31u;
+		buf = (((uint64_t)load(j) << 32) | load(j + 1)) << sh;
+		nb = 64u - sh;
+		wi = j + 2;
+		nxt = load(wi);
 	}
 	__device__ __forceinline__ void init(const GraphDev &g, uint64_t rel_pos) {
-		w = g.words;
-		nwords = g.nwords;
+		w = (const uint32_t *)g.words;
+		nw = g.nwords * 2;
 		seek(rel_pos);
 	}
-	// the next 64 bits of the stream, first bit in the most significant position
-	__device__ __forceinline__ uint64_t peek() const {
-		const unsigned s = (unsigned)pos & 63u;
-		return s ? (cur << s) | (nxt >> (64u - s)) : cur;
-	}
-	__device__ __forceinline__ void skip(uint64_t n) {
-		pos += n;
-		const uint64_t nw = pos >> 6;
-		if (nw != widx) {
-			cur = (nw == widx + 1) ? nxt : load(nw);
-			widx = nw;
-			nxt = load(nw + 1);
+	__device__ __forceinline__ uint64_t tell() const { return wi * 32 - nb; }
+	__device__ __forceinline__ bool past_end() const { return wi > nw + 2; }
+
+	// makes at least 33 bits valid
+	__device__ __forceinline__ void refill() {
+		if (nb <= 32) {
+			buf |= (uint64_t)nxt << (32u - nb);
+			nb += 32;
+			nxt = load(++wi);
 		}
 	}
-	__device__ __forceinline__ bool past_end() const { return widx >= nwords; }
+	__device__ __forceinline__ uint32_t top() const { return (uint32_t)(buf >> 32); }
+	__device__ __forceinline__ void consume(unsigned n) {  // n <= min(nb, 63)
+		buf <<= n;
+		nb -= n;
+	}
 
 	__device__ __forceinline__ uint64_t bits(unsigned n) {  // n in [0, 64]
-		if (n == 0) return 0;
-		const uint64_t v = peek() >> (64u - n);
-		skip(n);
+		uint64_t v = 0;
+		if (n > 32) {
+			refill();
+			v = top();
+			consume(32);
+			n -= 32;
+		}
+		if (n) {
+			refill();
+			v = (v << n) | (top() >> (32u - n));
+			consume(n);
+		}
 		return v;
 	}
 
 	__device__ __forceinline__ uint64_t unary() {
-		uint64_t win = peek();
-		if (win) {
-			const int z = __clzll((long long)win);
-			skip((uint64_t)z + 1);
-			return (uint64_t)z;
-		}
+		refill();
+		uint32_t t = top();
 		uint64_t total = 0;
-		do {
-			total += 64;
-			skip(64);
-			if (past_end()) return total;  // callers see garbage; the kernels raise ERR_OVERRUN on their own checks
-			win = peek();
-		} while (!win);
-		const int z = __clzll((long long)win);
-		skip((uint64_t)z + 1);
-		return total + (uint64_t)z;
+		while (t == 0) {
+			total += 32;
+			consume(32);
+			refill();
+			if (past_end()) return total;  // the kernels raise ERR_OVERRUN on their own checks
+			t = top();
+		}
+		const unsigned z = (unsigned)__clz((int)t);
+		consume(z + 1);
+		return total + z;
 	}
 
 	__device__ __forceinline__ uint64_t gamma() {
-		const uint64_t win = peek();
-		if (win >> 32) {  // at most 31 leading zeros: the whole code (<= 63 bits) is inside the window
-			const int z = __clzll((long long)win);
-			const uint64_t v = (win << z) >> (63 - z);
-			skip(2ull * z + 1);
-			return v - 1;
+		refill();
+		const uint32_t t = top();
+		if (t >> 16) {  // at most 15 leading zeros: the whole code (<= 31 bits) is in the top half
+			const unsigned z = (unsigned)__clz((int)t);
+			const uint32_t v = (t << z) >> (31u - z);
+			consume(2 * z + 1);
+			return (uint64_t)v - 1;
 		}
 		const uint64_t m = unary();
 		if (m > 63) return 0;
@@ -131,20 +146,21 @@ struct BitReader {
 	}
 
 	__device__ __forceinline__ uint64_t zeta(int k) {
-		const uint64_t win = peek();
-		const int h = win ? __clzll((long long)win) : 64;
-		const int nb = h * k + k - 1;  // payload bits before the optional extra one
-		if (h + 1 + nb + 1 <= 64) {
-			const uint64_t x = win << (h + 1);
-			const uint64_t left = 1ull << (h * k);
-			const uint64_t m = nb ? x >> (64 - nb) : 0;
+		refill();
+		const uint32_t t = top();
+		const int h = t ? __clz((int)t) : 32;
+		const int pb = h * k + k - 1;  // payload bits before the optional extra one
+		if (h + 2 + pb <= 32) {
+			const uint32_t x = t << (h + 1);
+			const uint32_t left = 1u << (h * k);
+			const uint32_t m = pb ? x >> (32 - pb) : 0u;
 			if (m < left) {
-				skip((uint64_t)(h + 1 + nb));
-				return m + left - 1;
+				consume((unsigned)(h + 1 + pb));
+				return (uint64_t)(m + left - 1);
 			}
-			const uint64_t b = (x >> (63 - nb)) & 1ull;
-			skip((uint64_t)(h + 2 + nb));
-			return ((m << 1) | b) - 1;
+			const uint32_t b = (x >> (31 - pb)) & 1u;
+			consume((unsigned)(h + 2 + pb));
+			return (uint64_t)(((m << 1) | b) - 1);
 		}
 		const uint64_t hh = unary();
 		if (hh * (uint64_t)k + (uint64_t)k > 64) return 0;

@@ -9,6 +9,8 @@
 // All of it is integer/bit work bound by HBM and the integer pipes; no tensor cores are involved.
 #include <stdio.h>
 
+#include <algorithm>
+
 #include "bv_kernels.cuh"
 #include "bv_rows.cuh"
 
@@ -259,69 +261,284 @@ __device__ __forceinline__ int64_t *row_slot(const RangeDev &R, int64_t i, int64
 	return (R.lo + i >= R.from) ? R.col + (p - rp_from) : R.halo + p;
 }
 
-// stage 3a: thread per node.  Rows without a reference come out complete.
-template <bool DEF>
-__global__ void __launch_bounds__(TPB) k_extras(GraphDev g, RangeDev R) {
-	const int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
-	const int64_t count = R.hi - R.lo;
-	if (i >= count) return;
-	const uint32_t d = R.deg[i];
-	if (d == 0 || R.depth[i] >= DEPTH_INVALID) return;
-	const int64_t x = R.lo + i;
-	const int64_t rp_from = R.rp[R.from - R.lo];
-	if (x >= R.from && (uint64_t)(R.rp[i + 1] - rp_from) > R.col_capacity) { raise(g, ERR_CAPACITY); return; }
-	BitReader r;
-	r.init(g, ef_get(g, x));
-	RowHead h;
-	const uint32_t rf = R.ref[i];
-	if (!row_head<DEF>(g, r, rf ? R.deg[i - rf] : 0, h)) return;
-	int64_t *dst = row_slot(R, i, rp_from);
-	row_extras<DEF>(g, r, x, h.d - h.ncopied, dst + h.ncopied);
+// Work binning.  Rows differ wildly in length, and a warp that mixes a 3-successor row with a 300-successor row
+// spends most of its issue slots on a handful of lanes (the first version of these kernels ran at ~4 active lanes
+// per instruction).  So every block first parses the heads of its 256 rows, then sorts the rows by the amount of
+// serial work they carry (a counting sort over 64 classes in shared memory, heaviest first), and only then does
+// the serial part: the 32 lanes of a warp now run rows of the same class.
+static constexpr int BIN_CLASSES = 64;
+
+// class of a work amount w >= 1: exact below 32, then two classes per octave; returned heaviest-first
+__device__ __forceinline__ int work_bucket(uint32_t w) {
+	int c;
+	if (w < 32) c = (int)w;
+	else {
+		const int lg = 31 - __clz(w);                 // >= 5
+		c = 32 + 2 * (lg - 5) + (int)((w >> (lg - 1)) & 1);
+		if (c > BIN_CLASSES - 1) c = BIN_CLASSES - 1;
+	}
+	return BIN_CLASSES - 1 - c;
 }
 
-void launch_extras(const Launch &L, const GraphDev &g, bool def, const RangeDev &r) {
+// Block-wide counting sort of up to TPB * RPT items, RPT per thread (bucket[q] < 0: no item in slot q; the id of
+// slot q of thread t is q * TPB + t).  On return order[0..*total) lists the item ids by ascending bucket, i.e.
+// heaviest class first.  All threads of the block must call it.
+template <int RPT>
+__device__ __forceinline__ void block_bin_sort(const int (&bucket)[RPT], uint32_t *hist /*[BIN_CLASSES+1]*/, uint16_t *order,
+                                               uint32_t *total) {
+	if (threadIdx.x <= BIN_CLASSES) hist[threadIdx.x] = 0;
+	__syncthreads();
+	uint32_t rank[RPT];
+#pragma unroll
+	for (int q = 0; q < RPT; q++) rank[q] = bucket[q] >= 0 ? atomicAdd(&hist[bucket[q]], 1u) : 0u;
+	__syncthreads();
+	if (threadIdx.x < 32) {
+		// exclusive scan of the 64 counters by one warp, two per lane
+		const uint32_t a = hist[2 * threadIdx.x], b = hist[2 * threadIdx.x + 1];
+		uint32_t inc = a + b;
+#pragma unroll
+		for (int o = 1; o < 32; o <<= 1) {
+			const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+			if ((int)threadIdx.x >= o) inc += t;
+		}
+		const uint32_t ex = inc - a - b;
+		hist[2 * threadIdx.x] = ex;
+		hist[2 * threadIdx.x + 1] = ex + a;
+		if (threadIdx.x == 31) hist[BIN_CLASSES] = inc;
+	}
+	__syncthreads();
+#pragma unroll
+	for (int q = 0; q < RPT; q++)
+		if (bucket[q] >= 0) order[hist[bucket[q]] + rank[q]] = (uint16_t)(q * TPB + threadIdx.x);
+	*total = hist[BIN_CLASSES];
+	__syncthreads();
+}
+
+static constexpr int RPT = 8;            // rows per thread
+static constexpr int TILE = TPB * RPT;   // rows per block: the sort domain (see the comment on work binning)
+
+// Rows with at least HEAVY extras are not decoded inside their tile: a tile holds only a handful of them, of very
+// different lengths, and whichever warp gets them runs nearly empty.  They are appended to a global list, sorted
+// by class over the whole range (k_heavy_scatter), and decoded by k_extras_heavy where every warp finds 32 rows of
+// one class.
+static constexpr uint32_t HEAVY = 64;
+
+// stage 3a: one block per TILE nodes.  Rows without a reference come out complete.
+template <bool DEF>
+__global__ void __launch_bounds__(TPB) k_extras(GraphDev g, RangeDev R, HeavyDev H) {
+	__shared__ uint64_t s_pos[TILE];
+	__shared__ uint32_t s_nextra[TILE], s_ncopied[TILE];
+	__shared__ uint32_t s_hist[BIN_CLASSES + 1];
+	__shared__ uint16_t s_order[TILE];
+	__shared__ uint32_t s_count[BIN_CLASSES];
+	__shared__ unsigned long long s_gbase;
+	const int64_t base = (int64_t)blockIdx.x * TILE;
+	const int64_t count = R.hi - R.lo;
+	const int64_t rp_from = R.rp[R.from - R.lo];
+	// heads of my rows (uniform loop: the warp reconverges at the end of every iteration)
+	int bucket[RPT];
+#pragma unroll 1
+	for (int q = 0; q < RPT; q++) {
+		const int id = q * TPB + threadIdx.x;
+		const int64_t i = base + id;
+		bucket[q] = -1;
+		if (i < count && R.deg[i] != 0 && R.depth[i] < DEPTH_INVALID) {
+			const int64_t x = R.lo + i;
+			if (x >= R.from && (uint64_t)(R.rp[i + 1] - rp_from) > R.col_capacity) raise(g, ERR_CAPACITY);
+			else {
+				BitReader r;
+				r.init(g, ef_get(g, x));
+				RowHead h;
+				const uint32_t rf = R.ref[i];
+				row_head<DEF>(g, r, rf ? R.deg[i - rf] : 0, h);
+				const uint32_t nextra = h.d - h.ncopied;
+				if (nextra) {
+					bucket[q] = work_bucket(nextra);
+					s_pos[id] = r.tell();
+					s_nextra[id] = nextra;
+					s_ncopied[id] = h.ncopied;
+				}
+			}
+		}
+		__syncwarp();
+	}
+	uint32_t total;
+	block_bin_sort<RPT>(bucket, s_hist, s_order, &total);
+	// after the sort s_hist[b] is the first position of class b; the classes of >= HEAVY extras come first
+	const int first_light = work_bucket(HEAVY - 1);
+	const uint32_t nheavy = H.rows ? s_hist[first_light] : 0;
+	if (nheavy) {
+		if (threadIdx.x < first_light) s_count[threadIdx.x] = s_hist[threadIdx.x + 1] - s_hist[threadIdx.x];
+		if (threadIdx.x == 0) s_gbase = atomicAdd(&H.counters[0], (unsigned long long)nheavy);
+		__syncthreads();
+		if (threadIdx.x < first_light && s_count[threadIdx.x]) atomicAdd(&H.counters[1 + threadIdx.x], (unsigned long long)s_count[threadIdx.x]);
+		for (uint32_t t = threadIdx.x; t < nheavy; t += TPB) {
+			const int id = s_order[t];
+			H.rows[s_gbase + t] = (uint32_t)(base + id);
+			H.cls[s_gbase + t] = (uint8_t)work_bucket(s_nextra[id]);
+		}
+	}
+	// serial part: the lanes of a warp take rows of the same class and run them in lock step
+#pragma unroll 1
+	for (uint32_t tb = nheavy + (threadIdx.x & ~31u); tb < total; tb += TPB) {
+		const uint32_t t = tb + (threadIdx.x & 31u);
+		const bool active = t < total;
+		const unsigned mask = __ballot_sync(FULL_MASK, active);
+		if (active) {
+			const int id = s_order[t];
+			const int64_t k = base + id;
+			BitReader r;
+			r.init(g, s_pos[id]);
+			row_extras<DEF>(g, r, R.lo + k, s_nextra[id], row_slot(R, k, rp_from) + s_ncopied[id], mask);
+		}
+	}
+}
+
+// class starts of the global heavy list: counters[1..64] = counts -> counters[65..128] = running cursors
+__global__ void k_heavy_offsets(HeavyDev H) {
+	const unsigned lane = threadIdx.x;
+	const unsigned long long a = H.counters[1 + 2 * lane], b = H.counters[2 + 2 * lane];
+	unsigned long long inc = a + b;
+#pragma unroll
+	for (int o = 1; o < 32; o <<= 1) {
+		const unsigned long long t = __shfl_up_sync(0xffffffffu, inc, o);
+		if ((int)lane >= o) inc += t;
+	}
+	const unsigned long long ex = inc - a - b;
+	H.counters[65 + 2 * lane] = ex;
+	H.counters[66 + 2 * lane] = ex + a;
+}
+
+// counting-sort scatter of the heavy list by class (block-aggregated reservations)
+__global__ void __launch_bounds__(TPB) k_heavy_scatter(HeavyDev H) {
+	__shared__ uint32_t s_cnt[BIN_CLASSES];
+	__shared__ unsigned long long s_start[BIN_CLASSES];
+	const unsigned long long total = H.counters[0];
+	for (unsigned long long tile = (unsigned long long)blockIdx.x * TILE; tile < total; tile += (unsigned long long)gridDim.x * TILE) {
+		if (threadIdx.x < BIN_CLASSES) s_cnt[threadIdx.x] = 0;
+		__syncthreads();
+		uint32_t rank[RPT];
+		int cls[RPT];
+#pragma unroll
+		for (int q = 0; q < RPT; q++) {
+			const unsigned long long t = tile + q * TPB + threadIdx.x;
+			cls[q] = t < total ? (int)H.cls[t] : -1;
+			rank[q] = cls[q] >= 0 ? atomicAdd(&s_cnt[cls[q]], 1u) : 0u;
+		}
+		__syncthreads();
+		if (threadIdx.x < BIN_CLASSES && s_cnt[threadIdx.x])
+			s_start[threadIdx.x] = atomicAdd(&H.counters[65 + threadIdx.x], (unsigned long long)s_cnt[threadIdx.x]);
+		__syncthreads();
+#pragma unroll
+		for (int q = 0; q < RPT; q++)
+			if (cls[q] >= 0) H.sorted[s_start[cls[q]] + rank[q]] = H.rows[tile + q * TPB + threadIdx.x];
+		__syncthreads();
+	}
+}
+
+// stage 3a for heavy rows: every warp takes 32 consecutive entries of the class-sorted list
+template <bool DEF>
+__global__ void __launch_bounds__(TPB) k_extras_heavy(GraphDev g, RangeDev R, HeavyDev H) {
+	const unsigned long long total = H.counters[0];
+	const int64_t rp_from = R.rp[R.from - R.lo];
+	const unsigned long long warps = (unsigned long long)gridDim.x * (TPB / 32);
+	const unsigned lane = threadIdx.x & 31;
+	for (unsigned long long c = (unsigned long long)blockIdx.x * (TPB / 32) + (threadIdx.x >> 5); c * 32 < total; c += warps) {
+		const unsigned long long t = c * 32 + lane;
+		const bool active = t < total;
+		const unsigned mask = __ballot_sync(FULL_MASK, active);
+		if (active) {
+			const int64_t i = H.sorted[t];
+			BitReader r;
+			r.init(g, ef_get(g, R.lo + i));
+			RowHead h;
+			const uint32_t rf = R.ref[i];
+			row_head<DEF>(g, r, rf ? R.deg[i - rf] : 0, h);
+			__syncwarp(mask);
+			row_extras<DEF>(g, r, R.lo + i, h.d - h.ncopied, row_slot(R, i, rp_from) + h.ncopied, mask);
+		}
+	}
+}
+
+void launch_extras(const Launch &L, const GraphDev &g, bool def, const RangeDev &r, const HeavyDev &h) {
 	const int64_t count = r.hi - r.lo;
 	if (count <= 0) return;
-	if (def) k_extras<true><<<grid_for(count, TPB), TPB, 0, L.stream>>>(g, r);
-	else k_extras<false><<<grid_for(count, TPB), TPB, 0, L.stream>>>(g, r);
+	if (h.rows) cudaMemsetAsync(h.counters, 0, 129 * sizeof(unsigned long long), L.stream);
+	if (def) k_extras<true><<<grid_for(count, TILE), TPB, 0, L.stream>>>(g, r, h);
+	else k_extras<false><<<grid_for(count, TILE), TPB, 0, L.stream>>>(g, r, h);
+	WGBV_LAUNCHED(L);
+	if (!h.rows) return;
+	k_heavy_offsets<<<1, 32, 0, L.stream>>>(h);
+	WGBV_LAUNCHED(L);
+	const unsigned grid = (unsigned)std::min<int64_t>(grid_for(count / 8 + 1, TILE), 148 * 8);
+	k_heavy_scatter<<<grid, TPB, 0, L.stream>>>(h);
+	WGBV_LAUNCHED(L);
+	if (def) k_extras_heavy<true><<<148 * 8, TPB, 0, L.stream>>>(g, r, h);
+	else k_extras_heavy<false><<<148 * 8, TPB, 0, L.stream>>>(g, r, h);
 	WGBV_LAUNCHED(L);
 }
 
-// stage 3b: thread per row of one depth level.
+// stage 3b: the rows of one depth level.  With a list, a block takes TILE list entries; without, it inspects TILE
+// consecutive nodes and keeps those at this level.
 template <bool DEF>
 __global__ void __launch_bounds__(TPB) k_copy_level(GraphDev g, RangeDev R, uint32_t level, const uint32_t *__restrict__ list,
                                                     uint64_t list_count) {
-	const uint64_t t = (uint64_t)blockIdx.x * TPB + threadIdx.x;
-	int64_t i;
-	if (list) {
-		if (t >= list_count) return;
-		i = list[t];
-	} else {
-		if ((int64_t)t >= R.hi - R.lo) return;
-		i = (int64_t)t;
-		if (R.depth[i] != level) return;
-	}
-	const uint32_t d = R.deg[i];
-	if (d == 0) return;
-	const int64_t x = R.lo + i;
+	__shared__ uint64_t s_pos[TILE];
+	__shared__ uint32_t s_row[TILE], s_bc[TILE], s_ncopied[TILE];
+	__shared__ uint32_t s_hist[BIN_CLASSES + 1];
+	__shared__ uint16_t s_order[TILE];
+	const uint64_t base = (uint64_t)blockIdx.x * TILE;
 	const int64_t rp_from = R.rp[R.from - R.lo];
-	if (x >= R.from && (uint64_t)(R.rp[i + 1] - rp_from) > R.col_capacity) return;
-	const uint32_t rf = R.ref[i];
-	const uint32_t dref = R.deg[i - rf];
-	BitReader r;
-	r.init(g, ef_get(g, x));
-	RowHead h;
-	if (!row_head<DEF>(g, r, dref, h)) return;
-	r.seek(h.blocks_pos);
-	row_copy<DEF>(g, r, row_slot(R, i - rf, rp_from), dref, row_slot(R, i, rp_from), h.d, h.bc, h.ncopied);
+	int bucket[RPT];
+#pragma unroll 1
+	for (int q = 0; q < RPT; q++) {
+		const int id = q * TPB + threadIdx.x;
+		const uint64_t t = base + id;
+		bucket[q] = -1;
+		int64_t i = -1;
+		if (list) {
+			if (t < list_count) i = list[t];
+		} else if ((int64_t)t < R.hi - R.lo && R.depth[t] == level) i = (int64_t)t;
+		if (i >= 0 && R.deg[i] != 0 && !(R.lo + i >= R.from && (uint64_t)(R.rp[i + 1] - rp_from) > R.col_capacity)) {
+			const uint32_t rf = R.ref[i];
+			BitReader r;
+			r.init(g, ef_get(g, R.lo + i));
+			RowHead h;
+			row_head<DEF>(g, r, R.deg[i - rf], h);
+			if (h.ncopied) {
+				bucket[q] = work_bucket(h.ncopied);
+				s_pos[id] = h.blocks_pos;
+				s_row[id] = (uint32_t)i;
+				s_bc[id] = h.bc;
+				s_ncopied[id] = h.ncopied;
+			}
+		}
+		__syncwarp();
+	}
+	uint32_t total;
+	block_bin_sort<RPT>(bucket, s_hist, s_order, &total);
+#pragma unroll 1
+	for (uint32_t tb = threadIdx.x & ~31u; tb < total; tb += TPB) {
+		const uint32_t t = tb + (threadIdx.x & 31u);
+		const bool active = t < total;
+		const unsigned mask = __ballot_sync(FULL_MASK, active);
+		if (active) {
+			const int id = s_order[t];
+			const int64_t k = s_row[id];
+			const uint32_t rf = R.ref[k];
+			BitReader r;
+			r.init(g, s_pos[id]);
+			row_copy<DEF>(g, r, row_slot(R, k - rf, rp_from), R.deg[k - rf], row_slot(R, k, rp_from), R.deg[k], s_bc[id], s_ncopied[id], mask);
+		}
+	}
 }
 
 void launch_copy_level(const Launch &L, const GraphDev &g, bool def, const RangeDev &r, uint32_t level, const uint32_t *list,
                        uint64_t list_count) {
 	const int64_t items = list ? (int64_t)list_count : r.hi - r.lo;
 	if (items <= 0) return;
-	if (def) k_copy_level<true><<<grid_for(items, TPB), TPB, 0, L.stream>>>(g, r, level, list, list_count);
-	else k_copy_level<false><<<grid_for(items, TPB), TPB, 0, L.stream>>>(g, r, level, list, list_count);
+	if (def) k_copy_level<true><<<grid_for(items, TILE), TPB, 0, L.stream>>>(g, r, level, list, list_count);
+	else k_copy_level<false><<<grid_for(items, TILE), TPB, 0, L.stream>>>(g, r, level, list, list_count);
 	WGBV_LAUNCHED(L);
 }
 
@@ -468,16 +685,17 @@ __device__ __forceinline__ int64_t *chain_slot(const ChainDev &c, uint64_t row) 
 template <bool DEF>
 __global__ void __launch_bounds__(TPB) k_chain_extras(GraphDev g, ChainDev c, uint64_t rows) {
 	const uint64_t row = (uint64_t)blockIdx.x * TPB + threadIdx.x;
-	if (row >= rows) return;
-	const uint32_t d = c.deg[row];
-	if (d == 0) return;
+	const bool active = row < rows && c.deg[row] != 0;
+	const unsigned mask = __ballot_sync(FULL_MASK, active);
+	if (!active) return;
 	const int64_t x = c.node[row];
 	const int32_t p = c.parent[row];
 	BitReader r;
 	r.init(g, ef_get(g, x));
 	RowHead h;
-	if (!row_head<DEF>(g, r, p >= 0 ? c.deg[p] : 0, h)) return;
-	row_extras<DEF>(g, r, x, h.d - h.ncopied, chain_slot(c, row) + h.ncopied);
+	row_head<DEF>(g, r, p >= 0 ? c.deg[p] : 0, h);
+	__syncwarp(mask);
+	row_extras<DEF>(g, r, x, h.d - h.ncopied, chain_slot(c, row) + h.ncopied, mask);
 }
 void launch_chain_extras(const Launch &L, const GraphDev &g, bool def, const ChainDev &c, uint64_t rows) {
 	if (!rows) return;
@@ -490,18 +708,19 @@ template <bool DEF>
 __global__ void __launch_bounds__(TPB) k_chain_copy(GraphDev g, ChainDev c, uint64_t rows, const uint32_t *__restrict__ level,
                                                     uint32_t this_level) {
 	const uint64_t row = (uint64_t)blockIdx.x * TPB + threadIdx.x;
-	if (row >= rows || level[row] != this_level) return;
-	const uint32_t d = c.deg[row];
+	const bool active = row < rows && level[row] == this_level && c.deg[row] != 0 && c.parent[row] >= 0;
+	const unsigned mask = __ballot_sync(FULL_MASK, active);
+	if (!active) return;
 	const int32_t p = c.parent[row];
-	if (d == 0 || p < 0) return;
 	const int64_t x = c.node[row];
 	const uint32_t dref = c.deg[p];
 	BitReader r;
 	r.init(g, ef_get(g, x));
 	RowHead h;
-	if (!row_head<DEF>(g, r, dref, h)) return;
+	row_head<DEF>(g, r, dref, h);
 	r.seek(h.blocks_pos);
-	row_copy<DEF>(g, r, chain_slot(c, (uint64_t)p), dref, chain_slot(c, row), h.d, h.bc, h.ncopied);
+	__syncwarp(mask);
+	row_copy<DEF>(g, r, chain_slot(c, (uint64_t)p), dref, chain_slot(c, row), h.d, h.bc, h.ncopied, mask);
 }
 void launch_chain_copy(const Launch &L, const GraphDev &g, bool def, const ChainDev &c, uint64_t rows, const uint32_t *level,
                        uint32_t this_level) {

@@ -35,6 +35,14 @@ struct ChainDev {
 	int64_t *store;
 };
 
+// The global list of rows whose extras are too long to be decoded inside their tile (see bv_kernels.cu).
+struct HeavyDev {
+	uint32_t *rows;    // row indices (relative to RangeDev.lo) in arrival order; nullptr disables the heavy path
+	uint8_t *cls;      // class of each entry
+	uint32_t *sorted;  // row indices sorted by class, heaviest first
+	unsigned long long *counters;  // [0] entries, [1..64] per-class counts, [65..128] per-class cursors
+};
+
 struct Launch {
 	cudaStream_t stream;
 	uint64_t *launches;  // incremented once per kernel launched
@@ -54,7 +62,7 @@ void launch_level_count(const Launch &L, const uint32_t *depth, int64_t count, u
 void launch_level_scatter(const Launch &L, const uint32_t *depth, int64_t count, uint32_t nlevels,
                           unsigned long long *level_cursor, uint32_t *list);
 // stage 3a: intervals + residuals of every row (whole row when it has no reference)
-void launch_extras(const Launch &L, const GraphDev &g, bool def, const RangeDev &r);
+void launch_extras(const Launch &L, const GraphDev &g, bool def, const RangeDev &r, const HeavyDev &h);
 // stage 3b: copy-block resolution of the rows at one depth level; list == nullptr: every node is inspected
 void launch_copy_level(const Launch &L, const GraphDev &g, bool def, const RangeDev &r, uint32_t level,
                        const uint32_t *list, uint64_t list_count);

@@ -68,6 +68,7 @@ struct wgbv_stream {
 	uint64_t *h_pin = nullptr;  // pinned host scratch for read-backs (16 words)
 	uint64_t launches = 0;
 	DevBuf deg, ref, depth, rp, scan_state, ticket, halo, levels, list, col, rowptr, ids, batch;
+	DevBuf heavy_rows, heavy_sorted, heavy_cls, heavy_counters;
 	DevBuf c_node, c_dst, c_parent, c_deg, c_isq, c_level, c_len, c_arcs, c_row0, c_soff, c_store;
 	cudaEvent_t ev[6]{};
 	bool ev_valid = false;
@@ -335,7 +336,7 @@ extern "C" void wgbv_stream_destroy(wgbv_stream *s) {
 	cudaSetDevice(s->g->device);
 	if (s->stream) cudaStreamSynchronize(s->stream);
 	for (DevBuf *b : {&s->deg, &s->ref, &s->depth, &s->rp, &s->scan_state, &s->ticket, &s->halo, &s->levels, &s->list, &s->col,
-	                  &s->rowptr, &s->ids, &s->batch, &s->c_node, &s->c_dst, &s->c_parent, &s->c_deg, &s->c_isq, &s->c_level,
+	                  &s->rowptr, &s->ids, &s->batch, &s->heavy_rows, &s->heavy_sorted, &s->heavy_cls, &s->heavy_counters, &s->c_node, &s->c_dst, &s->c_parent, &s->c_deg, &s->c_isq, &s->c_level,
 	                  &s->c_len, &s->c_arcs, &s->c_row0, &s->c_soff, &s->c_store})
 		b->release();
 	if (s->d_err) cudaFree(s->d_err);
@@ -485,7 +486,17 @@ static int decode_rows(wgbv_stream *s, int64_t from, int64_t to, const Prepared 
 	R.col = d_col;
 	R.halo = s->halo.as<int64_t>();
 	R.col_capacity = col_capacity;
-	launch_extras(L, s->dev, g->def_codes, R);
+	// rows with >= 64 extras go through a global, class-sorted list: at most total_arcs / 64 of them
+	HeavyDev H;
+	const size_t hcap = (size_t)((P.arcs + P.halo_arcs) / 64 + 1);
+	if ((rc = s->heavy_rows.ensure(hcap * 4)) || (rc = s->heavy_sorted.ensure(hcap * 4)) || (rc = s->heavy_cls.ensure(hcap)) ||
+	    (rc = s->heavy_counters.ensure(129 * 8)))
+		return rc;
+	H.rows = s->heavy_rows.as<uint32_t>();
+	H.sorted = s->heavy_sorted.as<uint32_t>();
+	H.cls = s->heavy_cls.as<uint8_t>();
+	H.counters = s->heavy_counters.as<unsigned long long>();
+	launch_extras(L, s->dev, g->def_codes, R, H);
 	if (P.max_depth <= 8) {
 		for (uint32_t lev = 1; lev <= P.max_depth; lev++) launch_copy_level(L, s->dev, g->def_codes, R, lev, nullptr, 0);
 	} else {
