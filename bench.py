@@ -47,6 +47,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--seed", type=int, default=2)
+    ap.add_argument("--max-degree", type=int, default=10000)
     return ap.parse_args()
 
 
@@ -68,7 +69,7 @@ def workload_name(args, world):
 def generate(args, rank, world, threads):
     import bvgen
     t0 = time.time()
-    e = bvgen.copy_model(args.nodes, seed=args.seed, mean_degree=args.mean_degree, params=bvgen.make_params(maxref=args.maxref),
+    e = bvgen.copy_model(args.nodes, seed=args.seed, mean_degree=args.mean_degree, params=bvgen.make_params(maxref=args.maxref), max_degree=args.max_degree,
                          nsplits=256, threads=threads, first_node=rank * args.nodes, global_n=world * args.nodes)
     return e, time.time() - t0
 

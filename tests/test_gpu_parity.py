@@ -249,3 +249,51 @@ def test_malformed_reference_is_reported():
     with pytest.raises(wg.IllegalStateException):
         g.decodeToCSR()
     g.close()
+
+
+def _similar_rows_graph(n, centers, width, size, seed):
+    """Rows around each centre hold large, nearly identical successor lists (so the encoder chains references across
+    tile boundaries); everything else is tiny."""
+    rng = np.random.default_rng(seed)
+    rows = [np.array([x], dtype=np.int64) if x % 3 else np.zeros(0, dtype=np.int64) for x in range(n)]
+    for c in centers:
+        base = np.unique(rng.integers(0, n, size))
+        for x in range(c - width, c + width):
+            keep = base[rng.random(base.size) < 0.97]
+            rows[x] = np.unique(np.concatenate([keep, rng.integers(0, n, 5)]))
+    rowptr = np.zeros(n + 1, dtype=np.int64)
+    rowptr[1:] = np.cumsum([r.size for r in rows])
+    return rowptr, np.concatenate(rows)
+
+
+def test_tiles_that_do_not_fit_shared_memory(monkeypatch):
+    """The fused tile kernel's slower modes: rows in global scratch (tile larger than shared memory, halo rows a few
+    thousand successors long) and the hand-over to the level-synchronous kernels (halo larger than the scratch)."""
+    monkeypatch.setenv("WGBV_TILE", "1")
+    for size, centers in ((4000, (256, 1000, 1536)), (40000, (512, 2048 + 256))):
+        n = 3000
+        rowptr, col = _similar_rows_graph(n, centers, 12, size, size)
+        e = bg.encode_csr(rowptr, col, bg.make_params(window=7, maxref=3, minint=4))
+        deg, ocol = oracle_of(e).decode_range()
+        assert np.array_equal(ocol, col)
+        with gpu_of(e) as g:
+            rp, c = g.decodeToCSR()
+            assert np.array_equal(rp, rowptr) and np.array_equal(c, col)
+            rp2, c2 = g.decodeToCSR(centers[0] + 3, n)
+            assert np.array_equal(c2, col[rowptr[centers[0] + 3]:])
+
+
+def test_fused_tile_kernel_equals_oracle(monkeypatch, cnr_basename, cnr_golden):
+    """The opt-in fused tile kernel (WGBV_TILE=1) on the golden fixture and on a synthetic graph."""
+    monkeypatch.setenv("WGBV_TILE", "1")
+    deg, rowptr, col = cnr_golden
+    with wg.GpuBVGraph.load(cnr_basename) as g:
+        rp, c = g.decodeToCSR()
+        assert np.array_equal(rp, rowptr) and np.array_equal(c, col)
+        rp, c = g.decodeToCSR(100000, 200000)
+        assert np.array_equal(c, col[rowptr[100000]:rowptr[200000]])
+    e = bg.copy_model(30000, seed=123, mean_degree=25, params=bg.make_params(window=7, maxref=3, minint=4), nsplits=2)
+    odeg, ocol = oracle_of(e).decode_range()
+    with gpu_of(e) as g:
+        rp, c = g.decodeToCSR()
+        assert np.array_equal(rp, rowptr_of(odeg)) and np.array_equal(c, ocol)

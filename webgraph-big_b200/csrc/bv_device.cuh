@@ -26,8 +26,9 @@ enum : uint32_t {
 
 // Everything a kernel needs to know about an opened graph; passed by value.
 struct GraphDev {
-	const uint64_t *words;  // bit stream, big-endian 64-bit words; words[0] holds absolute bits [bit_base, bit_base+64)
-	uint64_t nwords;        // words that may be loaded (includes zero padding)
+	const uint64_t *words;  // bit stream as 32-bit words, most significant bit first; read through (const uint32_t *)words.
+	                        // Word 0 holds absolute bits [bit_base, bit_base + 32)
+	uint64_t nwords;        // 64-bit units that may be loaded (includes zero padding): 2 * nwords 32-bit words
 	uint64_t bit_base;      // absolute bit offset of words[0] (multiple of 64)
 	uint64_t bit_end;       // absolute end of the stream held (exclusive)
 	// Elias-Fano list of the offsets of nodes [ef_first, ef_first + ef_count); values are absolute offsets minus bit_base
@@ -47,78 +48,109 @@ struct GraphDev {
 __device__ __forceinline__ void raise(const GraphDev &g, uint32_t bit) { atomicOr(g.err, bit); }
 
 // ------------------------------------------------------------------------------------------------ bit reader
-// The reader keeps a 64-bit, left-aligned bit buffer plus the next 32-bit word of the stream in registers.  After
-// refill() at least 33 bits are valid, so every code of up to 32 bits -- all but a vanishing fraction in practice
-// -- is decoded from the top half of the buffer with 32-bit arithmetic: one count-leading-zeros, a few shifts and
-// one funnel shift to consume it.  The refill is a handful of predicated instructions (no divergent branch) and the
-// load it issues is for the word AFTER the one it consumes, so its latency is off the critical path.
-// Longer codes take a slow path built from unary() and bits().  All positions are relative to g.bit_base.
-struct BitReader {
-	const uint32_t *__restrict__ w;  // the stream as 32-bit words; stream word j lives at index j ^ 1 (big-endian 64-bit storage)
-	uint64_t nw;                     // number of 32-bit words that may be loaded
-	uint64_t wi;                     // index of the stream word held in `nxt`
-	uint64_t buf;                    // next bits of the stream, first bit in the most significant position
-	uint32_t nb;                     // valid bits in buf
-	uint32_t nxt;                    // stream word wi, not yet in buf
+// The stream lives in device memory as 32-bit words whose most significant bit comes first (the loader byte-swaps
+// once at upload).  The reader holds three consecutive words in registers -- hi, lo and the prefetched nxt -- and
+// the number of bits of hi already consumed, so that
+//   * the next 32 bits of the stream are ONE funnel shift:  peek() = (hi:lo << sh) >> 32
+//   * consuming bits is an add, and crossing a word boundary is three register moves plus the load of the word
+//     after next (predicated, no divergent branch; its latency is off the critical path).
+// Every code of up to 32 bits -- all but a vanishing fraction in practice -- is decoded from peek() with 32-bit
+// arithmetic: one count-leading-zeros and a few shifts.  Longer codes take a slow path built from unary() and
+// bits().  All positions are relative to g.bit_base.
+// LDG = true: the words are in global memory and read through the read-only path; false: plain (generic) loads, so
+// that the same decoder runs on a tile of the stream staged in shared memory.
+template <bool LDG>
+struct BitReaderT {
+	const uint32_t *base;  // address of the word the last seek() started from
+	uint64_t j0;    // stream index of that word
+	uint32_t lim;   // words that may be loaded from base (saturated)
+	uint32_t idx;   // index (from base) of the word held in nxt
+	uint32_t hi, lo, nxt;
+	uint32_t sh;    // bits of hi already consumed, 0..31
 
-	__device__ __forceinline__ uint32_t load(uint64_t j) const { return j < nw ? __ldg(w + (j ^ 1)) : 0u; }
+	__device__ __forceinline__ uint32_t load(uint32_t i) const { return i < lim ? (LDG ? __ldg(base + i) : base[i]) : 0u; }
+	// The word after next is loaded with one refill of lead time only (the compiler waits for it at the head of the
+	// decoding loop), so a miss there costs a full DRAM round trip per lane.  Every 8 words (one 32-byte sector) the
+	// reader therefore asks for the sector PF_AHEAD words further on; the request carries no register, hence no wait.
+	static constexpr uint32_t PF_AHEAD = 64;
+	__device__ __forceinline__ void prefetch(uint32_t i) const {
+		if (LDG && (i & 7u) == 0 && i + PF_AHEAD < lim) asm volatile("prefetch.global.L2 [%0];" ::"l"(base + i + PF_AHEAD));
+	}
 
+	// positions the reader on an arbitrary word array (e.g. a staged tile): `words` holds `nwords` 32-bit words
+	__device__ __forceinline__ void init_words(const uint32_t *words, uint32_t nwords, uint32_t rel_pos) {
+		j0 = rel_pos >> 5;
+		if (j0 > nwords) j0 = nwords;
+		base = words + j0;
+		lim = nwords - (uint32_t)j0;
+		sh = rel_pos & 31u;
+		hi = load(0);
+		lo = load(1);
+		idx = 2;
+		nxt = load(2);
+	}
+
+	__device__ __forceinline__ void init(const GraphDev &g, uint64_t rel_pos) {
+		const uint64_t nw = g.nwords * 2;
+		j0 = rel_pos >> 5;
+		if (j0 > nw) j0 = nw;
+		base = (const uint32_t *)g.words + j0;
+		const uint64_t room = nw - j0;
+		lim = room > 0xffffffffull ? 0xffffffffu : (uint32_t)room;
+		sh = (uint32_t)rel_pos & 31u;
+		hi = load(0);
+		lo = load(1);
+		idx = 2;
+		nxt = load(2);
+	}
+	// re-positions inside the same stream (any position at or after the one given to init)
 	__device__ __forceinline__ void seek(uint64_t p) {
 		const uint64_t j = p >> 5;
-		const unsigned sh = (unsigned)p & 31u;
-		buf = (((uint64_t)load(j) << 32) | load(j + 1)) << sh;
-		nb = 64u - sh;
-		wi = j + 2;
-		nxt = load(wi);
+		const uint32_t i = (uint32_t)(j - j0);
+		sh = (uint32_t)p & 31u;
+		hi = load(i);
+		lo = load(i + 1);
+		idx = i + 2;
+		nxt = load(idx);
 	}
-	__device__ __forceinline__ void init(const GraphDev &g, uint64_t rel_pos) {
-		w = (const uint32_t *)g.words;
-		nw = g.nwords * 2;
-		seek(rel_pos);
-	}
-	__device__ __forceinline__ uint64_t tell() const { return wi * 32 - nb; }
-	__device__ __forceinline__ bool past_end() const { return wi > nw + 2; }
+	__device__ __forceinline__ uint64_t tell() const { return (j0 + idx - 2) * 32 + sh; }
+	__device__ __forceinline__ bool past_end() const { return idx >= 3 && idx - 3 > lim; }
 
-	// makes at least 33 bits valid
-	__device__ __forceinline__ void refill() {
-		if (nb <= 32) {
-			buf |= (uint64_t)nxt << (32u - nb);
-			nb += 32;
-			nxt = load(++wi);
+	// the next 32 bits of the stream, first bit in the most significant position
+	__device__ __forceinline__ uint32_t peek() const { return __funnelshift_l(lo, hi, sh); }
+	__device__ __forceinline__ void consume(uint32_t n) {  // n in [0, 32]
+		sh += n;
+		if (sh >= 32) {
+			sh -= 32;
+			hi = lo;
+			lo = nxt;
+			nxt = load(++idx);
+			prefetch(idx);
 		}
-	}
-	__device__ __forceinline__ uint32_t top() const { return (uint32_t)(buf >> 32); }
-	__device__ __forceinline__ void consume(unsigned n) {  // n <= min(nb, 63)
-		buf <<= n;
-		nb -= n;
 	}
 
 	__device__ __forceinline__ uint64_t bits(unsigned n) {  // n in [0, 64]
 		uint64_t v = 0;
 		if (n > 32) {
-			refill();
-			v = top();
+			v = peek();
 			consume(32);
 			n -= 32;
 		}
 		if (n) {
-			refill();
-			v = (v << n) | (top() >> (32u - n));
+			v = (v << n) | (peek() >> (32u - n));
 			consume(n);
 		}
 		return v;
 	}
 
 	__device__ __forceinline__ uint64_t unary() {
-		refill();
-		uint32_t t = top();
+		uint32_t t = peek();
 		uint64_t total = 0;
 		while (t == 0) {
 			total += 32;
 			consume(32);
-			refill();
 			if (past_end()) return total;  // the kernels raise ERR_OVERRUN on their own checks
-			t = top();
+			t = peek();
 		}
 		const unsigned z = (unsigned)__clz((int)t);
 		consume(z + 1);
@@ -126,9 +158,8 @@ struct BitReader {
 	}
 
 	__device__ __forceinline__ uint64_t gamma() {
-		refill();
-		const uint32_t t = top();
-		if (t >> 16) {  // at most 15 leading zeros: the whole code (<= 31 bits) is in the top half
+		const uint32_t t = peek();
+		if (t >> 16) {  // at most 15 leading zeros: the whole code (<= 31 bits) is in the window
 			const unsigned z = (unsigned)__clz((int)t);
 			const uint32_t v = (t << z) >> (31u - z);
 			consume(2 * z + 1);
@@ -146,21 +177,17 @@ struct BitReader {
 	}
 
 	__device__ __forceinline__ uint64_t zeta(int k) {
-		refill();
-		const uint32_t t = top();
+		const uint32_t t = peek();
 		const int h = t ? __clz((int)t) : 32;
 		const int pb = h * k + k - 1;  // payload bits before the optional extra one
 		if (h + 2 + pb <= 32) {
 			const uint32_t x = t << (h + 1);
 			const uint32_t left = 1u << (h * k);
 			const uint32_t m = pb ? x >> (32 - pb) : 0u;
-			if (m < left) {
-				consume((unsigned)(h + 1 + pb));
-				return (uint64_t)(m + left - 1);
-			}
+			const bool shorter = m < left;
 			const uint32_t b = (x >> (31 - pb)) & 1u;
-			consume((unsigned)(h + 2 + pb));
-			return (uint64_t)(((m << 1) | b) - 1);
+			consume((uint32_t)(h + 1 + pb) + (shorter ? 0u : 1u));
+			return (uint64_t)(shorter ? m + left - 1 : ((m << 1) | b) - 1);
 		}
 		const uint64_t hh = unary();
 		if (hh * (uint64_t)k + (uint64_t)k > 64) return 0;
@@ -209,17 +236,22 @@ struct BitReader {
 		}
 	}
 };
+using BitReader = BitReaderT<true>;
+using TileReader = BitReaderT<false>;
 
 // Fast.nat2int
 __device__ __forceinline__ int64_t nat2int(uint64_t x) { return (x & 1) ? -(int64_t)((x + 1) >> 1) : (int64_t)(x >> 1); }
 
-// The field readers.  DEF = the default codings (gamma outdegrees / blocks / block counts, unary references,
-// zeta residuals, BVG:526-542) compiled in; otherwise the codings are looked up at run time.
-template <bool DEF> __device__ __forceinline__ uint64_t rd_outdegree(BitReader &r, const GraphDev &g) { return DEF ? r.gamma() : r.code(g.outdegree_coding); }
-template <bool DEF> __device__ __forceinline__ uint64_t rd_reference(BitReader &r, const GraphDev &g) { return DEF ? r.unary() : r.code(g.reference_coding); }
-template <bool DEF> __device__ __forceinline__ uint64_t rd_blockcount(BitReader &r, const GraphDev &g) { return DEF ? r.gamma() : r.code(g.block_count_coding); }
-template <bool DEF> __device__ __forceinline__ uint64_t rd_block(BitReader &r, const GraphDev &g) { return DEF ? r.gamma() : r.code(g.block_coding); }
-template <bool DEF> __device__ __forceinline__ uint64_t rd_residual(BitReader &r, const GraphDev &g) { return DEF ? r.zeta(g.zeta_k) : r.residual(g.residual_coding, g.zeta_k); }
+// The field readers.  DEF selects how the codings are resolved: 0 = looked up at run time; 1 = the default codings
+// (gamma outdegrees / blocks / block counts, unary references, zeta residuals, BVG:526-542) compiled in, zeta_k at
+// run time; 2 = the default codings with zeta_k = 3 (the default k, BVG:473) compiled in.
+template <int DEF, class RD> __device__ __forceinline__ uint64_t rd_outdegree(RD &r, const GraphDev &g) { return DEF ? r.gamma() : r.code(g.outdegree_coding); }
+template <int DEF, class RD> __device__ __forceinline__ uint64_t rd_reference(RD &r, const GraphDev &g) { return DEF ? r.unary() : r.code(g.reference_coding); }
+template <int DEF, class RD> __device__ __forceinline__ uint64_t rd_blockcount(RD &r, const GraphDev &g) { return DEF ? r.gamma() : r.code(g.block_count_coding); }
+template <int DEF, class RD> __device__ __forceinline__ uint64_t rd_block(RD &r, const GraphDev &g) { return DEF ? r.gamma() : r.code(g.block_coding); }
+template <int DEF, class RD> __device__ __forceinline__ uint64_t rd_residual(RD &r, const GraphDev &g) {
+	return DEF == 2 ? r.zeta(3) : DEF == 1 ? r.zeta(g.zeta_k) : r.residual(g.residual_coding, g.zeta_k);
+}
 
 // ------------------------------------------------------------------------------------------------ Elias-Fano
 // position of the k-th (0-based) set bit of x; x must have more than k set bits

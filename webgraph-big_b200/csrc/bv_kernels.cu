@@ -13,18 +13,11 @@
 
 #include "bv_kernels.cuh"
 #include "bv_rows.cuh"
+#include "bv_block.cuh"
 
 namespace wgbv {
 
-static constexpr int TPB = 256;
 
-static inline unsigned grid_for(int64_t items, int per_block) {
-	int64_t b = (items + per_block - 1) / per_block;
-	if (b < 1) b = 1;
-	return (unsigned)b;
-}
-
-#define WGBV_LAUNCHED(L) do { if ((L).launches) ++*(L).launches; } while (0)
 
 // ------------------------------------------------------------------------------------------------ load-time
 __global__ void k_bswap(uint64_t *words, uint64_t nwords) {
@@ -32,7 +25,8 @@ __global__ void k_bswap(uint64_t *words, uint64_t nwords) {
 	if (i >= nwords) return;
 	const uint64_t v = words[i];
 	const uint32_t lo = (uint32_t)v, hi = (uint32_t)(v >> 32);
-	words[i] = ((uint64_t)__byte_perm(lo, 0, 0x0123) << 32) | __byte_perm(hi, 0, 0x0123);
+	// each 32-bit half is byte-swapped in place: 32-bit word j of the result holds stream bits [32j, 32j+32), MSB first
+	words[i] = ((uint64_t)__byte_perm(hi, 0, 0x0123) << 32) | __byte_perm(lo, 0, 0x0123);
 }
 
 void launch_bswap(const Launch &L, uint64_t *words, uint64_t nwords) {
@@ -44,7 +38,7 @@ void launch_bswap(const Launch &L, uint64_t *words, uint64_t nwords) {
 // ------------------------------------------------------------------------------------------------ stage 1
 // Outdegree and reference of every node: readOutdegree / readReference at the node's offset
 // (BVG:654-661, 692-703; the offset lookup is offsets.getLong(x), BVG:834).
-template <bool DEF>
+template <int DEF>
 __global__ void __launch_bounds__(TPB) k_header(GraphDev g, int64_t lo, int64_t count, uint32_t *__restrict__ deg, uint8_t *__restrict__ ref) {
 	const int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
 	if (i >= count) return;
@@ -63,10 +57,13 @@ __global__ void __launch_bounds__(TPB) k_header(GraphDev g, int64_t lo, int64_t 
 	ref[i] = (uint8_t)rf;
 }
 
-void launch_header(const Launch &L, const GraphDev &g, bool def, int64_t lo, int64_t count, uint32_t *deg, uint8_t *ref) {
+void launch_header(const Launch &L, const GraphDev &g, int def, int64_t lo, int64_t count, uint32_t *deg, uint8_t *ref) {
 	if (count <= 0) return;
-	if (def) k_header<true><<<grid_for(count, TPB), TPB, 0, L.stream>>>(g, lo, count, deg, ref);
-	else k_header<false><<<grid_for(count, TPB), TPB, 0, L.stream>>>(g, lo, count, deg, ref);
+	switch (def) {
+	case 2: k_header<2><<<grid_for(count, TPB), TPB, 0, L.stream>>>(g, lo, count, deg, ref); break;
+	case 1: k_header<1><<<grid_for(count, TPB), TPB, 0, L.stream>>>(g, lo, count, deg, ref); break;
+	default: k_header<0><<<grid_for(count, TPB), TPB, 0, L.stream>>>(g, lo, count, deg, ref);
+	}
 	WGBV_LAUNCHED(L);
 }
 
@@ -256,62 +253,81 @@ void launch_level_scatter(const Launch &L, const uint32_t *depth, int64_t count,
 }
 
 // ------------------------------------------------------------------------------------------------ stage 3
+// Ordered level lists for shallow chains (at most LEVELS_MAX levels): rows of one level, in node order, so that the
+// copy kernels find dense, memory-ordered work.  k_level_block_counts counts the rows of every level in blocks of
+// LTILE nodes (layout: level-major), a scan turns the counts into positions, k_level_fill writes the row indices.
+static constexpr int LEVELS_MAX = 8;
+static constexpr int LTILE = TPB * 8;
+
+__global__ void __launch_bounds__(TPB) k_level_block_counts(const uint32_t *__restrict__ depth, int64_t count, uint32_t nlevels,
+                                                            uint32_t nblocks, uint32_t *__restrict__ counts) {
+	__shared__ uint32_t s_cnt[LEVELS_MAX + 1];
+	if (threadIdx.x <= LEVELS_MAX) s_cnt[threadIdx.x] = 0;
+	__syncthreads();
+	const int64_t base = (int64_t)blockIdx.x * LTILE;
+	for (int q = 0; q < 8; q++) {
+		const int64_t i = base + q * TPB + threadIdx.x;
+		const uint32_t d = i < count ? depth[i] : 0u;
+		for (uint32_t l = 1; l <= nlevels; l++) {
+			const unsigned m = __ballot_sync(0xffffffffu, d == l);
+			if ((threadIdx.x & 31) == 0 && m) atomicAdd(&s_cnt[l], (uint32_t)__popc(m));
+		}
+	}
+	__syncthreads();
+	if (threadIdx.x >= 1 && threadIdx.x <= nlevels) counts[(size_t)(threadIdx.x - 1) * nblocks + blockIdx.x] = s_cnt[threadIdx.x];
+}
+
+__global__ void __launch_bounds__(TPB) k_level_fill(const uint32_t *__restrict__ depth, int64_t count, uint32_t nlevels,
+                                                    uint32_t nblocks, const int64_t *__restrict__ pos, uint32_t *__restrict__ list) {
+	__shared__ uint32_t s_cnt[8][TPB / 32][LEVELS_MAX + 1];  // rows of each level per (iteration, warp), then their prefix
+	const int64_t base = (int64_t)blockIdx.x * LTILE;
+	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	uint32_t myd[8], myrank[8];
+	for (int q = 0; q < 8; q++) {
+		const int64_t i = base + q * TPB + threadIdx.x;
+		const uint32_t d = i < count ? depth[i] : 0u;
+		myd[q] = d;
+		myrank[q] = 0;
+		for (uint32_t l = 1; l <= nlevels; l++) {
+			const unsigned m = __ballot_sync(0xffffffffu, d == l);
+			if (d == l) myrank[q] = (uint32_t)__popc(m & ((1u << lane) - 1));
+			if (lane == 0) s_cnt[q][warp][l] = (uint32_t)__popc(m);
+		}
+	}
+	__syncthreads();
+	if (threadIdx.x >= 1 && threadIdx.x <= nlevels) {
+		const uint32_t l = threadIdx.x;
+		uint32_t run = 0;
+		for (int q = 0; q < 8; q++)
+			for (int w = 0; w < TPB / 32; w++) {
+				const uint32_t c = s_cnt[q][w][l];
+				s_cnt[q][w][l] = run;
+				run += c;
+			}
+	}
+	__syncthreads();
+	for (int q = 0; q < 8; q++) {
+		const uint32_t d = myd[q];
+		if (d >= 1 && d <= nlevels) {
+			const int64_t i = base + q * TPB + threadIdx.x;
+			list[pos[(size_t)(d - 1) * nblocks + blockIdx.x] + s_cnt[q][warp][d] + myrank[q]] = (uint32_t)i;
+		}
+	}
+}
+
+void launch_level_lists(const Launch &L, const uint32_t *depth, int64_t count, uint32_t nlevels, uint32_t *counts, int64_t *pos,
+                        uint32_t *list, uint64_t *scan_state, uint32_t *ticket) {
+	const uint32_t nblocks = grid_for(count, LTILE);
+	k_level_block_counts<<<nblocks, TPB, 0, L.stream>>>(depth, count, nlevels, nblocks, counts);
+	WGBV_LAUNCHED(L);
+	launch_scan(L, counts, pos, (int64_t)nlevels * nblocks, scan_state, ticket);
+	k_level_fill<<<nblocks, TPB, 0, L.stream>>>(depth, count, nlevels, nblocks, pos, list);
+	WGBV_LAUNCHED(L);
+}
+
 __device__ __forceinline__ int64_t *row_slot(const RangeDev &R, int64_t i, int64_t rp_from) {
 	const int64_t p = R.rp[i];
 	return (R.lo + i >= R.from) ? R.col + (p - rp_from) : R.halo + p;
-}
-
-// Work binning.  Rows differ wildly in length, and a warp that mixes a 3-successor row with a 300-successor row
-// spends most of its issue slots on a handful of lanes (the first version of these kernels ran at ~4 active lanes
-// per instruction).  So every block first parses the heads of its 256 rows, then sorts the rows by the amount of
-// serial work they carry (a counting sort over 64 classes in shared memory, heaviest first), and only then does
-// the serial part: the 32 lanes of a warp now run rows of the same class.
-static constexpr int BIN_CLASSES = 64;
-
-// class of a work amount w >= 1: exact below 32, then two classes per octave; returned heaviest-first
-__device__ __forceinline__ int work_bucket(uint32_t w) {
-	int c;
-	if (w < 32) c = (int)w;
-	else {
-		const int lg = 31 - __clz(w);                 // >= 5
-		c = 32 + 2 * (lg - 5) + (int)((w >> (lg - 1)) & 1);
-		if (c > BIN_CLASSES - 1) c = BIN_CLASSES - 1;
-	}
-	return BIN_CLASSES - 1 - c;
-}
-
-// Block-wide counting sort of up to TPB * RPT items, RPT per thread (bucket[q] < 0: no item in slot q; the id of
-// slot q of thread t is q * TPB + t).  On return order[0..*total) lists the item ids by ascending bucket, i.e.
-// heaviest class first.  All threads of the block must call it.
-template <int RPT>
-__device__ __forceinline__ void block_bin_sort(const int (&bucket)[RPT], uint32_t *hist /*[BIN_CLASSES+1]*/, uint16_t *order,
-                                               uint32_t *total) {
-	if (threadIdx.x <= BIN_CLASSES) hist[threadIdx.x] = 0;
-	__syncthreads();
-	uint32_t rank[RPT];
-#pragma unroll
-	for (int q = 0; q < RPT; q++) rank[q] = bucket[q] >= 0 ? atomicAdd(&hist[bucket[q]], 1u) : 0u;
-	__syncthreads();
-	if (threadIdx.x < 32) {
-		// exclusive scan of the 64 counters by one warp, two per lane
-		const uint32_t a = hist[2 * threadIdx.x], b = hist[2 * threadIdx.x + 1];
-		uint32_t inc = a + b;
-#pragma unroll
-		for (int o = 1; o < 32; o <<= 1) {
-			const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
-			if ((int)threadIdx.x >= o) inc += t;
-		}
-		const uint32_t ex = inc - a - b;
-		hist[2 * threadIdx.x] = ex;
-		hist[2 * threadIdx.x + 1] = ex + a;
-		if (threadIdx.x == 31) hist[BIN_CLASSES] = inc;
-	}
-	__syncthreads();
-#pragma unroll
-	for (int q = 0; q < RPT; q++)
-		if (bucket[q] >= 0) order[hist[bucket[q]] + rank[q]] = (uint16_t)(q * TPB + threadIdx.x);
-	*total = hist[BIN_CLASSES];
-	__syncthreads();
 }
 
 static constexpr int RPT = 8;            // rows per thread
@@ -324,17 +340,28 @@ static constexpr int TILE = TPB * RPT;   // rows per block: the sort domain (see
 static constexpr uint32_t HEAVY = 64;
 
 // stage 3a: one block per TILE nodes.  Rows without a reference come out complete.
-template <bool DEF>
+template <int DEF>
 __global__ void __launch_bounds__(TPB) k_extras(GraphDev g, RangeDev R, HeavyDev H) {
 	__shared__ uint64_t s_pos[TILE];
 	__shared__ uint32_t s_nextra[TILE], s_ncopied[TILE];
-	__shared__ uint32_t s_hist[BIN_CLASSES + 1];
+	__shared__ uint32_t s_hist[NBUCKETS + 1];
 	__shared__ uint16_t s_order[TILE];
 	__shared__ uint32_t s_count[BIN_CLASSES];
+	__shared__ uint8_t s_cls[TILE];
 	__shared__ unsigned long long s_gbase;
 	const int64_t base = (int64_t)blockIdx.x * TILE;
 	const int64_t count = R.hi - R.lo;
 	const int64_t rp_from = R.rp[R.from - R.lo];
+	// the records of the tile's rows are contiguous in the bit stream: ask for all of it up front
+	{
+		__shared__ uint64_t s_span[2];
+		if (threadIdx.x == 0) s_span[0] = ef_get(g, R.lo + base);
+		if (threadIdx.x == 32) s_span[1] = ef_get(g, R.lo + (base + TILE < count ? base + TILE : count));
+		__syncthreads();
+		const char *p0 = (const char *)g.words + ((s_span[0] >> 3) & ~127ull);
+		const char *p1 = (const char *)g.words + (s_span[1] >> 3);
+		for (const char *p = p0 + (size_t)threadIdx.x * 128; p < p1; p += (size_t)TPB * 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+	}
 	// heads of my rows (uniform loop: the warp reconverges at the end of every iteration)
 	int bucket[RPT];
 #pragma unroll 1
@@ -353,10 +380,14 @@ __global__ void __launch_bounds__(TPB) k_extras(GraphDev g, RangeDev R, HeavyDev
 				row_head<DEF>(g, r, rf ? R.deg[i - rf] : 0, h);
 				const uint32_t nextra = h.d - h.ncopied;
 				if (nextra) {
-					bucket[q] = work_bucket(nextra);
+					// rows with intervals first inside each class: warps without any skip the merging loop of row_extras
+					bool has_int = false;
+					if (g.min_interval != 0) { BitReader t = r; has_int = t.gamma() != 0; }
+					bucket[q] = 2 * work_bucket(nextra) + (has_int ? 0 : 1);
 					s_pos[id] = r.tell();
 					s_nextra[id] = nextra;
 					s_ncopied[id] = h.ncopied;
+					s_cls[id] = (uint8_t)bucket[q];
 				}
 			}
 		}
@@ -365,7 +396,7 @@ __global__ void __launch_bounds__(TPB) k_extras(GraphDev g, RangeDev R, HeavyDev
 	uint32_t total;
 	block_bin_sort<RPT>(bucket, s_hist, s_order, &total);
 	// after the sort s_hist[b] is the first position of class b; the classes of >= HEAVY extras come first
-	const int first_light = work_bucket(HEAVY - 1);
+	const int first_light = 2 * work_bucket(HEAVY - 1);
 	const uint32_t nheavy = H.rows ? s_hist[first_light] : 0;
 	if (nheavy) {
 		if (threadIdx.x < first_light) s_count[threadIdx.x] = s_hist[threadIdx.x + 1] - s_hist[threadIdx.x];
@@ -375,7 +406,7 @@ __global__ void __launch_bounds__(TPB) k_extras(GraphDev g, RangeDev R, HeavyDev
 		for (uint32_t t = threadIdx.x; t < nheavy; t += TPB) {
 			const int id = s_order[t];
 			H.rows[s_gbase + t] = (uint32_t)(base + id);
-			H.cls[s_gbase + t] = (uint8_t)work_bucket(s_nextra[id]);
+			H.cls[s_gbase + t] = s_cls[id];
 		}
 	}
 	// serial part: the lanes of a warp take rows of the same class and run them in lock step
@@ -437,7 +468,7 @@ __global__ void __launch_bounds__(TPB) k_heavy_scatter(HeavyDev H) {
 }
 
 // stage 3a for heavy rows: every warp takes 32 consecutive entries of the class-sorted list
-template <bool DEF>
+template <int DEF>
 __global__ void __launch_bounds__(TPB) k_extras_heavy(GraphDev g, RangeDev R, HeavyDev H) {
 	const unsigned long long total = H.counters[0];
 	const int64_t rp_from = R.rp[R.from - R.lo];
@@ -460,12 +491,15 @@ __global__ void __launch_bounds__(TPB) k_extras_heavy(GraphDev g, RangeDev R, He
 	}
 }
 
-void launch_extras(const Launch &L, const GraphDev &g, bool def, const RangeDev &r, const HeavyDev &h) {
+void launch_extras(const Launch &L, const GraphDev &g, int def, const RangeDev &r, const HeavyDev &h) {
 	const int64_t count = r.hi - r.lo;
 	if (count <= 0) return;
 	if (h.rows) cudaMemsetAsync(h.counters, 0, 129 * sizeof(unsigned long long), L.stream);
-	if (def) k_extras<true><<<grid_for(count, TILE), TPB, 0, L.stream>>>(g, r, h);
-	else k_extras<false><<<grid_for(count, TILE), TPB, 0, L.stream>>>(g, r, h);
+	switch (def) {
+	case 2: k_extras<2><<<grid_for(count, TILE), TPB, 0, L.stream>>>(g, r, h); break;
+	case 1: k_extras<1><<<grid_for(count, TILE), TPB, 0, L.stream>>>(g, r, h); break;
+	default: k_extras<0><<<grid_for(count, TILE), TPB, 0, L.stream>>>(g, r, h);
+	}
 	WGBV_LAUNCHED(L);
 	if (!h.rows) return;
 	k_heavy_offsets<<<1, 32, 0, L.stream>>>(h);
@@ -473,19 +507,22 @@ void launch_extras(const Launch &L, const GraphDev &g, bool def, const RangeDev 
 	const unsigned grid = (unsigned)std::min<int64_t>(grid_for(count / 8 + 1, TILE), 148 * 8);
 	k_heavy_scatter<<<grid, TPB, 0, L.stream>>>(h);
 	WGBV_LAUNCHED(L);
-	if (def) k_extras_heavy<true><<<148 * 8, TPB, 0, L.stream>>>(g, r, h);
-	else k_extras_heavy<false><<<148 * 8, TPB, 0, L.stream>>>(g, r, h);
+	switch (def) {
+	case 2: k_extras_heavy<2><<<148 * 8, TPB, 0, L.stream>>>(g, r, h); break;
+	case 1: k_extras_heavy<1><<<148 * 8, TPB, 0, L.stream>>>(g, r, h); break;
+	default: k_extras_heavy<0><<<148 * 8, TPB, 0, L.stream>>>(g, r, h);
+	}
 	WGBV_LAUNCHED(L);
 }
 
 // stage 3b: the rows of one depth level.  With a list, a block takes TILE list entries; without, it inspects TILE
 // consecutive nodes and keeps those at this level.
-template <bool DEF>
+template <int DEF>
 __global__ void __launch_bounds__(TPB) k_copy_level(GraphDev g, RangeDev R, uint32_t level, const uint32_t *__restrict__ list,
                                                     uint64_t list_count) {
 	__shared__ uint64_t s_pos[TILE];
 	__shared__ uint32_t s_row[TILE], s_bc[TILE], s_ncopied[TILE];
-	__shared__ uint32_t s_hist[BIN_CLASSES + 1];
+	__shared__ uint32_t s_hist[NBUCKETS + 1];
 	__shared__ uint16_t s_order[TILE];
 	const uint64_t base = (uint64_t)blockIdx.x * TILE;
 	const int64_t rp_from = R.rp[R.from - R.lo];
@@ -506,7 +543,7 @@ __global__ void __launch_bounds__(TPB) k_copy_level(GraphDev g, RangeDev R, uint
 			RowHead h;
 			row_head<DEF>(g, r, R.deg[i - rf], h);
 			if (h.ncopied) {
-				bucket[q] = work_bucket(h.ncopied);
+				bucket[q] = 2 * work_bucket(h.d);  // the merge loop runs up to d times (copied + extras moved forward)
 				s_pos[id] = h.blocks_pos;
 				s_row[id] = (uint32_t)i;
 				s_bc[id] = h.bc;
@@ -533,12 +570,15 @@ __global__ void __launch_bounds__(TPB) k_copy_level(GraphDev g, RangeDev R, uint
 	}
 }
 
-void launch_copy_level(const Launch &L, const GraphDev &g, bool def, const RangeDev &r, uint32_t level, const uint32_t *list,
+void launch_copy_level(const Launch &L, const GraphDev &g, int def, const RangeDev &r, uint32_t level, const uint32_t *list,
                        uint64_t list_count) {
 	const int64_t items = list ? (int64_t)list_count : r.hi - r.lo;
 	if (items <= 0) return;
-	if (def) k_copy_level<true><<<grid_for(items, TILE), TPB, 0, L.stream>>>(g, r, level, list, list_count);
-	else k_copy_level<false><<<grid_for(items, TILE), TPB, 0, L.stream>>>(g, r, level, list, list_count);
+	switch (def) {
+	case 2: k_copy_level<2><<<grid_for(items, TILE), TPB, 0, L.stream>>>(g, r, level, list, list_count); break;
+	case 1: k_copy_level<1><<<grid_for(items, TILE), TPB, 0, L.stream>>>(g, r, level, list, list_count); break;
+	default: k_copy_level<0><<<grid_for(items, TILE), TPB, 0, L.stream>>>(g, r, level, list, list_count);
+	}
 	WGBV_LAUNCHED(L);
 }
 
@@ -576,7 +616,7 @@ void launch_checksum(const Launch &L, int64_t first_node, int64_t rows, const in
 
 // ------------------------------------------------------------------------------------------------ random access
 // outdegree(x) for arbitrary x (BVG:821-851).  Ids outside [lo, hi) raise the index error.
-template <bool DEF>
+template <int DEF>
 __global__ void __launch_bounds__(TPB) k_batch_degrees(GraphDev g, const int64_t *__restrict__ ids, uint64_t k, int64_t lo,
                                                        int64_t hi, uint32_t *__restrict__ deg) {
 	const uint64_t q = (uint64_t)blockIdx.x * TPB + threadIdx.x;
@@ -589,18 +629,21 @@ __global__ void __launch_bounds__(TPB) k_batch_degrees(GraphDev g, const int64_t
 	if (d > 0x7fffffffull) { raise(g, ERR_DEGREE); deg[q] = 0; return; }
 	deg[q] = (uint32_t)d;
 }
-void launch_batch_degrees(const Launch &L, const GraphDev &g, bool def, const int64_t *ids, uint64_t k, int64_t lo, int64_t hi,
+void launch_batch_degrees(const Launch &L, const GraphDev &g, int def, const int64_t *ids, uint64_t k, int64_t lo, int64_t hi,
                           uint32_t *deg) {
 	if (!k) return;
-	if (def) k_batch_degrees<true><<<grid_for((int64_t)k, TPB), TPB, 0, L.stream>>>(g, ids, k, lo, hi, deg);
-	else k_batch_degrees<false><<<grid_for((int64_t)k, TPB), TPB, 0, L.stream>>>(g, ids, k, lo, hi, deg);
+	switch (def) {
+	case 2: k_batch_degrees<2><<<grid_for((int64_t)k, TPB), TPB, 0, L.stream>>>(g, ids, k, lo, hi, deg); break;
+	case 1: k_batch_degrees<1><<<grid_for((int64_t)k, TPB), TPB, 0, L.stream>>>(g, ids, k, lo, hi, deg); break;
+	default: k_batch_degrees<0><<<grid_for((int64_t)k, TPB), TPB, 0, L.stream>>>(g, ids, k, lo, hi, deg);
+	}
 	WGBV_LAUNCHED(L);
 }
 
 // The reference resolves successors(x) recursively through x - ref (BVG:1084).  Here every query's chain
 // x, x - r1, x - r1 - r2, ... is laid out as explicit rows: the query row goes to the output, its ancestors to a
 // scratch store; rows are then decoded with the same two steps as the bulk path, root level first.
-template <bool DEF>
+template <int DEF>
 __device__ __forceinline__ void chain_step(const GraphDev &g, int64_t y, uint32_t &d, uint32_t &rf) {
 	BitReader r;
 	r.init(g, ef_get(g, y));
@@ -614,7 +657,7 @@ __device__ __forceinline__ void chain_step(const GraphDev &g, int64_t y, uint32_
 	}
 }
 
-template <bool DEF>
+template <int DEF>
 __global__ void __launch_bounds__(TPB) k_chain_walk(GraphDev g, const int64_t *__restrict__ ids, uint64_t k, int64_t lo,
                                                     uint32_t *__restrict__ chain_len, unsigned long long *__restrict__ chain_arcs,
                                                     uint32_t *stats) {
@@ -636,15 +679,18 @@ __global__ void __launch_bounds__(TPB) k_chain_walk(GraphDev g, const int64_t *_
 	chain_arcs[q] = arcs;
 	atomicMax(&stats[1], len);
 }
-void launch_chain_walk(const Launch &L, const GraphDev &g, bool def, const int64_t *ids, uint64_t k, int64_t lo,
+void launch_chain_walk(const Launch &L, const GraphDev &g, int def, const int64_t *ids, uint64_t k, int64_t lo,
                        uint32_t *chain_len, unsigned long long *chain_arcs, uint32_t *stats) {
 	if (!k) return;
-	if (def) k_chain_walk<true><<<grid_for((int64_t)k, TPB), TPB, 0, L.stream>>>(g, ids, k, lo, chain_len, chain_arcs, stats);
-	else k_chain_walk<false><<<grid_for((int64_t)k, TPB), TPB, 0, L.stream>>>(g, ids, k, lo, chain_len, chain_arcs, stats);
+	switch (def) {
+	case 2: k_chain_walk<2><<<grid_for((int64_t)k, TPB), TPB, 0, L.stream>>>(g, ids, k, lo, chain_len, chain_arcs, stats); break;
+	case 1: k_chain_walk<1><<<grid_for((int64_t)k, TPB), TPB, 0, L.stream>>>(g, ids, k, lo, chain_len, chain_arcs, stats); break;
+	default: k_chain_walk<0><<<grid_for((int64_t)k, TPB), TPB, 0, L.stream>>>(g, ids, k, lo, chain_len, chain_arcs, stats);
+	}
 	WGBV_LAUNCHED(L);
 }
 
-template <bool DEF>
+template <int DEF>
 __global__ void __launch_bounds__(TPB) k_chain_fill(GraphDev g, const int64_t *__restrict__ ids, uint64_t k,
                                                     const int64_t *__restrict__ chain_row0, const int64_t *__restrict__ store_off0,
                                                     const int64_t *__restrict__ rowptr, int64_t *node, int64_t *dst_off,
@@ -669,12 +715,15 @@ __global__ void __launch_bounds__(TPB) k_chain_fill(GraphDev g, const int64_t *_
 		y -= rf;
 	}
 }
-void launch_chain_fill(const Launch &L, const GraphDev &g, bool def, const int64_t *ids, uint64_t k, const int64_t *chain_row0,
+void launch_chain_fill(const Launch &L, const GraphDev &g, int def, const int64_t *ids, uint64_t k, const int64_t *chain_row0,
                        const int64_t *store_off0, const int64_t *rowptr, int64_t *node, int64_t *dst_off, int32_t *parent,
                        uint32_t *deg, uint8_t *is_query, uint32_t *level) {
 	if (!k) return;
-	if (def) k_chain_fill<true><<<grid_for((int64_t)k, TPB), TPB, 0, L.stream>>>(g, ids, k, chain_row0, store_off0, rowptr, node, dst_off, parent, deg, is_query, level);
-	else k_chain_fill<false><<<grid_for((int64_t)k, TPB), TPB, 0, L.stream>>>(g, ids, k, chain_row0, store_off0, rowptr, node, dst_off, parent, deg, is_query, level);
+	switch (def) {
+	case 2: k_chain_fill<2><<<grid_for((int64_t)k, TPB), TPB, 0, L.stream>>>(g, ids, k, chain_row0, store_off0, rowptr, node, dst_off, parent, deg, is_query, level); break;
+	case 1: k_chain_fill<1><<<grid_for((int64_t)k, TPB), TPB, 0, L.stream>>>(g, ids, k, chain_row0, store_off0, rowptr, node, dst_off, parent, deg, is_query, level); break;
+	default: k_chain_fill<0><<<grid_for((int64_t)k, TPB), TPB, 0, L.stream>>>(g, ids, k, chain_row0, store_off0, rowptr, node, dst_off, parent, deg, is_query, level);
+	}
 	WGBV_LAUNCHED(L);
 }
 
@@ -682,7 +731,7 @@ __device__ __forceinline__ int64_t *chain_slot(const ChainDev &c, uint64_t row) 
 	return (c.is_query[row] ? c.col : c.store) + c.dst_off[row];
 }
 
-template <bool DEF>
+template <int DEF>
 __global__ void __launch_bounds__(TPB) k_chain_extras(GraphDev g, ChainDev c, uint64_t rows) {
 	const uint64_t row = (uint64_t)blockIdx.x * TPB + threadIdx.x;
 	const bool active = row < rows && c.deg[row] != 0;
@@ -697,14 +746,17 @@ __global__ void __launch_bounds__(TPB) k_chain_extras(GraphDev g, ChainDev c, ui
 	__syncwarp(mask);
 	row_extras<DEF>(g, r, x, h.d - h.ncopied, chain_slot(c, row) + h.ncopied, mask);
 }
-void launch_chain_extras(const Launch &L, const GraphDev &g, bool def, const ChainDev &c, uint64_t rows) {
+void launch_chain_extras(const Launch &L, const GraphDev &g, int def, const ChainDev &c, uint64_t rows) {
 	if (!rows) return;
-	if (def) k_chain_extras<true><<<grid_for((int64_t)rows, TPB), TPB, 0, L.stream>>>(g, c, rows);
-	else k_chain_extras<false><<<grid_for((int64_t)rows, TPB), TPB, 0, L.stream>>>(g, c, rows);
+	switch (def) {
+	case 2: k_chain_extras<2><<<grid_for((int64_t)rows, TPB), TPB, 0, L.stream>>>(g, c, rows); break;
+	case 1: k_chain_extras<1><<<grid_for((int64_t)rows, TPB), TPB, 0, L.stream>>>(g, c, rows); break;
+	default: k_chain_extras<0><<<grid_for((int64_t)rows, TPB), TPB, 0, L.stream>>>(g, c, rows);
+	}
 	WGBV_LAUNCHED(L);
 }
 
-template <bool DEF>
+template <int DEF>
 __global__ void __launch_bounds__(TPB) k_chain_copy(GraphDev g, ChainDev c, uint64_t rows, const uint32_t *__restrict__ level,
                                                     uint32_t this_level) {
 	const uint64_t row = (uint64_t)blockIdx.x * TPB + threadIdx.x;
@@ -722,11 +774,14 @@ __global__ void __launch_bounds__(TPB) k_chain_copy(GraphDev g, ChainDev c, uint
 	__syncwarp(mask);
 	row_copy<DEF>(g, r, chain_slot(c, (uint64_t)p), dref, chain_slot(c, row), h.d, h.bc, h.ncopied, mask);
 }
-void launch_chain_copy(const Launch &L, const GraphDev &g, bool def, const ChainDev &c, uint64_t rows, const uint32_t *level,
+void launch_chain_copy(const Launch &L, const GraphDev &g, int def, const ChainDev &c, uint64_t rows, const uint32_t *level,
                        uint32_t this_level) {
 	if (!rows) return;
-	if (def) k_chain_copy<true><<<grid_for((int64_t)rows, TPB), TPB, 0, L.stream>>>(g, c, rows, level, this_level);
-	else k_chain_copy<false><<<grid_for((int64_t)rows, TPB), TPB, 0, L.stream>>>(g, c, rows, level, this_level);
+	switch (def) {
+	case 2: k_chain_copy<2><<<grid_for((int64_t)rows, TPB), TPB, 0, L.stream>>>(g, c, rows, level, this_level); break;
+	case 1: k_chain_copy<1><<<grid_for((int64_t)rows, TPB), TPB, 0, L.stream>>>(g, c, rows, level, this_level); break;
+	default: k_chain_copy<0><<<grid_for((int64_t)rows, TPB), TPB, 0, L.stream>>>(g, c, rows, level, this_level);
+	}
 	WGBV_LAUNCHED(L);
 }
 

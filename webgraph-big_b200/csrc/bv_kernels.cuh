@@ -43,13 +43,22 @@ struct HeavyDev {
 	unsigned long long *counters;  // [0] entries, [1..64] per-class counts, [65..128] per-class cursors
 };
 
+// The fused tile kernel (bv_tile.cu): per-block scratch for tiles that do not fit shared memory.
+static constexpr int TILE_MAX_HALO = 64;  // largest window_size * max_ref_count the tile kernel handles
+struct TileDev {
+	int64_t *scratch;        // blocks * scratch_cap successors
+	uint32_t scratch_cap;    // per block
+	int32_t halo;            // window_size * max_ref_count of the graph
+	uint32_t *fallback;      // set to 1 when some tile has to be left to the level-synchronous kernels
+};
+
 struct Launch {
 	cudaStream_t stream;
 	uint64_t *launches;  // incremented once per kernel launched
 };
 
 // stage 1: outdegree and reference of every node of [lo, lo+count)
-void launch_header(const Launch &L, const GraphDev &g, bool def, int64_t lo, int64_t count, uint32_t *deg, uint8_t *ref);
+void launch_header(const Launch &L, const GraphDev &g, int def, int64_t lo, int64_t count, uint32_t *deg, uint8_t *ref);
 // stage 2: exclusive prefix sum (single pass, decoupled look-back).  state: count/2048+2 words, ticket: 1 word
 void launch_scan(const Launch &L, const uint32_t *deg, int64_t *rp, int64_t count, uint64_t *state, uint32_t *ticket);
 // rowptr_out[i] = rp[skip + i] - rp[skip] (+ base), i = 0..count
@@ -61,28 +70,35 @@ void launch_depth(const Launch &L, const GraphDev &g, const uint8_t *ref, uint32
 void launch_level_count(const Launch &L, const uint32_t *depth, int64_t count, uint32_t nlevels, unsigned long long *level_count);
 void launch_level_scatter(const Launch &L, const uint32_t *depth, int64_t count, uint32_t nlevels,
                           unsigned long long *level_cursor, uint32_t *list);
+// ordered level lists for shallow chains (nlevels <= 8): counts and pos hold nlevels * ceil(count / 2048) entries (+1 for pos);
+// level l (1-based) occupies list[pos[(l-1) * nblocks] .. pos[l * nblocks])
+void launch_level_lists(const Launch &L, const uint32_t *depth, int64_t count, uint32_t nlevels, uint32_t *counts, int64_t *pos,
+                        uint32_t *list, uint64_t *scan_state, uint32_t *ticket);
 // stage 3a: intervals + residuals of every row (whole row when it has no reference)
-void launch_extras(const Launch &L, const GraphDev &g, bool def, const RangeDev &r, const HeavyDev &h);
+void launch_extras(const Launch &L, const GraphDev &g, int def, const RangeDev &r, const HeavyDev &h);
 // stage 3b: copy-block resolution of the rows at one depth level; list == nullptr: every node is inspected
-void launch_copy_level(const Launch &L, const GraphDev &g, bool def, const RangeDev &r, uint32_t level,
+void launch_copy_level(const Launch &L, const GraphDev &g, int def, const RangeDev &r, uint32_t level,
                        const uint32_t *list, uint64_t list_count);
 // checksum of a CSR
 void launch_checksum(const Launch &L, int64_t first_node, int64_t rows, const int64_t *rowptr, const int64_t *col,
                      unsigned long long *out);
 
 // random access
-void launch_batch_degrees(const Launch &L, const GraphDev &g, bool def, const int64_t *ids, uint64_t k, int64_t lo,
+void launch_batch_degrees(const Launch &L, const GraphDev &g, int def, const int64_t *ids, uint64_t k, int64_t lo,
                           int64_t hi, uint32_t *deg);
 // walks the reference chain of every query: chain_len[q] rows, chain_arcs[q] successors in ancestor rows
-void launch_chain_walk(const Launch &L, const GraphDev &g, bool def, const int64_t *ids, uint64_t k, int64_t lo,
+void launch_chain_walk(const Launch &L, const GraphDev &g, int def, const int64_t *ids, uint64_t k, int64_t lo,
                        uint32_t *chain_len, unsigned long long *chain_arcs, uint32_t *stats);
-void launch_chain_fill(const Launch &L, const GraphDev &g, bool def, const int64_t *ids, uint64_t k,
+void launch_chain_fill(const Launch &L, const GraphDev &g, int def, const int64_t *ids, uint64_t k,
                        const int64_t *chain_row0, const int64_t *store_off0, const int64_t *rowptr, int64_t *node,
                        int64_t *dst_off, int32_t *parent, uint32_t *deg, uint8_t *is_query, uint32_t *level);
-void launch_chain_extras(const Launch &L, const GraphDev &g, bool def, const ChainDev &c, uint64_t rows);
-void launch_chain_copy(const Launch &L, const GraphDev &g, bool def, const ChainDev &c, uint64_t rows,
+void launch_chain_extras(const Launch &L, const GraphDev &g, int def, const ChainDev &c, uint64_t rows);
+void launch_chain_copy(const Launch &L, const GraphDev &g, int def, const ChainDev &c, uint64_t rows,
                        const uint32_t *level, uint32_t this_level);
 void launch_scan64(const Launch &L, const unsigned long long *in, int64_t *out, int64_t count, uint64_t *state, uint32_t *ticket);
+// stage 3, fused: one block decodes a tile of rows completely in shared memory (bounded reference chains only)
+size_t tile_smem_bytes();
+int launch_tile(const Launch &L, const GraphDev &g, int def, const RangeDev &r, const TileDev &t, int blocks);
 // byte-swap the uploaded stream into big-endian 64-bit words, in place
 void launch_bswap(const Launch &L, uint64_t *words, uint64_t nwords);
 

@@ -36,8 +36,8 @@ struct RowHead {
 
 // Reads outdegree, reference, block count and sums the blocks; leaves the reader after the last block (at the
 // interval section).  dref = outdegree of the reference row (only used when rf > 0).  BVG:1010-1033.
-template <bool DEF>
-__device__ __forceinline__ void row_head(const GraphDev &g, BitReader &r, uint32_t dref, RowHead &h) {
+template <int DEF, class RD>
+__device__ __forceinline__ void row_head(const GraphDev &g, RD &r, uint32_t dref, RowHead &h) {
 	const uint64_t d = rd_outdegree<DEF>(r, g);
 	h.d = (uint32_t)d;
 	h.rf = 0;
@@ -70,11 +70,13 @@ __device__ __forceinline__ void row_head(const GraphDev &g, BitReader &r, uint32
 	}
 }
 
-// Decodes the interval section and the residuals of row x (reader positioned right after the blocks) and writes
-// the `nextra` merged values, in increasing order, to out[0..nextra).  BVG:1037-1073, 902-954.
-// Warp-synchronous: every lane of `mask` must call it (nextra == 0 for lanes without work).
-template <bool DEF>
-__device__ __forceinline__ void row_extras(const GraphDev &g, BitReader &r, int64_t x, uint32_t nextra, int64_t *out, unsigned mask) {
+// Decodes the interval section and the residuals of row x (reader positioned at the interval count, i.e. right
+// after the blocks) and writes the `nextra` merged values, in increasing order, to out[0..nextra).
+// BVG:1037-1073, 902-954.  Warp-synchronous: every lane of `mask` must call it (nextra == 0: no work).
+// Two loops: a merging one that runs while some lane of the warp still has interval material, then a tight one
+// for pure gap decoding (the kernels sort rows so that most warps never enter the first).
+template <int DEF, class RD>
+__device__ __forceinline__ void row_extras(const GraphDev &g, RD &r, int64_t x, uint32_t nextra, int64_t *out, unsigned mask) {
 	uint32_t ic = 0, nres = nextra;
 	uint64_t int_pos = 0;
 	if (nextra && g.min_interval != 0) {
@@ -91,13 +93,14 @@ __device__ __forceinline__ void row_extras(const GraphDev &g, BitReader &r, int6
 		if (covered > nextra) { raise(g, ERR_DEGREE); ic = 0; nextra = 0; covered = 0; }
 		nres = nextra - (uint32_t)covered;
 	}
-	BitReader ri = r;  // interval cursor; r stays the residual cursor
+	RD ri = r;  // interval cursor; r stays the residual cursor
 	if (ic) ri.seek(int_pos);
 
 	int64_t cur = 0, end = 0;  // current interval [cur, end)
-	int64_t res = 0;           // pending residual, valid iff have_res
+	int64_t res = x;           // last residual decoded; pending (not yet written) iff have_res
 	bool have_res = false, first_res = true, first_int = true;
-	for (uint32_t o = 0; __any_sync(mask, o < nextra); o++) {
+	uint32_t o = 0;
+	for (; __any_sync(mask, o < nextra && (cur != end || ic != 0)); o++) {
 		if (o < nextra) {
 			if (cur == end && ic) {  // next interval (rare: once per interval)
 				const uint64_t gap = ri.gamma();
@@ -119,6 +122,15 @@ __device__ __forceinline__ void row_extras(const GraphDev &g, BitReader &r, int6
 			else have_res = false;
 		}
 	}
+	if (have_res && o < nextra) out[o++] = res;  // a residual decoded above but not written yet
+	for (; __any_sync(mask, o < nextra); o++) {
+		if (o < nextra) {
+			const uint64_t code = rd_residual<DEF>(r, g);
+			res = first_res ? x + nat2int(code) : res + 1 + (int64_t)code;
+			first_res = false;
+			out[o] = res;
+		}
+	}
 	if (nextra && r.past_end()) raise(g, ERR_OVERRUN);
 }
 
@@ -126,8 +138,8 @@ __device__ __forceinline__ void row_extras(const GraphDev &g, BitReader &r, int6
 // last d - ncopied positions hold the extras.  The reader is positioned at the first block.
 // MaskedLongIterator.java:67-100 + MergedLongIterator.java:54-92 of the reference.
 // Warp-synchronous: every lane of `mask` must call it (ncopied == 0 for lanes without work).
-template <bool DEF>
-__device__ __forceinline__ void row_copy(const GraphDev &g, BitReader &r, const int64_t *__restrict__ src, uint32_t dref,
+template <int DEF, class RD>
+__device__ __forceinline__ void row_copy(const GraphDev &g, RD &r, const int64_t *src, uint32_t dref,
                                          int64_t *dst, uint32_t d, uint32_t bc, uint32_t ncopied, unsigned mask) {
 	uint32_t ei = ncopied;  // read index of the waiting extras
 	uint32_t out = 0, k = 0, run = 0, blk = 0, left = ncopied;

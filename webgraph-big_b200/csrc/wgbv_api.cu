@@ -1,6 +1,7 @@
 // wgbv_api.cu -- the C ABI of libwgbv (include/wgbv.h): handles, device memory, and the orchestration of the
 // decode pipeline.  Host code only; the kernels live in bv_kernels.cu.
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -23,7 +24,7 @@ using namespace wgbv;
 struct wgbv_graph {
 	wgbv_props props{};
 	int device = 0;
-	bool def_codes = true;
+	int def_codes = 2;  // 0: codings resolved at run time, 1: default codings, 2: default codings with zeta_k = 3
 	int64_t shard_lo = 0, shard_hi = 0;  // nodes this handle decodes
 	int64_t avail_lo = 0;                // first node whose record is held (shard_lo minus the halo)
 	int64_t halo_nodes = 0;              // window_size * max_ref_count, or -1 if unbounded
@@ -33,6 +34,7 @@ struct wgbv_graph {
 	uint64_t byte0 = 0, byte1 = 0, data_words = 0;  // the byte range of the caller's buffer that is resident
 	EliasFano ef;  // host copy, for accounting
 	int streams = 0;
+	int sm_count = 148;
 };
 
 // A grow-only device buffer.
@@ -68,7 +70,8 @@ struct wgbv_stream {
 	uint64_t *h_pin = nullptr;  // pinned host scratch for read-backs (16 words)
 	uint64_t launches = 0;
 	DevBuf deg, ref, depth, rp, scan_state, ticket, halo, levels, list, col, rowptr, ids, batch;
-	DevBuf heavy_rows, heavy_sorted, heavy_cls, heavy_counters;
+	DevBuf heavy_rows, heavy_sorted, heavy_cls, heavy_counters, tile_scratch, level_pos;
+	bool force_levels = true;   // false: use the fused tile kernel where it applies (WGBV_TILE=1)
 	DevBuf c_node, c_dst, c_parent, c_deg, c_isq, c_level, c_len, c_arcs, c_row0, c_soff, c_store;
 	cudaEvent_t ev[6]{};
 	bool ev_valid = false;
@@ -136,9 +139,11 @@ static int build_graph(const wgbv_props *props, const uint8_t *graph, uint64_t g
 	if (!g) return fail(WGBV_EARG, "out of host memory");
 	g->props = *props;
 	g->device = device;
-	g->def_codes = props->outdegree_coding == WGBV_GAMMA && props->block_coding == WGBV_GAMMA && props->residual_coding == WGBV_ZETA &&
-	               props->reference_coding == WGBV_UNARY && props->block_count_coding == WGBV_GAMMA;
+	const bool defaults = props->outdegree_coding == WGBV_GAMMA && props->block_coding == WGBV_GAMMA && props->residual_coding == WGBV_ZETA &&
+	                      props->reference_coding == WGBV_UNARY && props->block_count_coding == WGBV_GAMMA;
+	g->def_codes = defaults ? (props->zeta_k == 3 ? 2 : 1) : 0;
 	g->halo_nodes = halo_nodes;
+	cudaDeviceGetAttribute(&g->sm_count, cudaDevAttrMultiProcessorCount, device);
 	g->shard_lo = shard_lo;
 	g->shard_hi = shard_hi;
 	g->avail_lo = avail_lo;
@@ -326,6 +331,11 @@ extern "C" int wgbv_stream_create(wgbv_graph *g, void *cuda_stream, wgbv_stream 
 	for (auto &e : s->ev) cudaEventCreate(&e);
 	s->dev = g->dev;
 	s->dev.err = s->d_err;
+	// WGBV_TILE=1 selects the fused tile kernel (bv_tile.cu) for graphs with bounded reference chains.  It moves the
+	// algorithmic minimum of bytes but, as measured on B200 (profiles/), its block-wide barriers make it slower than
+	// the level-synchronous kernels on graphs with long rows, so it is opt-in for now.
+	const char *tl = getenv("WGBV_TILE");
+	s->force_levels = !(tl && tl[0] == '1');
 	g->streams++;
 	*out = s;
 	return WGBV_OK;
@@ -336,7 +346,7 @@ extern "C" void wgbv_stream_destroy(wgbv_stream *s) {
 	cudaSetDevice(s->g->device);
 	if (s->stream) cudaStreamSynchronize(s->stream);
 	for (DevBuf *b : {&s->deg, &s->ref, &s->depth, &s->rp, &s->scan_state, &s->ticket, &s->halo, &s->levels, &s->list, &s->col,
-	                  &s->rowptr, &s->ids, &s->batch, &s->heavy_rows, &s->heavy_sorted, &s->heavy_cls, &s->heavy_counters, &s->c_node, &s->c_dst, &s->c_parent, &s->c_deg, &s->c_isq, &s->c_level,
+	                  &s->rowptr, &s->ids, &s->batch, &s->heavy_rows, &s->heavy_sorted, &s->heavy_cls, &s->heavy_counters, &s->tile_scratch, &s->level_pos, &s->c_node, &s->c_dst, &s->c_parent, &s->c_deg, &s->c_isq, &s->c_level,
 	                  &s->c_len, &s->c_arcs, &s->c_row0, &s->c_soff, &s->c_store})
 		b->release();
 	if (s->d_err) cudaFree(s->d_err);
@@ -393,12 +403,32 @@ struct Prepared {
 	int64_t lo = 0, cnt = 0, halo_n = 0;
 	int64_t halo_arcs = 0, arcs = 0;
 	uint32_t max_depth = 0;
+	bool have_depth = false;
 	const int64_t *rp = nullptr;
 };
 
 // Stages 1, 2 and 2b for [from, to): degrees, row pointers and depth levels.  Leaves the row pointers of
 // [lo, to) in s->rp and writes those of [from, to) to d_rowptr.  Synchronises once to learn the arc counts.
-static int prepare(wgbv_stream *s, int64_t from, int64_t to, int64_t *d_rowptr, bool want_depth, Prepared &P) {
+// Stage 2b: reference-chain depth of every row of the prepared range (only the level-synchronous path needs it).
+static int compute_depth(wgbv_stream *s, int64_t from, Prepared &P) {
+	const Launch L = s->launch();
+	int rc;
+	if ((rc = s->depth.ensure((size_t)std::max<int64_t>(P.cnt, 1) * 4))) return rc;
+	uint32_t *hs = (uint32_t *)(s->h_pin + 4);
+	for (int pass = 0;; pass++) {
+		CU(cudaMemsetAsync(s->d_stats, 0, 8, s->stream));
+		launch_depth(L, s->dev, s->ref.as<uint8_t>(), s->depth.as<uint32_t>(), P.lo, from, P.cnt, pass == 0, s->d_stats);
+		CU(cudaMemcpyAsync(hs, s->d_stats, 8, cudaMemcpyDeviceToHost, s->stream));
+		CU(cudaStreamSynchronize(s->stream));
+		if (hs[0] == 0) break;
+		if (pass > (1 << 26)) return fail(WGBV_ESTATE, "reference chains do not resolve");
+	}
+	P.max_depth = hs[1];
+	P.have_depth = true;
+	return WGBV_OK;
+}
+
+static int prepare(wgbv_stream *s, int64_t from, int64_t to, int64_t *d_rowptr, Prepared &P) {
 	wgbv_graph *g = s->g;
 	const Launch L = s->launch();
 	P.lo = halo_start(g, from);
@@ -410,7 +440,6 @@ static int prepare(wgbv_stream *s, int64_t from, int64_t to, int64_t *d_rowptr, 
 	if ((rc = s->deg.ensure(c * 4)) || (rc = s->ref.ensure(c)) || (rc = s->rp.ensure((c + 1) * 8)) ||
 	    (rc = s->scan_state.ensure(((c + 1) / 2048 + 2) * 8)) || (rc = s->ticket.ensure(64)))
 		return rc;
-	if (want_depth && (rc = s->depth.ensure(c * 4))) return rc;
 	cudaEventRecord(s->ev[0], s->stream);
 	launch_header(L, s->dev, g->def_codes, P.lo, P.cnt, s->deg.as<uint32_t>(), s->ref.as<uint8_t>());
 	cudaEventRecord(s->ev[1], s->stream);
@@ -419,26 +448,9 @@ static int prepare(wgbv_stream *s, int64_t from, int64_t to, int64_t *d_rowptr, 
 	if (rp != d_rowptr && d_rowptr) launch_emit_rowptr(L, rp, P.halo_n, to - from, d_rowptr);
 	P.rp = rp;
 	cudaEventRecord(s->ev[2], s->stream);
-	uint32_t *hs = (uint32_t *)(s->h_pin + 4);
-	if (want_depth) {
-		for (int pass = 0;; pass++) {
-			CU(cudaMemsetAsync(s->d_stats, 0, 8, s->stream));
-			launch_depth(L, s->dev, s->ref.as<uint8_t>(), s->depth.as<uint32_t>(), P.lo, from, P.cnt, pass == 0, s->d_stats);
-			CU(cudaMemcpyAsync(hs, s->d_stats, 8, cudaMemcpyDeviceToHost, s->stream));
-			if (pass == 0) {
-				CU(cudaMemcpyAsync(s->h_pin, rp + P.halo_n, 8, cudaMemcpyDeviceToHost, s->stream));
-				CU(cudaMemcpyAsync(s->h_pin + 1, rp + P.cnt, 8, cudaMemcpyDeviceToHost, s->stream));
-			}
-			CU(cudaStreamSynchronize(s->stream));
-			if (hs[0] == 0) break;
-			if (pass > (1 << 26)) return fail(WGBV_ESTATE, "reference chains do not resolve");
-		}
-		P.max_depth = hs[1];
-	} else {
-		CU(cudaMemcpyAsync(s->h_pin, rp + P.halo_n, 8, cudaMemcpyDeviceToHost, s->stream));
-		CU(cudaMemcpyAsync(s->h_pin + 1, rp + P.cnt, 8, cudaMemcpyDeviceToHost, s->stream));
-		CU(cudaStreamSynchronize(s->stream));
-	}
+	CU(cudaMemcpyAsync(s->h_pin, rp + P.halo_n, 8, cudaMemcpyDeviceToHost, s->stream));
+	CU(cudaMemcpyAsync(s->h_pin + 1, rp + P.cnt, 8, cudaMemcpyDeviceToHost, s->stream));
+	CU(cudaStreamSynchronize(s->stream));
 	P.halo_arcs = (int64_t)s->h_pin[0];
 	P.arcs = (int64_t)s->h_pin[1] - P.halo_arcs;
 	cudaEventRecord(s->ev[3], s->stream);
@@ -469,12 +481,11 @@ extern "C" int wgbv_decode_degrees(wgbv_stream *s, int64_t from, int64_t to, int
 }
 
 // Stage 3 on a prepared range.
-static int decode_rows(wgbv_stream *s, int64_t from, int64_t to, const Prepared &P, int64_t *d_col, uint64_t col_capacity) {
+static int decode_rows(wgbv_stream *s, int64_t from, int64_t to, Prepared &P, int64_t *d_col, uint64_t col_capacity) {
 	wgbv_graph *g = s->g;
 	const Launch L = s->launch();
 	int rc;
 	if ((uint64_t)P.arcs > col_capacity) return fail(WGBV_EARG, "col_capacity (%llu) is smaller than the %lld arcs of [%lld, %lld)", (unsigned long long)col_capacity, (long long)P.arcs, (long long)from, (long long)to);
-	if ((rc = s->halo.ensure((size_t)std::max<int64_t>(P.halo_arcs, 1) * 8))) return rc;
 	RangeDev R;
 	R.lo = P.lo;
 	R.from = from;
@@ -486,6 +497,29 @@ static int decode_rows(wgbv_stream *s, int64_t from, int64_t to, const Prepared 
 	R.col = d_col;
 	R.halo = s->halo.as<int64_t>();
 	R.col_capacity = col_capacity;
+	// Bounded reference chains: the fused tile kernel decodes everything on chip in one launch.  The
+	// level-synchronous kernels below remain the general path (unbounded chains, tiles that fit nowhere).
+	if (g->halo_nodes >= 0 && g->halo_nodes <= TILE_MAX_HALO && !s->force_levels) {
+		TileDev T;
+		const int blocks = g->sm_count * 3;
+		T.scratch_cap = 1u << 16;
+		if ((rc = s->tile_scratch.ensure((size_t)blocks * T.scratch_cap * 8))) return rc;
+		T.scratch = s->tile_scratch.as<int64_t>();
+		T.halo = (int32_t)g->halo_nodes;
+		T.fallback = s->d_err + 2;
+		CU(cudaMemsetAsync(T.fallback, 0, 4, s->stream));
+		if (launch_tile(L, s->dev, g->def_codes, R, T, blocks)) return fail(WGBV_ECUDA, "launch of the tile kernel failed: %s", cudaGetErrorString(cudaGetLastError()));
+		uint32_t *hf = (uint32_t *)(s->h_pin + 9);
+		CU(cudaMemcpyAsync(hf, T.fallback, 4, cudaMemcpyDeviceToHost, s->stream));
+		cudaEventRecord(s->ev[4], s->stream);
+		s->ev_valid = true;
+		CU(cudaStreamSynchronize(s->stream));
+		if (!*hf) return WGBV_OK;
+	}
+	if (!P.have_depth && (rc = compute_depth(s, from, P))) return rc;
+	if ((rc = s->halo.ensure((size_t)std::max<int64_t>(P.halo_arcs, 1) * 8))) return rc;
+	R.depth = s->depth.as<uint32_t>();
+	R.halo = s->halo.as<int64_t>();
 	// rows with >= 64 extras go through a global, class-sorted list: at most total_arcs / 64 of them
 	HeavyDev H;
 	const size_t hcap = (size_t)((P.arcs + P.halo_arcs) / 64 + 1);
@@ -497,8 +531,23 @@ static int decode_rows(wgbv_stream *s, int64_t from, int64_t to, const Prepared 
 	H.cls = s->heavy_cls.as<uint8_t>();
 	H.counters = s->heavy_counters.as<unsigned long long>();
 	launch_extras(L, s->dev, g->def_codes, R, H);
-	if (P.max_depth <= 8) {
-		for (uint32_t lev = 1; lev <= P.max_depth; lev++) launch_copy_level(L, s->dev, g->def_codes, R, lev, nullptr, 0);
+	if (P.max_depth == 0) {
+	} else if (P.max_depth <= 8) {
+		// shallow chains: ordered lists of the rows of every level
+		const uint32_t nlev = P.max_depth;
+		const size_t nblocks = (size_t)((P.cnt + 2047) / 2048);
+		if ((rc = s->levels.ensure(nlev * nblocks * 4)) || (rc = s->level_pos.ensure((nlev * nblocks + 1) * 8)) ||
+		    (rc = s->list.ensure((size_t)std::max<int64_t>(P.cnt, 1) * 4)) || (rc = s->scan_state.ensure(((nlev * nblocks + 1) / 2048 + 2) * 8)))
+			return rc;
+		launch_level_lists(L, R.depth, P.cnt, nlev, s->levels.as<uint32_t>(), s->level_pos.as<int64_t>(), s->list.as<uint32_t>(),
+		                   s->scan_state.as<uint64_t>(), s->ticket.as<uint32_t>());
+		int64_t bounds[9];
+		for (uint32_t l = 0; l <= nlev; l++)
+			CU(cudaMemcpyAsync(&bounds[l], s->level_pos.as<int64_t>() + (size_t)l * nblocks, 8, cudaMemcpyDeviceToHost, s->stream));
+		CU(cudaStreamSynchronize(s->stream));
+		for (uint32_t lev = 1; lev <= nlev; lev++)
+			if (bounds[lev] > bounds[lev - 1])
+				launch_copy_level(L, s->dev, g->def_codes, R, lev, s->list.as<uint32_t>() + bounds[lev - 1], (uint64_t)(bounds[lev] - bounds[lev - 1]));
 	} else {
 		// deep chains: one compacted list of rows per level
 		const uint32_t nlev = P.max_depth + 1;
@@ -532,7 +581,7 @@ extern "C" int wgbv_decode_csr(wgbv_stream *s, int64_t from, int64_t to, int64_t
 	int rc = check_range(s->g, from, to);
 	if (rc) return rc;
 	Prepared P;
-	if ((rc = prepare(s, from, to, d_rowptr, true, P))) return rc;
+	if ((rc = prepare(s, from, to, d_rowptr, P))) return rc;
 	return decode_rows(s, from, to, P, d_col, col_capacity);
 }
 
@@ -556,7 +605,7 @@ extern "C" int wgbv_decode_csr_host(wgbv_stream *s, int64_t from, int64_t to, in
 	const int64_t cnt = to - from;
 	if ((rc = s->rowptr.ensure((size_t)(cnt + 1) * 8))) return rc;
 	Prepared P;
-	if ((rc = prepare(s, from, to, s->rowptr.as<int64_t>(), h_col != nullptr, P))) return rc;
+	if ((rc = prepare(s, from, to, s->rowptr.as<int64_t>(), P))) return rc;
 	if (arcs_out) *arcs_out = P.arcs;
 	CU(cudaMemcpyAsync(h_rowptr, s->rowptr.as<int64_t>(), (size_t)(cnt + 1) * 8, cudaMemcpyDeviceToHost, s->stream));
 	if (h_col) {
