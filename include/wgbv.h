@@ -189,6 +189,33 @@ WGBV_API int wgbv_successors_batch_host(wgbv_stream *s, const int64_t *h_ids, ui
 WGBV_API int wgbv_csr_checksum(wgbv_stream *s, int64_t first_node, int64_t rows, const int64_t *d_rowptr, const int64_t *d_col,
                       uint64_t *checksum_out);
 
+/*
+ * Row pointers from outdegrees with NO allocation.  (This entry point has no counterpart in the reference: the
+ * Java code never has to think about where a prefix sum keeps its scratch.)
+ *
+ * d_rowptr[i] = d_degrees[0] + ... + d_degrees[i-1] for i = 0..count (count + 1 int64 values), computed on the
+ * CURRENT device by the same single-pass prefix-sum kernel design as wgbv_decode_degrees, except that its
+ * tile-status table lives in a file-scope __device__ array inside the library instead of cudaMalloc'ed memory.
+ * It is meant for callers that own their input and output buffers but cannot call the allocator when they need the
+ * row pointers: processes whose device memory is entirely held by another component's pool, and latency-critical
+ * threads that must not trigger the device-wide synchronisation cudaMalloc / cudaFree may cause.  The function
+ * calls neither of them, nor any library routine that allocates.
+ *
+ *   - Limit: count <= WGBV_STATIC_SCAN_MAX_COUNT (about 134 million degrees); larger inputs fail with WGBV_EARG.
+ *     The static array is 8 * (WGBV_STATIC_SCAN_TILES + 32) bytes (about 513 KiB); every GPU on which the library
+ *     is loaded keeps it until the process exits.
+ *   - The first call on each device looks up the device address of that array (cudaGetSymbolAddress); make this
+ *     first call before starting any stream capture on that device.
+ *   - All calls on a device share the array, which keeps the contents of the previous call; every call clears the
+ *     words it uses first.  Calls whose kernels could overlap on the GPU (different streams without ordering) race
+ *     on it: order them.
+ *   - d_degrees and d_rowptr are device pointers on the current device; the work is queued on cuda_stream
+ *     (a cudaStream_t, NULL for the default stream) and is asynchronous.
+ */
+#define WGBV_STATIC_SCAN_TILES 65536
+#define WGBV_STATIC_SCAN_MAX_COUNT ((int64_t)WGBV_STATIC_SCAN_TILES * 2048 - 1)
+WGBV_API int wgbv_scan_degrees_static(const uint32_t *d_degrees, int64_t count, int64_t *d_rowptr, void *cuda_stream);
+
 /* Timing of the stages of the last wgbv_decode_csr on this stream, in milliseconds (CUDA events on the stream):
  * out[0] header pass, [1] scan, [2] depth levels, [3] successor decode, [4] total.  Synchronises the stream. */
 WGBV_API int wgbv_last_stage_ms(wgbv_stream *s, float out[5]);

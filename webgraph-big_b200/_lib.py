@@ -72,6 +72,7 @@ SYMBOLS = [
     ("wgbv_successors_batch", C.c_int, [_P, _P, C.c_uint64, _P, _P, C.c_uint64]),
     ("wgbv_successors_batch_host", C.c_int, [_P, _P, C.c_uint64, _P, _P, C.c_uint64, C.POINTER(C.c_int64)]),
     ("wgbv_csr_checksum", C.c_int, [_P, C.c_int64, C.c_int64, _P, _P, C.POINTER(C.c_uint64)]),
+    ("wgbv_scan_degrees_static", C.c_int, [_P, C.c_int64, _P, _P]),
     ("wgbv_last_stage_ms", C.c_int, [_P, C.POINTER(C.c_float * 5)]),
     ("wgbv_kernel_launches", C.c_uint64, [_P]),
     ("wgbv_algorithmic_bytes", C.c_uint64, [_P, C.c_int64, C.c_int64, C.c_int64]),
