@@ -99,6 +99,13 @@ WGBV_API int wgbv_open(const char *basename, int device, int shard_index, int sh
 WGBV_API int wgbv_open_mem(const wgbv_props *props, const uint8_t *graph, uint64_t graph_bytes, const uint8_t *offsets,
                   uint64_t offsets_bytes, int device, int shard_index, int shard_count, wgbv_graph **out);
 
+/* The shard plan wgbv_open uses, without touching a device (host only): bounds_out[k] is the first node of shard k,
+ * bounds_out[shard_count] = nodes; shards are contiguous and balanced by compressed bits (the arc-balancing idea of
+ * algo/EliasFanoCumulativeOutdegreeList.java:139-151 applied to bit offsets).  *halo_out = window_size *
+ * max_ref_count, the number of predecessor nodes every shard keeps (cf. the window pre-fill, BVG:1139-1143). */
+WGBV_API int wgbv_plan_shards(const wgbv_props *props, const uint8_t *offsets, uint64_t offsets_bytes, int shard_count,
+                              int64_t *bounds_out, int64_t *halo_out);
+
 /*
  * Opening from a pre-cut slice, for callers that read only their own byte range of a large file (one process per
  * GPU, each holding one shard).  `bits` is a piece of the .graph bit stream and `offsets` a gamma/delta coded stream

@@ -52,6 +52,7 @@ SYMBOLS = [
     ("wgbv_parse_properties", C.c_int, [C.c_char_p, C.POINTER(Props)]),
     ("wgbv_open", C.c_int, [C.c_char_p, C.c_int, C.c_int, C.c_int, C.POINTER(_P)]),
     ("wgbv_open_mem", C.c_int, [C.POINTER(Props), _P, C.c_uint64, _P, C.c_uint64, C.c_int, C.c_int, C.c_int, C.POINTER(_P)]),
+    ("wgbv_plan_shards", C.c_int, [C.POINTER(Props), _P, C.c_uint64, C.c_int, _P, C.POINTER(C.c_int64)]),
     ("wgbv_open_slice", C.c_int, [C.POINTER(Props), C.c_int64, C.c_int64, C.c_int64, _P, C.c_uint64, _P, C.c_uint64, C.c_int, C.POINTER(_P)]),
     ("wgbv_upload_stream", C.c_int, [_P, _P, C.c_uint64]),
     ("wgbv_close", None, [_P]),

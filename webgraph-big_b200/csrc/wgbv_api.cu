@@ -238,6 +238,24 @@ extern "C" int wgbv_open_mem(const wgbv_props *props, const uint8_t *graph, uint
 	return build_graph(props, graph, graph_bytes, off, 0, avail_lo, lo, hi, halo, device, out);
 }
 
+extern "C" int wgbv_plan_shards(const wgbv_props *props, const uint8_t *offsets, uint64_t offsets_bytes, int shard_count,
+                                int64_t *bounds_out, int64_t *halo_out) {
+	clear_error();
+	if (!props || !offsets || !bounds_out) return fail(WGBV_EARG, "null argument");
+	if (shard_count < 1) return fail(WGBV_EARG, "bad shard count %d", shard_count);
+	std::vector<uint64_t> off;
+	int rc;
+	if ((rc = decode_offsets(*props, offsets, offsets_bytes, props->nodes + 1, off))) return rc;
+	const int64_t halo = halo_of(props);
+	if (halo < 0 && shard_count > 1)
+		return fail(WGBV_EUNSUPPORTED, "maxrefcount=%d makes reference chains unbounded: the graph cannot be sharded", props->max_ref_count);
+	std::vector<int64_t> bounds;
+	plan_shards(off, shard_count, bounds);
+	for (int k = 0; k <= shard_count; k++) bounds_out[k] = bounds[(size_t)k];
+	if (halo_out) *halo_out = halo;
+	return WGBV_OK;
+}
+
 extern "C" int wgbv_open_slice(const wgbv_props *props, int64_t first_node, int64_t node_count, int64_t halo_nodes,
                                const uint8_t *bits, uint64_t nbytes, const uint8_t *offsets, uint64_t offsets_bytes, int device,
                                wgbv_graph **out) {

@@ -1,0 +1,182 @@
+// wgbv.hpp -- header-only C++ host mirror of webgraph-big's ImmutableGraph API over the C ABI of libwgbv.
+//
+// Same method names, argument meaning and error behaviour as the reference's Java classes
+// (ImmutableGraph.java:201-447, NodeIterator.java:34-133, LazyLongIterator.java:28-43, BVGraph.java:821-1265),
+// with the reference's exceptions as C++ exception types.  Link with -lwgbv; no CUDA headers are needed.
+#pragma once
+#include <cstdint>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <utility>
+#include <vector>
+
+#include "../../include/wgbv.h"
+
+namespace wgbv {
+
+struct IllegalArgumentException : std::invalid_argument { using std::invalid_argument::invalid_argument; };
+struct IllegalStateException : std::logic_error { using std::logic_error::logic_error; };
+struct IOException : std::runtime_error { using std::runtime_error::runtime_error; };
+struct UnsupportedOperationException : std::logic_error { using std::logic_error::logic_error; };
+struct NoSuchElementException : std::out_of_range { using std::out_of_range::out_of_range; };
+struct CudaError : std::runtime_error { using std::runtime_error::runtime_error; };
+
+inline void check(int rc) {
+	if (rc == WGBV_OK) return;
+	const std::string msg = wgbv_last_error();
+	switch (rc) {
+	case WGBV_EINDEX:
+	case WGBV_EARG: throw IllegalArgumentException(msg);
+	case WGBV_ESTATE: throw IllegalStateException(msg);
+	case WGBV_EIO: throw IOException(msg);
+	case WGBV_EUNSUPPORTED: throw UnsupportedOperationException(msg);
+	default: throw CudaError(msg);
+	}
+}
+
+// LazyLongIterator.java:28-43: nextLong() returns -1 when the list is exhausted.
+class LazyLongIterator {
+	const int64_t *p_, *end_;
+	std::shared_ptr<const std::vector<int64_t>> keep_;
+
+public:
+	LazyLongIterator(const int64_t *b, const int64_t *e, std::shared_ptr<const std::vector<int64_t>> keep = nullptr)
+	    : p_(b), end_(e), keep_(std::move(keep)) {}
+	int64_t nextLong() { return p_ == end_ ? -1 : *p_++; }
+	int64_t skip(int64_t n) {
+		const int64_t k = n < end_ - p_ ? n : end_ - p_;
+		p_ += k;
+		return k;
+	}
+};
+
+class Graph;
+
+// BVGraphNodeIterator (BVGraph.java:1100-1245) served from chunked bulk decodes on the GPU.
+class NodeIterator {
+	friend class Graph;
+	std::shared_ptr<Graph> g_;
+	int64_t from_, curr_, limit_, c0_ = 0, c1_ = 0;
+	std::vector<int64_t> rowptr_, col_;
+	NodeIterator(std::shared_ptr<Graph> g, int64_t from, int64_t upper);
+
+public:
+	static constexpr int64_t CHUNK_NODES = 1 << 18;
+	bool hasNext() const { return curr_ < limit_; }
+	int64_t nextLong();
+	int64_t outdegree() const {
+		if (curr_ == from_ - 1) throw IllegalStateException("nextLong() has not been called");  // BVGraph.java:1207
+		return rowptr_[curr_ - c0_ + 1] - rowptr_[curr_ - c0_];
+	}
+	// valid until the next nextLong(), like the reference's window slot (BVGraph.java:1171-1172)
+	std::pair<const int64_t *, int64_t> successorArray() const {
+		const int64_t d = outdegree();
+		return {col_.data() + rowptr_[curr_ - c0_], d};
+	}
+	LazyLongIterator successors() const {
+		auto a = successorArray();
+		return LazyLongIterator(a.first, a.first + a.second);
+	}
+	int64_t skip(int64_t n) {
+		if (n < 0) throw IllegalArgumentException("Argument must be nonnegative");
+		int64_t k = 0;
+		while (k < n && hasNext()) { nextLong(); k++; }
+		return k;
+	}
+	NodeIterator copy(int64_t upperBound) const;  // BVGraph.java:1223-1229
+};
+
+// A BVGraph decoded on the GPU: the sibling of it.unimi.dsi.big.webgraph.BVGraph.
+class Graph : public std::enable_shared_from_this<Graph> {
+	struct Shared {
+		wgbv_graph *h = nullptr;
+		std::string basename;
+		~Shared() { if (h) wgbv_close(h); }
+	};
+	std::shared_ptr<Shared> sh_;
+	wgbv_stream *st_ = nullptr;
+	explicit Graph(std::shared_ptr<Shared> sh) : sh_(std::move(sh)) { check(wgbv_stream_create(sh_->h, nullptr, &st_)); }
+
+public:
+	Graph(const Graph &) = delete;
+	Graph &operator=(const Graph &) = delete;
+	~Graph() { if (st_) wgbv_stream_destroy(st_); }
+
+	// BVGraph.load(basename), BVGraph.java:1345-1383
+	static std::shared_ptr<Graph> load(const std::string &basename, int device = 0, int shard_index = 0, int shard_count = 1) {
+		auto sh = std::make_shared<Shared>();
+		sh->basename = basename;
+		check(wgbv_open(basename.c_str(), device, shard_index, shard_count, &sh->h));
+		return std::shared_ptr<Graph>(new Graph(sh));
+	}
+	int64_t numNodes() const { return wgbv_num_nodes(sh_->h); }
+	int64_t numArcs() const { return wgbv_num_arcs(sh_->h); }
+	bool randomAccess() const { return true; }
+	bool hasCopiableIterators() const { return true; }
+	const std::string &basename() const { return sh_->basename; }
+	// flyweight copy: shares the device-resident graph, owns its stream (ImmutableGraph.java:187-197, :447)
+	std::shared_ptr<Graph> copy() const { return std::shared_ptr<Graph>(new Graph(sh_)); }
+
+	int64_t outdegree(int64_t x) {  // BVGraph.java:821-842
+		int64_t d = 0;
+		check(wgbv_outdegrees(st_, &x, 1, &d));
+		return d;
+	}
+	// batched random access: (rowptr[k+1], col)
+	std::pair<std::vector<int64_t>, std::vector<int64_t>> successorsBatch(const std::vector<int64_t> &ids) {
+		std::vector<int64_t> rp(ids.size() + 1), col;
+		int64_t arcs = 0;
+		check(wgbv_successors_batch_host(st_, ids.data(), ids.size(), rp.data(), nullptr, 0, &arcs));
+		col.resize((size_t)arcs);
+		check(wgbv_successors_batch_host(st_, ids.data(), ids.size(), rp.data(), col.data(), col.size(), &arcs));
+		return {std::move(rp), std::move(col)};
+	}
+	std::vector<int64_t> successorArray(int64_t x) { return successorsBatch({x}).second; }  // ImmutableGraph.java:329-333
+	LazyLongIterator successors(int64_t x) {                                                 // BVGraph.java:860-867
+		auto v = std::make_shared<const std::vector<int64_t>>(successorArray(x));
+		return LazyLongIterator(v->data(), v->data() + v->size(), v);
+	}
+	// the bulk call: CSR of [from, to) in host vectors
+	std::pair<std::vector<int64_t>, std::vector<int64_t>> decodeToCSR(int64_t from, int64_t to) {
+		std::vector<int64_t> rp((size_t)(to > from ? to - from : 0) + 1), col;
+		int64_t arcs = 0;
+		check(wgbv_decode_csr_host(st_, from, to, rp.data(), nullptr, 0, &arcs));
+		col.resize((size_t)arcs);
+		check(wgbv_decode_csr_host(st_, from, to, rp.data(), col.data(), col.size(), &arcs));
+		return {std::move(rp), std::move(col)};
+	}
+	NodeIterator nodeIterator(int64_t from = 0) {  // BVGraph.java:1257
+		if (from < 0 || from > numNodes()) throw IllegalArgumentException("Node index out of range: " + std::to_string(from));
+		return NodeIterator(shared_from_this(), from, numNodes());
+	}
+	// ImmutableGraph.java:405-436: contiguous ranges of ceil(n / howMany) nodes
+	std::vector<NodeIterator> splitNodeIterators(int howMany) {
+		if (howMany < 1) throw IllegalArgumentException("howMany < 1");
+		const int64_t n = numNodes(), m = (n + howMany - 1) / howMany;
+		std::vector<NodeIterator> res;
+		for (int64_t f = 0; f < n; f += m) res.push_back(NodeIterator(copy(), f, f + m < n ? f + m : n));
+		while ((int)res.size() < howMany) res.push_back(NodeIterator(shared_from_this(), n, n));
+		return res;
+	}
+	wgbv_stream *stream() const { return st_; }
+};
+
+inline NodeIterator::NodeIterator(std::shared_ptr<Graph> g, int64_t from, int64_t upper)
+    : g_(std::move(g)), from_(from), curr_(from - 1), limit_((upper < g_->numNodes() ? upper : g_->numNodes()) - 1), c0_(from), c1_(from) {}
+
+inline int64_t NodeIterator::nextLong() {
+	if (!hasNext()) throw NoSuchElementException("no more nodes");  // BVGraph.java:1165
+	if (++curr_ >= c1_) {
+		c0_ = curr_;
+		c1_ = c0_ + CHUNK_NODES < limit_ + 1 ? c0_ + CHUNK_NODES : limit_ + 1;
+		auto csr = g_->decodeToCSR(c0_, c1_);
+		rowptr_ = std::move(csr.first);
+		col_ = std::move(csr.second);
+	}
+	return curr_;
+}
+
+inline NodeIterator NodeIterator::copy(int64_t upperBound) const { return NodeIterator(g_->copy(), curr_ + 1, upperBound); }
+
+}  // namespace wgbv
