@@ -61,6 +61,7 @@ __device__ __forceinline__ void raise(const GraphDev &g, uint32_t bit) { atomicO
 // that the same decoder runs on a tile of the stream staged in shared memory.
 template <bool LDG>
 struct BitReaderT {
+	static constexpr bool IS_GLOBAL = LDG;
 	const uint32_t *base;  // address of the word the last seek() started from
 	uint64_t j0;    // stream index of that word
 	uint32_t lim;   // words that may be loaded from base (saturated)
@@ -72,9 +73,9 @@ struct BitReaderT {
 	// The word after next is loaded with one refill of lead time only (the compiler waits for it at the head of the
 	// decoding loop), so a miss there costs a full DRAM round trip per lane.  Every 8 words (one 32-byte sector) the
 	// reader therefore asks for the sector PF_AHEAD words further on; the request carries no register, hence no wait.
-	static constexpr uint32_t PF_AHEAD = 64;
+	static constexpr uint32_t PF_AHEAD = 16;
 	__device__ __forceinline__ void prefetch(uint32_t i) const {
-		if (LDG && (i & 7u) == 0 && i + PF_AHEAD < lim) asm volatile("prefetch.global.L2 [%0];" ::"l"(base + i + PF_AHEAD));
+		if (LDG && (i & 7u) == 0 && i + PF_AHEAD < lim) asm volatile("prefetch.global.L1 [%0];" ::"l"(base + i + PF_AHEAD));
 	}
 
 	// positions the reader on an arbitrary word array (e.g. a staged tile): `words` holds `nwords` 32-bit words

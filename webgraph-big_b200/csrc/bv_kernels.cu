@@ -339,33 +339,45 @@ static constexpr int TILE = TPB * RPT;   // rows per block: the sort domain (see
 // one class.
 static constexpr uint32_t HEAVY = 64;
 
-// stage 3a: one block per TILE nodes.  Rows without a reference come out complete.
-template <int DEF>
-__global__ void __launch_bounds__(TPB) k_extras(GraphDev g, RangeDev R, HeavyDev H) {
-	__shared__ uint64_t s_pos[TILE];
-	__shared__ uint32_t s_nextra[TILE], s_ncopied[TILE];
-	__shared__ uint32_t s_hist[NBUCKETS + 1];
-	__shared__ uint16_t s_order[TILE];
-	__shared__ uint32_t s_count[BIN_CLASSES];
-	__shared__ uint8_t s_cls[TILE];
-	__shared__ unsigned long long s_gbase;
-	const int64_t base = (int64_t)blockIdx.x * TILE;
-	const int64_t count = R.hi - R.lo;
-	const int64_t rp_from = R.rp[R.from - R.lo];
-	// the records of the tile's rows are contiguous in the bit stream: ask for all of it up front
-	{
-		__shared__ uint64_t s_span[2];
-		if (threadIdx.x == 0) s_span[0] = ef_get(g, R.lo + base);
-		if (threadIdx.x == 32) s_span[1] = ef_get(g, R.lo + (base + TILE < count ? base + TILE : count));
-		__syncthreads();
-		const char *p0 = (const char *)g.words + ((s_span[0] >> 3) & ~127ull);
-		const char *p1 = (const char *)g.words + (s_span[1] >> 3);
-		for (const char *p = p0 + (size_t)threadIdx.x * 128; p < p1; p += (size_t)TPB * 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
-	}
+// stage 3a: one block per ETILE consecutive nodes.  Rows without a reference come out complete.
+// The records of consecutive rows are contiguous in the bit stream, so the block first copies the tile's whole span
+// into shared memory with coalesced loads (STAGED) and every decoder of the block then reads words with ~30-cycle
+// shared-memory latency instead of waiting for L2/DRAM at every word boundary of every lane; a tile whose span does
+// not fit (a very long row in it) reads global memory instead.
+static constexpr int ERPT = 4;
+static constexpr int ETILE = TPB * ERPT;
+static constexpr int EBITS = 9216;  // 32-bit words of the stream a tile may stage (36 KiB)
+
+struct ExtrasSmem {
+	uint32_t bits[EBITS];
+	uint64_t pos[ETILE];
+	uint32_t nextra[ETILE], ncopied[ETILE];
+	uint32_t hist[NBUCKETS + 1];
+	uint32_t count[BIN_CLASSES];
+	uint16_t order[ETILE];
+	uint8_t cls[ETILE];
+	unsigned long long gbase;
+	uint64_t span[2];
+	uint64_t wbase;  // stream word index of bits[0]
+	uint32_t nw;     // words staged
+};
+
+template <class RD>
+__device__ __forceinline__ void tile_reader(RD &r, const GraphDev &g, const ExtrasSmem &S, uint64_t pos);
+template <>
+__device__ __forceinline__ void tile_reader<BitReader>(BitReader &r, const GraphDev &g, const ExtrasSmem &, uint64_t pos) { r.init(g, pos); }
+template <>
+__device__ __forceinline__ void tile_reader<TileReader>(TileReader &r, const GraphDev &, const ExtrasSmem &S, uint64_t pos) {
+	r.init_words(S.bits, S.nw, (uint32_t)(pos - (S.wbase << 5)));
+}
+
+template <int DEF, class RD>
+__device__ __forceinline__ void extras_tile(const GraphDev &g, const RangeDev &R, const HeavyDev &H, ExtrasSmem &S, int64_t base, int64_t count,
+                                            int64_t rp_from) {
 	// heads of my rows (uniform loop: the warp reconverges at the end of every iteration)
-	int bucket[RPT];
+	int bucket[ERPT];
 #pragma unroll 1
-	for (int q = 0; q < RPT; q++) {
+	for (int q = 0; q < ERPT; q++) {
 		const int id = q * TPB + threadIdx.x;
 		const int64_t i = base + id;
 		bucket[q] = -1;
@@ -373,8 +385,8 @@ __global__ void __launch_bounds__(TPB) k_extras(GraphDev g, RangeDev R, HeavyDev
 			const int64_t x = R.lo + i;
 			if (x >= R.from && (uint64_t)(R.rp[i + 1] - rp_from) > R.col_capacity) raise(g, ERR_CAPACITY);
 			else {
-				BitReader r;
-				r.init(g, ef_get(g, x));
+				RD r;
+				tile_reader<RD>(r, g, S, ef_get(g, x));
 				RowHead h;
 				const uint32_t rf = R.ref[i];
 				row_head<DEF>(g, r, rf ? R.deg[i - rf] : 0, h);
@@ -382,31 +394,31 @@ __global__ void __launch_bounds__(TPB) k_extras(GraphDev g, RangeDev R, HeavyDev
 				if (nextra) {
 					// rows with intervals first inside each class: warps without any skip the merging loop of row_extras
 					bool has_int = false;
-					if (g.min_interval != 0) { BitReader t = r; has_int = t.gamma() != 0; }
+					if (g.min_interval != 0) { RD t = r; has_int = t.gamma() != 0; }
 					bucket[q] = 2 * work_bucket(nextra) + (has_int ? 0 : 1);
-					s_pos[id] = r.tell();
-					s_nextra[id] = nextra;
-					s_ncopied[id] = h.ncopied;
-					s_cls[id] = (uint8_t)bucket[q];
+					S.pos[id] = r.tell() + (RD::IS_GLOBAL ? 0ull : (S.wbase << 5));  // absolute: tile_reader() converts back
+					S.nextra[id] = nextra;
+					S.ncopied[id] = h.ncopied;
+					S.cls[id] = (uint8_t)bucket[q];
 				}
 			}
 		}
 		__syncwarp();
 	}
 	uint32_t total;
-	block_bin_sort<RPT>(bucket, s_hist, s_order, &total);
-	// after the sort s_hist[b] is the first position of class b; the classes of >= HEAVY extras come first
+	block_bin_sort<ERPT>(bucket, S.hist, S.order, &total);
+	// after the sort S.hist[b] is the first position of class b; the classes of >= HEAVY extras come first
 	const int first_light = 2 * work_bucket(HEAVY - 1);
-	const uint32_t nheavy = H.rows ? s_hist[first_light] : 0;
+	const uint32_t nheavy = H.rows ? S.hist[first_light] : 0;
 	if (nheavy) {
-		if (threadIdx.x < first_light) s_count[threadIdx.x] = s_hist[threadIdx.x + 1] - s_hist[threadIdx.x];
-		if (threadIdx.x == 0) s_gbase = atomicAdd(&H.counters[0], (unsigned long long)nheavy);
+		if (threadIdx.x < first_light) S.count[threadIdx.x] = S.hist[threadIdx.x + 1] - S.hist[threadIdx.x];
+		if (threadIdx.x == 0) S.gbase = atomicAdd(&H.counters[0], (unsigned long long)nheavy);
 		__syncthreads();
-		if (threadIdx.x < first_light && s_count[threadIdx.x]) atomicAdd(&H.counters[1 + threadIdx.x], (unsigned long long)s_count[threadIdx.x]);
+		if (threadIdx.x < first_light && S.count[threadIdx.x]) atomicAdd(&H.counters[1 + threadIdx.x], (unsigned long long)S.count[threadIdx.x]);
 		for (uint32_t t = threadIdx.x; t < nheavy; t += TPB) {
-			const int id = s_order[t];
-			H.rows[s_gbase + t] = (uint32_t)(base + id);
-			H.cls[s_gbase + t] = s_cls[id];
+			const int id = S.order[t];
+			H.rows[S.gbase + t] = (uint32_t)(base + id);
+			H.cls[S.gbase + t] = S.cls[id];
 		}
 	}
 	// serial part: the lanes of a warp take rows of the same class and run them in lock step
@@ -416,13 +428,37 @@ __global__ void __launch_bounds__(TPB) k_extras(GraphDev g, RangeDev R, HeavyDev
 		const bool active = t < total;
 		const unsigned mask = __ballot_sync(FULL_MASK, active);
 		if (active) {
-			const int id = s_order[t];
+			const int id = S.order[t];
 			const int64_t k = base + id;
-			BitReader r;
-			r.init(g, s_pos[id]);
-			row_extras<DEF>(g, r, R.lo + k, s_nextra[id], row_slot(R, k, rp_from) + s_ncopied[id], mask);
+			RD r;
+			tile_reader<RD>(r, g, S, S.pos[id]);
+			row_extras<DEF>(g, r, R.lo + k, S.nextra[id], row_slot(R, k, rp_from) + S.ncopied[id], mask);
 		}
 	}
+}
+
+template <int DEF>
+__global__ void __launch_bounds__(TPB) k_extras(GraphDev g, RangeDev R, HeavyDev H) {
+	extern __shared__ __align__(16) unsigned char smem_raw[];
+	ExtrasSmem &S = *reinterpret_cast<ExtrasSmem *>(smem_raw);
+	const int64_t base = (int64_t)blockIdx.x * ETILE;
+	const int64_t count = R.hi - R.lo;
+	const int64_t rp_from = R.rp[R.from - R.lo];
+	if (threadIdx.x == 0) S.span[0] = ef_get(g, R.lo + base);
+	if (threadIdx.x == 32) S.span[1] = ef_get(g, R.lo + (base + ETILE < count ? base + ETILE : count));
+	__syncthreads();
+	const uint64_t w0 = S.span[0] >> 5;
+	const uint64_t nw = ((S.span[1] + 31) >> 5) - w0 + 2;
+	const bool staged = nw <= (uint64_t)EBITS;
+	if (staged) {
+		const uint64_t avail = g.nwords * 2 > w0 ? g.nwords * 2 - w0 : 0;
+		const uint32_t *src = (const uint32_t *)g.words + w0;
+		for (uint32_t w = threadIdx.x; w < (uint32_t)nw; w += TPB) S.bits[w] = w < avail ? __ldg(src + w) : 0u;
+		if (threadIdx.x == 0) { S.wbase = w0; S.nw = (uint32_t)nw; }
+	}
+	__syncthreads();
+	if (staged) extras_tile<DEF, TileReader>(g, R, H, S, base, count, rp_from);
+	else extras_tile<DEF, BitReader>(g, R, H, S, base, count, rp_from);
 }
 
 // class starts of the global heavy list: counters[1..64] = counts -> counters[65..128] = running cursors
@@ -495,10 +531,19 @@ void launch_extras(const Launch &L, const GraphDev &g, int def, const RangeDev &
 	const int64_t count = r.hi - r.lo;
 	if (count <= 0) return;
 	if (h.rows) cudaMemsetAsync(h.counters, 0, 129 * sizeof(unsigned long long), L.stream);
+	const size_t smem = sizeof(ExtrasSmem);
 	switch (def) {
-	case 2: k_extras<2><<<grid_for(count, TILE), TPB, 0, L.stream>>>(g, r, h); break;
-	case 1: k_extras<1><<<grid_for(count, TILE), TPB, 0, L.stream>>>(g, r, h); break;
-	default: k_extras<0><<<grid_for(count, TILE), TPB, 0, L.stream>>>(g, r, h);
+	case 2:
+		cudaFuncSetAttribute(k_extras<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+		k_extras<2><<<grid_for(count, ETILE), TPB, smem, L.stream>>>(g, r, h);
+		break;
+	case 1:
+		cudaFuncSetAttribute(k_extras<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+		k_extras<1><<<grid_for(count, ETILE), TPB, smem, L.stream>>>(g, r, h);
+		break;
+	default:
+		cudaFuncSetAttribute(k_extras<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+		k_extras<0><<<grid_for(count, ETILE), TPB, smem, L.stream>>>(g, r, h);
 	}
 	WGBV_LAUNCHED(L);
 	if (!h.rows) return;
@@ -515,20 +560,37 @@ void launch_extras(const Launch &L, const GraphDev &g, int def, const RangeDev &
 	WGBV_LAUNCHED(L);
 }
 
-// stage 3b: the rows of one depth level.  With a list, a block takes TILE list entries; without, it inspects TILE
-// consecutive nodes and keeps those at this level.
+// stage 3b: the rows of one depth level.  With a list, a block takes CTILE list entries; without, it inspects CTILE
+// consecutive nodes and keeps those at this level.  Before a warp merges its 32 rows it copies their reference rows
+// and their extras into shared memory with coalesced loads (when they fit): the serial merge loops then read with
+// shared-memory latency instead of stalling on one global load per element.
+static constexpr int CRPT = 4;
+static constexpr int CTILE = TPB * CRPT;
+static constexpr int CAPW = 0;    // successors one warp may stage per round (0: staging disabled, see profiles/r01_notes.md)
+
+__device__ __forceinline__ void cp_async8(void *smem_dst, const void *gmem_src) {
+	const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+	asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d), "l"(gmem_src));
+}
+
+struct CopySmem {
+	int64_t stage[TPB / 32][CAPW ? CAPW : 1];
+	uint64_t pos[CTILE];
+	uint32_t row[CTILE], bc[CTILE], ncopied[CTILE];
+	uint32_t hist[NBUCKETS + 1];
+	uint16_t order[CTILE];
+};
+
 template <int DEF>
 __global__ void __launch_bounds__(TPB) k_copy_level(GraphDev g, RangeDev R, uint32_t level, const uint32_t *__restrict__ list,
                                                     uint64_t list_count) {
-	__shared__ uint64_t s_pos[TILE];
-	__shared__ uint32_t s_row[TILE], s_bc[TILE], s_ncopied[TILE];
-	__shared__ uint32_t s_hist[NBUCKETS + 1];
-	__shared__ uint16_t s_order[TILE];
-	const uint64_t base = (uint64_t)blockIdx.x * TILE;
+	extern __shared__ __align__(16) unsigned char smem_raw[];
+	CopySmem &S = *reinterpret_cast<CopySmem *>(smem_raw);
+	const uint64_t base = (uint64_t)blockIdx.x * CTILE;
 	const int64_t rp_from = R.rp[R.from - R.lo];
-	int bucket[RPT];
+	int bucket[CRPT];
 #pragma unroll 1
-	for (int q = 0; q < RPT; q++) {
+	for (int q = 0; q < CRPT; q++) {
 		const int id = q * TPB + threadIdx.x;
 		const uint64_t t = base + id;
 		bucket[q] = -1;
@@ -544,29 +606,73 @@ __global__ void __launch_bounds__(TPB) k_copy_level(GraphDev g, RangeDev R, uint
 			row_head<DEF>(g, r, R.deg[i - rf], h);
 			if (h.ncopied) {
 				bucket[q] = 2 * work_bucket(h.d);  // the merge loop runs up to d times (copied + extras moved forward)
-				s_pos[id] = h.blocks_pos;
-				s_row[id] = (uint32_t)i;
-				s_bc[id] = h.bc;
-				s_ncopied[id] = h.ncopied;
+				S.pos[id] = h.blocks_pos;
+				S.row[id] = (uint32_t)i;
+				S.bc[id] = h.bc;
+				S.ncopied[id] = h.ncopied;
 			}
 		}
 		__syncwarp();
 	}
 	uint32_t total;
-	block_bin_sort<RPT>(bucket, s_hist, s_order, &total);
+	block_bin_sort<CRPT>(bucket, S.hist, S.order, &total);
+	const unsigned lane = threadIdx.x & 31u;
+	int64_t *const W = S.stage[threadIdx.x >> 5];
 #pragma unroll 1
 	for (uint32_t tb = threadIdx.x & ~31u; tb < total; tb += TPB) {
-		const uint32_t t = tb + (threadIdx.x & 31u);
+		const uint32_t t = tb + lane;
 		const bool active = t < total;
 		const unsigned mask = __ballot_sync(FULL_MASK, active);
+		// my row
+		int id = 0;
+		int64_t k = 0;
+		uint32_t dref = 0, d = 0, ncopied = 0;
+		const int64_t *src = nullptr;
+		int64_t *dst = nullptr;
 		if (active) {
-			const int id = s_order[t];
-			const int64_t k = s_row[id];
+			id = S.order[t];
+			k = S.row[id];
 			const uint32_t rf = R.ref[k];
-			BitReader r;
-			r.init(g, s_pos[id]);
-			row_copy<DEF>(g, r, row_slot(R, k - rf, rp_from), R.deg[k - rf], row_slot(R, k, rp_from), R.deg[k], s_bc[id], s_ncopied[id], mask);
+			dref = R.deg[k - rf];
+			d = R.deg[k];
+			ncopied = S.ncopied[id];
+			src = row_slot(R, k - rf, rp_from);
+			dst = row_slot(R, k, rp_from);
 		}
+		// staging plan: [reference row | extras] of every lane, back to back
+		const uint32_t ne = d - ncopied;
+		const uint32_t need = active ? dref + ne : 0u;
+		uint32_t inc = need;
+#pragma unroll
+		for (int o = 1; o < 32; o <<= 1) {
+			const uint32_t v = __shfl_up_sync(FULL_MASK, inc, o);
+			if ((int)lane >= o) inc += v;
+		}
+		const uint32_t off = inc - need;
+		const uint32_t all = __shfl_sync(FULL_MASK, inc, 31);
+		const bool staged = CAPW != 0 && all <= (uint32_t)CAPW;
+		if (staged) {
+			for (int rr = 0; rr < 32; rr++) {
+				const uint32_t n_src = __shfl_sync(FULL_MASK, dref, rr), n_ext = __shfl_sync(FULL_MASK, ne, rr);
+				const uint32_t n_act = __shfl_sync(FULL_MASK, need, rr);
+				if (n_act == 0) continue;  // uniform
+				const uint32_t o_r = __shfl_sync(FULL_MASK, off, rr);
+				const int64_t *p_src = (const int64_t *)__shfl_sync(FULL_MASK, (unsigned long long)src, rr);
+				const int64_t *p_ext = (const int64_t *)__shfl_sync(FULL_MASK, (unsigned long long)dst, rr) + __shfl_sync(FULL_MASK, ncopied, rr);
+				// asynchronous copies (LDGSTS): nothing waits until all 32 rows are in flight
+				for (uint32_t j = lane; j < n_src; j += 32) cp_async8(W + o_r + j, p_src + j);
+				for (uint32_t j = lane; j < n_ext; j += 32) cp_async8(W + o_r + n_src + j, p_ext + j);
+			}
+			asm volatile("cp.async.wait_all;" ::: "memory");
+			__syncwarp();
+		}
+		if (active) {
+			BitReader r;
+			r.init(g, S.pos[id]);
+			if (staged) row_copy<DEF>(g, r, W + off, dref, W + off + dref, dst, d, S.bc[id], ncopied, mask);
+			else row_copy<DEF>(g, r, src, dref, dst + ncopied, dst, d, S.bc[id], ncopied, mask);
+		}
+		__syncwarp();
 	}
 }
 
@@ -574,10 +680,20 @@ void launch_copy_level(const Launch &L, const GraphDev &g, int def, const RangeD
                        uint64_t list_count) {
 	const int64_t items = list ? (int64_t)list_count : r.hi - r.lo;
 	if (items <= 0) return;
+	const size_t smem = sizeof(CopySmem);
+	const unsigned grid = grid_for(items, CTILE);
 	switch (def) {
-	case 2: k_copy_level<2><<<grid_for(items, TILE), TPB, 0, L.stream>>>(g, r, level, list, list_count); break;
-	case 1: k_copy_level<1><<<grid_for(items, TILE), TPB, 0, L.stream>>>(g, r, level, list, list_count); break;
-	default: k_copy_level<0><<<grid_for(items, TILE), TPB, 0, L.stream>>>(g, r, level, list, list_count);
+	case 2:
+		cudaFuncSetAttribute(k_copy_level<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+		k_copy_level<2><<<grid, TPB, smem, L.stream>>>(g, r, level, list, list_count);
+		break;
+	case 1:
+		cudaFuncSetAttribute(k_copy_level<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+		k_copy_level<1><<<grid, TPB, smem, L.stream>>>(g, r, level, list, list_count);
+		break;
+	default:
+		cudaFuncSetAttribute(k_copy_level<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+		k_copy_level<0><<<grid, TPB, smem, L.stream>>>(g, r, level, list, list_count);
 	}
 	WGBV_LAUNCHED(L);
 }
@@ -772,7 +888,7 @@ __global__ void __launch_bounds__(TPB) k_chain_copy(GraphDev g, ChainDev c, uint
 	row_head<DEF>(g, r, dref, h);
 	r.seek(h.blocks_pos);
 	__syncwarp(mask);
-	row_copy<DEF>(g, r, chain_slot(c, (uint64_t)p), dref, chain_slot(c, row), h.d, h.bc, h.ncopied, mask);
+	row_copy<DEF>(g, r, chain_slot(c, (uint64_t)p), dref, chain_slot(c, row) + h.ncopied, chain_slot(c, row), h.d, h.bc, h.ncopied, mask);
 }
 void launch_chain_copy(const Launch &L, const GraphDev &g, int def, const ChainDev &c, uint64_t rows, const uint32_t *level,
                        uint32_t this_level) {

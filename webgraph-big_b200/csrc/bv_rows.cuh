@@ -25,6 +25,9 @@ namespace wgbv {
 
 static constexpr unsigned FULL_MASK = 0xffffffffu;
 
+// a prefetch may name any address: it never faults
+__device__ __forceinline__ void prefetch_l1(const void *p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+
 struct RowHead {
 	uint32_t d;        // outdegree
 	uint32_t rf;       // reference (0: none)
@@ -134,16 +137,20 @@ __device__ __forceinline__ void row_extras(const GraphDev &g, RD &r, int64_t x, 
 	if (nextra && r.past_end()) raise(g, ERR_OVERRUN);
 }
 
-// Copy-block resolution of one row: src[0..dref) is the finished reference row, dst[0..d) the row's slot whose
-// last d - ncopied positions hold the extras.  The reader is positioned at the first block.
-// MaskedLongIterator.java:67-100 + MergedLongIterator.java:54-92 of the reference.
+// Copy-block resolution of one row: src[0..dref) is the finished reference row, ext[0..d-ncopied) the row's extras
+// (in increasing order) and dst[0..d) the row's slot.  In place operation is allowed and is the normal case:
+// ext == dst + ncopied, i.e. the extras wait in the tail of the slot; the write position can never overtake the read
+// position of the extras.  Extras that follow the last copied successor are NOT written: they are expected to sit in
+// dst's tail already (true in place, and also when ext is a staged copy of that tail).  The reader is positioned at
+// the first block.  MaskedLongIterator.java:67-100 + MergedLongIterator.java:54-92 of the reference.
 // Warp-synchronous: every lane of `mask` must call it (ncopied == 0 for lanes without work).
 template <int DEF, class RD>
-__device__ __forceinline__ void row_copy(const GraphDev &g, RD &r, const int64_t *src, uint32_t dref,
-                                         int64_t *dst, uint32_t d, uint32_t bc, uint32_t ncopied, unsigned mask) {
-	uint32_t ei = ncopied;  // read index of the waiting extras
+__device__ __forceinline__ void row_copy(const GraphDev &g, RD &r, const int64_t *src, uint32_t dref, const int64_t *ext, int64_t *dst,
+                                         uint32_t d, uint32_t bc, uint32_t ncopied, unsigned mask) {
+	const uint32_t ne = d - ncopied;
+	uint32_t ei = 0;  // extras consumed
 	uint32_t out = 0, k = 0, run = 0, blk = 0, left = ncopied;
-	int64_t e = (left && ei < d) ? dst[ei] : INT64_MAX;
+	int64_t e = (left && ne) ? ext[0] : INT64_MAX;
 	// An iteration either starts the next block or emits exactly one successor (single block-decoding site).
 	while (__any_sync(mask, left != 0)) {
 		if (left) {
@@ -159,9 +166,13 @@ __device__ __forceinline__ void row_copy(const GraphDev &g, RD &r, const int64_t
 				}
 			} else {
 				const int64_t c = src[k];
+				// both streams are read one element at a time and each new 32-byte sector would cost a full memory round trip:
+				// ask for the sectors two ahead (no register, no wait)
+				if ((k & 3u) == 0) prefetch_l1(src + k + 8);
 				if (e < c) {
 					dst[out++] = e;
-					e = ++ei < d ? dst[ei] : INT64_MAX;
+					if ((ei & 3u) == 0) prefetch_l1(ext + ei + 8);
+					e = ++ei < ne ? ext[ei] : INT64_MAX;
 				} else {
 					if (e == c) raise(g, ERR_NOT_SORTED);
 					dst[out++] = c;
@@ -172,7 +183,6 @@ __device__ __forceinline__ void row_copy(const GraphDev &g, RD &r, const int64_t
 			}
 		}
 	}
-	// the remaining extras already sit in their final positions (out == ei here)
 }
 
 }  // namespace wgbv

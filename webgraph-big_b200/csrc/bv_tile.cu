@@ -227,7 +227,7 @@ __global__ void __launch_bounds__(TPB) k_tile(GraphDev g, RangeDev R, TileDev T)
 					const int y = j - S.ref[j];
 					TileReader r;
 					r.init_words(words, nw, S.bpos[j]);
-					row_copy<DEF>(g, r, row_ptr(y), S.deg[y], row_ptr(j), S.deg[j], S.bc[j], S.ncopied[j], mask);
+					row_copy<DEF>(g, r, row_ptr(y), S.deg[y], row_ptr(j) + S.ncopied[j], row_ptr(j), S.deg[j], S.bc[j], S.ncopied[j], mask);
 				}
 			}
 			if (!fits_rows) __threadfence_block();
