@@ -171,6 +171,22 @@ WGBV_API int wgbv_decode_csr(wgbv_stream *s, int64_t from, int64_t to, int64_t *
 WGBV_API int wgbv_decode_csr_host(wgbv_stream *s, int64_t from, int64_t to, int64_t *h_rowptr, int64_t *h_col,
                          uint64_t col_capacity, int64_t *arcs_out);
 
+/*
+ * Streaming scan of [from, to): the bulk form of nodeIterator(from) (BVG:1100-1245) for host-side consumers.  The
+ * library decodes chunk_nodes nodes at a time on the device and copies each chunk back into pinned host buffers it
+ * owns, keeping the next chunks decoding and copying while the caller works on the current one.
+ *   wgbv_scan_begin   starts a scan (one scan per wgbv_stream at a time)
+ *   wgbv_scan_next    returns 1 and the next chunk -- nodes [*first, *last), *h_rowptr[0 .. last-first] (relative to the
+ *                     chunk: h_rowptr[0] = 0) and *h_col[0 .. *arcs) -- 0 when the range is exhausted, or a negative
+ *                     status.  The buffers stay valid until the next wgbv_scan_next / wgbv_scan_end on this stream:
+ *                     the ownership rule of the reference's iterator, whose arrays are valid until the next
+ *                     nextLong() (BVG:1171-1172).
+ *   wgbv_scan_end     waits for outstanding work and ends the scan.
+ */
+WGBV_API int wgbv_scan_begin(wgbv_stream *s, int64_t from, int64_t to, int64_t chunk_nodes);
+WGBV_API int wgbv_scan_next(wgbv_stream *s, int64_t *first, int64_t *last, const int64_t **h_rowptr, const int64_t **h_col, int64_t *arcs);
+WGBV_API void wgbv_scan_end(wgbv_stream *s);
+
 /* outdegree(x) for a batch of arbitrary nodes (BVG:821-851): h_out[i] = outdegree(h_ids[i]).  Host buffers. */
 WGBV_API int wgbv_outdegrees(wgbv_stream *s, const int64_t *h_ids, uint64_t k, int64_t *h_out);
 

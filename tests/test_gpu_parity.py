@@ -297,3 +297,24 @@ def test_fused_tile_kernel_equals_oracle(monkeypatch, cnr_basename, cnr_golden):
     with gpu_of(e) as g:
         rp, c = g.decodeToCSR()
         assert np.array_equal(rp, rowptr_of(odeg)) and np.array_equal(c, ocol)
+
+
+def test_streaming_scan_equals_golden(cnr, cnr_golden):
+    """wgbv_scan_*: the pipelined bulk form of nodeIterator(); chunks must tile the range and carry the golden rows."""
+    deg, rowptr, col = cnr_golden
+    n = cnr.numNodes()
+    for lo, hi, chunk in ((0, n, 50000), (12345, 99999, 7777), (5, 6, 10), (n - 1, n, 1), (100, 100, 5)):
+        nxt, total = lo, 0
+        for a, b, rp, c in cnr.scan(lo, hi, chunk):
+            assert a == nxt and b == min(a + chunk, hi)
+            nxt = b
+            assert np.array_equal(rp, rowptr[a:b + 1] - rowptr[a])
+            assert np.array_equal(c, col[rowptr[a]:rowptr[b]])
+            total += c.size
+        assert nxt == hi and total == rowptr[hi] - rowptr[lo]
+    # a scan abandoned half way must not wedge the stream
+    it = cnr.scan(0, n, 1000)
+    next(it)
+    it.close()
+    rp, c = cnr.decodeToCSR(0, 100)
+    assert np.array_equal(c, col[:rowptr[100]])

@@ -266,6 +266,31 @@ class GpuBVGraph:
                                           col.size, C.byref(arcs)))
         return rowptr, col
 
+    def scan(self, from_=None, to=None, chunk_nodes=1 << 20):
+        """Streaming scan of [from, to): yields (first, last, rowptr, col) per chunk of nodes, rowptr relative to the chunk.
+        The arrays are views of pinned buffers owned by the library and are only valid until the next chunk is requested
+        (the reference's rule for iterator arrays, BVG:1171-1172); decode and copy-back of the following chunks overlap
+        with the caller's work on the current one."""
+        from_ = self._lo if from_ is None else from_
+        to = self._hi if to is None else to
+        L = _lib.lib()
+        _lib.check(L.wgbv_scan_begin(self._st.h, from_, to, chunk_nodes))
+        first, last, arcs = C.c_int64(), C.c_int64(), C.c_int64()
+        rp, col = C.c_void_p(), C.c_void_p()
+        try:
+            while True:
+                rc = L.wgbv_scan_next(self._st.h, C.byref(first), C.byref(last), C.byref(rp), C.byref(col), C.byref(arcs))
+                if rc == 0:
+                    return
+                if rc < 0:
+                    _lib.check(rc)
+                n = last.value - first.value
+                r = np.ctypeslib.as_array(C.cast(rp, C.POINTER(C.c_int64)), shape=(n + 1,))
+                c = np.ctypeslib.as_array(C.cast(col, C.POINTER(C.c_int64)), shape=(max(arcs.value, 1),))[:arcs.value]
+                yield first.value, last.value, r, c
+        finally:
+            L.wgbv_scan_end(self._st.h)
+
     def decodeDegreesDevice(self, from_, to, d_rowptr):
         """Header pass + scan into a device buffer (int pointer); returns the arc count of [from, to)."""
         arcs = C.c_int64()

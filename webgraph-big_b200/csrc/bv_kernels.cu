@@ -561,12 +561,11 @@ void launch_extras(const Launch &L, const GraphDev &g, int def, const RangeDev &
 }
 
 // stage 3b: the rows of one depth level.  With a list, a block takes CTILE list entries; without, it inspects CTILE
-// consecutive nodes and keeps those at this level.  Before a warp merges its 32 rows it copies their reference rows
-// and their extras into shared memory with coalesced loads (when they fit): the serial merge loops then read with
-// shared-memory latency instead of stalling on one global load per element.
+// consecutive nodes and keeps those at this level.  Long rows are merged by a whole warp each (row_copy_warp),
+// short ones by one lane each, 32 rows of one class per warp (row_copy).
 static constexpr int CRPT = 4;
 static constexpr int CTILE = TPB * CRPT;
-static constexpr int CAPW = 0;    // successors one warp may stage per round (0: staging disabled, see profiles/r01_notes.md)
+static constexpr uint32_t WARP_ROW = 48;  // rows with at least this many successors are merged by a whole warp
 
 __device__ __forceinline__ void cp_async8(void *smem_dst, const void *gmem_src) {
 	const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
@@ -574,7 +573,6 @@ __device__ __forceinline__ void cp_async8(void *smem_dst, const void *gmem_src) 
 }
 
 struct CopySmem {
-	int64_t stage[TPB / 32][CAPW ? CAPW : 1];
 	uint64_t pos[CTILE];
 	uint32_t row[CTILE], bc[CTILE], ncopied[CTILE];
 	uint32_t hist[NBUCKETS + 1];
@@ -617,62 +615,36 @@ __global__ void __launch_bounds__(TPB) k_copy_level(GraphDev g, RangeDev R, uint
 	uint32_t total;
 	block_bin_sort<CRPT>(bucket, S.hist, S.order, &total);
 	const unsigned lane = threadIdx.x & 31u;
-	int64_t *const W = S.stage[threadIdx.x >> 5];
+	// rows of at least WARP_ROW successors (they come first in the sorted order): one warp per row, cooperative merge
+	const uint32_t nbig = S.hist[2 * work_bucket(WARP_ROW - 1)];
 #pragma unroll 1
-	for (uint32_t tb = threadIdx.x & ~31u; tb < total; tb += TPB) {
+	for (uint32_t t = threadIdx.x >> 5; t < nbig; t += TPB / 32) {
+		const int id = S.order[t];
+		const int64_t k = S.row[id];
+		const uint32_t rf = R.ref[k];
+		const uint32_t ncopied = S.ncopied[id];
+		int64_t *dst = row_slot(R, k, rp_from);
+		BitReader r;
+		r.init(g, S.pos[id]);
+		row_copy_warp<DEF>(g, r, row_slot(R, k - rf, rp_from), R.deg[k - rf], dst + ncopied, dst, R.deg[k], S.bc[id], ncopied);
+	}
+	__syncwarp();
+	// the other rows: one lane per row, 32 rows of one class per warp
+#pragma unroll 1
+	for (uint32_t tb = nbig + (threadIdx.x & ~31u); tb < total; tb += TPB) {
 		const uint32_t t = tb + lane;
 		const bool active = t < total;
 		const unsigned mask = __ballot_sync(FULL_MASK, active);
-		// my row
-		int id = 0;
-		int64_t k = 0;
-		uint32_t dref = 0, d = 0, ncopied = 0;
-		const int64_t *src = nullptr;
-		int64_t *dst = nullptr;
 		if (active) {
-			id = S.order[t];
-			k = S.row[id];
+			const int id = S.order[t];
+			const int64_t k = S.row[id];
 			const uint32_t rf = R.ref[k];
-			dref = R.deg[k - rf];
-			d = R.deg[k];
-			ncopied = S.ncopied[id];
-			src = row_slot(R, k - rf, rp_from);
-			dst = row_slot(R, k, rp_from);
-		}
-		// staging plan: [reference row | extras] of every lane, back to back
-		const uint32_t ne = d - ncopied;
-		const uint32_t need = active ? dref + ne : 0u;
-		uint32_t inc = need;
-#pragma unroll
-		for (int o = 1; o < 32; o <<= 1) {
-			const uint32_t v = __shfl_up_sync(FULL_MASK, inc, o);
-			if ((int)lane >= o) inc += v;
-		}
-		const uint32_t off = inc - need;
-		const uint32_t all = __shfl_sync(FULL_MASK, inc, 31);
-		const bool staged = CAPW != 0 && all <= (uint32_t)CAPW;
-		if (staged) {
-			for (int rr = 0; rr < 32; rr++) {
-				const uint32_t n_src = __shfl_sync(FULL_MASK, dref, rr), n_ext = __shfl_sync(FULL_MASK, ne, rr);
-				const uint32_t n_act = __shfl_sync(FULL_MASK, need, rr);
-				if (n_act == 0) continue;  // uniform
-				const uint32_t o_r = __shfl_sync(FULL_MASK, off, rr);
-				const int64_t *p_src = (const int64_t *)__shfl_sync(FULL_MASK, (unsigned long long)src, rr);
-				const int64_t *p_ext = (const int64_t *)__shfl_sync(FULL_MASK, (unsigned long long)dst, rr) + __shfl_sync(FULL_MASK, ncopied, rr);
-				// asynchronous copies (LDGSTS): nothing waits until all 32 rows are in flight
-				for (uint32_t j = lane; j < n_src; j += 32) cp_async8(W + o_r + j, p_src + j);
-				for (uint32_t j = lane; j < n_ext; j += 32) cp_async8(W + o_r + n_src + j, p_ext + j);
-			}
-			asm volatile("cp.async.wait_all;" ::: "memory");
-			__syncwarp();
-		}
-		if (active) {
+			const uint32_t ncopied = S.ncopied[id];
+			int64_t *dst = row_slot(R, k, rp_from);
 			BitReader r;
 			r.init(g, S.pos[id]);
-			if (staged) row_copy<DEF>(g, r, W + off, dref, W + off + dref, dst, d, S.bc[id], ncopied, mask);
-			else row_copy<DEF>(g, r, src, dref, dst + ncopied, dst, d, S.bc[id], ncopied, mask);
+			row_copy<DEF>(g, r, row_slot(R, k - rf, rp_from), R.deg[k - rf], dst + ncopied, dst, R.deg[k], S.bc[id], ncopied, mask);
 		}
-		__syncwarp();
 	}
 }
 

@@ -185,4 +185,89 @@ __device__ __forceinline__ void row_copy(const GraphDev &g, RD &r, const int64_t
 	}
 }
 
+// The same merge done by a whole warp on ONE row (all 32 lanes pass the same arguments and each keeps its own copy of
+// the block reader, so the block codes are decoded redundantly but uniformly).  The reference row is read 32
+// positions at a time and the extras 32 at a time, both coalesced; every round emits everything that is not larger
+// than the last element of either window, each element going straight to its final position
+// (rank among its own kind + rank among the other kind), so the serial dependency of the one-lane merge -- and with
+// it the long tail of very long rows -- disappears.  In place operation (ext == dst + ncopied) is safe for the same
+// reason as in row_copy: a round writes below the position of the first extra it has not loaded yet.
+template <int DEF, class RD>
+__device__ __forceinline__ void row_copy_warp(const GraphDev &g, RD &r, const int64_t *src, uint32_t dref, const int64_t *ext,
+                                              int64_t *dst, uint32_t d, uint32_t bc, uint32_t ncopied) {
+	const unsigned lane = threadIdx.x & 31u;
+	const unsigned lt = (1u << lane) - 1u;
+	const uint32_t ne = d - ncopied;
+	uint32_t kb = 0;           // first position of the current window of the reference row
+	uint32_t ei = 0;           // extras emitted so far
+	uint32_t done = 0;         // copied successors emitted so far
+	// block state: the block [bs, be) of reference positions currently open, whether it copies, blocks decoded so far
+	uint32_t bs = 0, be = 0, blk = 0;
+	bool bcopy = false;
+	unsigned cmask = 0;        // copied positions of the current window not emitted yet
+	int64_t c = 0;             // my reference element of the current window
+	bool fresh = true;         // the window at kb has not been loaded yet
+	while (done < ncopied) {
+		if (fresh) {
+			const uint32_t p = kb + lane;
+			c = p < dref ? src[p] : INT64_MAX;
+			bool f = false;
+			// walk the blocks that overlap [kb, kb + 32)
+			for (;;) {
+				if (p >= bs && p < be && bcopy) f = true;
+				if (be >= kb + 32 || be >= dref || blk > bc) break;
+				const uint32_t len = blk < bc ? (uint32_t)rd_block<DEF>(r, g) + (blk ? 1u : 0u) : dref - be;
+				bcopy = !(blk & 1);
+				blk++;
+				bs = be;
+				be = len > dref - be ? dref : be + len;
+			}
+			cmask = __ballot_sync(FULL_MASK, f && p < dref);
+			fresh = false;
+			if (kb + 32 >= dref && cmask == 0) break;  // malformed: announced copies that do not exist
+			if (cmask == 0) { kb += 32; fresh = true; continue; }
+		}
+		// A: the copied elements of the window still to emit, compacted to lanes 0..nA-1
+		const unsigned nA = (unsigned)__popc(cmask);
+		const int srcl = lane < nA ? (int)__fns(cmask, 0, (int)lane + 1) : 0;
+		int64_t A = __shfl_sync(FULL_MASK, c, srcl);
+		if (lane >= nA) A = INT64_MAX;
+		// B: the next extras
+		const uint32_t nB = ne - ei < 32u ? ne - ei : 32u;
+		const int64_t B = lane < nB ? ext[ei + lane] : INT64_MAX;
+		const bool src_last = kb + 32 >= dref;   // nothing copied follows this window
+		const bool ext_last = ei + nB >= ne;     // no extra follows this window
+		const int64_t a_last = __shfl_sync(FULL_MASK, A, (int)nA - 1);
+		const int64_t b_last = nB ? __shfl_sync(FULL_MASK, B, (int)nB - 1) : INT64_MIN;
+		const int64_t lim_a = src_last ? INT64_MAX : a_last;
+		const int64_t lim_b = ext_last ? INT64_MAX : b_last;
+		const int64_t limit = lim_a < lim_b ? lim_a : lim_b;
+		// ranks in the other window by binary search over lanes (both windows are sorted, padded with +inf)
+		uint32_t a_in_b = 0, b_in_a = 0;  // #B < A_lane, #A < B_lane
+#pragma unroll
+		for (int step = 16; step; step >>= 1) {
+			const int64_t vb = __shfl_sync(FULL_MASK, B, (int)(a_in_b + step - 1));
+			const int64_t va = __shfl_sync(FULL_MASK, A, (int)(b_in_a + step - 1));
+			if (vb < A) a_in_b += step;
+			if (va < B) b_in_a += step;
+		}
+		if (__shfl_sync(FULL_MASK, B, (int)a_in_b) < A && a_in_b < 32) a_in_b++;
+		if (__shfl_sync(FULL_MASK, A, (int)b_in_a) < B && b_in_a < 32) b_in_a++;
+		const bool emitA = lane < nA && A <= limit;
+		const bool emitB = lane < nB && B <= limit;
+		const uint32_t out = done + ei;
+		if (emitA) dst[out + lane + a_in_b] = A;
+		if (emitB) dst[out + lane + b_in_a] = B;
+		const unsigned eA = (unsigned)__popc(__ballot_sync(FULL_MASK, emitA));
+		const unsigned eB = (unsigned)__popc(__ballot_sync(FULL_MASK, emitB));
+		if (eA == 0 && eB == 0) break;  // cannot happen on well-formed input
+		done += eA;
+		ei += eB;
+		// drop the emitted copied positions (the eA lowest set bits of cmask)
+		for (unsigned i = 0; i < eA; i++) cmask &= cmask - 1;
+		if (cmask == 0) { kb += 32; fresh = true; }
+		__syncwarp();
+	}
+}
+
 }  // namespace wgbv

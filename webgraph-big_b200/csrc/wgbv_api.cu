@@ -76,6 +76,22 @@ struct wgbv_stream {
 	cudaEvent_t ev[6]{};
 	bool ev_valid = false;
 	Launch launch() { return Launch{stream, &launches}; }
+
+	// streaming scan (wgbv_scan_*): a ring of chunk buffers, decoded on `stream`, copied back on `copy_stream`
+	struct ScanSlot {
+		DevBuf d_rowptr, d_col;
+		int64_t *h_rowptr = nullptr, *h_col = nullptr;
+		size_t h_rowptr_cap = 0, h_col_cap = 0;  // elements
+		cudaEvent_t decoded = nullptr, ready = nullptr;
+		int64_t first = 0, last = 0, arcs = 0;
+		uint32_t *h_err = nullptr;  // pinned copy of the error word taken after this chunk
+	};
+	static constexpr int SCAN_SLOTS = 3;
+	ScanSlot slot[SCAN_SLOTS];
+	cudaStream_t copy_stream = nullptr;
+	bool scanning = false;
+	int64_t scan_to = 0, scan_chunk = 0, scan_issue = 0, scan_take = 0;  // next node to issue / to hand out
+	int64_t issued = 0, taken = 0;                                       // chunks issued / handed out
 };
 
 // ------------------------------------------------------------------------------------------------ misc
@@ -367,6 +383,16 @@ extern "C" void wgbv_stream_destroy(wgbv_stream *s) {
 	                  &s->rowptr, &s->ids, &s->batch, &s->heavy_rows, &s->heavy_sorted, &s->heavy_cls, &s->heavy_counters, &s->tile_scratch, &s->level_pos, &s->c_node, &s->c_dst, &s->c_parent, &s->c_deg, &s->c_isq, &s->c_level,
 	                  &s->c_len, &s->c_arcs, &s->c_row0, &s->c_soff, &s->c_store})
 		b->release();
+	for (auto &sl : s->slot) {
+		sl.d_rowptr.release();
+		sl.d_col.release();
+		if (sl.h_rowptr) cudaFreeHost(sl.h_rowptr);
+		if (sl.h_col) cudaFreeHost(sl.h_col);
+		if (sl.h_err) cudaFreeHost(sl.h_err);
+		if (sl.decoded) cudaEventDestroy(sl.decoded);
+		if (sl.ready) cudaEventDestroy(sl.ready);
+	}
+	if (s->copy_stream) cudaStreamDestroy(s->copy_stream);
 	if (s->d_err) cudaFree(s->d_err);
 	if (s->h_pin) cudaFreeHost(s->h_pin);
 	for (auto &e : s->ev) if (e) cudaEventDestroy(e);
@@ -374,6 +400,8 @@ extern "C" void wgbv_stream_destroy(wgbv_stream *s) {
 	s->g->streams--;
 	delete s;
 }
+
+static int error_from_bits(wgbv_stream *s, uint32_t e);
 
 // Reads and clears the sticky error word; maps it onto a status code.
 static int collect_errors(wgbv_stream *s) {
@@ -383,6 +411,10 @@ static int collect_errors(wgbv_stream *s) {
 	const uint32_t e = h[0];
 	if (!e) return WGBV_OK;
 	CU(cudaMemsetAsync(s->d_err, 0, 4, s->stream));
+	return error_from_bits(s, e);
+}
+
+static int error_from_bits(wgbv_stream *s, uint32_t e) {
 	if (e & ERR_INDEX) return fail(WGBV_EINDEX, "Node index out of range");
 	if (e & ERR_REF_WINDOW) return fail(WGBV_ESTATE, "The required reference is incompatible with the window size (%d)", s->g->props.window_size);
 	if (e & ERR_OVERRUN) return fail(WGBV_EIO, "a code runs past the end of the bit stream");
@@ -633,6 +665,105 @@ extern "C" int wgbv_decode_csr_host(wgbv_stream *s, int64_t from, int64_t to, in
 		if (P.arcs) CU(cudaMemcpyAsync(h_col, s->col.as<int64_t>(), (size_t)P.arcs * 8, cudaMemcpyDeviceToHost, s->stream));
 	}
 	return collect_errors(s);
+}
+
+// ------------------------------------------------------------------------------------------------ streaming scan
+static int error_from_bits(wgbv_stream *s, uint32_t e);
+
+static int pinned_ensure(int64_t **p, size_t *cap, size_t elems) {
+	if (elems <= *cap) return WGBV_OK;
+	if (*p) cudaFreeHost(*p);
+	*p = nullptr;
+	*cap = 0;
+	const size_t want = elems + elems / 4 + 1024;
+	if (cudaMallocHost((void **)p, want * 8) != cudaSuccess) return fail(WGBV_ECUDA, "cudaMallocHost of %zu bytes failed", want * 8);
+	*cap = want;
+	return WGBV_OK;
+}
+
+// Queues the decode of the next chunk and its copy back to pinned host memory.
+static int scan_issue_one(wgbv_stream *s) {
+	wgbv_stream::ScanSlot &sl = s->slot[s->issued % wgbv_stream::SCAN_SLOTS];
+	const int64_t a = s->scan_issue, b = std::min(a + s->scan_chunk, s->scan_to);
+	int rc;
+	if ((rc = sl.d_rowptr.ensure((size_t)(b - a + 1) * 8))) return rc;
+	Prepared P;
+	if ((rc = prepare(s, a, b, sl.d_rowptr.as<int64_t>(), P))) return rc;  // synchronises `stream`: the previous chunk is decoded
+	if ((rc = sl.d_col.ensure((size_t)std::max<int64_t>(P.arcs, 1) * 8))) return rc;
+	if ((rc = pinned_ensure(&sl.h_rowptr, &sl.h_rowptr_cap, (size_t)(b - a + 1))) || (rc = pinned_ensure(&sl.h_col, &sl.h_col_cap, (size_t)std::max<int64_t>(P.arcs, 1)))) return rc;
+	if ((rc = decode_rows(s, a, b, P, sl.d_col.as<int64_t>(), (uint64_t)P.arcs))) return rc;
+	CU(cudaEventRecord(sl.decoded, s->stream));
+	CU(cudaStreamWaitEvent(s->copy_stream, sl.decoded, 0));
+	CU(cudaMemcpyAsync(sl.h_rowptr, sl.d_rowptr.as<int64_t>(), (size_t)(b - a + 1) * 8, cudaMemcpyDeviceToHost, s->copy_stream));
+	if (P.arcs) CU(cudaMemcpyAsync(sl.h_col, sl.d_col.as<int64_t>(), (size_t)P.arcs * 8, cudaMemcpyDeviceToHost, s->copy_stream));
+	CU(cudaMemcpyAsync(sl.h_err, s->d_err, 4, cudaMemcpyDeviceToHost, s->copy_stream));
+	CU(cudaEventRecord(sl.ready, s->copy_stream));
+	sl.first = a;
+	sl.last = b;
+	sl.arcs = P.arcs;
+	s->scan_issue = b;
+	s->issued++;
+	return WGBV_OK;
+}
+
+extern "C" int wgbv_scan_begin(wgbv_stream *s, int64_t from, int64_t to, int64_t chunk_nodes) {
+	clear_error();
+	if (!s) return fail(WGBV_EARG, "null argument");
+	if (chunk_nodes < 1) return fail(WGBV_EARG, "chunk_nodes must be positive");
+	CU(cudaSetDevice(s->g->device));
+	int rc = check_range(s->g, from, to);
+	if (rc) return rc;
+	if (!s->copy_stream) {
+		CU(cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking));
+		for (auto &sl : s->slot) {
+			CU(cudaEventCreateWithFlags(&sl.decoded, cudaEventDisableTiming));
+			CU(cudaEventCreateWithFlags(&sl.ready, cudaEventDisableTiming));
+			CU(cudaMallocHost((void **)&sl.h_err, 64));
+		}
+	}
+	CU(cudaStreamSynchronize(s->copy_stream));
+	s->scanning = true;
+	s->scan_to = to;
+	s->scan_chunk = chunk_nodes;
+	s->scan_issue = s->scan_take = from;
+	s->issued = s->taken = 0;
+	return WGBV_OK;
+}
+
+extern "C" int wgbv_scan_next(wgbv_stream *s, int64_t *first, int64_t *last, const int64_t **h_rowptr, const int64_t **h_col, int64_t *arcs) {
+	clear_error();
+	if (!s || !first || !last || !h_rowptr || !h_col) return fail(WGBV_EARG, "null argument");
+	if (!s->scanning) return fail(WGBV_ESTATE, "wgbv_scan_begin has not been called");
+	CU(cudaSetDevice(s->g->device));
+	if (s->scan_take >= s->scan_to && s->taken == s->issued) return 0;
+	int rc;
+	// keep the pipeline full: the chunk handed out now plus the ones decoding / copying behind it; the slot of the chunk
+	// handed out by the PREVIOUS call becomes reusable here (its buffers were valid until this call)
+	while (s->scan_issue < s->scan_to && s->issued - s->taken < wgbv_stream::SCAN_SLOTS - 1)
+		if ((rc = scan_issue_one(s))) return rc;
+	if (s->issued == s->taken) return 0;
+	wgbv_stream::ScanSlot &sl = s->slot[s->taken % wgbv_stream::SCAN_SLOTS];
+	CU(cudaEventSynchronize(sl.ready));
+	if (sl.h_err[0]) {
+		cudaMemsetAsync(s->d_err, 0, 4, s->stream);
+		return error_from_bits(s, sl.h_err[0]);
+	}
+	*first = sl.first;
+	*last = sl.last;
+	*h_rowptr = sl.h_rowptr;
+	*h_col = sl.h_col;
+	if (arcs) *arcs = sl.arcs;
+	s->scan_take = sl.last;
+	s->taken++;
+	return 1;
+}
+
+extern "C" void wgbv_scan_end(wgbv_stream *s) {
+	if (!s || !s->scanning) return;
+	cudaSetDevice(s->g->device);
+	cudaStreamSynchronize(s->stream);
+	if (s->copy_stream) cudaStreamSynchronize(s->copy_stream);
+	s->scanning = false;
 }
 
 // ------------------------------------------------------------------------------------------------ random access
