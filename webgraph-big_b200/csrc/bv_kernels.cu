@@ -503,27 +503,113 @@ __global__ void __launch_bounds__(TPB) k_heavy_scatter(HeavyDev H) {
 	}
 }
 
-// stage 3a for heavy rows: every warp takes 32 consecutive entries of the class-sorted list
+// stage 3a for heavy rows: every warp takes 32 consecutive entries of the class-sorted list.
+// Each lane walks its own long stream of residual codes, 32 different places of the bit stream per warp: read
+// directly, every lane would fetch and re-fetch its own cache lines (L1 cannot hold 32 streams per warp) and the
+// warp would wait for the slowest lane at every word boundary.  Instead the warp keeps a WINDOW of the next
+// HW_WORDS words of every lane's stream in shared memory, filled by all 32 lanes together with one coalesced
+// 128-byte load per row; the decoders read the window and the warp refills it whenever some lane runs low.
+static constexpr int HW_WORDS = 32;   // words of stream per lane and refill
+static constexpr int HW_PITCH = 35;   // row pitch in words (odd multiple: the 32 lanes hit 32 banks)
+static constexpr uint32_t HW_LOW = 29;  // refill when a reader's prefetched word index reaches this
+
+struct HeavyWindow {
+	static constexpr bool enabled = true;
+	uint32_t *win;          // this warp's HW_PITCH * 32 words
+	const uint32_t *words;  // the whole stream
+	uint64_t nwords32;
+	uint64_t wbase;         // stream word index of my row's window[0]
+	__device__ __forceinline__ bool low(const TileReader &r) const { return r.idx >= HW_LOW; }
+	// all lanes of the warp call this together; lanes outside `mask` take part in the loads only
+	__device__ __forceinline__ void fill(TileReader &r, uint64_t pos, bool mine) {
+		const unsigned lane = threadIdx.x & 31u;
+		const uint64_t my_w = pos >> 5;
+#pragma unroll 4
+		for (int rr = 0; rr < 32; rr++) {
+			const uint64_t w = __shfl_sync(FULL_MASK, my_w, rr);
+			const uint64_t j = w + lane;
+			win[rr * HW_PITCH + lane] = j < nwords32 ? __ldg(words + j) : 0u;
+		}
+		__syncwarp();
+		if (mine) {
+			wbase = my_w;
+			r.init_words(win + lane * HW_PITCH, HW_WORDS, (uint32_t)(pos & 31u));
+		}
+	}
+	__device__ __forceinline__ uint64_t tell(const TileReader &r) const { return (wbase << 5) + r.tell(); }
+	__device__ __forceinline__ void refill(TileReader &r, unsigned mask) {
+		// only lanes of `mask` are here; the others idle in the caller, so the loads are done by the lanes present
+		const unsigned lane = threadIdx.x & 31u;
+		const uint64_t pos = tell(r);
+		const uint64_t my_w = pos >> 5;
+		__syncwarp(mask);
+		for (unsigned m = mask; m; m &= m - 1) {
+			const int rr = __ffs(m) - 1;
+			const uint64_t w = __shfl_sync(mask, my_w, rr);
+			for (unsigned l = (unsigned)__popc(mask & ((1u << lane) - 1u)); l < (unsigned)HW_WORDS; l += (unsigned)__popc(mask)) {
+				const uint64_t j = w + l;
+				win[rr * HW_PITCH + l] = j < nwords32 ? __ldg(words + j) : 0u;
+			}
+		}
+		__syncwarp(mask);
+		wbase = my_w;
+		r.init_words(win + lane * HW_PITCH, HW_WORDS, (uint32_t)(pos & 31u));
+	}
+};
+
 template <int DEF>
 __global__ void __launch_bounds__(TPB) k_extras_heavy(GraphDev g, RangeDev R, HeavyDev H) {
+	__shared__ uint32_t s_win[TPB / 32][32 * HW_PITCH];
 	const unsigned long long total = H.counters[0];
 	const int64_t rp_from = R.rp[R.from - R.lo];
 	const unsigned long long warps = (unsigned long long)gridDim.x * (TPB / 32);
 	const unsigned lane = threadIdx.x & 31;
+	HeavyWindow win;
+	win.win = s_win[threadIdx.x >> 5];
+	win.words = (const uint32_t *)g.words;
+	win.nwords32 = g.nwords * 2;
+	win.wbase = 0;
 	for (unsigned long long c = (unsigned long long)blockIdx.x * (TPB / 32) + (threadIdx.x >> 5); c * 32 < total; c += warps) {
 		const unsigned long long t = c * 32 + lane;
 		const bool active = t < total;
 		const unsigned mask = __ballot_sync(FULL_MASK, active);
+		// heads and interval sections straight from global memory (short), then the residuals through the window
+		int64_t i = 0;
+		uint32_t nextra = 0, ic = 0, nres = 0, ncopied = 0;
+		uint64_t int_pos = 0, res_pos = 0;
+		BitReader rh;
 		if (active) {
-			const int64_t i = H.sorted[t];
-			BitReader r;
-			r.init(g, ef_get(g, R.lo + i));
+			i = H.sorted[t];
+			rh.init(g, ef_get(g, R.lo + i));
 			RowHead h;
 			const uint32_t rf = R.ref[i];
-			row_head<DEF>(g, r, rf ? R.deg[i - rf] : 0, h);
-			__syncwarp(mask);
-			row_extras<DEF>(g, r, R.lo + i, h.d - h.ncopied, row_slot(R, i, rp_from) + h.ncopied, mask);
+			row_head<DEF>(g, rh, rf ? R.deg[i - rf] : 0, h);
+			nextra = h.d - h.ncopied;
+			ncopied = h.ncopied;
+			row_intervals(g, rh, nextra, ic, int_pos, nres);
+			res_pos = rh.tell();
+			if (ic) rh.seek(int_pos);  // rh becomes the interval cursor
 		}
+		__syncwarp();
+		if (DEF == 0) {
+			// run-time codings include Golomb / unary residuals, whose codes can be longer than any window: read them
+			// straight from global memory
+			if (active) {
+				BitReader r = rh;
+				r.seek(res_pos);
+				NoWindow nw;
+				row_extras_core<DEF>(g, rh, r, R.lo + i, nextra, ic, nres, row_slot(R, i, rp_from) + ncopied, mask, nw);
+				if (nextra && r.past_end()) raise(g, ERR_OVERRUN);
+			}
+		} else {
+			TileReader r;
+			win.fill(r, res_pos, active);
+			if (active) {
+				row_extras_core<DEF>(g, rh, r, R.lo + i, nextra, ic, nres, row_slot(R, i, rp_from) + ncopied, mask, win);
+				if (nextra && win.tell(r) > ((g.nwords * 2) << 5)) raise(g, ERR_OVERRUN);
+			}
+		}
+		__syncwarp();
 	}
 }
 

@@ -73,21 +73,25 @@ __device__ __forceinline__ void row_head(const GraphDev &g, RD &r, uint32_t dref
 	}
 }
 
-// Decodes the interval section and the residuals of row x (reader positioned at the interval count, i.e. right
-// after the blocks) and writes the `nextra` merged values, in increasing order, to out[0..nextra).
-// BVG:1037-1073, 902-954.  Warp-synchronous: every lane of `mask` must call it (nextra == 0: no work).
-// Two loops: a merging one that runs while some lane of the warp still has interval material, then a tight one
-// for pure gap decoding (the kernels sort rows so that most warps never enter the first).
-template <int DEF, class RD>
-__device__ __forceinline__ void row_extras(const GraphDev &g, RD &r, int64_t x, uint32_t nextra, int64_t *out, unsigned mask) {
-	uint32_t ic = 0, nres = nextra;
-	uint64_t int_pos = 0;
+// No-op window policy of row_extras_core: the residual reader needs no refilling.
+struct NoWindow {
+	static constexpr bool enabled = false;
+	template <class RD> __device__ __forceinline__ bool low(const RD &) const { return false; }
+	template <class RD> __device__ __forceinline__ void refill(RD &, unsigned) {}
+};
+
+// First pass over the interval section (reader at the interval count): number of intervals, where they start, and
+// how many of the `nextra` extras are residuals.  Leaves the reader at the first residual.  BVG:1037-1060.
+template <class RD>
+__device__ __forceinline__ void row_intervals(const GraphDev &g, RD &r, uint32_t &nextra, uint32_t &ic, uint64_t &int_pos, uint32_t &nres) {
+	ic = 0;
+	int_pos = 0;
+	nres = nextra;
 	if (nextra && g.min_interval != 0) {
 		uint64_t c = r.gamma();
 		if (c > nextra) { raise(g, ERR_DEGREE); c = 0; nextra = 0; }
 		ic = (uint32_t)c;
 		int_pos = r.tell();
-		// first pass over the intervals: only their total length, to find the number of residuals and where they start
 		uint64_t covered = 0;
 		for (uint32_t i = 0; i < ic; i++) {
 			r.gamma();
@@ -96,14 +100,22 @@ __device__ __forceinline__ void row_extras(const GraphDev &g, RD &r, int64_t x, 
 		if (covered > nextra) { raise(g, ERR_DEGREE); ic = 0; nextra = 0; covered = 0; }
 		nres = nextra - (uint32_t)covered;
 	}
-	RD ri = r;  // interval cursor; r stays the residual cursor
-	if (ic) ri.seek(int_pos);
+}
 
+// The merge of intervals (cursor ri, `ic` of them) and residuals (cursor r, `nres` of them) into out[0..nextra).
+// Warp-synchronous: every lane of `mask` must call it (nextra == 0: no work).  Two loops: a merging one that runs
+// while some lane of the warp still has interval material, then a tight one for pure gap decoding (the kernels sort
+// rows so that most warps never enter the first).  WIN lets the residual reader run on a small window of the stream
+// that the warp refills together (see k_extras_heavy); with NoWindow that code vanishes.
+template <int DEF, class RDI, class RDR, class WIN>
+__device__ __forceinline__ void row_extras_core(const GraphDev &g, RDI &ri, RDR &r, int64_t x, uint32_t nextra, uint32_t ic, uint32_t nres,
+                                                int64_t *out, unsigned mask, WIN &win) {
 	int64_t cur = 0, end = 0;  // current interval [cur, end)
 	int64_t res = x;           // last residual decoded; pending (not yet written) iff have_res
 	bool have_res = false, first_res = true, first_int = true;
 	uint32_t o = 0;
 	for (; __any_sync(mask, o < nextra && (cur != end || ic != 0)); o++) {
+		if (WIN::enabled && __any_sync(mask, win.low(r))) win.refill(r, mask);
 		if (o < nextra) {
 			if (cur == end && ic) {  // next interval (rare: once per interval)
 				const uint64_t gap = ri.gamma();
@@ -127,6 +139,7 @@ __device__ __forceinline__ void row_extras(const GraphDev &g, RD &r, int64_t x, 
 	}
 	if (have_res && o < nextra) out[o++] = res;  // a residual decoded above but not written yet
 	for (; __any_sync(mask, o < nextra); o++) {
+		if (WIN::enabled && __any_sync(mask, win.low(r))) win.refill(r, mask);
 		if (o < nextra) {
 			const uint64_t code = rd_residual<DEF>(r, g);
 			res = first_res ? x + nat2int(code) : res + 1 + (int64_t)code;
@@ -134,6 +147,20 @@ __device__ __forceinline__ void row_extras(const GraphDev &g, RD &r, int64_t x, 
 			out[o] = res;
 		}
 	}
+}
+
+// Decodes the interval section and the residuals of row x (reader positioned at the interval count, i.e. right
+// after the blocks) and writes the `nextra` merged values, in increasing order, to out[0..nextra).
+// BVG:1037-1073, 902-954.  Warp-synchronous: every lane of `mask` must call it (nextra == 0: no work).
+template <int DEF, class RD>
+__device__ __forceinline__ void row_extras(const GraphDev &g, RD &r, int64_t x, uint32_t nextra, int64_t *out, unsigned mask) {
+	uint32_t ic, nres;
+	uint64_t int_pos;
+	row_intervals(g, r, nextra, ic, int_pos, nres);
+	RD ri = r;  // interval cursor; r stays the residual cursor
+	if (ic) ri.seek(int_pos);
+	NoWindow nw;
+	row_extras_core<DEF>(g, ri, r, x, nextra, ic, nres, out, mask, nw);
 	if (nextra && r.past_end()) raise(g, ERR_OVERRUN);
 }
 
