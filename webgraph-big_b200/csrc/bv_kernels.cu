@@ -259,15 +259,34 @@ void launch_level_scatter(const Launch &L, const uint32_t *depth, int64_t count,
 static constexpr int LEVELS_MAX = 8;
 static constexpr int LTILE = TPB * 8;
 
-__global__ void __launch_bounds__(TPB) k_level_block_counts(const uint32_t *__restrict__ depth, int64_t count, uint32_t nlevels,
-                                                            uint32_t nblocks, uint32_t *__restrict__ counts) {
+// With `ref` given the kernel also COMPUTES the depths (chains of at most nlevels hops: a bounded walk over the
+// reference array, which stage 1 left in memory) and stores them for the kernels that follow, so that the separate
+// depth pass is not needed; a chain longer than nlevels sets *deep and the host falls back to k_depth.
+__global__ void __launch_bounds__(TPB) k_level_block_counts(GraphDev g, const uint8_t *__restrict__ ref, uint32_t *depth, int64_t lo, int64_t from,
+                                                            int64_t count, uint32_t nlevels, uint32_t nblocks, uint32_t *__restrict__ counts,
+                                                            uint32_t *deep) {
 	__shared__ uint32_t s_cnt[LEVELS_MAX + 1];
 	if (threadIdx.x <= LEVELS_MAX) s_cnt[threadIdx.x] = 0;
 	__syncthreads();
 	const int64_t base = (int64_t)blockIdx.x * LTILE;
 	for (int q = 0; q < 8; q++) {
 		const int64_t i = base + q * TPB + threadIdx.x;
-		const uint32_t d = i < count ? depth[i] : 0u;
+		uint32_t d = 0;
+		if (i < count) {
+			if (ref) {
+				int64_t y = i;
+				for (;;) {
+					const uint32_t rf = ref[y];
+					if (rf == 0) break;
+					if (y < (int64_t)rf) { d = DEPTH_INVALID; break; }
+					if (d == nlevels) { d = DEPTH_UNRESOLVED; atomicExch(deep, 1u); break; }
+					y -= rf;
+					d++;
+				}
+				if (d == DEPTH_INVALID && lo + i >= from) raise(g, ERR_REF_UNRESOLVED);
+				depth[i] = d;
+			} else d = depth[i];
+		}
 		for (uint32_t l = 1; l <= nlevels; l++) {
 			const unsigned m = __ballot_sync(0xffffffffu, d == l);
 			if ((threadIdx.x & 31) == 0 && m) atomicAdd(&s_cnt[l], (uint32_t)__popc(m));
@@ -315,10 +334,10 @@ __global__ void __launch_bounds__(TPB) k_level_fill(const uint32_t *__restrict__
 	}
 }
 
-void launch_level_lists(const Launch &L, const uint32_t *depth, int64_t count, uint32_t nlevels, uint32_t *counts, int64_t *pos,
-                        uint32_t *list, uint64_t *scan_state, uint32_t *ticket) {
+void launch_level_lists(const Launch &L, const GraphDev &g, const uint8_t *ref, uint32_t *depth, int64_t lo, int64_t from, int64_t count,
+                        uint32_t nlevels, uint32_t *counts, int64_t *pos, uint32_t *list, uint64_t *scan_state, uint32_t *ticket, uint32_t *deep) {
 	const uint32_t nblocks = grid_for(count, LTILE);
-	k_level_block_counts<<<nblocks, TPB, 0, L.stream>>>(depth, count, nlevels, nblocks, counts);
+	k_level_block_counts<<<nblocks, TPB, 0, L.stream>>>(g, ref, depth, lo, from, count, nlevels, nblocks, counts, deep);
 	WGBV_LAUNCHED(L);
 	launch_scan(L, counts, pos, (int64_t)nlevels * nblocks, scan_state, ticket);
 	k_level_fill<<<nblocks, TPB, 0, L.stream>>>(depth, count, nlevels, nblocks, pos, list);
@@ -381,7 +400,8 @@ __device__ __forceinline__ void extras_tile(const GraphDev &g, const RangeDev &R
 		const int id = q * TPB + threadIdx.x;
 		const int64_t i = base + id;
 		bucket[q] = -1;
-		if (i < count && R.deg[i] != 0 && R.depth[i] < DEPTH_INVALID) {
+		// a halo row whose reference lies before the decoded range is never needed (and cannot be decoded): skip it
+		if (i < count && R.deg[i] != 0 && (R.depth ? R.depth[i] < DEPTH_INVALID : (int64_t)R.ref[i] <= i)) {
 			const int64_t x = R.lo + i;
 			if (x >= R.from && (uint64_t)(R.rp[i + 1] - rp_from) > R.col_capacity) raise(g, ERR_CAPACITY);
 			else {

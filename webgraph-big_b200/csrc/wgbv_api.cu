@@ -566,9 +566,12 @@ static int decode_rows(wgbv_stream *s, int64_t from, int64_t to, Prepared &P, in
 		CU(cudaStreamSynchronize(s->stream));
 		if (!*hf) return WGBV_OK;
 	}
-	if (!P.have_depth && (rc = compute_depth(s, from, P))) return rc;
-	if ((rc = s->halo.ensure((size_t)std::max<int64_t>(P.halo_arcs, 1) * 8))) return rc;
-	R.depth = s->depth.as<uint32_t>();
+	// Shallow chains (max_ref_count <= 8, the usual case): no separate depth pass -- the level-list kernels walk the
+	// chains themselves.  Otherwise (or if a chain turns out longer than the properties promise) k_depth runs first.
+	bool walk = !P.have_depth && g->halo_nodes >= 0 && g->props.max_ref_count <= 8;
+	if (!walk && !P.have_depth && (rc = compute_depth(s, from, P))) return rc;
+	if ((rc = s->halo.ensure((size_t)std::max<int64_t>(P.halo_arcs, 1) * 8)) || (rc = s->depth.ensure((size_t)std::max<int64_t>(P.cnt, 1) * 4))) return rc;
+	R.depth = walk ? nullptr : s->depth.as<uint32_t>();
 	R.halo = s->halo.as<int64_t>();
 	// rows with >= 64 extras go through a global, class-sorted list: at most total_arcs / 64 of them
 	HeavyDev H;
@@ -581,23 +584,37 @@ static int decode_rows(wgbv_stream *s, int64_t from, int64_t to, Prepared &P, in
 	H.cls = s->heavy_cls.as<uint8_t>();
 	H.counters = s->heavy_counters.as<unsigned long long>();
 	launch_extras(L, s->dev, g->def_codes, R, H);
-	if (P.max_depth == 0) {
-	} else if (P.max_depth <= 8) {
+	R.depth = s->depth.as<uint32_t>();
+	uint32_t nlev = walk ? (uint32_t)std::max(g->props.max_ref_count, 0) : P.max_depth;
+	for (int attempt = 0; attempt < 2 && nlev > 0 && nlev <= 8; attempt++) {
 		// shallow chains: ordered lists of the rows of every level
-		const uint32_t nlev = P.max_depth;
 		const size_t nblocks = (size_t)((P.cnt + 2047) / 2048);
 		if ((rc = s->levels.ensure(nlev * nblocks * 4)) || (rc = s->level_pos.ensure((nlev * nblocks + 1) * 8)) ||
 		    (rc = s->list.ensure((size_t)std::max<int64_t>(P.cnt, 1) * 4)) || (rc = s->scan_state.ensure(((nlev * nblocks + 1) / 2048 + 2) * 8)))
 			return rc;
-		launch_level_lists(L, R.depth, P.cnt, nlev, s->levels.as<uint32_t>(), s->level_pos.as<int64_t>(), s->list.as<uint32_t>(),
-		                   s->scan_state.as<uint64_t>(), s->ticket.as<uint32_t>());
+		uint32_t *deep = s->d_err + 3;
+		CU(cudaMemsetAsync(deep, 0, 4, s->stream));
+		launch_level_lists(L, s->dev, walk ? s->ref.as<uint8_t>() : nullptr, s->depth.as<uint32_t>(), P.lo, from, P.cnt, nlev, s->levels.as<uint32_t>(),
+		                   s->level_pos.as<int64_t>(), s->list.as<uint32_t>(), s->scan_state.as<uint64_t>(), s->ticket.as<uint32_t>(), deep);
 		int64_t bounds[9];
+		uint32_t *hdeep = (uint32_t *)(s->h_pin + 10);
 		for (uint32_t l = 0; l <= nlev; l++)
 			CU(cudaMemcpyAsync(&bounds[l], s->level_pos.as<int64_t>() + (size_t)l * nblocks, 8, cudaMemcpyDeviceToHost, s->stream));
+		CU(cudaMemcpyAsync(hdeep, deep, 4, cudaMemcpyDeviceToHost, s->stream));
 		CU(cudaStreamSynchronize(s->stream));
+		if (walk && *hdeep) {
+			// a chain longer than max_ref_count: the properties lied (or the file is malformed); take the general route
+			walk = false;
+			if ((rc = compute_depth(s, from, P))) return rc;
+			nlev = P.max_depth;
+			continue;
+		}
 		for (uint32_t lev = 1; lev <= nlev; lev++)
 			if (bounds[lev] > bounds[lev - 1])
 				launch_copy_level(L, s->dev, g->def_codes, R, lev, s->list.as<uint32_t>() + bounds[lev - 1], (uint64_t)(bounds[lev] - bounds[lev - 1]));
+		nlev = 0;  // done
+	}
+	if (nlev == 0) {
 	} else {
 		// deep chains: one compacted list of rows per level
 		const uint32_t nlev = P.max_depth + 1;
