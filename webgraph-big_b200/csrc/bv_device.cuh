@@ -121,12 +121,24 @@ struct BitReaderT {
 	__device__ __forceinline__ uint32_t peek() const { return __funnelshift_l(lo, hi, sh); }
 	__device__ __forceinline__ void consume(uint32_t n) {  // n in [0, 32]
 		sh += n;
-		if (sh >= 32) {
-			sh -= 32;
-			hi = lo;
-			lo = nxt;
-			nxt = load(++idx);
-			prefetch(idx);
+		if (LDG) {
+			if (sh >= 32) {
+				sh -= 32;
+				hi = lo;
+				lo = nxt;
+				nxt = load(++idx);
+				prefetch(idx);
+			}
+		} else {
+			// words in shared memory: load the candidate unconditionally (cheap, uniform) and select, so that the lanes
+			// of a warp -- which cross word boundaries at different times -- do not split into two instruction streams
+			const uint32_t cand = base[idx + 1 < lim ? idx + 1 : lim - 1];
+			const bool adv = sh >= 32;
+			sh = adv ? sh - 32 : sh;
+			hi = adv ? lo : hi;
+			lo = adv ? nxt : lo;
+			nxt = adv ? cand : nxt;
+			idx += adv ? 1u : 0u;
 		}
 	}
 
