@@ -352,11 +352,11 @@ __device__ __forceinline__ int64_t *row_slot(const RangeDev &R, int64_t i, int64
 static constexpr int RPT = 8;            // rows per thread
 static constexpr int TILE = TPB * RPT;   // rows per block: the sort domain (see the comment on work binning)
 
-// Rows with at least HEAVY extras are not decoded inside their tile: a tile holds only a handful of them, of very
+// Rows with at least HEAVY (128) extras are not decoded inside their tile: a tile holds only a handful of them, of very
 // different lengths, and whichever warp gets them runs nearly empty.  They are appended to a global list, sorted
 // by class over the whole range (k_heavy_scatter), and decoded by k_extras_heavy where every warp finds 32 rows of
 // one class.
-static constexpr uint32_t HEAVY = 64;
+static constexpr uint32_t HEAVY = 128;
 
 // stage 3a: one block per ETILE consecutive nodes.  Rows without a reference come out complete.
 // The records of consecutive rows are contiguous in the bit stream, so the block first copies the tile's whole span
