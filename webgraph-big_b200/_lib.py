@@ -4,7 +4,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libwgbv.so")
+LIB_PATH = os.environ.get("WGBV_LIBRARY") or os.path.join(_HERE, "lib", "libwgbv.so")  # WGBV_LIBRARY: another build of the same library
 
 OK, EINDEX, ESTATE, EIO, EUNSUPPORTED, ECUDA, EARG = 0, -1, -2, -3, -4, -5, -6
 
