@@ -263,8 +263,8 @@ static constexpr int LTILE = TPB * 8;
 // reference array, which stage 1 left in memory) and stores them for the kernels that follow, so that the separate
 // depth pass is not needed; a chain longer than nlevels sets *deep and the host falls back to k_depth.
 __global__ void __launch_bounds__(TPB) k_level_block_counts(GraphDev g, const uint8_t *__restrict__ ref, uint32_t *depth, int64_t lo, int64_t from,
-                                                            int64_t count, uint32_t nlevels, uint32_t nblocks, uint32_t *__restrict__ counts,
-                                                            uint32_t *deep) {
+                                                            int64_t count, uint32_t level0, uint32_t nlevels, uint32_t nblocks,
+                                                            uint32_t *__restrict__ counts, uint32_t *deep) {
 	__shared__ uint32_t s_cnt[LEVELS_MAX + 1];
 	if (threadIdx.x <= LEVELS_MAX) s_cnt[threadIdx.x] = 0;
 	__syncthreads();
@@ -287,6 +287,7 @@ __global__ void __launch_bounds__(TPB) k_level_block_counts(GraphDev g, const ui
 				depth[i] = d;
 			} else d = depth[i];
 		}
+		d = (d > level0 && d < DEPTH_INVALID) ? d - level0 : 0u;  // levels level0+1 .. level0+nlevels are listed in this pass
 		for (uint32_t l = 1; l <= nlevels; l++) {
 			const unsigned m = __ballot_sync(0xffffffffu, d == l);
 			if ((threadIdx.x & 31) == 0 && m) atomicAdd(&s_cnt[l], (uint32_t)__popc(m));
@@ -296,7 +297,7 @@ __global__ void __launch_bounds__(TPB) k_level_block_counts(GraphDev g, const ui
 	if (threadIdx.x >= 1 && threadIdx.x <= nlevels) counts[(size_t)(threadIdx.x - 1) * nblocks + blockIdx.x] = s_cnt[threadIdx.x];
 }
 
-__global__ void __launch_bounds__(TPB) k_level_fill(const uint32_t *__restrict__ depth, int64_t count, uint32_t nlevels,
+__global__ void __launch_bounds__(TPB) k_level_fill(const uint32_t *__restrict__ depth, int64_t count, uint32_t level0, uint32_t nlevels,
                                                     uint32_t nblocks, const int64_t *__restrict__ pos, uint32_t *__restrict__ list) {
 	__shared__ uint32_t s_cnt[8][TPB / 32][LEVELS_MAX + 1];  // rows of each level per (iteration, warp), then their prefix
 	const int64_t base = (int64_t)blockIdx.x * LTILE;
@@ -304,7 +305,8 @@ __global__ void __launch_bounds__(TPB) k_level_fill(const uint32_t *__restrict__
 	uint32_t myd[8], myrank[8];
 	for (int q = 0; q < 8; q++) {
 		const int64_t i = base + q * TPB + threadIdx.x;
-		const uint32_t d = i < count ? depth[i] : 0u;
+		uint32_t d = i < count ? depth[i] : 0u;
+		d = (d > level0 && d < DEPTH_INVALID) ? d - level0 : 0u;
 		myd[q] = d;
 		myrank[q] = 0;
 		for (uint32_t l = 1; l <= nlevels; l++) {
@@ -335,12 +337,13 @@ __global__ void __launch_bounds__(TPB) k_level_fill(const uint32_t *__restrict__
 }
 
 void launch_level_lists(const Launch &L, const GraphDev &g, const uint8_t *ref, uint32_t *depth, int64_t lo, int64_t from, int64_t count,
-                        uint32_t nlevels, uint32_t *counts, int64_t *pos, uint32_t *list, uint64_t *scan_state, uint32_t *ticket, uint32_t *deep) {
+                        uint32_t level0, uint32_t nlevels, uint32_t *counts, int64_t *pos, uint32_t *list, uint64_t *scan_state, uint32_t *ticket,
+                        uint32_t *deep) {
 	const uint32_t nblocks = grid_for(count, LTILE);
-	k_level_block_counts<<<nblocks, TPB, 0, L.stream>>>(g, ref, depth, lo, from, count, nlevels, nblocks, counts, deep);
+	k_level_block_counts<<<nblocks, TPB, 0, L.stream>>>(g, ref, depth, lo, from, count, level0, nlevels, nblocks, counts, deep);
 	WGBV_LAUNCHED(L);
 	launch_scan(L, counts, pos, (int64_t)nlevels * nblocks, scan_state, ticket);
-	k_level_fill<<<nblocks, TPB, 0, L.stream>>>(depth, count, nlevels, nblocks, pos, list);
+	k_level_fill<<<nblocks, TPB, 0, L.stream>>>(depth, count, level0, nlevels, nblocks, pos, list);
 	WGBV_LAUNCHED(L);
 }
 

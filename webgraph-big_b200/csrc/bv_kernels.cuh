@@ -71,10 +71,11 @@ void launch_level_count(const Launch &L, const uint32_t *depth, int64_t count, u
 void launch_level_scatter(const Launch &L, const uint32_t *depth, int64_t count, uint32_t nlevels,
                           unsigned long long *level_cursor, uint32_t *list);
 // ordered level lists for shallow chains (nlevels <= 8): counts and pos hold nlevels * ceil(count / 2048) entries (+1 for pos);
-// level l (1-based) occupies list[pos[(l-1) * nblocks] .. pos[l * nblocks]).  With ref != nullptr the depths are computed
+// the pass lists levels level0+1 .. level0+nlevels; level level0+l (l 1-based) occupies list[pos[(l-1) * nblocks] .. pos[l * nblocks]).  With ref != nullptr the depths are computed
 // on the way (bounded walk, *deep set if a chain is longer than nlevels) and stored to depth[]; with ref == nullptr depth[] is input.
 void launch_level_lists(const Launch &L, const GraphDev &g, const uint8_t *ref, uint32_t *depth, int64_t lo, int64_t from, int64_t count,
-                        uint32_t nlevels, uint32_t *counts, int64_t *pos, uint32_t *list, uint64_t *scan_state, uint32_t *ticket, uint32_t *deep);
+                        uint32_t level0, uint32_t nlevels, uint32_t *counts, int64_t *pos, uint32_t *list, uint64_t *scan_state, uint32_t *ticket,
+                        uint32_t *deep);
 // stage 3a: intervals + residuals of every row (whole row when it has no reference)
 void launch_extras(const Launch &L, const GraphDev &g, int def, const RangeDev &r, const HeavyDev &h);
 // stage 3b: copy-block resolution of the rows at one depth level; list == nullptr: every node is inspected

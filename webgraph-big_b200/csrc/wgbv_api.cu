@@ -594,7 +594,7 @@ static int decode_rows(wgbv_stream *s, int64_t from, int64_t to, Prepared &P, in
 			return rc;
 		uint32_t *deep = s->d_err + 3;
 		CU(cudaMemsetAsync(deep, 0, 4, s->stream));
-		launch_level_lists(L, s->dev, walk ? s->ref.as<uint8_t>() : nullptr, s->depth.as<uint32_t>(), P.lo, from, P.cnt, nlev, s->levels.as<uint32_t>(),
+		launch_level_lists(L, s->dev, walk ? s->ref.as<uint8_t>() : nullptr, s->depth.as<uint32_t>(), P.lo, from, P.cnt, 0, nlev, s->levels.as<uint32_t>(),
 		                   s->level_pos.as<int64_t>(), s->list.as<uint32_t>(), s->scan_state.as<uint64_t>(), s->ticket.as<uint32_t>(), deep);
 		int64_t bounds[9];
 		uint32_t *hdeep = (uint32_t *)(s->h_pin + 10);
@@ -616,23 +616,23 @@ static int decode_rows(wgbv_stream *s, int64_t from, int64_t to, Prepared &P, in
 	}
 	if (nlev == 0) {
 	} else {
-		// deep chains: one compacted list of rows per level
-		const uint32_t nlev = P.max_depth + 1;
-		if ((rc = s->levels.ensure((size_t)(nlev + 1) * 8 * 2)) || (rc = s->list.ensure((size_t)std::max<int64_t>(P.cnt, 1) * 4))) return rc;
-		unsigned long long *counts = s->levels.as<unsigned long long>();
-		unsigned long long *cursor = counts + nlev + 1;
-		CU(cudaMemsetAsync(counts, 0, (size_t)(nlev + 1) * 8, s->stream));
-		launch_level_count(L, R.depth, P.cnt, nlev, counts);
-		std::vector<unsigned long long> h(nlev + 1), start(nlev + 1);
-		CU(cudaMemcpyAsync(h.data(), counts, (size_t)(nlev + 1) * 8, cudaMemcpyDeviceToHost, s->stream));
-		CU(cudaStreamSynchronize(s->stream));
-		unsigned long long acc = 0;
-		for (uint32_t i = 0; i <= nlev; i++) { start[i] = acc; acc += h[i]; }
-		CU(cudaMemcpyAsync(cursor, start.data(), (size_t)(nlev + 1) * 8, cudaMemcpyHostToDevice, s->stream));
-		launch_level_scatter(L, R.depth, P.cnt, nlev, cursor, s->list.as<uint32_t>());
-		CU(cudaStreamSynchronize(s->stream));  // `start` must outlive the copy above
-		for (uint32_t lev = 1; lev <= P.max_depth; lev++)
-			if (h[lev]) launch_copy_level(L, s->dev, g->def_codes, R, lev, s->list.as<uint32_t>() + start[lev], h[lev]);
+		// deep chains (depths from k_depth): the same ordered lists, eight levels per pass
+		const size_t nblocks = (size_t)((P.cnt + 2047) / 2048);
+		if ((rc = s->levels.ensure(8 * nblocks * 4)) || (rc = s->level_pos.ensure((8 * nblocks + 1) * 8)) ||
+		    (rc = s->list.ensure((size_t)std::max<int64_t>(P.cnt, 1) * 4)) || (rc = s->scan_state.ensure(((8 * nblocks + 1) / 2048 + 2) * 8)))
+			return rc;
+		for (uint32_t level0 = 0; level0 < P.max_depth; level0 += 8) {
+			const uint32_t n8 = std::min<uint32_t>(8, P.max_depth - level0);
+			launch_level_lists(L, s->dev, nullptr, s->depth.as<uint32_t>(), P.lo, from, P.cnt, level0, n8, s->levels.as<uint32_t>(),
+			                   s->level_pos.as<int64_t>(), s->list.as<uint32_t>(), s->scan_state.as<uint64_t>(), s->ticket.as<uint32_t>(), s->d_err + 3);
+			int64_t bounds[9];
+			for (uint32_t l = 0; l <= n8; l++)
+				CU(cudaMemcpyAsync(&bounds[l], s->level_pos.as<int64_t>() + (size_t)l * nblocks, 8, cudaMemcpyDeviceToHost, s->stream));
+			CU(cudaStreamSynchronize(s->stream));
+			for (uint32_t l = 1; l <= n8; l++)
+				if (bounds[l] > bounds[l - 1])
+					launch_copy_level(L, s->dev, g->def_codes, R, level0 + l, s->list.as<uint32_t>() + bounds[l - 1], (uint64_t)(bounds[l] - bounds[l - 1]));
+		}
 	}
 	cudaEventRecord(s->ev[4], s->stream);
 	s->ev_valid = true;
