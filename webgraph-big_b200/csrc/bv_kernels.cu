@@ -370,6 +370,11 @@ static constexpr int ERPT = 4;
 static constexpr int ETILE = TPB * ERPT;
 static constexpr int EBITS = 9216;  // 32-bit words of the stream a tile may stage (36 KiB)
 
+__device__ __forceinline__ void cp_async16(void *smem_dst, const void *gmem_src) {
+	const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+	asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gmem_src));
+}
+
 struct ExtrasSmem {
 	uint32_t bits[EBITS];
 	uint64_t pos[ETILE];
@@ -467,16 +472,47 @@ __global__ void __launch_bounds__(TPB) k_extras(GraphDev g, RangeDev R, HeavyDev
 	const int64_t base = (int64_t)blockIdx.x * ETILE;
 	const int64_t count = R.hi - R.lo;
 	const int64_t rp_from = R.rp[R.from - R.lo];
+	const int64_t tend = base + ETILE < count ? base + ETILE : count;
 	if (threadIdx.x == 0) S.span[0] = ef_get(g, R.lo + base);
-	if (threadIdx.x == 32) S.span[1] = ef_get(g, R.lo + (base + ETILE < count ? base + ETILE : count));
+	if (threadIdx.x == 32) S.span[1] = ef_get(g, R.lo + tend);
+	// everything the heads are going to read, asked for up front (the reads themselves are dependent chains):
+	// degrees, references and row pointers of the tile, and the tile's part of the Elias-Fano arrays
+	{
+		const char *p;
+		const int t = threadIdx.x;
+		p = (const char *)(R.deg + base) + (size_t)t * 128;
+		if (p < (const char *)(R.deg + tend)) prefetch_l1(p);
+		p = (const char *)(R.rp + base) + (size_t)t * 128;
+		if (p < (const char *)(R.rp + tend + 1)) prefetch_l1(p);
+		p = (const char *)(R.ref + base) + (size_t)t * 128;
+		if (p < (const char *)(R.ref + tend)) prefetch_l1(p);
+		const uint64_t e0 = (uint64_t)(R.lo + base - g.ef_first), e1 = (uint64_t)(R.lo + tend - g.ef_first);
+		p = (const char *)(g.ef_lower + (e0 * (uint64_t)g.ef_l >> 6)) + (size_t)t * 128;
+		if (p <= (const char *)(g.ef_lower + (e1 * (uint64_t)g.ef_l >> 6))) prefetch_l1(p);
+		p = (const char *)(g.ef_hints + (e0 >> 6)) + (size_t)t * 128;
+		if (p <= (const char *)(g.ef_hints + (e1 >> 6))) prefetch_l1(p);
+	}
 	__syncthreads();
-	const uint64_t w0 = S.span[0] >> 5;
-	const uint64_t nw = ((S.span[1] + 31) >> 5) - w0 + 2;
+	// the upper-bits words of the tile lie between the positions of its first and last element
+	{
+		const uint64_t e0 = (uint64_t)(R.lo + base - g.ef_first), e1 = (uint64_t)(R.lo + tend - g.ef_first);
+		const uint64_t u0 = ((S.span[0] >> g.ef_l) + e0) >> 6, u1 = ((S.span[1] >> g.ef_l) + e1) >> 6;
+		const char *p = (const char *)(g.ef_upper + u0) + (size_t)threadIdx.x * 128;
+		if (p <= (const char *)(g.ef_upper + u1)) prefetch_l1(p);
+	}
+	const uint64_t w0 = (S.span[0] >> 5) & ~3ull;  // 16-byte aligned: the staging copies are 16 bytes each
+	const uint64_t nw = ((((S.span[1] + 31) >> 5) - w0 + 2) + 3) & ~3ull;
 	const bool staged = nw <= (uint64_t)EBITS;
 	if (staged) {
 		const uint64_t avail = g.nwords * 2 > w0 ? g.nwords * 2 - w0 : 0;
 		const uint32_t *src = (const uint32_t *)g.words + w0;
-		for (uint32_t w = threadIdx.x; w < (uint32_t)nw; w += TPB) S.bits[w] = w < avail ? __ldg(src + w) : 0u;
+		// asynchronous 16-byte copies (LDGSTS): all of them in flight before anything waits
+		for (uint32_t w = threadIdx.x * 4; w < (uint32_t)nw; w += TPB * 4) {
+			if (w + 4 <= avail) cp_async16(&S.bits[w], src + w);
+			else
+				for (int j = 0; j < 4; j++) S.bits[w + j] = w + j < avail ? __ldg(src + w + j) : 0u;
+		}
+		asm volatile("cp.async.wait_all;" ::: "memory");
 		if (threadIdx.x == 0) { S.wbase = w0; S.nw = (uint32_t)nw; }
 	}
 	__syncthreads();
