@@ -195,10 +195,10 @@ __device__ __forceinline__ void row_copy(const GraphDev &g, RD &r, const int64_t
 				const int64_t c = src[k];
 				// both streams are read one element at a time and each new 32-byte sector would cost a full memory round trip:
 				// ask for the sectors two ahead (no register, no wait)
-				if ((k & 3u) == 0) prefetch_l1(src + k + 8);
+				if ((k & 3u) == 0 && k + 8 < dref) prefetch_l1(src + k + 8);
 				if (e < c) {
 					dst[out++] = e;
-					if ((ei & 3u) == 0) prefetch_l1(ext + ei + 8);
+					if ((ei & 3u) == 0 && ei + 8 < ne) prefetch_l1(ext + ei + 8);
 					e = ++ei < ne ? ext[ei] : INT64_MAX;
 				} else {
 					if (e == c) raise(g, ERR_NOT_SORTED);
