@@ -418,6 +418,13 @@ __device__ __forceinline__ void extras_tile(const GraphDev &g, const RangeDev &R
 				RowHead h;
 				const uint32_t rf = R.ref[i];
 				row_head<DEF>(g, r, rf ? R.deg[i - rf] : 0, h);
+				if (rf && R.info) {
+					RowInfo ri;
+					ri.blocks_pos = h.blocks_pos + (RD::IS_GLOBAL ? 0ull : (S.wbase << 5));
+					ri.ncopied = h.ncopied;
+					ri.bc = h.bc;
+					R.info[i] = ri;
+				}
 				const uint32_t nextra = h.d - h.ncopied;
 				if (nextra) {
 					// rows with intervals first inside each class: warps without any skip the merging loop of row_extras
@@ -742,11 +749,20 @@ __global__ void __launch_bounds__(TPB) k_copy_level(GraphDev g, RangeDev R, uint
 			if (t < list_count) i = list[t];
 		} else if ((int64_t)t < R.hi - R.lo && R.depth[t] == level) i = (int64_t)t;
 		if (i >= 0 && R.deg[i] != 0 && !(R.lo + i >= R.from && (uint64_t)(R.rp[i + 1] - rp_from) > R.col_capacity)) {
-			const uint32_t rf = R.ref[i];
-			BitReader r;
-			r.init(g, ef_get(g, R.lo + i));
 			RowHead h;
-			row_head<DEF>(g, r, R.deg[i - rf], h);
+			if (R.info) {
+				// stage 3a left what it parsed
+				const RowInfo ri = R.info[i];
+				h.d = R.deg[i];
+				h.ncopied = ri.ncopied;
+				h.bc = ri.bc;
+				h.blocks_pos = ri.blocks_pos;
+			} else {
+				const uint32_t rf = R.ref[i];
+				BitReader r;
+				r.init(g, ef_get(g, R.lo + i));
+				row_head<DEF>(g, r, R.deg[i - rf], h);
+			}
 			if (h.ncopied) {
 				bucket[q] = 2 * work_bucket(h.d);  // the merge loop runs up to d times (copied + extras moved forward)
 				S.pos[id] = h.blocks_pos;

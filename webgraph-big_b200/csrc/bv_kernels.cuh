@@ -12,6 +12,14 @@ enum : uint32_t {
 	DEPTH_INVALID = 0xfffffffeu,     // chain leaves the decodable range (halo rows only)
 };
 
+// What stage 3a learns about a row with a reference and stage 3b needs again: kept so that the copy kernels do not
+// have to look the row's offset up and parse its head a second time.
+struct RowInfo {
+	uint64_t blocks_pos;  // bit position of the first block
+	uint32_t ncopied;     // successors copied from the reference row
+	uint32_t bc;          // block count
+};
+
 // One bulk decode job: nodes [lo, hi) are decoded, of which [from, hi) were requested; [lo, from) is the halo.
 struct RangeDev {
 	int64_t lo, from, hi;
@@ -22,6 +30,7 @@ struct RangeDev {
 	int64_t *col;           // successors of [from, hi): row x starts at col + rp[x-lo] - rp[from-lo]
 	int64_t *halo;          // successors of [lo, from): row x starts at halo + rp[x-lo]
 	uint64_t col_capacity;  // elements available at col
+	RowInfo *info;          // written by k_extras for every row with a reference, read by k_copy_level (may be nullptr)
 };
 
 // One random-access job list: `rows` chain rows, each decoded into its own slot.

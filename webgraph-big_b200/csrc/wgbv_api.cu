@@ -70,7 +70,7 @@ struct wgbv_stream {
 	uint64_t *h_pin = nullptr;  // pinned host scratch for read-backs (16 words)
 	uint64_t launches = 0;
 	DevBuf deg, ref, depth, rp, scan_state, ticket, halo, levels, list, col, rowptr, ids, batch;
-	DevBuf heavy_rows, heavy_sorted, heavy_cls, heavy_counters, tile_scratch, level_pos;
+	DevBuf heavy_rows, heavy_sorted, heavy_cls, heavy_counters, tile_scratch, level_pos, row_info;
 	bool force_levels = true;   // false: use the fused tile kernel where it applies (WGBV_TILE=1)
 	DevBuf c_node, c_dst, c_parent, c_deg, c_isq, c_level, c_len, c_arcs, c_row0, c_soff, c_store;
 	cudaEvent_t ev[6]{};
@@ -380,7 +380,7 @@ extern "C" void wgbv_stream_destroy(wgbv_stream *s) {
 	cudaSetDevice(s->g->device);
 	if (s->stream) cudaStreamSynchronize(s->stream);
 	for (DevBuf *b : {&s->deg, &s->ref, &s->depth, &s->rp, &s->scan_state, &s->ticket, &s->halo, &s->levels, &s->list, &s->col,
-	                  &s->rowptr, &s->ids, &s->batch, &s->heavy_rows, &s->heavy_sorted, &s->heavy_cls, &s->heavy_counters, &s->tile_scratch, &s->level_pos, &s->c_node, &s->c_dst, &s->c_parent, &s->c_deg, &s->c_isq, &s->c_level,
+	                  &s->rowptr, &s->ids, &s->batch, &s->heavy_rows, &s->heavy_sorted, &s->heavy_cls, &s->heavy_counters, &s->tile_scratch, &s->level_pos, &s->row_info, &s->c_node, &s->c_dst, &s->c_parent, &s->c_deg, &s->c_isq, &s->c_level,
 	                  &s->c_len, &s->c_arcs, &s->c_row0, &s->c_soff, &s->c_store})
 		b->release();
 	for (auto &sl : s->slot) {
@@ -547,6 +547,7 @@ static int decode_rows(wgbv_stream *s, int64_t from, int64_t to, Prepared &P, in
 	R.col = d_col;
 	R.halo = s->halo.as<int64_t>();
 	R.col_capacity = col_capacity;
+	R.info = nullptr;
 	// Bounded reference chains: the fused tile kernel decodes everything on chip in one launch.  The
 	// level-synchronous kernels below remain the general path (unbounded chains, tiles that fit nowhere).
 	if (g->halo_nodes >= 0 && g->halo_nodes <= TILE_MAX_HALO && !s->force_levels) {
@@ -573,6 +574,8 @@ static int decode_rows(wgbv_stream *s, int64_t from, int64_t to, Prepared &P, in
 	if ((rc = s->halo.ensure((size_t)std::max<int64_t>(P.halo_arcs, 1) * 8)) || (rc = s->depth.ensure((size_t)std::max<int64_t>(P.cnt, 1) * 4))) return rc;
 	R.depth = walk ? nullptr : s->depth.as<uint32_t>();
 	R.halo = s->halo.as<int64_t>();
+	if ((rc = s->row_info.ensure((size_t)std::max<int64_t>(P.cnt, 1) * sizeof(RowInfo)))) return rc;
+	R.info = s->row_info.as<RowInfo>();
 	// rows with >= 64 extras go through a global, class-sorted list: at most total_arcs / 64 of them
 	HeavyDev H;
 	const size_t hcap = (size_t)((P.arcs + P.halo_arcs) / 64 + 1);
