@@ -274,7 +274,15 @@ def main():
     # device time so that no stage is hidden
     dom_ms = float(stage_ms[4])
     achieved = alg_bytes / (dom_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+    # DRAM bytes actually moved per step, from the committed ncu capture of this very workload (None for other sizes)
+    traffic = None
+    try:
+        tr = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))
+        if args.nodes == 100_000_000 and args.maxref == 3 and args.max_degree == 10000:
+            traffic = tr["dram_bytes_per_step"]
+    except Exception:
+        pass
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                 "peak_source": peak_src, "kernel": "whole decode (header + scan + depth + successor decode)",
                 "algorithmic_bytes_per_step": alg_bytes, "stage_ms": {"header": float(stage_ms[0]), "scan": float(stage_ms[1]),
                                                                      "depth": float(stage_ms[2]), "successors": float(stage_ms[3]),
