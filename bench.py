@@ -300,11 +300,10 @@ def main():
         barrier()
         t0 = time.perf_counter()
         for _ in range(max(1, args.e2e_steps)):
-            g.uploadStream(h_graph.data_ptr(), e.graph.size)
             got = 0
-            # the streaming form of nodeIterator(): chunks arrive in pinned host buffers owned by the library while the
-            # following chunks are still being decoded and copied
-            for a, b, rp, col in g.scan(first, first + n, chunk):
+            # the streaming form of nodeIterator(): the compressed stream goes up piece by piece from pinned host memory,
+            # chunks come back in pinned host buffers owned by the library while the following chunks are decoded
+            for a, b, rp, col in g.scan(first, first + n, chunk, upload=(h_graph.data_ptr(), e.graph.size)):
                 got += col.size
                 d2h += (b - a + 1) * 8 + col.size * 8
                 consumed[0] += int(rp[-1]) + (int(col[-1]) if col.size else 0)  # touch the result on the host
@@ -316,8 +315,8 @@ def main():
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         e2e = {"value": total_arcs / float(tt.item()), "unit": UNIT, "h2d_bytes_per_step": int(e.graph.size) * world,
                "d2h_bytes_per_step": int(d2h // max(1, args.e2e_steps)) * world, "ms_per_step": float(tt.item()) * 1e3,
-               "how": f"wgbv_upload_stream (pinned host -> device) + wgbv_scan_* over {chunk}-node chunks: decode on the device, "
-                      "copy-back to pinned host buffers overlapped with the decode of the next chunk"}
+               "how": f"wgbv_scan_begin_upload / wgbv_scan_next over {chunk}-node chunks: upload of the compressed stream from pinned "
+                      "host memory, decode on the device and copy-back to pinned host buffers, the three overlapped chunk by chunk"}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:

@@ -184,6 +184,11 @@ WGBV_API int wgbv_decode_csr_host(wgbv_stream *s, int64_t from, int64_t to, int6
  *   wgbv_scan_end     waits for outstanding work and ends the scan.
  */
 WGBV_API int wgbv_scan_begin(wgbv_stream *s, int64_t from, int64_t to, int64_t chunk_nodes);
+/* The same scan for callers that keep the compressed graph in (pinned) host memory and stream it in for every pass:
+ * the bit stream is uploaded piece by piece while the scan runs -- the words of chunk k+1 travel to the device while
+ * chunk k is decoded and chunk k-1 is copied back -- instead of in one wgbv_upload_stream before it.  `graph` must be
+ * the buffer (or an identical copy) the handle was opened from; `from` must be the first node of the handle. */
+WGBV_API int wgbv_scan_begin_upload(wgbv_stream *s, const uint8_t *graph, uint64_t graph_bytes, int64_t from, int64_t to, int64_t chunk_nodes);
 WGBV_API int wgbv_scan_next(wgbv_stream *s, int64_t *first, int64_t *last, const int64_t **h_rowptr, const int64_t **h_col, int64_t *arcs);
 WGBV_API void wgbv_scan_end(wgbv_stream *s);
 

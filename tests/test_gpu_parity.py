@@ -318,3 +318,50 @@ def test_streaming_scan_equals_golden(cnr, cnr_golden):
     it.close()
     rp, c = cnr.decodeToCSR(0, 100)
     assert np.array_equal(c, col[:rowptr[100]])
+
+
+def test_streaming_scan_with_upload(cnr_basename, cnr_golden):
+    """wgbv_scan_begin_upload: the bit stream is re-sent piece by piece during the scan; results must not change, also
+    when the scan is abandoned half way (the rest of the stream is then sent before the handle is used again)."""
+    torch = pytest.importorskip("torch")
+    deg, rowptr, col = cnr_golden
+    raw = np.fromfile(cnr_basename + ".graph", dtype=np.uint8)
+    pinned = torch.empty(raw.size + 16, dtype=torch.uint8, pin_memory=True)
+    pinned[: raw.size] = torch.from_numpy(raw)
+    with wg.GpuBVGraph.load(cnr_basename) as g:
+        n = g.numNodes()
+        for chunk in (40000, 1 << 20):
+            nxt = 0
+            for a, b, rp, c in g.scan(0, n, chunk, upload=(pinned.data_ptr(), raw.size)):
+                assert a == nxt
+                nxt = b
+                assert np.array_equal(rp, rowptr[a:b + 1] - rowptr[a]) and np.array_equal(c, col[rowptr[a]:rowptr[b]])
+            assert nxt == n
+        it = g.scan(0, n, 30000, upload=(pinned.data_ptr(), raw.size))
+        next(it)
+        it.close()
+        rp, c = g.decodeToCSR(n - 5000, n)
+        assert np.array_equal(c, col[rowptr[n - 5000]:])
+
+
+def test_open_slice_with_halo():
+    """wgbv_open_slice: a process that holds only its own byte range of the file (plus the window*maxref halo)."""
+    e = bg.copy_model(30000, seed=21, mean_degree=14, nsplits=1)
+    deg, col = oracle_of(e).decode_range()
+    rowptr = rowptr_of(deg)
+    lo, hi, halo = 12000, 25000, 21
+    first = lo - halo
+    byte0 = int(e.offsets[first]) // 8
+    byte1 = (int(e.offsets[hi]) + 7) // 8
+    rel = e.offsets[first:hi + 1].astype(np.int64) - 8 * byte0
+    deltas = np.concatenate([rel[:1], np.diff(rel)]).astype(np.uint64)
+    off_stream, _ = bg.write_codes(bg.GAMMA, deltas)
+    g = wg.GpuBVGraph.load_slice(e.properties_text(), first, hi - first, e.graph[byte0:byte1], off_stream, halo_nodes=halo)
+    assert g.shardRange() == (lo, hi) and g.numNodes() == 30000
+    rp, c = g.decodeToCSR()
+    assert np.array_equal(rp, rowptr[lo:hi + 1] - rowptr[lo]) and np.array_equal(c, col[rowptr[lo]:rowptr[hi]])
+    rp2, c2 = g.successorsBatch(np.array([lo, hi - 1, 20000], dtype=np.int64))
+    assert np.array_equal(c2, np.concatenate([col[rowptr[x]:rowptr[x + 1]] for x in (lo, hi - 1, 20000)]))
+    with pytest.raises(wg.IllegalArgumentException):
+        g.decodeToCSR(lo - 1, hi)
+    g.close()

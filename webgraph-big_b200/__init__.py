@@ -266,7 +266,7 @@ class GpuBVGraph:
                                           col.size, C.byref(arcs)))
         return rowptr, col
 
-    def scan(self, from_=None, to=None, chunk_nodes=1 << 20):
+    def scan(self, from_=None, to=None, chunk_nodes=1 << 20, upload=None):
         """Streaming scan of [from, to): yields (first, last, rowptr, col) per chunk of nodes, rowptr relative to the chunk.
         The arrays are views of pinned buffers owned by the library and are only valid until the next chunk is requested
         (the reference's rule for iterator arrays, BVG:1171-1172); decode and copy-back of the following chunks overlap
@@ -274,7 +274,10 @@ class GpuBVGraph:
         from_ = self._lo if from_ is None else from_
         to = self._hi if to is None else to
         L = _lib.lib()
-        _lib.check(L.wgbv_scan_begin(self._st.h, from_, to, chunk_nodes))
+        if upload is None:
+            _lib.check(L.wgbv_scan_begin(self._st.h, from_, to, chunk_nodes))
+        else:  # (host pointer, bytes) of the compressed stream: uploaded piece by piece while the scan runs
+            _lib.check(L.wgbv_scan_begin_upload(self._st.h, C.c_void_p(upload[0]), upload[1], from_, to, chunk_nodes))
         first, last, arcs = C.c_int64(), C.c_int64(), C.c_int64()
         rp, col = C.c_void_p(), C.c_void_p()
         try:

@@ -69,6 +69,7 @@ SYMBOLS = [
     ("wgbv_decode_csr", C.c_int, [_P, C.c_int64, C.c_int64, _P, _P, C.c_uint64]),
     ("wgbv_decode_csr_host", C.c_int, [_P, C.c_int64, C.c_int64, _P, _P, C.c_uint64, C.POINTER(C.c_int64)]),
     ("wgbv_scan_begin", C.c_int, [_P, C.c_int64, C.c_int64, C.c_int64]),
+    ("wgbv_scan_begin_upload", C.c_int, [_P, _P, C.c_uint64, C.c_int64, C.c_int64, C.c_int64]),
     ("wgbv_scan_next", C.c_int, [_P, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(_P), C.POINTER(_P), C.POINTER(C.c_int64)]),
     ("wgbv_scan_end", None, [_P]),
     ("wgbv_outdegrees", C.c_int, [_P, _P, C.c_uint64, _P]),

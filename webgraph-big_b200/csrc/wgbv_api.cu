@@ -88,7 +88,11 @@ struct wgbv_stream {
 	};
 	static constexpr int SCAN_SLOTS = 3;
 	ScanSlot slot[SCAN_SLOTS];
-	cudaStream_t copy_stream = nullptr;
+	cudaStream_t copy_stream = nullptr, upload_stream = nullptr;
+	cudaEvent_t uploaded[2]{};          // the words a chunk needs are on the device (alternating)
+	const uint8_t *up_graph = nullptr;  // host copy of the bit stream to upload while scanning (wgbv_scan_begin_upload)
+	uint64_t up_next_word = 0;          // first 64-bit unit of the device buffer not uploaded yet
+	int64_t up_chunks = 0;              // chunks whose words have been queued
 	bool scanning = false;
 	int64_t scan_to = 0, scan_chunk = 0, scan_issue = 0, scan_take = 0;  // next node to issue / to hand out
 	int64_t issued = 0, taken = 0;                                       // chunks issued / handed out
@@ -393,6 +397,8 @@ extern "C" void wgbv_stream_destroy(wgbv_stream *s) {
 		if (sl.ready) cudaEventDestroy(sl.ready);
 	}
 	if (s->copy_stream) cudaStreamDestroy(s->copy_stream);
+	if (s->upload_stream) cudaStreamDestroy(s->upload_stream);
+	for (auto &e : s->uploaded) if (e) cudaEventDestroy(e);
 	if (s->d_err) cudaFree(s->d_err);
 	if (s->h_pin) cudaFreeHost(s->h_pin);
 	for (auto &e : s->ev) if (e) cudaEventDestroy(e);
@@ -701,11 +707,40 @@ static int pinned_ensure(int64_t **p, size_t *cap, size_t elems) {
 	return WGBV_OK;
 }
 
+// Streaming upload: queues, on the upload stream, the part of the bit stream that chunk number `c` (nodes up to `b`)
+// needs and that has not been sent yet.  Pieces are disjoint 64-bit-unit ranges in stream order, each ending with the
+// unit that holds the last bit of its chunk, so a piece never rewrites words an earlier chunk may still be reading.
+static int scan_upload_chunk(wgbv_stream *s, int64_t c, int64_t b) {
+	wgbv_graph *g = s->g;
+	if (c < s->up_chunks) return WGBV_OK;
+	const uint64_t end_bit = g->ef.get((uint64_t)(b - g->avail_lo));  // relative to the first resident word
+	uint64_t end_word = b >= s->scan_to ? g->data_words : std::min<uint64_t>(g->data_words, (end_bit >> 6) + 1);
+	if (end_word > s->up_next_word) {
+		const uint64_t w0 = s->up_next_word, n = end_word - w0;
+		const uint64_t src0 = g->byte0 + w0 * 8, avail = g->byte1 > src0 ? g->byte1 - src0 : 0;
+		const uint64_t bytes = std::min<uint64_t>(n * 8, avail);
+		if (bytes < n * 8) CU(cudaMemsetAsync(g->d_words + w0 + bytes / 8, 0, (size_t)(n * 8 - (bytes / 8) * 8), s->upload_stream));
+		if (bytes) CU(cudaMemcpyAsync(g->d_words + w0, s->up_graph + src0, (size_t)bytes, cudaMemcpyHostToDevice, s->upload_stream));
+		Launch L{s->upload_stream, &s->launches};
+		launch_bswap(L, g->d_words + w0, n);
+		s->up_next_word = end_word;
+	}
+	CU(cudaEventRecord(s->uploaded[c & 1], s->upload_stream));
+	s->up_chunks = c + 1;
+	return WGBV_OK;
+}
+
 // Queues the decode of the next chunk and its copy back to pinned host memory.
 static int scan_issue_one(wgbv_stream *s) {
 	wgbv_stream::ScanSlot &sl = s->slot[s->issued % wgbv_stream::SCAN_SLOTS];
 	const int64_t a = s->scan_issue, b = std::min(a + s->scan_chunk, s->scan_to);
 	int rc;
+	if (s->up_graph) {
+		// this chunk's words, then (so that they travel while this chunk is decoded) the next chunk's
+		if ((rc = scan_upload_chunk(s, s->issued, b))) return rc;
+		CU(cudaStreamWaitEvent(s->stream, s->uploaded[s->issued & 1], 0));
+		if (b < s->scan_to && (rc = scan_upload_chunk(s, s->issued + 1, std::min(b + s->scan_chunk, s->scan_to)))) return rc;
+	}
 	if ((rc = sl.d_rowptr.ensure((size_t)(b - a + 1) * 8))) return rc;
 	Prepared P;
 	if ((rc = prepare(s, a, b, sl.d_rowptr.as<int64_t>(), P))) return rc;  // synchronises `stream`: the previous chunk is decoded
@@ -742,11 +777,32 @@ extern "C" int wgbv_scan_begin(wgbv_stream *s, int64_t from, int64_t to, int64_t
 		}
 	}
 	CU(cudaStreamSynchronize(s->copy_stream));
+	s->up_graph = nullptr;
 	s->scanning = true;
 	s->scan_to = to;
 	s->scan_chunk = chunk_nodes;
 	s->scan_issue = s->scan_take = from;
 	s->issued = s->taken = 0;
+	return WGBV_OK;
+}
+
+extern "C" int wgbv_scan_begin_upload(wgbv_stream *s, const uint8_t *graph, uint64_t graph_bytes, int64_t from, int64_t to, int64_t chunk_nodes) {
+	clear_error();
+	if (!s || !graph) return fail(WGBV_EARG, "null argument");
+	wgbv_graph *g = s->g;
+	if (graph_bytes < g->byte1) return fail(WGBV_EARG, "the buffer (%llu bytes) is shorter than the stream that was opened (%llu bytes)", (unsigned long long)graph_bytes, (unsigned long long)g->byte1);
+	if (from != g->shard_lo) return fail(WGBV_EARG, "a scan that uploads the stream has to start at the first node of the handle (%lld)", (long long)g->shard_lo);
+	int rc = wgbv_scan_begin(s, from, to, chunk_nodes);
+	if (rc) return rc;
+	if (!s->upload_stream) {
+		CU(cudaStreamCreateWithFlags(&s->upload_stream, cudaStreamNonBlocking));
+		for (auto &e : s->uploaded) CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+	}
+	CU(cudaStreamSynchronize(s->stream));
+	CU(cudaStreamSynchronize(s->upload_stream));
+	s->up_graph = graph;
+	s->up_next_word = 0;
+	s->up_chunks = 0;
 	return WGBV_OK;
 }
 
@@ -783,6 +839,14 @@ extern "C" void wgbv_scan_end(wgbv_stream *s) {
 	cudaSetDevice(s->g->device);
 	cudaStreamSynchronize(s->stream);
 	if (s->copy_stream) cudaStreamSynchronize(s->copy_stream);
+	if (s->upload_stream) cudaStreamSynchronize(s->upload_stream);
+	if (s->up_graph && s->up_next_word < s->g->data_words) {
+		// the scan was abandoned: send the rest so that the handle holds the whole stream again
+		s->scan_to = s->g->shard_hi;
+		scan_upload_chunk(s, s->up_chunks, s->scan_to);
+		cudaStreamSynchronize(s->upload_stream);
+	}
+	s->up_graph = nullptr;
 	s->scanning = false;
 }
 
