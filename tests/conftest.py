@@ -11,6 +11,15 @@ for p in (ROOT, os.path.join(ROOT, "oracle"), os.path.join(ROOT, "datagen")):
 
 GOLDEN = os.path.join(ROOT, "tests", "golden")
 
+# test infrastructure: if the CUDA library has not been built yet (fresh checkout) and nvcc is here, build it; the
+# package itself never builds or falls back -- it refuses to load without lib/libwgbv.so
+if not os.path.exists(os.path.join(ROOT, "webgraph-big_b200", "lib", "libwgbv.so")):
+    import shutil
+    if shutil.which("nvcc") or os.path.exists("/usr/local/cuda/bin/nvcc"):
+        sys.path.insert(0, ROOT)
+        import __graft_entry__
+        __graft_entry__.build()
+
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")

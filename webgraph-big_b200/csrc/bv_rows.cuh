@@ -223,7 +223,6 @@ template <int DEF, class RD>
 __device__ __forceinline__ void row_copy_warp(const GraphDev &g, RD &r, const int64_t *src, uint32_t dref, const int64_t *ext,
                                               int64_t *dst, uint32_t d, uint32_t bc, uint32_t ncopied) {
 	const unsigned lane = threadIdx.x & 31u;
-	const unsigned lt = (1u << lane) - 1u;
 	const uint32_t ne = d - ncopied;
 	uint32_t kb = 0;           // first position of the current window of the reference row
 	uint32_t ei = 0;           // extras emitted so far

@@ -519,7 +519,6 @@ extern "C" int wgbv_decode_degrees(wgbv_stream *s, int64_t from, int64_t to, int
 	CU(cudaSetDevice(s->g->device));
 	int rc = check_range(s->g, from, to);
 	if (rc) return rc;
-	Prepared P;
 	// no halo is needed for degrees alone
 	wgbv_graph *g = s->g;
 	const Launch L = s->launch();
@@ -532,7 +531,6 @@ extern "C" int wgbv_decode_degrees(wgbv_stream *s, int64_t from, int64_t to, int
 	CU(cudaMemcpyAsync(s->h_pin, d_rowptr + cnt, 8, cudaMemcpyDeviceToHost, s->stream));
 	if ((rc = collect_errors(s))) return rc;
 	if (arcs_out) *arcs_out = (int64_t)s->h_pin[0];
-	(void)P;
 	return WGBV_OK;
 }
 
