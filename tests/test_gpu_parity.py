@@ -299,6 +299,29 @@ def test_fused_tile_kernel_equals_oracle(monkeypatch, cnr_basename, cnr_golden):
         assert np.array_equal(rp, rowptr_of(odeg)) and np.array_equal(c, ocol)
 
 
+def test_fused_levels_kernel_equals_oracle(monkeypatch, cnr_basename, cnr_golden):
+    """The opt-in single-launch copy stage (WGBV_FUSED_LEVELS=1: task queue + per-row dependency flags) on the golden
+    fixture, on ranges that start inside a tile, and on synthetic graphs with 1..8 levels and rows on both merge paths."""
+    monkeypatch.setenv("WGBV_FUSED_LEVELS", "1")
+    deg, rowptr, col = cnr_golden
+    with wg.GpuBVGraph.load(cnr_basename) as g:
+        rp, c = g.decodeToCSR()
+        assert np.array_equal(rp, rowptr) and np.array_equal(c, col)
+        rp, c = g.decodeToCSR(100001, 200003)
+        assert np.array_equal(c, col[rowptr[100001]:rowptr[200003]])
+    for maxref, window, md in ((1, 1, 12), (3, 7, 25), (4, 7, 60), (8, 16, 25)):
+        e = bg.copy_model(60000, seed=7 + maxref, mean_degree=md, params=bg.make_params(window=window, maxref=maxref, minint=4), nsplits=2)
+        odeg, ocol = oracle_of(e).decode_range()
+        with gpu_of(e) as g:
+            rp, c = g.decodeToCSR()
+            assert np.array_equal(rp, rowptr_of(odeg)) and np.array_equal(c, ocol)
+    rowptr2, col2 = _similar_rows_graph(3000, (256, 1000, 1536), 12, 4000, 4000)
+    e = bg.encode_csr(rowptr2, col2, bg.make_params(window=7, maxref=3, minint=4))
+    with gpu_of(e) as g:
+        rp, c = g.decodeToCSR()
+        assert np.array_equal(rp, rowptr2) and np.array_equal(c, col2)
+
+
 def test_streaming_scan_equals_golden(cnr, cnr_golden):
     """wgbv_scan_*: the pipelined bulk form of nodeIterator(); chunks must tile the range and carry the golden rows."""
     deg, rowptr, col = cnr_golden

@@ -13,12 +13,17 @@ enum : uint32_t {
 };
 
 // What stage 3a learns about a row with a reference and stage 3b needs again: kept so that the copy kernels do not
-// have to look the row's offset up and parse its head a second time.
+// have to look the row's offset up and parse its head a second time.  Two shapes, told apart by the outdegrees of the
+// row and of its reference row (row_is_masked), which every kernel has at hand:
+//   masked rows: a = bits 0..63, b = bits 64..127 of the mask of copied positions of the reference row
+//   other rows:  a = bit position of the first block, b = ncopied | block count << 32
 struct RowInfo {
-	uint64_t blocks_pos;  // bit position of the first block
-	uint32_t ncopied;     // successors copied from the reference row
-	uint32_t bc;          // block count
+	uint64_t a, b;
 };
+// Rows of fewer than WARP_ROW successors whose reference row has at most 128 are merged by one lane from the mask of
+// copied positions (row_copy_masked); all the others by a whole warp from the block codes (row_copy_warp).
+static constexpr uint32_t WARP_ROW = 128;
+__host__ __device__ inline bool row_is_masked(uint32_t d, uint32_t dref) { return d < WARP_ROW && dref <= 128; }
 
 // One bulk decode job: nodes [lo, hi) are decoded, of which [from, hi) were requested; [lo, from) is the halo.
 struct RangeDev {
@@ -31,6 +36,11 @@ struct RangeDev {
 	int64_t *halo;          // successors of [lo, from): row x starts at halo + rp[x-lo]
 	uint64_t col_capacity;  // elements available at col
 	RowInfo *info;          // written by k_extras for every row with a reference, read by k_copy_level (may be nullptr)
+	// shallow chains without a depth pass: k_extras walks the reference array itself (at most walk_levels hops),
+	// stores the depths here and sets *deep if some chain is longer (all three unused when depth_out is nullptr)
+	uint32_t *depth_out = nullptr;
+	uint32_t walk_levels = 0;
+	uint32_t *deep = nullptr;
 };
 
 // One random-access job list: `rows` chain rows, each decoded into its own slot.
@@ -88,6 +98,10 @@ void launch_level_lists(const Launch &L, const GraphDev &g, const uint8_t *ref, 
 // stage 3a: intervals + residuals of every row (whole row when it has no reference)
 void launch_extras(const Launch &L, const GraphDev &g, int def, const RangeDev &r, const HeavyDev &h);
 // stage 3b: copy-block resolution of the rows at one depth level; list == nullptr: every node is inspected
+// all levels of shallow chains in one launch (see k_copy_fused); ticket and flags[tiles] must be zero
+uint32_t copy_fused_tiles(int64_t count);
+void launch_copy_fused(const Launch &L, const GraphDev &g, int def, const RangeDev &r, uint32_t nlevels, uint32_t *ticket, uint32_t *flags,
+                       const uint32_t *deep);
 void launch_copy_level(const Launch &L, const GraphDev &g, int def, const RangeDev &r, uint32_t level,
                        const uint32_t *list, uint64_t list_count);
 // checksum of a CSR

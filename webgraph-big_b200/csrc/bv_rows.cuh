@@ -28,12 +28,30 @@ static constexpr unsigned FULL_MASK = 0xffffffffu;
 // a prefetch may name any address: it never faults
 __device__ __forceinline__ void prefetch_l1(const void *p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
 
+// bits [from, from + len) of a 64-bit mask (what falls beyond bit 63 is dropped)
+__device__ __forceinline__ uint64_t bit_span(uint64_t from, uint64_t len) {
+	if (from >= 64 || len == 0) return 0;
+	return (len >= 64 ? ~0ull : (1ull << len) - 1ull) << from;
+}
+
+// sets bits [from, from + len) of a 128-bit mask (what falls beyond bit 127 is dropped)
+__device__ __forceinline__ void mask_span(uint64_t (&m)[2], uint64_t from, uint64_t len) {
+	m[0] |= bit_span(from, len);
+	if (len > 128) len = 128;
+	const uint64_t end = from + len;
+	if (end > 64 && from < 128) {
+		const uint64_t hf = from > 64 ? from - 64 : 0;
+		m[1] |= bit_span(hf, end - 64 - hf);
+	}
+}
+
 struct RowHead {
 	uint32_t d;        // outdegree
 	uint32_t rf;       // reference (0: none)
 	uint32_t bc;       // block count
 	uint32_t ncopied;  // successors copied from the reference row
 	uint64_t blocks_pos;  // bit position of the first block (after the block count)
+	uint64_t cmask[2];    // bit k set: position k of the reference row is copied (complete only when dref <= 128)
 	bool ok;           // false: inconsistent counts (an error bit has been raised); d and ncopied are zeroed
 };
 
@@ -47,6 +65,7 @@ __device__ __forceinline__ void row_head(const GraphDev &g, RD &r, uint32_t dref
 	h.bc = 0;
 	h.ncopied = 0;
 	h.blocks_pos = 0;
+	h.cmask[0] = h.cmask[1] = 0;
 	h.ok = true;
 	if (d != 0 && g.window > 0) h.rf = (uint32_t)rd_reference<DEF>(r, g);
 	if (h.rf > 0) {
@@ -57,11 +76,17 @@ __device__ __forceinline__ void row_head(const GraphDev &g, RD &r, uint32_t dref
 		uint64_t copied = 0, total = 0;
 		for (uint32_t i = 0; i < h.bc; i++) {
 			const uint64_t b = rd_block<DEF>(r, g) + (i ? 1 : 0);
+			if (!(i & 1)) {
+				copied += b;
+				mask_span(h.cmask, total, b);
+			}
 			total += b;
-			if (!(i & 1)) copied += b;
 		}
 		if (total > dref) h.ok = false;
-		else if (!(h.bc & 1)) copied += dref - total;
+		else if (!(h.bc & 1)) {
+			copied += dref - total;
+			mask_span(h.cmask, total, dref - total);
+		}
 		if (copied > d) h.ok = false;
 		h.ncopied = (uint32_t)copied;
 	}
@@ -70,6 +95,7 @@ __device__ __forceinline__ void row_head(const GraphDev &g, RD &r, uint32_t dref
 		h.d = 0;
 		h.ncopied = 0;
 		h.bc = 0;
+		h.cmask[0] = h.cmask[1] = 0;
 	}
 }
 
@@ -212,6 +238,57 @@ __device__ __forceinline__ void row_copy(const GraphDev &g, RD &r, const int64_t
 	}
 }
 
+// The one-lane merge for a reference row of at most 128 successors, whose copy blocks stage 3a has already turned into
+// a bit mask (m, m1) of copied positions (RowHead.cmask): no block is decoded here and positions that are not copied
+// are never visited, so every iteration emits exactly one successor -- the smaller of the next extra and the next
+// copied element -- through one instruction stream.  ext[0..ne) are the extras; in place operation as in row_copy.
+// Warp-synchronous: every lane of `mask` must call it (m == 0 for lanes without work).
+// cg (warp-uniform): read the reference row past the L1 (it was written by another block of the running kernel).
+__device__ __forceinline__ void row_copy_masked(const GraphDev &g, const int64_t *src, uint64_t m, uint64_t m1, const int64_t *ext,
+                                                int64_t *dst, uint32_t ne, unsigned mask, bool cg = false) {
+	uint32_t ei = 0;
+	if (!m) { m = m1; m1 = 0; src += 64; }
+	int pos = m ? __ffsll((long long)m) - 1 : 0;
+	int64_t e = (m && ne) ? ext[0] : INT64_MAX;
+	int64_t c = m ? (cg ? __ldcg(src + pos) : src[pos]) : 0;
+	while (__any_sync(mask, m != 0)) {
+		if (m) {
+			const bool take_e = e < c;
+			if (e == c) raise(g, ERR_NOT_SORTED);
+			*dst++ = take_e ? e : c;
+			if (take_e) {
+				// each new 32-byte sector of a stream would cost a memory round trip: ask for the one two ahead
+				if ((ei & 3u) == 0 && ei + 8 < ne) prefetch_l1(ext + ei + 8);
+				e = ++ei < ne ? ext[ei] : INT64_MAX;
+			} else {
+				m &= m - 1;
+				if (!m && m1) { m = m1; m1 = 0; src += 64; pos -= 64; }
+				if (m) {
+					const int q = __ffsll((long long)m) - 1;
+					if (!cg && (q >> 2) != (pos >> 2)) prefetch_l1(src + (q & ~3) + 8);
+					pos = q;
+					c = cg ? __ldcg(src + q) : src[q];
+				}
+			}
+		}
+	}
+}
+
+// position of the n-th (0-based) set bit of m; n < popc(m)
+__device__ __forceinline__ uint32_t nth_set_bit(uint32_t m, uint32_t n) {
+	uint32_t pos = 0, t;
+	t = (uint32_t)__popc(m & 0xffffu);
+	if (n >= t) { n -= t; pos += 16; m >>= 16; }
+	t = (uint32_t)__popc(m & 0xffu);
+	if (n >= t) { n -= t; pos += 8; m >>= 8; }
+	t = (uint32_t)__popc(m & 0xfu);
+	if (n >= t) { n -= t; pos += 4; m >>= 4; }
+	t = (uint32_t)__popc(m & 0x3u);
+	if (n >= t) { n -= t; pos += 2; m >>= 2; }
+	if (n >= (m & 1u)) pos += 1;
+	return pos;
+}
+
 // The same merge done by a whole warp on ONE row (all 32 lanes pass the same arguments and each keeps its own copy of
 // the block reader, so the block codes are decoded redundantly but uniformly).  The reference row is read 32
 // positions at a time and the extras 32 at a time, both coalesced; every round emits everything that is not larger
@@ -221,7 +298,7 @@ __device__ __forceinline__ void row_copy(const GraphDev &g, RD &r, const int64_t
 // reason as in row_copy: a round writes below the position of the first extra it has not loaded yet.
 template <int DEF, class RD>
 __device__ __forceinline__ void row_copy_warp(const GraphDev &g, RD &r, const int64_t *src, uint32_t dref, const int64_t *ext,
-                                              int64_t *dst, uint32_t d, uint32_t bc, uint32_t ncopied) {
+                                              int64_t *dst, uint32_t d, uint32_t bc, uint32_t ncopied, bool cg = false) {
 	const unsigned lane = threadIdx.x & 31u;
 	const uint32_t ne = d - ncopied;
 	uint32_t kb = 0;           // first position of the current window of the reference row
@@ -236,7 +313,7 @@ __device__ __forceinline__ void row_copy_warp(const GraphDev &g, RD &r, const in
 	while (done < ncopied) {
 		if (fresh) {
 			const uint32_t p = kb + lane;
-			c = p < dref ? src[p] : INT64_MAX;
+			c = p < dref ? (cg ? __ldcg(src + p) : src[p]) : INT64_MAX;
 			bool f = false;
 			// walk the blocks that overlap [kb, kb + 32)
 			for (;;) {
@@ -255,7 +332,7 @@ __device__ __forceinline__ void row_copy_warp(const GraphDev &g, RD &r, const in
 		}
 		// A: the copied elements of the window still to emit, compacted to lanes 0..nA-1
 		const unsigned nA = (unsigned)__popc(cmask);
-		const int srcl = lane < nA ? (int)__fns(cmask, 0, (int)lane + 1) : 0;
+		const int srcl = lane < nA ? (int)nth_set_bit(cmask, lane) : 0;
 		int64_t A = __shfl_sync(FULL_MASK, c, srcl);
 		if (lane >= nA) A = INT64_MAX;
 		// B: the next extras
@@ -289,8 +366,8 @@ __device__ __forceinline__ void row_copy_warp(const GraphDev &g, RD &r, const in
 		if (eA == 0 && eB == 0) break;  // cannot happen on well-formed input
 		done += eA;
 		ei += eB;
-		// drop the emitted copied positions (the eA lowest set bits of cmask)
-		for (unsigned i = 0; i < eA; i++) cmask &= cmask - 1;
+		// drop the emitted copied positions (the eA lowest set bits of cmask): lane eA-1 knows where the last of them is
+		if (eA) cmask &= ~((2u << __shfl_sync(FULL_MASK, srcl, (int)eA - 1)) - 1u);
 		if (cmask == 0) { kb += 32; fresh = true; }
 		__syncwarp();
 	}

@@ -71,6 +71,7 @@ struct wgbv_stream {
 	uint64_t launches = 0;
 	DevBuf deg, ref, depth, rp, scan_state, ticket, halo, levels, list, col, rowptr, ids, batch;
 	DevBuf heavy_rows, heavy_sorted, heavy_cls, heavy_counters, tile_scratch, level_pos, row_info;
+	bool fused_levels = false;  // true: all levels of shallow chains in one launch, k_copy_fused (WGBV_FUSED_LEVELS=1)
 	bool force_levels = true;   // false: use the fused tile kernel where it applies (WGBV_TILE=1)
 	DevBuf c_node, c_dst, c_parent, c_deg, c_isq, c_level, c_len, c_arcs, c_row0, c_soff, c_store;
 	cudaEvent_t ev[6]{};
@@ -374,6 +375,8 @@ extern "C" int wgbv_stream_create(wgbv_graph *g, void *cuda_stream, wgbv_stream 
 	// the level-synchronous kernels on graphs with long rows, so it is opt-in for now.
 	const char *tl = getenv("WGBV_TILE");
 	s->force_levels = !(tl && tl[0] == '1');
+	const char *fl = getenv("WGBV_FUSED_LEVELS");
+	s->fused_levels = fl && fl[0] == '1';
 	g->streams++;
 	*out = s;
 	return WGBV_OK;
@@ -590,16 +593,48 @@ static int decode_rows(wgbv_stream *s, int64_t from, int64_t to, Prepared &P, in
 	H.sorted = s->heavy_sorted.as<uint32_t>();
 	H.cls = s->heavy_cls.as<uint8_t>();
 	H.counters = s->heavy_counters.as<unsigned long long>();
+	uint32_t nlev = walk ? (uint32_t)std::max(g->props.max_ref_count, 0) : P.max_depth;
+	uint32_t *deep = s->d_err + 3;
+	// Shallow chains, opt-in (WGBV_FUSED_LEVELS=1): all levels in one launch (k_copy_fused), with the depths from
+	// k_extras' own walk when there was no depth pass.  It moves a third of the DRAM bytes of the per-level launches
+	// over ordered lists below but is not faster yet (profiles/r01_notes.md), so the lists remain the default.
+	const bool fused = nlev > 0 && nlev <= 8 && s->fused_levels;
+	if (fused) {
+		CU(cudaMemsetAsync(deep, 0, 4, s->stream));
+		if (walk) {
+			R.depth_out = s->depth.as<uint32_t>();
+			R.walk_levels = nlev;
+			R.deep = deep;
+		}
+	}
 	launch_extras(L, s->dev, g->def_codes, R, H);
 	R.depth = s->depth.as<uint32_t>();
-	uint32_t nlev = walk ? (uint32_t)std::max(g->props.max_ref_count, 0) : P.max_depth;
+	R.depth_out = nullptr;
+	if (fused) {
+		const uint32_t tiles = copy_fused_tiles(P.cnt);
+		if ((rc = s->levels.ensure((size_t)tiles * 4))) return rc;
+		CU(cudaMemsetAsync(s->levels.as<uint32_t>(), 0, (size_t)tiles * 4, s->stream));
+		CU(cudaMemsetAsync(s->ticket.as<uint32_t>(), 0, 4, s->stream));
+		launch_copy_fused(L, s->dev, g->def_codes, R, nlev, s->ticket.as<uint32_t>(), s->levels.as<uint32_t>(), deep);
+		if (walk) {
+			uint32_t *hdeep = (uint32_t *)(s->h_pin + 10);
+			CU(cudaMemcpyAsync(hdeep, deep, 4, cudaMemcpyDeviceToHost, s->stream));
+			CU(cudaStreamSynchronize(s->stream));
+			if (*hdeep) {
+				// a chain longer than max_ref_count: the properties lied (or the file is malformed) and the fused kernel has
+				// done nothing; take the general route
+				walk = false;
+				if ((rc = compute_depth(s, from, P))) return rc;
+				nlev = P.max_depth;
+			} else nlev = 0;
+		} else nlev = 0;
+	}
 	for (int attempt = 0; attempt < 2 && nlev > 0 && nlev <= 8; attempt++) {
 		// shallow chains: ordered lists of the rows of every level
 		const size_t nblocks = (size_t)((P.cnt + 2047) / 2048);
 		if ((rc = s->levels.ensure(nlev * nblocks * 4)) || (rc = s->level_pos.ensure((nlev * nblocks + 1) * 8)) ||
 		    (rc = s->list.ensure((size_t)std::max<int64_t>(P.cnt, 1) * 4)) || (rc = s->scan_state.ensure(((nlev * nblocks + 1) / 2048 + 2) * 8)))
 			return rc;
-		uint32_t *deep = s->d_err + 3;
 		CU(cudaMemsetAsync(deep, 0, 4, s->stream));
 		launch_level_lists(L, s->dev, walk ? s->ref.as<uint8_t>() : nullptr, s->depth.as<uint32_t>(), P.lo, from, P.cnt, 0, nlev, s->levels.as<uint32_t>(),
 		                   s->level_pos.as<int64_t>(), s->list.as<uint32_t>(), s->scan_state.as<uint64_t>(), s->ticket.as<uint32_t>(), deep);
