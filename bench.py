@@ -46,6 +46,7 @@ def parse_args():
     ap.add_argument("--cpu-sample-nodes", type=int, default=0, help="0: sized from the core count")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--e2e-trace", action="store_true", help="print the arrival time of every chunk of the last e2e step to stderr")
     ap.add_argument("--seed", type=int, default=2)
     ap.add_argument("--max-degree", type=int, default=10000)
     return ap.parse_args()
@@ -290,33 +291,47 @@ def main():
 
     # end to end through the C ABI with HOST buffers: upload of the compressed stream + decode + read-back of the
     # CSR, chunk by chunk into pinned buffers that are reused (what a host-side NodeIterator consumes)
-    e2e = None
-    if not args.no_e2e:
+    def run_e2e(narrow):
         chunk = 1 << 22
         d2h = 0
+        esz = 4 if narrow else 8
         consumed = np.zeros(1, dtype=np.int64)
-        for a, b, rp, col in g.scan(first, first + min(n, 3 * chunk + 1), chunk):  # untimed warm-up: the library sizes its chunk buffers
+        for a, b, rp, col in g.scan(first, first + min(n, 3 * chunk + 1), chunk, narrow=narrow):  # untimed warm-up: the library sizes its chunk buffers
             pass
         barrier()
         t0 = time.perf_counter()
         for _ in range(max(1, args.e2e_steps)):
             got = 0
+            stamps = [time.perf_counter()]
             # the streaming form of nodeIterator(): the compressed stream goes up piece by piece from pinned host memory,
             # chunks come back in pinned host buffers owned by the library while the following chunks are decoded
-            for a, b, rp, col in g.scan(first, first + n, chunk, upload=(h_graph.data_ptr(), e.graph.size)):
+            for a, b, rp, col in g.scan(first, first + n, chunk, upload=(h_graph.data_ptr(), e.graph.size), narrow=narrow):
                 got += col.size
-                d2h += (b - a + 1) * 8 + col.size * 8
+                d2h += (b - a + 1) * 8 + col.size * esz
                 consumed[0] += int(rp[-1]) + (int(col[-1]) if col.size else 0)  # touch the result on the host
+                stamps.append(time.perf_counter())
             assert got == arcs
+        if args.e2e_trace and rank == 0:
+            print("e2e chunk arrivals (ms since the previous one):", " ".join(f"{(y - x) * 1e3:.1f}" for x, y in zip(stamps, stamps[1:])),
+                  file=sys.stderr)
         barrier()
         dt = (time.perf_counter() - t0) / max(1, args.e2e_steps)
         tt = torch.tensor([dt], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        e2e = {"value": total_arcs / float(tt.item()), "unit": UNIT, "h2d_bytes_per_step": int(e.graph.size) * world,
-               "d2h_bytes_per_step": int(d2h // max(1, args.e2e_steps)) * world, "ms_per_step": float(tt.item()) * 1e3,
-               "how": f"wgbv_scan_begin_upload / wgbv_scan_next over {chunk}-node chunks: upload of the compressed stream from pinned "
-                      "host memory, decode on the device and copy-back to pinned host buffers, the three overlapped chunk by chunk"}
+        return {"value": total_arcs / float(tt.item()), "unit": UNIT, "h2d_bytes_per_step": int(e.graph.size) * world,
+                "d2h_bytes_per_step": int(d2h // max(1, args.e2e_steps)) * world, "ms_per_step": float(tt.item()) * 1e3,
+                "successor_type": "uint32" if narrow else "int64",
+                "how": f"wgbv_scan_begin_upload / wgbv_scan_next over {chunk}-node chunks: upload of the compressed stream from pinned "
+                       "host memory, decode on the device and copy-back to pinned host buffers, the three overlapped chunk by chunk"}
+
+    # e2e: successors delivered as int64, the reference's own type (long).  e2e_narrow: the same scan with
+    # wgbv_scan_set_narrow (uint32 successors, same values, half the PCIe bytes), reported beside it, never instead of it.
+    e2e = e2e_narrow = None
+    if not args.no_e2e:
+        e2e = run_e2e(False)
+        if n * world <= 1 << 32:
+            e2e_narrow = run_e2e(True)
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -335,7 +350,7 @@ def main():
                        "compressed_bytes_rank0": int(e.graph.size), "bits_per_arc": e.graph_bits / max(arcs, 1),
                        "l2": "inputs and outputs exceed L2 (compressed stream and 8 B/arc output are GBs per step)",
                        "parallelism": f"{world} contiguous shard(s), no data-path collective; all-gather of arc counts"},
-            "roofline": roofline, "e2e": e2e, "cpu_baseline": cpu, "gpu_launches": int(launches), "clocks": clocks,
+            "roofline": roofline, "e2e": e2e, "e2e_narrow": e2e_narrow, "cpu_baseline": cpu, "gpu_launches": int(launches), "clocks": clocks,
             "verified": bool(verified), "global_row_base_rank0": global_base, "generation_s": gen_s, "load_s": load_s,
         }
         print(json.dumps(line))

@@ -191,6 +191,12 @@ WGBV_API int wgbv_scan_begin(wgbv_stream *s, int64_t from, int64_t to, int64_t c
 WGBV_API int wgbv_scan_begin_upload(wgbv_stream *s, const uint8_t *graph, uint64_t graph_bytes, int64_t from, int64_t to, int64_t chunk_nodes);
 WGBV_API int wgbv_scan_next(wgbv_stream *s, int64_t *first, int64_t *last, const int64_t **h_rowptr, const int64_t **h_col, int64_t *arcs);
 WGBV_API void wgbv_scan_end(wgbv_stream *s);
+/* Narrow delivery for the scans of this stream (no counterpart in the reference, whose successor lists are long[]):
+ * with on != 0 the chunks' successors reach the host as uint32 -- *h_col of wgbv_scan_next then points to
+ * uint32_t[*arcs] -- which halves the bytes that cross PCIe, the bound of a host-side scan.  Only for graphs whose
+ * node ids fit (wgbv_num_nodes <= 2^32: WGBV_EUNSUPPORTED otherwise); row pointers stay int64.  The values are the
+ * same; a Java binding widens them when it fills its long arrays.  Not while a scan is running (WGBV_ESTATE). */
+WGBV_API int wgbv_scan_set_narrow(wgbv_stream *s, int on);
 
 /* outdegree(x) for a batch of arbitrary nodes (BVG:821-851): h_out[i] = outdegree(h_ids[i]).  Host buffers. */
 WGBV_API int wgbv_outdegrees(wgbv_stream *s, const int64_t *h_ids, uint64_t k, int64_t *h_out);

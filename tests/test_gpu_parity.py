@@ -299,6 +299,21 @@ def test_fused_tile_kernel_equals_oracle(monkeypatch, cnr_basename, cnr_golden):
         assert np.array_equal(rp, rowptr_of(odeg)) and np.array_equal(c, ocol)
 
 
+def test_narrow_scan_delivers_the_same_successors(cnr, cnr_golden):
+    """wgbv_scan_set_narrow: successors as uint32, same values, on plain and uploading scans; back to int64 afterwards."""
+    deg, rowptr, col = cnr_golden
+    n = cnr.numNodes()
+    for lo, hi, chunk in ((0, n, 60000), (777, 54321, 5000), (9, 9, 4)):
+        got = []
+        for a, b, rp, c in cnr.scan(lo, hi, chunk, narrow=True):
+            assert c.dtype == np.uint32
+            assert np.array_equal(rp, rowptr[a:b + 1] - rowptr[a])
+            got.append(c.astype(np.int64))
+        assert np.array_equal(np.concatenate(got) if got else np.zeros(0, np.int64), col[rowptr[lo]:rowptr[hi]])
+    for a, b, rp, c in cnr.scan(0, 1000, 1000):
+        assert c.dtype == np.int64 and np.array_equal(c, col[:rowptr[1000]])
+
+
 def test_fused_levels_kernel_equals_oracle(monkeypatch, cnr_basename, cnr_golden):
     """The opt-in single-launch copy stage (WGBV_FUSED_LEVELS=1: task queue + per-row dependency flags) on the golden
     fixture, on ranges that start inside a tile, and on synthetic graphs with 1..8 levels and rows on both merge paths."""

@@ -266,14 +266,17 @@ class GpuBVGraph:
                                           col.size, C.byref(arcs)))
         return rowptr, col
 
-    def scan(self, from_=None, to=None, chunk_nodes=1 << 20, upload=None):
+    def scan(self, from_=None, to=None, chunk_nodes=1 << 20, upload=None, narrow=False):
         """Streaming scan of [from, to): yields (first, last, rowptr, col) per chunk of nodes, rowptr relative to the chunk.
         The arrays are views of pinned buffers owned by the library and are only valid until the next chunk is requested
         (the reference's rule for iterator arrays, BVG:1171-1172); decode and copy-back of the following chunks overlap
-        with the caller's work on the current one."""
+        with the caller's work on the current one.  narrow=True (graphs of at most 2^32 nodes): col arrives as uint32,
+        half the bytes over PCIe, same values."""
         from_ = self._lo if from_ is None else from_
         to = self._hi if to is None else to
         L = _lib.lib()
+        _lib.check(L.wgbv_scan_set_narrow(self._st.h, 1 if narrow else 0))
+        ctype, = (C.c_uint32,) if narrow else (C.c_int64,)
         if upload is None:
             _lib.check(L.wgbv_scan_begin(self._st.h, from_, to, chunk_nodes))
         else:  # (host pointer, bytes) of the compressed stream: uploaded piece by piece while the scan runs
@@ -289,7 +292,7 @@ class GpuBVGraph:
                     _lib.check(rc)
                 n = last.value - first.value
                 r = np.ctypeslib.as_array(C.cast(rp, C.POINTER(C.c_int64)), shape=(n + 1,))
-                c = np.ctypeslib.as_array(C.cast(col, C.POINTER(C.c_int64)), shape=(max(arcs.value, 1),))[:arcs.value]
+                c = np.ctypeslib.as_array(C.cast(col, C.POINTER(ctype)), shape=(max(arcs.value, 1),))[:arcs.value]
                 yield first.value, last.value, r, c
         finally:
             L.wgbv_scan_end(self._st.h)

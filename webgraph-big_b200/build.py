@@ -32,19 +32,26 @@ def needs_build():
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force=False, verbose=False):
-    if not force and not needs_build():
+def build(force=False, verbose=False, out=None, extra_flags=()):
+    """out / extra_flags: an experimental variant under another name (A/B runs through WGBV_LIBRARY), e.g.
+    ``python build.py --variant name -DSOME_SWITCH=1`` writes lib/libwgbv_name.so."""
+    if out is None and not force and not needs_build():
         return LIB
     os.makedirs(LIBDIR, exist_ok=True)
-    cmd = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + \
-          [os.path.join(CSRC, f) for f in SOURCES] + ["-o", LIB]
+    cmd = [_nvcc()] + NVCC_FLAGS + list(extra_flags) + (["-Xptxas", "-v"] if verbose else []) + \
+          [os.path.join(CSRC, f) for f in SOURCES] + ["-o", out or LIB]
     res = subprocess.run(cmd, cwd=CSRC, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     if verbose or res.returncode:
         sys.stderr.write(res.stdout)
     if res.returncode:
         raise RuntimeError("nvcc failed building libwgbv.so")
-    return LIB
+    return out or LIB
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    if "--variant" in sys.argv:
+        i = sys.argv.index("--variant")
+        print(build(verbose="-v" in sys.argv, out=os.path.join(LIBDIR, "libwgbv_%s.so" % sys.argv[i + 1]),
+                    extra_flags=[a for a in sys.argv[i + 2:] if a.startswith("-D")]))
+    else:
+        print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))

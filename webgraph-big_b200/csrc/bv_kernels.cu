@@ -35,6 +35,33 @@ void launch_bswap(const Launch &L, uint64_t *words, uint64_t nwords) {
 	WGBV_LAUNCHED(L);
 }
 
+__global__ void k_peek(PeekArgs a, uint64_t *dst) {
+	const unsigned t = threadIdx.x;
+	if (t < a.n) dst[t] = a.bytes[t] == 8 ? *static_cast<const uint64_t *>(a.src[t]) : (uint64_t) * static_cast<const uint32_t *>(a.src[t]);
+}
+
+void launch_peek(const Launch &L, const PeekArgs &a, uint64_t *mapped_dst) {
+	if (!a.n) return;
+	k_peek<<<1, 32, 0, L.stream>>>(a, mapped_dst);
+	WGBV_LAUNCHED(L);
+}
+
+// successors as uint32 for narrow delivery: four per thread (two 16-byte loads, one 16-byte store)
+__global__ void __launch_bounds__(TPB) k_narrow(const int64_t *__restrict__ in, uint32_t *__restrict__ out, uint64_t count) {
+	const uint64_t i = ((uint64_t)blockIdx.x * TPB + threadIdx.x) * 4;
+	if (i + 4 <= count) {
+		const longlong2 a = *reinterpret_cast<const longlong2 *>(in + i), b = *reinterpret_cast<const longlong2 *>(in + i + 2);
+		*reinterpret_cast<uint4 *>(out + i) = make_uint4((uint32_t)a.x, (uint32_t)a.y, (uint32_t)b.x, (uint32_t)b.y);
+	} else
+		for (uint64_t j = i; j < count; j++) out[j] = (uint32_t)in[j];
+}
+
+void launch_narrow(const Launch &L, const int64_t *in, uint32_t *out, uint64_t count) {
+	if (!count) return;
+	k_narrow<<<grid_for((int64_t)((count + 3) / 4), TPB), TPB, 0, L.stream>>>(in, out, count);
+	WGBV_LAUNCHED(L);
+}
+
 // ------------------------------------------------------------------------------------------------ stage 1
 // Outdegree and reference of every node: readOutdegree / readReference at the node's offset
 // (BVG:654-661, 692-703; the offset lookup is offsets.getLong(x), BVG:834).

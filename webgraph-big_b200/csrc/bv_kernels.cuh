@@ -126,5 +126,17 @@ size_t tile_smem_bytes();
 int launch_tile(const Launch &L, const GraphDev &g, int def, const RangeDev &r, const TileDev &t, int blocks);
 // byte-swap the uploaded stream into big-endian 64-bit words, in place
 void launch_bswap(const Launch &L, uint64_t *words, uint64_t nwords);
+// A handful of device scalars for the host, written by a kernel straight into mapped pinned host memory: unlike a small
+// cudaMemcpyAsync they do not queue behind a large device-to-host copy that another stream has on the copy engine.
+struct PeekArgs {
+	static constexpr int MAX = 12;
+	const void *src[MAX];
+	uint8_t bytes[MAX];  // 4 or 8
+	uint32_t n = 0;
+	void add(const void *p, int size) { src[n] = p; bytes[n] = (uint8_t)size; n++; }
+};
+void launch_peek(const Launch &L, const PeekArgs &a, uint64_t *mapped_dst);
+// out[i] = (uint32_t)in[i]: successors for narrow delivery (wgbv_scan_set_narrow)
+void launch_narrow(const Launch &L, const int64_t *in, uint32_t *out, uint64_t count);
 
 }  // namespace wgbv

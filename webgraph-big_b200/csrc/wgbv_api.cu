@@ -67,7 +67,8 @@ struct wgbv_stream {
 	GraphDev dev{};            // the graph's view with this stream's error word
 	uint32_t *d_err = nullptr;  // [0] sticky error bits, [1..3] spare
 	uint32_t *d_stats = nullptr;  // [0] unresolved, [1] max depth, [2..3] spare
-	uint64_t *h_pin = nullptr;  // pinned host scratch for read-backs (16 words)
+	uint64_t *h_pin = nullptr;  // pinned, mapped host scratch for read-backs (32 words)
+	uint64_t *d_pin = nullptr;  // the device's address of h_pin: kernels write scalars for the host there (launch_peek)
 	uint64_t launches = 0;
 	DevBuf deg, ref, depth, rp, scan_state, ticket, halo, levels, list, col, rowptr, ids, batch;
 	DevBuf heavy_rows, heavy_sorted, heavy_cls, heavy_counters, tile_scratch, level_pos, row_info;
@@ -80,7 +81,7 @@ struct wgbv_stream {
 
 	// streaming scan (wgbv_scan_*): a ring of chunk buffers, decoded on `stream`, copied back on `copy_stream`
 	struct ScanSlot {
-		DevBuf d_rowptr, d_col;
+		DevBuf d_rowptr, d_col;  // with narrow delivery d_col holds the uint32 copy (the decode goes to the stream's col)
 		int64_t *h_rowptr = nullptr, *h_col = nullptr;
 		size_t h_rowptr_cap = 0, h_col_cap = 0;  // elements
 		cudaEvent_t decoded = nullptr, ready = nullptr;
@@ -95,6 +96,7 @@ struct wgbv_stream {
 	uint64_t up_next_word = 0;          // first 64-bit unit of the device buffer not uploaded yet
 	int64_t up_chunks = 0;              // chunks whose words have been queued
 	bool scanning = false;
+	bool narrow = false;                // deliver successors as uint32 (wgbv_scan_set_narrow)
 	int64_t scan_to = 0, scan_chunk = 0, scan_issue = 0, scan_take = 0;  // next node to issue / to hand out
 	int64_t issued = 0, taken = 0;                                       // chunks issued / handed out
 };
@@ -362,7 +364,8 @@ extern "C" int wgbv_stream_create(wgbv_graph *g, void *cuda_stream, wgbv_stream 
 		s->own_stream = true;
 	}
 	if (cudaMalloc((void **)&s->d_err, 32) != cudaSuccess || cudaMemset(s->d_err, 0, 32) != cudaSuccess ||
-	    cudaMallocHost((void **)&s->h_pin, 16 * 8) != cudaSuccess) {
+	    cudaHostAlloc((void **)&s->h_pin, 32 * 8, cudaHostAllocMapped) != cudaSuccess ||
+	    cudaHostGetDevicePointer((void **)&s->d_pin, s->h_pin, 0) != cudaSuccess) {
 		wgbv_stream_destroy(s);
 		return fail(WGBV_ECUDA, "allocation of the stream state failed");
 	}
@@ -507,8 +510,10 @@ static int prepare(wgbv_stream *s, int64_t from, int64_t to, int64_t *d_rowptr, 
 	if (rp != d_rowptr && d_rowptr) launch_emit_rowptr(L, rp, P.halo_n, to - from, d_rowptr);
 	P.rp = rp;
 	cudaEventRecord(s->ev[2], s->stream);
-	CU(cudaMemcpyAsync(s->h_pin, rp + P.halo_n, 8, cudaMemcpyDeviceToHost, s->stream));
-	CU(cudaMemcpyAsync(s->h_pin + 1, rp + P.cnt, 8, cudaMemcpyDeviceToHost, s->stream));
+	PeekArgs pk;
+	pk.add(rp + P.halo_n, 8);
+	pk.add(rp + P.cnt, 8);
+	launch_peek(L, pk, s->d_pin);
 	CU(cudaStreamSynchronize(s->stream));
 	P.halo_arcs = (int64_t)s->h_pin[0];
 	P.arcs = (int64_t)s->h_pin[1] - P.halo_arcs;
@@ -617,10 +622,11 @@ static int decode_rows(wgbv_stream *s, int64_t from, int64_t to, Prepared &P, in
 		CU(cudaMemsetAsync(s->ticket.as<uint32_t>(), 0, 4, s->stream));
 		launch_copy_fused(L, s->dev, g->def_codes, R, nlev, s->ticket.as<uint32_t>(), s->levels.as<uint32_t>(), deep);
 		if (walk) {
-			uint32_t *hdeep = (uint32_t *)(s->h_pin + 10);
-			CU(cudaMemcpyAsync(hdeep, deep, 4, cudaMemcpyDeviceToHost, s->stream));
+			PeekArgs pk;
+			pk.add(deep, 4);
+			launch_peek(L, pk, s->d_pin + 10);
 			CU(cudaStreamSynchronize(s->stream));
-			if (*hdeep) {
+			if (s->h_pin[10]) {
 				// a chain longer than max_ref_count: the properties lied (or the file is malformed) and the fused kernel has
 				// done nothing; take the general route
 				walk = false;
@@ -638,13 +644,15 @@ static int decode_rows(wgbv_stream *s, int64_t from, int64_t to, Prepared &P, in
 		CU(cudaMemsetAsync(deep, 0, 4, s->stream));
 		launch_level_lists(L, s->dev, walk ? s->ref.as<uint8_t>() : nullptr, s->depth.as<uint32_t>(), P.lo, from, P.cnt, 0, nlev, s->levels.as<uint32_t>(),
 		                   s->level_pos.as<int64_t>(), s->list.as<uint32_t>(), s->scan_state.as<uint64_t>(), s->ticket.as<uint32_t>(), deep);
-		int64_t bounds[9];
-		uint32_t *hdeep = (uint32_t *)(s->h_pin + 10);
-		for (uint32_t l = 0; l <= nlev; l++)
-			CU(cudaMemcpyAsync(&bounds[l], s->level_pos.as<int64_t>() + (size_t)l * nblocks, 8, cudaMemcpyDeviceToHost, s->stream));
-		CU(cudaMemcpyAsync(hdeep, deep, 4, cudaMemcpyDeviceToHost, s->stream));
+		const int64_t *bounds = (const int64_t *)(s->h_pin + 16);
+		PeekArgs pk;
+		for (uint32_t l = 0; l <= nlev; l++) pk.add(s->level_pos.as<int64_t>() + (size_t)l * nblocks, 8);
+		launch_peek(L, pk, s->d_pin + 16);
+		PeekArgs pd;
+		pd.add(deep, 4);
+		launch_peek(L, pd, s->d_pin + 10);
 		CU(cudaStreamSynchronize(s->stream));
-		if (walk && *hdeep) {
+		if (walk && s->h_pin[10]) {
 			// a chain longer than max_ref_count: the properties lied (or the file is malformed); take the general route
 			walk = false;
 			if ((rc = compute_depth(s, from, P))) return rc;
@@ -667,9 +675,10 @@ static int decode_rows(wgbv_stream *s, int64_t from, int64_t to, Prepared &P, in
 			const uint32_t n8 = std::min<uint32_t>(8, P.max_depth - level0);
 			launch_level_lists(L, s->dev, nullptr, s->depth.as<uint32_t>(), P.lo, from, P.cnt, level0, n8, s->levels.as<uint32_t>(),
 			                   s->level_pos.as<int64_t>(), s->list.as<uint32_t>(), s->scan_state.as<uint64_t>(), s->ticket.as<uint32_t>(), s->d_err + 3);
-			int64_t bounds[9];
-			for (uint32_t l = 0; l <= n8; l++)
-				CU(cudaMemcpyAsync(&bounds[l], s->level_pos.as<int64_t>() + (size_t)l * nblocks, 8, cudaMemcpyDeviceToHost, s->stream));
+			const int64_t *bounds = (const int64_t *)(s->h_pin + 16);
+			PeekArgs pk;
+			for (uint32_t l = 0; l <= n8; l++) pk.add(s->level_pos.as<int64_t>() + (size_t)l * nblocks, 8);
+			launch_peek(L, pk, s->d_pin + 16);
 			CU(cudaStreamSynchronize(s->stream));
 			for (uint32_t l = 1; l <= n8; l++)
 				if (bounds[l] > bounds[l - 1])
@@ -777,13 +786,22 @@ static int scan_issue_one(wgbv_stream *s) {
 	if ((rc = sl.d_rowptr.ensure((size_t)(b - a + 1) * 8))) return rc;
 	Prepared P;
 	if ((rc = prepare(s, a, b, sl.d_rowptr.as<int64_t>(), P))) return rc;  // synchronises `stream`: the previous chunk is decoded
-	if ((rc = sl.d_col.ensure((size_t)std::max<int64_t>(P.arcs, 1) * 8))) return rc;
-	if ((rc = pinned_ensure(&sl.h_rowptr, &sl.h_rowptr_cap, (size_t)(b - a + 1))) || (rc = pinned_ensure(&sl.h_col, &sl.h_col_cap, (size_t)std::max<int64_t>(P.arcs, 1)))) return rc;
-	if ((rc = decode_rows(s, a, b, P, sl.d_col.as<int64_t>(), (uint64_t)P.arcs))) return rc;
+	const size_t esz = s->narrow ? 4 : 8;  // bytes per delivered successor
+	if ((rc = sl.d_col.ensure((size_t)std::max<int64_t>(P.arcs, 1) * esz))) return rc;
+	if (s->narrow && (rc = s->col.ensure((size_t)std::max<int64_t>(P.arcs, 1) * 8))) return rc;
+	// (the pinned buffers are sized in 8-byte units)
+	if ((rc = pinned_ensure(&sl.h_rowptr, &sl.h_rowptr_cap, (size_t)(b - a + 1))) ||
+	    (rc = pinned_ensure(&sl.h_col, &sl.h_col_cap, (size_t)(std::max<int64_t>(P.arcs, 1) * esz + 7) / 8)))
+		return rc;
+	if (s->narrow) {
+		// decode into the stream's own buffer (the next chunk's decode follows the narrowing kernel in stream order)
+		if ((rc = decode_rows(s, a, b, P, s->col.as<int64_t>(), (uint64_t)P.arcs))) return rc;
+		launch_narrow(s->launch(), s->col.as<int64_t>(), sl.d_col.as<uint32_t>(), (uint64_t)P.arcs);
+	} else if ((rc = decode_rows(s, a, b, P, sl.d_col.as<int64_t>(), (uint64_t)P.arcs))) return rc;
 	CU(cudaEventRecord(sl.decoded, s->stream));
 	CU(cudaStreamWaitEvent(s->copy_stream, sl.decoded, 0));
 	CU(cudaMemcpyAsync(sl.h_rowptr, sl.d_rowptr.as<int64_t>(), (size_t)(b - a + 1) * 8, cudaMemcpyDeviceToHost, s->copy_stream));
-	if (P.arcs) CU(cudaMemcpyAsync(sl.h_col, sl.d_col.as<int64_t>(), (size_t)P.arcs * 8, cudaMemcpyDeviceToHost, s->copy_stream));
+	if (P.arcs) CU(cudaMemcpyAsync(sl.h_col, sl.d_col.as<char>(), (size_t)P.arcs * esz, cudaMemcpyDeviceToHost, s->copy_stream));
 	CU(cudaMemcpyAsync(sl.h_err, s->d_err, 4, cudaMemcpyDeviceToHost, s->copy_stream));
 	CU(cudaEventRecord(sl.ready, s->copy_stream));
 	sl.first = a;
@@ -865,6 +883,16 @@ extern "C" int wgbv_scan_next(wgbv_stream *s, int64_t *first, int64_t *last, con
 	s->scan_take = sl.last;
 	s->taken++;
 	return 1;
+}
+
+extern "C" int wgbv_scan_set_narrow(wgbv_stream *s, int on) {
+	clear_error();
+	if (!s) return fail(WGBV_EARG, "null argument");
+	if (s->scanning) return fail(WGBV_ESTATE, "a scan is running on this stream");
+	if (on && (uint64_t)s->g->props.nodes > (1ull << 32))
+		return fail(WGBV_EUNSUPPORTED, "node ids of a graph with %lld nodes do not fit 32 bits", (long long)s->g->props.nodes);
+	s->narrow = on != 0;
+	return WGBV_OK;
 }
 
 extern "C" void wgbv_scan_end(wgbv_stream *s) {
