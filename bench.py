@@ -46,6 +46,7 @@ def parse_args():
     ap.add_argument("--cpu-sample-nodes", type=int, default=0, help="0: sized from the core count")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-transpose", action="store_true", help="skip the transpose of the decoded CSR (SURVEY 8f-1, N=1 only)")
     ap.add_argument("--e2e-trace", action="store_true", help="print the arrival time of every chunk of the last e2e step to stderr")
     ap.add_argument("--seed", type=int, default=2)
     ap.add_argument("--max-degree", type=int, default=10000)
@@ -263,6 +264,38 @@ def main():
         raise SystemExit(f"rank {rank}: decoded CSR does not match the generator's checksum ({chk:#x} != {e.checksum:#x})")
     global_base = int(counts[:rank].sum().item()) if world > 1 else 0
 
+    # the transpose of the CSR just decoded, device to device (what Transform.transposeOffline is for).
+    # Checked at full size by the involution: the transpose of the transpose must hash to the generator's checksum.
+    transpose = None
+    if world == 1 and not args.no_transpose and n < (1 << 32):
+        t_rp = torch.empty(n + 1, dtype=torch.int64, device=dev)
+        t_col = torch.empty(max(arcs, 1), dtype=torch.int64, device=dev)
+        g.transposeCSRDevice(n, d_rowptr.data_ptr(), d_col.data_ptr(), t_rp.data_ptr(), t_col.data_ptr())  # warm-up: sizes the scratch
+        g.sync()
+        reps = 3
+        l0 = g.kernelLaunches()
+        tv0, tv1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        tv0.record()
+        for _ in range(reps):
+            g.transposeCSRDevice(n, d_rowptr.data_ptr(), d_col.data_ptr(), t_rp.data_ptr(), t_col.data_ptr())
+        tv1.record()
+        g.sync()
+        t_ms = tv0.elapsed_time(tv1) / reps
+        t_launches = (g.kernelLaunches() - l0) // reps
+        b_rp = torch.empty(n + 1, dtype=torch.int64, device=dev)
+        g.transposeCSRDevice(n, t_rp.data_ptr(), t_col.data_ptr(), b_rp.data_ptr(), d_col.data_ptr())  # back into d_col
+        g.sync()
+        t_ok = g.csrChecksumDevice(first, n, b_rp.data_ptr(), d_col.data_ptr()) == e.checksum and bool(torch.equal(b_rp, d_rowptr))
+        # algorithmic bytes: CSR in (8 B per arc + row pointers), transposed CSR out
+        t_bytes = 2 * (8 * arcs + 8 * (n + 1))
+        transpose = {"metric": "transposed arcs/s (CSR -> CSR, device resident)", "value": arcs / (t_ms * 1e-3), "unit": UNIT, "ms": t_ms,
+                     "gpu_launches": int(t_launches), "verified_by_involution": bool(t_ok),
+                     "roofline": {"bound": "hbm", "achieved": t_bytes / (t_ms * 1e-3) / 1e9, "unit": "GB/s",
+                                  "frac": t_bytes / (t_ms * 1e-3) / 1e9 / peaks()[0], "algorithmic_bytes": t_bytes}}
+        del t_rp, t_col, b_rp
+        if not t_ok:
+            raise SystemExit("transpose(transpose(CSR)) does not hash to the generator's checksum")
+
     total_arcs = torch.tensor([arcs], dtype=torch.int64, device=dev)
     if world > 1:
         dist.all_reduce(total_arcs)
@@ -350,7 +383,7 @@ def main():
                        "compressed_bytes_rank0": int(e.graph.size), "bits_per_arc": e.graph_bits / max(arcs, 1),
                        "l2": "inputs and outputs exceed L2 (compressed stream and 8 B/arc output are GBs per step)",
                        "parallelism": f"{world} contiguous shard(s), no data-path collective; all-gather of arc counts"},
-            "roofline": roofline, "e2e": e2e, "e2e_narrow": e2e_narrow, "cpu_baseline": cpu, "gpu_launches": int(launches), "clocks": clocks,
+            "roofline": roofline, "e2e": e2e, "e2e_narrow": e2e_narrow, "transpose": transpose, "cpu_baseline": cpu, "gpu_launches": int(launches), "clocks": clocks,
             "verified": bool(verified), "global_row_base_rank0": global_base, "generation_s": gen_s, "load_s": load_s,
         }
         print(json.dumps(line))

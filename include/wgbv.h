@@ -198,6 +198,16 @@ WGBV_API void wgbv_scan_end(wgbv_stream *s);
  * same; a Java binding widens them when it fills its long arrays.  Not while a scan is running (WGBV_ESTATE). */
 WGBV_API int wgbv_scan_set_narrow(wgbv_stream *s, int on);
 
+/*
+ * Transpose of a CSR in device memory: the device form of what Transform.transposeOffline
+ * (Transform.java:1098-1144) computes from a sequential scan -- for every node y the increasing list of the x with
+ * y in successors(x).  d_rowptr[0 .. n] / d_col describe a graph with n nodes whose successors are node ids of the same
+ * graph (the output of wgbv_decode_csr over [0, n)); d_t_rowptr gets n + 1 entries and d_t_col as many as d_col has
+ * (d_rowptr[n] - d_rowptr[0]).  All four are device pointers; the call is asynchronous on the stream except for one
+ * read-back of the arc count.  n < 2^32 (WGBV_EUNSUPPORTED beyond); a successor outside [0, n) gives WGBV_EINDEX.
+ */
+WGBV_API int wgbv_transpose_csr(wgbv_stream *s, int64_t n, const int64_t *d_rowptr, const int64_t *d_col, int64_t *d_t_rowptr, int64_t *d_t_col);
+
 /* outdegree(x) for a batch of arbitrary nodes (BVG:821-851): h_out[i] = outdegree(h_ids[i]).  Host buffers. */
 WGBV_API int wgbv_outdegrees(wgbv_stream *s, const int64_t *h_ids, uint64_t k, int64_t *h_out);
 

@@ -205,3 +205,18 @@ def _err(code):
     return {-1: IndexError("Node index out of range"), -2: RuntimeError("illegal state (malformed stream / bad reference)"),
             -3: IOError("bit stream overrun"), -4: NotImplementedError("unsupported coding"),
             -5: MemoryError("capacity")}.get(code, RuntimeError(f"oracle error {code}"))
+
+
+def transpose_csr(n, rowptr, col):
+    """CPU restatement of what Transform.transposeOffline / Transform.transpose compute (Transform.java:1098-1144:
+    every arc (x, y) of the scan becomes (y, x), arcs are sorted by (target, source) in batches and merged): returns
+    (t_rowptr, t_col) with the sources of every target increasing.  TEST INFRASTRUCTURE ONLY, like the rest of oracle/.
+    Parity status: unpinned by the reference (its tests only check transpose(transpose(g)) == g, TransformTest); pinned
+    here by that involution on the cnr-2000 golden and by this definition."""
+    rowptr = np.asarray(rowptr, dtype=np.int64)
+    col = np.asarray(col, dtype=np.int64)
+    src = np.repeat(np.arange(n, dtype=np.int64), np.diff(rowptr))
+    order = np.lexsort((src, col))  # by target, then by source
+    t_rowptr = np.zeros(n + 1, dtype=np.int64)
+    np.cumsum(np.bincount(col, minlength=n)[:n], out=t_rowptr[1:])
+    return t_rowptr, src[order]

@@ -403,3 +403,63 @@ def test_open_slice_with_halo():
     with pytest.raises(wg.IllegalArgumentException):
         g.decodeToCSR(lo - 1, hi)
     g.close()
+
+
+def test_node_ids_beyond_32_bits():
+    """A part of a 6*10^9-node graph (the reference's big arrays exist for n > 2^31, BVGraphSlowTest): successors and
+    node ids need all 64 bits; the decoded CSR must hash to what the generator hashed before encoding, and random access
+    must agree with the bulk decode."""
+    first, n = 5_000_000_000, 20000
+    e = bg.copy_model(n, seed=5, mean_degree=12, nsplits=1, first_node=first, global_n=6_000_000_000)
+    props = e.properties_text().replace(f"nodes={n}", "nodes=6000000000")  # the properties of the whole graph
+    g = wg.GpuBVGraph.load_slice(props, first, n, e.graph, e.offsets_stream)
+    assert g.numNodes() == 6_000_000_000 and g.shardRange() == (first, first + n)
+    rp, c = g.decodeToCSR()
+    assert int(rp[-1]) == e.arcs and c.max() > 2 ** 32 and c.min() >= 0
+    assert bg.csr_checksum(first, rp, c) == e.checksum
+    ids = np.array([first, first + 77, first + n - 1], dtype=np.int64)
+    rp2, c2 = g.successorsBatch(ids)
+    assert np.array_equal(c2, np.concatenate([c[rp[x - first]:rp[x - first + 1]] for x in ids]))
+    with pytest.raises(wg.UnsupportedOperationException):
+        next(iter(g.scan(first, first + 10, 10, narrow=True)))
+    g.close()
+
+
+def _transpose_on_gpu(g, n, rowptr, col):
+    torch = pytest.importorskip("torch")
+    d_rp = torch.from_numpy(np.ascontiguousarray(rowptr, dtype=np.int64)).cuda()
+    d_col = torch.from_numpy(np.ascontiguousarray(col, dtype=np.int64)).cuda()
+    d_trp = torch.empty(n + 1, dtype=torch.int64, device="cuda")
+    d_tcol = torch.empty(max(col.size, 1), dtype=torch.int64, device="cuda")
+    g.transposeCSRDevice(n, d_rp.data_ptr(), d_col.data_ptr(), d_trp.data_ptr(), d_tcol.data_ptr())
+    torch.cuda.synchronize()
+    return d_trp.cpu().numpy(), d_tcol.cpu().numpy()[: col.size]
+
+
+def test_transpose_equals_oracle_and_is_an_involution(cnr, cnr_golden):
+    """wgbv_transpose_csr against the CPU restatement of Transform.transpose, on the golden fixture (two
+    radix passes), on its own transpose (the reference's own test: transpose(transpose(g)) == g), and on shapes that
+    stress the sort: empty graph, empty rows, a star (one target for every arc), one pass, three passes."""
+    deg, rowptr, col = cnr_golden
+    n = cnr.numNodes()
+    trp, tcol = _transpose_on_gpu(cnr, n, rowptr, col)
+    orp, ocol = bo.transpose_csr(n, rowptr, col)
+    assert np.array_equal(trp, orp) and np.array_equal(tcol, ocol)
+    brp, bcol = _transpose_on_gpu(cnr, n, trp, tcol)
+    assert np.array_equal(brp, rowptr) and np.array_equal(bcol, col)
+    rng = np.random.default_rng(3)
+    for nn, m in ((1, 0), (5, 0), (300, 2000), (70000, 300000), (300000, 1200000)):
+        pairs = np.unique(np.stack([rng.integers(0, nn, m), rng.integers(0, nn, m)], axis=1), axis=0) if m else np.zeros((0, 2), np.int64)
+        rp = np.zeros(nn + 1, dtype=np.int64)
+        np.cumsum(np.bincount(pairs[:, 0], minlength=nn), out=rp[1:])
+        c = pairs[:, 1].astype(np.int64)
+        trp, tcol = _transpose_on_gpu(cnr, nn, rp, c)
+        orp, ocol = bo.transpose_csr(nn, rp, c)
+        assert np.array_equal(trp, orp) and np.array_equal(tcol, ocol), (nn, m)
+    star_rp = np.arange(0, 50001, dtype=np.int64)
+    star_rp[0] = 0
+    star_col = np.full(50000, 7, dtype=np.int64)
+    trp, tcol = _transpose_on_gpu(cnr, 50000, star_rp, star_col)
+    assert trp[7] == 0 and trp[8] == 50000 and np.array_equal(tcol, np.arange(50000))
+    with pytest.raises(wg.IllegalArgumentException):
+        _transpose_on_gpu(cnr, 10, np.array([0, 1] + [1] * 9, dtype=np.int64), np.array([10], dtype=np.int64))

@@ -328,6 +328,12 @@ class GpuBVGraph:
         _lib.check(_lib.lib().wgbv_csr_checksum(self._st.h, first_node, rows, C.c_void_p(d_rowptr), C.c_void_p(d_col), C.byref(out)))
         return out.value
 
+    def transposeCSRDevice(self, n, d_rowptr, d_col, d_t_rowptr, d_t_col):
+        """Transpose of a CSR in device memory (int pointers; Transform.transposeOffline, Transform.java:1098-1144, on the
+        device): d_t_rowptr gets n + 1 entries, d_t_col as many as d_col; sources of every target come out increasing."""
+        _lib.check(_lib.lib().wgbv_transpose_csr(self._st.h, n, C.c_void_p(d_rowptr), C.c_void_p(d_col), C.c_void_p(d_t_rowptr),
+                                                 C.c_void_p(d_t_col)))
+
     def successorsBatchDevice(self, d_ids, k, d_rowptr, d_col=None, col_capacity=0):
         """Batched random access on device buffers.  With d_col None only the row pointers are produced."""
         L = _lib.lib()

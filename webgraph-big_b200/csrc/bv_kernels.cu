@@ -393,9 +393,13 @@ static constexpr uint32_t HEAVY = 128;
 // into shared memory with coalesced loads (STAGED) and every decoder of the block then reads words with ~30-cycle
 // shared-memory latency instead of waiting for L2/DRAM at every word boundary of every lane; a tile whose span does
 // not fit (a very long row in it) reads global memory instead.
-static constexpr int ERPT = 4;
+#ifndef WGBV_ERPT
+#define WGBV_ERPT 4
+#define WGBV_EBITS 9216
+#endif
+static constexpr int ERPT = WGBV_ERPT;
 static constexpr int ETILE = TPB * ERPT;
-static constexpr int EBITS = 9216;  // 32-bit words of the stream a tile may stage (36 KiB)
+static constexpr int EBITS = WGBV_EBITS;  // 32-bit words of the stream a tile may stage (36 KiB)
 
 __device__ __forceinline__ void cp_async16(void *smem_dst, const void *gmem_src) {
 	const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);

@@ -124,6 +124,16 @@ void launch_scan64(const Launch &L, const unsigned long long *in, int64_t *out, 
 // stage 3, fused: one block decodes a tile of rows completely in shared memory (bounded reference chains only)
 size_t tile_smem_bytes();
 int launch_tile(const Launch &L, const GraphDev &g, int def, const RangeDev &r, const TileDev &t, int blocks);
+// transpose of a device CSR (bv_transpose.cu): pack arcs into target << 32 | source words and count in-degrees, then
+// LSD radix passes over the target half (hist -> scan of counts[digit * tiles + tile] -> stable scatter; the last
+// scatter writes the sources to t_col)
+uint64_t transpose_tiles(uint64_t arcs);
+int transpose_digits();
+int transpose_passes(uint64_t nodes);
+void launch_transpose_pack(const Launch &L, const GraphDev &g, int64_t n, const int64_t *rowptr, const int64_t *col, uint64_t arcs,
+                           uint64_t *pairs, uint32_t *indeg);
+void launch_radix_hist(const Launch &L, const uint64_t *in, uint64_t count, int pass, uint32_t *counts);
+void launch_radix_scatter(const Launch &L, const uint64_t *in, uint64_t count, int pass, const int64_t *pos, uint64_t *out, int64_t *t_col);
 // byte-swap the uploaded stream into big-endian 64-bit words, in place
 void launch_bswap(const Launch &L, uint64_t *words, uint64_t nwords);
 // A handful of device scalars for the host, written by a kernel straight into mapped pinned host memory: unlike a small

@@ -8,6 +8,7 @@
 
 #include <algorithm>
 #include <map>
+#include <thread>
 
 namespace wgbv {
 
@@ -188,6 +189,17 @@ struct HostBits {
 		return v;
 	}
 	uint64_t gamma() {
+		// the whole code inside the window (at most 28 leading zeros): one load, one count, two shifts
+		if (pos + 64 <= nbits) {
+			uint64_t w;
+			memcpy(&w, p + (pos >> 3), 8);
+			w = __builtin_bswap64(w) << (pos & 7);
+			if (w >> 35) {
+				const int lz = __builtin_clzll(w);
+				pos += 2 * (uint64_t)lz + 1;
+				return ((w << lz) >> (63 - lz)) - 1;
+			}
+		}
 		const uint64_t m = unary();
 		if (m > 63) { overrun = true; return 0; }
 		return ((1ull << m) | (m ? bits((unsigned)m) : 0)) - 1;
@@ -222,7 +234,7 @@ int decode_offsets(const wgbv_props &p, const uint8_t *bytes, uint64_t nbytes, i
 void EliasFano::build(const uint64_t *values, uint64_t n, uint64_t base) {
 	count = n;
 	lower.clear(); upper.clear(); hints.clear(); sparse.clear();
-	if (n == 0) { l = 0; upper.assign(2, 0); hints.assign(1, 0); lower.assign(2, 0); return; }
+	if (n == 0) { l = 0; upper.assign(2, 0); hints.assign(1, 0); lower.assign(2, 0); sparse.assign(1, 0); return; }
 	const uint64_t u = values[n - 1] - base + 1;
 	l = 0;
 	if (u / n >= 2) l = 63 - __builtin_clzll(u / n);
@@ -231,26 +243,58 @@ void EliasFano::build(const uint64_t *values, uint64_t n, uint64_t base) {
 	lower.assign((size_t)((n * (uint64_t)l + 63) / 64 + 2), 0);
 	hints.assign((size_t)((n + 63) / 64 + 1), 0);
 	const uint64_t lmask = l ? ((1ull << l) - 1) : 0;
-	std::vector<uint64_t> blockpos(64);
-	for (uint64_t i = 0; i < n; i++) {
-		const uint64_t v = values[i] - base;
-		const uint64_t pos = (v >> l) + i;
-		upper[(size_t)(pos >> 6)] |= 1ull << (pos & 63);
-		if (l) {
-			const uint64_t lb = i * (uint64_t)l;
-			lower[(size_t)(lb >> 6)] |= (v & lmask) << (lb & 63);
-			if ((lb & 63) + l > 64) lower[(size_t)(lb >> 6) + 1] |= (v & lmask) >> (64 - (lb & 63));
-		}
-		blockpos[(size_t)(i & 63)] = pos;
-		if ((i & 63) == 63 || i == n - 1) {
-			const uint64_t k = i >> 6;
-			const uint64_t first = blockpos[0];
-			if (pos - first > 4096) {
-				hints[(size_t)k] = (1ull << 63) | (uint64_t)(sparse.size() / 64);
-				for (uint64_t j = 0; j < 64; j++) sparse.push_back(j <= (i & 63) ? blockpos[(size_t)j] : pos);
+	// Blocks of 64 elements are independent except for the words two neighbouring ranges share: the lower bits of 64
+	// elements fill whole words (64 * l bits), the upper-bits words at the seams are merged with atomic ORs.  Sparse
+	// blocks (rare: a giant record inside) are collected per range and numbered afterwards.
+	const uint64_t nblocks = (n + 63) / 64;
+	unsigned nt = std::thread::hardware_concurrency();
+	if (nt == 0) nt = 1;
+	if (nt > 16) nt = 16;
+	if (nblocks < 4096) nt = 1;
+	struct Sparse { uint64_t block; uint64_t pos[64]; };
+	std::vector<std::vector<Sparse>> found(nt);
+	auto work = [&](unsigned t) {
+		const uint64_t b0 = nblocks * t / nt, b1 = nblocks * (t + 1) / nt;
+		uint64_t cur_word = ~0ull, cur_bits = 0;
+		auto flush = [&]() {
+			if (cur_word != ~0ull) __atomic_fetch_or(&upper[(size_t)cur_word], cur_bits, __ATOMIC_RELAXED);
+		};
+		for (uint64_t k = b0; k < b1; k++) {
+			const uint64_t i0 = k * 64, i1 = std::min(n, i0 + 64);
+			uint64_t blockpos[64];
+			for (uint64_t i = i0; i < i1; i++) {
+				const uint64_t v = values[i] - base;
+				const uint64_t pos = (v >> l) + i;
+				if ((pos >> 6) != cur_word) { flush(); cur_word = pos >> 6; cur_bits = 0; }
+				cur_bits |= 1ull << (pos & 63);
+				if (l) {
+					const uint64_t lb = i * (uint64_t)l;
+					lower[(size_t)(lb >> 6)] |= (v & lmask) << (lb & 63);
+					if ((lb & 63) + l > 64) lower[(size_t)(lb >> 6) + 1] |= (v & lmask) >> (64 - (lb & 63));
+				}
+				blockpos[i - i0] = pos;
+			}
+			const uint64_t first = blockpos[0], last = blockpos[i1 - i0 - 1];
+			if (last - first > 4096) {
+				Sparse sp;
+				sp.block = k;
+				for (uint64_t j = 0; j < 64; j++) sp.pos[j] = j < i1 - i0 ? blockpos[j] : last;
+				found[t].push_back(sp);
 			} else hints[(size_t)k] = first;
 		}
+		flush();
+	};
+	if (nt == 1) work(0);
+	else {
+		std::vector<std::thread> th;
+		for (unsigned t = 0; t < nt; t++) th.emplace_back(work, t);
+		for (auto &x : th) x.join();
 	}
+	for (auto &f : found)
+		for (auto &sp : f) {
+			hints[(size_t)sp.block] = (1ull << 63) | (uint64_t)(sparse.size() / 64);
+			sparse.insert(sparse.end(), sp.pos, sp.pos + 64);
+		}
 	if (sparse.empty()) sparse.assign(1, 0);
 }
 

@@ -1,0 +1,172 @@
+// bv_transpose.cu -- transpose of a CSR held in device memory.
+//
+// The most common consumer of a full sequential decode in the reference is Transform.transposeOffline
+// (Transform.java:1098-1144): scan the graph, turn every arc (x, y) into (y, x), sort batches by (target, source),
+// merge them.  With the CSR already in HBM the same result -- for every y the increasing list of the x with
+// y in successors(x) -- is a stable sort of the arcs by target: the arcs of a CSR come in increasing source order, so
+// a STABLE sort by target alone leaves every target's sources increasing.
+//
+//   k_t_pack      arc j -> one 64-bit word  target << 32 | source   (node ids below 2^32), counts in-degrees
+//   k_rs_hist     per pass: digit histogram of every tile of RS_TILE words
+//   (k_scan)      digit-major scan of the tile histograms = first output position of every (digit, tile)
+//   k_rs_scatter  per pass: stable scatter of the tile's words; the last pass writes the sources straight to t_col
+//
+// LSD radix sort, RS_BITS bits per pass over the target half only: ceil(log2(n) / RS_BITS) passes (3 for 10^8 nodes).
+// Ranks are computed without atomics on the data path: a warp owns 512 consecutive words of the tile, finds the lanes
+// that hold the same digit with __match_any_sync (rank in the warp = number of lower lanes with that digit) and keeps
+// one running base per (warp, digit) in shared memory, which is what makes the pass stable.
+#include "bv_block.cuh"
+#include "bv_kernels.cuh"
+
+namespace wgbv {
+
+static constexpr unsigned FULL_MASK_T = 0xffffffffu;
+static constexpr int RS_BITS = 9;
+static constexpr int RS_DIGITS = 1 << RS_BITS;
+static constexpr int RS_ITEMS = 16;               // words per thread
+static constexpr int RS_TILE = TPB * RS_ITEMS;    // words per block
+static constexpr int RS_WARP_ITEMS = 32 * RS_ITEMS;
+
+uint64_t transpose_tiles(uint64_t arcs) { return arcs ? (arcs + RS_TILE - 1) / RS_TILE : 0; }
+int transpose_digits() { return RS_DIGITS; }
+int transpose_passes(uint64_t nodes) {
+	int bits = 1;
+	while (bits < 32 && (1ull << bits) < nodes) bits++;
+	return (bits + RS_BITS - 1) / RS_BITS;
+}
+
+// One block per PACK_TILE consecutive arcs; the rows that hold them are found by binary search in the row pointers
+// (first the block's range of rows, then every arc inside that range: a handful of steps that hit L1).
+static constexpr int PACK_ITEMS = 8;
+static constexpr int PACK_TILE = TPB * PACK_ITEMS;
+
+__device__ __forceinline__ int64_t row_of(const int64_t *__restrict__ rp, int64_t lo, int64_t hi, int64_t a) {
+	// the last row r in [lo, hi] with rp[r] <= a
+	while (lo < hi) {
+		const int64_t mid = lo + (hi - lo + 1) / 2;
+		if (rp[mid] <= a) lo = mid;
+		else hi = mid - 1;
+	}
+	return lo;
+}
+
+__global__ void __launch_bounds__(TPB) k_t_pack(GraphDev g, int64_t n, const int64_t *__restrict__ rp, const int64_t *__restrict__ col,
+                                                uint64_t arcs, uint64_t *__restrict__ pairs, uint32_t *indeg) {
+	__shared__ int64_t s_row[2];
+	const uint64_t j0 = (uint64_t)blockIdx.x * PACK_TILE;
+	const uint64_t j1 = j0 + PACK_TILE < arcs ? j0 + PACK_TILE : arcs;
+	const int64_t base = rp[0];
+	if (threadIdx.x == 0) s_row[0] = row_of(rp, 0, n - 1, base + (int64_t)j0);
+	if (threadIdx.x == 32) s_row[1] = row_of(rp, 0, n - 1, base + (int64_t)j1 - 1);
+	__syncthreads();
+	const int64_t r0 = s_row[0], r1 = s_row[1];
+#pragma unroll
+	for (int q = 0; q < PACK_ITEMS; q++) {
+		const uint64_t j = j0 + (uint64_t)q * TPB + threadIdx.x;
+		if (j < j1) {
+			const int64_t y = col[j];
+			const int64_t x = row_of(rp, r0, r1, base + (int64_t)j);
+			if (y < 0 || y >= n) {
+				raise(g, ERR_INDEX);
+				pairs[j] = (uint64_t)x;  // keeps the sort well defined; the call fails anyway
+			} else {
+				pairs[j] = (uint64_t)y << 32 | (uint64_t)x;
+				atomicAdd(&indeg[y], 1u);
+			}
+		}
+	}
+}
+
+__global__ void __launch_bounds__(TPB) k_rs_hist(const uint64_t *__restrict__ in, uint64_t count, int shift, uint32_t nblocks,
+                                                 uint32_t *__restrict__ counts) {
+	__shared__ uint32_t hist[RS_DIGITS];
+	for (int d = threadIdx.x; d < RS_DIGITS; d += TPB) hist[d] = 0;
+	__syncthreads();
+	const uint64_t t0 = (uint64_t)blockIdx.x * RS_TILE;
+#pragma unroll
+	for (int q = 0; q < RS_ITEMS; q++) {
+		const uint64_t j = t0 + (uint64_t)q * TPB + threadIdx.x;
+		if (j < count) atomicAdd(&hist[(uint32_t)(in[j] >> shift) & (RS_DIGITS - 1)], 1u);
+	}
+	__syncthreads();
+	for (int d = threadIdx.x; d < RS_DIGITS; d += TPB) counts[(size_t)d * nblocks + blockIdx.x] = hist[d];
+}
+
+// FINAL: the last pass; the sorted words are not needed any more, only their source halves, as int64, in t_col.
+template <bool FINAL>
+__global__ void __launch_bounds__(TPB, 4) k_rs_scatter(const uint64_t *__restrict__ in, uint64_t count, int shift, uint32_t nblocks,
+                                                    const int64_t *__restrict__ pos, uint64_t *__restrict__ out, int64_t *__restrict__ t_col) {
+	__shared__ uint32_t wbase[TPB / 32][RS_DIGITS];  // per warp: count of the digit, then the running base inside the tile
+	__shared__ int64_t gbase[RS_DIGITS];             // first output position of the tile's words with that digit
+	const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+	const unsigned lt = (1u << lane) - 1u;
+	for (int i = threadIdx.x; i < (TPB / 32) * RS_DIGITS; i += TPB) (&wbase[0][0])[i] = 0;
+	__syncthreads();
+	const uint64_t w0 = (uint64_t)blockIdx.x * RS_TILE + (uint64_t)warp * RS_WARP_ITEMS;
+	uint64_t key[RS_ITEMS];
+	// counts per (warp, digit)
+#pragma unroll
+	for (int r = 0; r < RS_ITEMS; r++) {
+		const uint64_t j = w0 + (uint64_t)r * 32 + lane;
+		const bool valid = j < count;
+		key[r] = valid ? in[j] : 0;
+		const uint32_t d = valid ? (uint32_t)(key[r] >> shift) & (RS_DIGITS - 1) : (uint32_t)RS_DIGITS;  // RS_DIGITS: no word
+		const unsigned peers = __match_any_sync(FULL_MASK_T, d);
+		if (valid && (peers & lt) == 0) wbase[warp][d] += (uint32_t)__popc(peers);
+		__syncwarp();
+	}
+	__syncthreads();
+	for (int d = threadIdx.x; d < RS_DIGITS; d += TPB) {
+		uint32_t run = 0;
+#pragma unroll
+		for (int w = 0; w < TPB / 32; w++) {
+			const uint32_t c = wbase[w][d];
+			wbase[w][d] = run;
+			run += c;
+		}
+		gbase[d] = pos[(size_t)d * nblocks + blockIdx.x];
+	}
+	__syncthreads();
+#pragma unroll
+	for (int r = 0; r < RS_ITEMS; r++) {
+		const uint64_t j = w0 + (uint64_t)r * 32 + lane;
+		const bool valid = j < count;
+		const uint32_t d = valid ? (uint32_t)(key[r] >> shift) & (RS_DIGITS - 1) : (uint32_t)RS_DIGITS;
+		const unsigned peers = __match_any_sync(FULL_MASK_T, d);
+		const uint32_t rank = (uint32_t)__popc(peers & lt);
+		uint32_t b = 0;
+		if (valid) b = wbase[warp][d];
+		__syncwarp();
+		if (valid && rank == 0) wbase[warp][d] = b + (uint32_t)__popc(peers);
+		__syncwarp();
+		if (valid) {
+			const int64_t p = gbase[d] + b + rank;
+			if (FINAL) t_col[p] = (int64_t)(key[r] & 0xffffffffull);
+			else out[p] = key[r];
+		}
+	}
+}
+
+void launch_transpose_pack(const Launch &L, const GraphDev &g, int64_t n, const int64_t *rowptr, const int64_t *col, uint64_t arcs,
+                           uint64_t *pairs, uint32_t *indeg) {
+	if (!arcs) return;
+	k_t_pack<<<grid_for((int64_t)arcs, PACK_TILE), TPB, 0, L.stream>>>(g, n, rowptr, col, arcs, pairs, indeg);
+	WGBV_LAUNCHED(L);
+}
+
+void launch_radix_hist(const Launch &L, const uint64_t *in, uint64_t count, int pass, uint32_t *counts) {
+	const uint32_t nblocks = (uint32_t)transpose_tiles(count);
+	if (!nblocks) return;
+	k_rs_hist<<<nblocks, TPB, 0, L.stream>>>(in, count, 32 + pass * RS_BITS, nblocks, counts);
+	WGBV_LAUNCHED(L);
+}
+
+void launch_radix_scatter(const Launch &L, const uint64_t *in, uint64_t count, int pass, const int64_t *pos, uint64_t *out, int64_t *t_col) {
+	const uint32_t nblocks = (uint32_t)transpose_tiles(count);
+	if (!nblocks) return;
+	if (t_col) k_rs_scatter<true><<<nblocks, TPB, 0, L.stream>>>(in, count, 32 + pass * RS_BITS, nblocks, pos, nullptr, t_col);
+	else k_rs_scatter<false><<<nblocks, TPB, 0, L.stream>>>(in, count, 32 + pass * RS_BITS, nblocks, pos, out, nullptr);
+	WGBV_LAUNCHED(L);
+}
+
+}  // namespace wgbv

@@ -71,6 +71,7 @@ struct wgbv_stream {
 	uint64_t *d_pin = nullptr;  // the device's address of h_pin: kernels write scalars for the host there (launch_peek)
 	uint64_t launches = 0;
 	DevBuf deg, ref, depth, rp, scan_state, ticket, halo, levels, list, col, rowptr, ids, batch;
+	DevBuf t_pairs[2], t_indeg, t_counts, t_pos;  // wgbv_transpose_csr
 	DevBuf heavy_rows, heavy_sorted, heavy_cls, heavy_counters, tile_scratch, level_pos, row_info;
 	bool fused_levels = false;  // true: all levels of shallow chains in one launch, k_copy_fused (WGBV_FUSED_LEVELS=1)
 	bool force_levels = true;   // false: use the fused tile kernel where it applies (WGBV_TILE=1)
@@ -389,6 +390,7 @@ extern "C" void wgbv_stream_destroy(wgbv_stream *s) {
 	if (!s) return;
 	cudaSetDevice(s->g->device);
 	if (s->stream) cudaStreamSynchronize(s->stream);
+	for (DevBuf *b : {&s->t_pairs[0], &s->t_pairs[1], &s->t_indeg, &s->t_counts, &s->t_pos}) b->release();
 	for (DevBuf *b : {&s->deg, &s->ref, &s->depth, &s->rp, &s->scan_state, &s->ticket, &s->halo, &s->levels, &s->list, &s->col,
 	                  &s->rowptr, &s->ids, &s->batch, &s->heavy_rows, &s->heavy_sorted, &s->heavy_cls, &s->heavy_counters, &s->tile_scratch, &s->level_pos, &s->row_info, &s->c_node, &s->c_dst, &s->c_parent, &s->c_deg, &s->c_isq, &s->c_level,
 	                  &s->c_len, &s->c_arcs, &s->c_row0, &s->c_soff, &s->c_store})
@@ -909,6 +911,49 @@ extern "C" void wgbv_scan_end(wgbv_stream *s) {
 	}
 	s->up_graph = nullptr;
 	s->scanning = false;
+}
+
+// ------------------------------------------------------------------------------------------------ transpose
+extern "C" int wgbv_transpose_csr(wgbv_stream *s, int64_t n, const int64_t *d_rowptr, const int64_t *d_col, int64_t *d_t_rowptr, int64_t *d_t_col) {
+	clear_error();
+	if (!s || !d_rowptr || !d_t_rowptr || n < 0) return fail(WGBV_EARG, "null argument or negative node count");
+	if ((uint64_t)n >= (1ull << 32)) return fail(WGBV_EUNSUPPORTED, "wgbv_transpose_csr packs node ids in 32 bits: %lld nodes are too many", (long long)n);
+	CU(cudaSetDevice(s->g->device));
+	const Launch L = s->launch();
+	int rc;
+	PeekArgs pk;
+	pk.add(d_rowptr, 8);
+	pk.add(d_rowptr + n, 8);
+	launch_peek(L, pk, s->d_pin);
+	CU(cudaStreamSynchronize(s->stream));
+	const int64_t arcs = (int64_t)s->h_pin[1] - (int64_t)s->h_pin[0];
+	if (arcs < 0) return fail(WGBV_EARG, "row pointers are not increasing");
+	if (arcs && (!d_col || !d_t_col)) return fail(WGBV_EARG, "null argument");
+	const size_t nn = (size_t)std::max<int64_t>(n, 1), na = (size_t)std::max<int64_t>(arcs, 1);
+	const uint64_t tiles = transpose_tiles((uint64_t)arcs);
+	const size_t ncounts = (size_t)std::max<uint64_t>(tiles * (uint64_t)transpose_digits(), 1);
+	const size_t scan_items = std::max(ncounts, nn);
+	if ((rc = s->t_indeg.ensure(nn * 4)) || (rc = s->t_pairs[0].ensure(na * 8)) || (rc = s->t_counts.ensure(ncounts * 4)) ||
+	    (rc = s->t_pos.ensure((ncounts + 1) * 8)) || (rc = s->scan_state.ensure(((scan_items + 1) / 2048 + 2) * 8)) || (rc = s->ticket.ensure(64)))
+		return rc;
+	const int passes = arcs ? transpose_passes((uint64_t)n) : 0;
+	if (passes > 1 && (rc = s->t_pairs[1].ensure(na * 8))) return rc;
+	CU(cudaMemsetAsync(s->t_indeg.as<uint32_t>(), 0, nn * 4, s->stream));
+	launch_transpose_pack(L, s->dev, n, d_rowptr, d_col, (uint64_t)arcs, s->t_pairs[0].as<uint64_t>(), s->t_indeg.as<uint32_t>());
+	// in-degrees -> row pointers of the transpose
+	launch_scan(L, s->t_indeg.as<uint32_t>(), d_t_rowptr, n, s->scan_state.as<uint64_t>(), s->ticket.as<uint32_t>());
+	int cur = 0;
+	for (int p = 0; p < passes; p++) {
+		const uint64_t *in = s->t_pairs[cur].as<uint64_t>();
+		launch_radix_hist(L, in, (uint64_t)arcs, p, s->t_counts.as<uint32_t>());
+		launch_scan(L, s->t_counts.as<uint32_t>(), s->t_pos.as<int64_t>(), (int64_t)ncounts, s->scan_state.as<uint64_t>(), s->ticket.as<uint32_t>());
+		const bool last = p == passes - 1;
+		launch_radix_scatter(L, in, (uint64_t)arcs, p, s->t_pos.as<int64_t>(), last ? nullptr : s->t_pairs[cur ^ 1].as<uint64_t>(), last ? d_t_col : nullptr);
+		cur ^= 1;
+	}
+	const cudaError_t e = cudaGetLastError();
+	if (e != cudaSuccess) return fail(WGBV_ECUDA, "kernel launch failed: %s", cudaGetErrorString(e));
+	return collect_errors(s);
 }
 
 // ------------------------------------------------------------------------------------------------ random access
