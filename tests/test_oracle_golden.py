@@ -76,3 +76,19 @@ def test_flag_parsing():
         bo.params_from_properties({"graphclass": "it.unimi.dsi.big.webgraph.EFGraph", "version": "0"})
     with pytest.raises(IOError):
         bo.params_from_properties({"graphclass": "it.unimi.dsi.webgraph.BVGraph"})
+
+
+def test_transpose_restatement(cnr_golden):
+    """oracle.transpose_csr (Transform.transpose restated): a hand-checked case, arc conservation and the involution the
+    reference's own TransformTest relies on, on the golden fixture."""
+    import bvoracle as bo
+    rp = np.array([0, 2, 3, 3, 5], dtype=np.int64)
+    col = np.array([1, 3, 0, 0, 2], dtype=np.int64)
+    trp, tcol = bo.transpose_csr(4, rp, col)
+    assert trp.tolist() == [0, 2, 3, 4, 5] and tcol.tolist() == [1, 3, 0, 3, 0]
+    deg, rowptr, gcol = cnr_golden
+    n = deg.size
+    trp, tcol = bo.transpose_csr(n, rowptr, gcol)
+    assert trp[-1] == rowptr[-1] and np.all(np.diff(trp) >= 0)
+    brp, bcol = bo.transpose_csr(n, trp, tcol)
+    assert np.array_equal(brp, rowptr) and np.array_equal(bcol, gcol)

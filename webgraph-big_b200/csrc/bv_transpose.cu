@@ -26,6 +26,7 @@ static constexpr int RS_DIGITS = 1 << RS_BITS;
 static constexpr int RS_ITEMS = 16;               // words per thread
 static constexpr int RS_TILE = TPB * RS_ITEMS;    // words per block
 static constexpr int RS_WARP_ITEMS = 32 * RS_ITEMS;
+static_assert(RS_DIGITS == 2 * TPB, "the scatter kernel scans two digits per thread");
 
 uint64_t transpose_tiles(uint64_t arcs) { return arcs ? (arcs + RS_TILE - 1) / RS_TILE : 0; }
 int transpose_digits() { return RS_DIGITS; }
@@ -93,16 +94,27 @@ __global__ void __launch_bounds__(TPB) k_rs_hist(const uint64_t *__restrict__ in
 }
 
 // FINAL: the last pass; the sorted words are not needed any more, only their source halves, as int64, in t_col.
+// The tile is first put in digit order in shared memory and then written out by consecutive threads, so that the words
+// of one digit -- a run of consecutive output positions -- leave in whole sectors instead of 8 bytes at a time.
+struct ScatterSmem {
+	uint64_t sorted[RS_TILE];                // the tile's words in digit order
+	uint32_t wbase[TPB / 32][RS_DIGITS];     // per warp: count of the digit, then the running base inside the tile's digit run
+	int64_t gbase[RS_DIGITS];                // first output position of the tile's words with that digit, minus dstart
+	uint32_t dstart[RS_DIGITS];              // first slot of the digit in sorted[]
+	uint32_t wsum[TPB / 32];
+};
+
 template <bool FINAL>
 __global__ void __launch_bounds__(TPB, 4) k_rs_scatter(const uint64_t *__restrict__ in, uint64_t count, int shift, uint32_t nblocks,
-                                                    const int64_t *__restrict__ pos, uint64_t *__restrict__ out, int64_t *__restrict__ t_col) {
-	__shared__ uint32_t wbase[TPB / 32][RS_DIGITS];  // per warp: count of the digit, then the running base inside the tile
-	__shared__ int64_t gbase[RS_DIGITS];             // first output position of the tile's words with that digit
+                                                       const int64_t *__restrict__ pos, uint64_t *__restrict__ out, int64_t *__restrict__ t_col) {
+	extern __shared__ __align__(16) unsigned char smem_raw[];
+	ScatterSmem &S = *reinterpret_cast<ScatterSmem *>(smem_raw);
 	const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
 	const unsigned lt = (1u << lane) - 1u;
-	for (int i = threadIdx.x; i < (TPB / 32) * RS_DIGITS; i += TPB) (&wbase[0][0])[i] = 0;
+	for (int i = threadIdx.x; i < (TPB / 32) * RS_DIGITS; i += TPB) (&S.wbase[0][0])[i] = 0;
 	__syncthreads();
-	const uint64_t w0 = (uint64_t)blockIdx.x * RS_TILE + (uint64_t)warp * RS_WARP_ITEMS;
+	const uint64_t t0 = (uint64_t)blockIdx.x * RS_TILE;
+	const uint64_t w0 = t0 + (uint64_t)warp * RS_WARP_ITEMS;
 	uint64_t key[RS_ITEMS];
 	// counts per (warp, digit)
 #pragma unroll
@@ -112,20 +124,40 @@ __global__ void __launch_bounds__(TPB, 4) k_rs_scatter(const uint64_t *__restric
 		key[r] = valid ? in[j] : 0;
 		const uint32_t d = valid ? (uint32_t)(key[r] >> shift) & (RS_DIGITS - 1) : (uint32_t)RS_DIGITS;  // RS_DIGITS: no word
 		const unsigned peers = __match_any_sync(FULL_MASK_T, d);
-		if (valid && (peers & lt) == 0) wbase[warp][d] += (uint32_t)__popc(peers);
+		if (valid && (peers & lt) == 0) S.wbase[warp][d] += (uint32_t)__popc(peers);
 		__syncwarp();
 	}
 	__syncthreads();
-	for (int d = threadIdx.x; d < RS_DIGITS; d += TPB) {
+	// per digit: bases of the warps inside the digit's run; then the runs' first slots (exclusive scan over the digits,
+	// two digits per thread)
+	uint32_t tot[2];
+#pragma unroll
+	for (int k = 0; k < 2; k++) {
+		const int d = 2 * threadIdx.x + k;
 		uint32_t run = 0;
 #pragma unroll
 		for (int w = 0; w < TPB / 32; w++) {
-			const uint32_t c = wbase[w][d];
-			wbase[w][d] = run;
+			const uint32_t c = S.wbase[w][d];
+			S.wbase[w][d] = run;
 			run += c;
 		}
-		gbase[d] = pos[(size_t)d * nblocks + blockIdx.x];
+		tot[k] = run;
 	}
+	uint32_t inc = tot[0] + tot[1];
+#pragma unroll
+	for (int o = 1; o < 32; o <<= 1) {
+		const uint32_t t = __shfl_up_sync(FULL_MASK_T, inc, o);
+		if ((int)lane >= o) inc += t;
+	}
+	if (lane == 31) S.wsum[warp] = inc;
+	__syncthreads();
+	uint32_t before = 0;
+	for (unsigned w = 0; w < warp; w++) before += S.wsum[w];
+	const uint32_t ex = before + inc - (tot[0] + tot[1]);
+	S.dstart[2 * threadIdx.x] = ex;
+	S.dstart[2 * threadIdx.x + 1] = ex + tot[0];
+	S.gbase[2 * threadIdx.x] = pos[(size_t)(2 * threadIdx.x) * nblocks + blockIdx.x] - (int64_t)ex;
+	S.gbase[2 * threadIdx.x + 1] = pos[(size_t)(2 * threadIdx.x + 1) * nblocks + blockIdx.x] - (int64_t)(ex + tot[0]);
 	__syncthreads();
 #pragma unroll
 	for (int r = 0; r < RS_ITEMS; r++) {
@@ -135,15 +167,19 @@ __global__ void __launch_bounds__(TPB, 4) k_rs_scatter(const uint64_t *__restric
 		const unsigned peers = __match_any_sync(FULL_MASK_T, d);
 		const uint32_t rank = (uint32_t)__popc(peers & lt);
 		uint32_t b = 0;
-		if (valid) b = wbase[warp][d];
+		if (valid) b = S.wbase[warp][d];
 		__syncwarp();
-		if (valid && rank == 0) wbase[warp][d] = b + (uint32_t)__popc(peers);
+		if (valid && rank == 0) S.wbase[warp][d] = b + (uint32_t)__popc(peers);
 		__syncwarp();
-		if (valid) {
-			const int64_t p = gbase[d] + b + rank;
-			if (FINAL) t_col[p] = (int64_t)(key[r] & 0xffffffffull);
-			else out[p] = key[r];
-		}
+		if (valid) S.sorted[S.dstart[d] + b + rank] = key[r];
+	}
+	__syncthreads();
+	const uint32_t here = count - t0 < (uint64_t)RS_TILE ? (uint32_t)(count - t0) : (uint32_t)RS_TILE;
+	for (uint32_t i = threadIdx.x; i < here; i += TPB) {
+		const uint64_t k = S.sorted[i];
+		const int64_t p = S.gbase[(uint32_t)(k >> shift) & (RS_DIGITS - 1)] + i;
+		if (FINAL) t_col[p] = (int64_t)(k & 0xffffffffull);
+		else out[p] = k;
 	}
 }
 
@@ -164,8 +200,14 @@ void launch_radix_hist(const Launch &L, const uint64_t *in, uint64_t count, int 
 void launch_radix_scatter(const Launch &L, const uint64_t *in, uint64_t count, int pass, const int64_t *pos, uint64_t *out, int64_t *t_col) {
 	const uint32_t nblocks = (uint32_t)transpose_tiles(count);
 	if (!nblocks) return;
-	if (t_col) k_rs_scatter<true><<<nblocks, TPB, 0, L.stream>>>(in, count, 32 + pass * RS_BITS, nblocks, pos, nullptr, t_col);
-	else k_rs_scatter<false><<<nblocks, TPB, 0, L.stream>>>(in, count, 32 + pass * RS_BITS, nblocks, pos, out, nullptr);
+	const size_t smem = sizeof(ScatterSmem);
+	if (t_col) {
+		cudaFuncSetAttribute(k_rs_scatter<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+		k_rs_scatter<true><<<nblocks, TPB, smem, L.stream>>>(in, count, 32 + pass * RS_BITS, nblocks, pos, nullptr, t_col);
+	} else {
+		cudaFuncSetAttribute(k_rs_scatter<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+		k_rs_scatter<false><<<nblocks, TPB, smem, L.stream>>>(in, count, 32 + pass * RS_BITS, nblocks, pos, out, nullptr);
+	}
 	WGBV_LAUNCHED(L);
 }
 
