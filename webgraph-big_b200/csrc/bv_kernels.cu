@@ -418,7 +418,16 @@ struct ExtrasSmem {
 	uint64_t span[2];
 	uint64_t wbase;  // stream word index of bits[0]
 	uint32_t nw;     // words staged
+	// one-launch front end.  (The outdegrees of the rows just before the tile, reference rows of its first rows, are
+	// kept in `order`, which is not needed before the sort: 256 uint32 -- see hdeg().  Four blocks of this size fit an SM.)
+	uint64_t warp_sum[TPB / 32];
+	uint64_t tile_base;          // arcs before the tile
+	uint32_t tile;
 };
+
+static_assert(sizeof(ExtrasSmem) <= 56 * 1024, "four blocks of k_extras per SM");
+static_assert(ETILE * sizeof(uint16_t) >= 256 * sizeof(uint32_t), "hdeg() borrows ExtrasSmem::order");
+__device__ __forceinline__ uint32_t *hdeg(ExtrasSmem &S) { return reinterpret_cast<uint32_t *>(S.order); }
 
 template <class RD>
 __device__ __forceinline__ void tile_reader(RD &r, const GraphDev &g, const ExtrasSmem &S, uint64_t pos);
@@ -429,9 +438,114 @@ __device__ __forceinline__ void tile_reader<TileReader>(TileReader &r, const Gra
 	r.init_words(S.bits, S.nw, (uint32_t)(pos - (S.wbase << 5)));
 }
 
+// Stages 1 and 2 for the rows of a tile, inside k_extras (RangeDev::rp_w): outdegree and reference of every row, then
+// the exclusive scan of the outdegrees -- inside the tile through shared memory, across tiles by decoupled look-back
+// on tile_state (tiles are handed out by a ticket, so a tile only waits for tiles that are running).  Leaves deg, ref
+// and rp of the tile's rows in global memory, the rows' offsets in S.pos and the outdegrees of the window before the
+// tile in S.hdeg.  Same checks as k_header.
 template <int DEF, class RD>
+__device__ __forceinline__ void tile_front_end(const GraphDev &g, const RangeDev &R, ExtrasSmem &S, int64_t base, int64_t count) {
+	const int64_t tend = base + ETILE < count ? base + ETILE : count;
+	// outdegrees of the rows before the tile: not in the staged bits, a handful of global reads
+	if ((int)threadIdx.x < g.window && (int64_t)threadIdx.x < base && threadIdx.x < 256) {
+		BitReader r;
+		r.init(g, ef_get(g, R.lo + base - 1 - threadIdx.x));
+		hdeg(S)[threadIdx.x] = (uint32_t)rd_outdegree<DEF>(r, g);
+	}
+#pragma unroll 1
+	for (int q = 0; q < ERPT; q++) {
+		const int id = q * TPB + threadIdx.x;
+		const int64_t i = base + id;
+		uint32_t dd = 0;
+		if (i < count) {
+			const int64_t x = R.lo + i;
+			const uint64_t off = ef_get(g, x);
+			RD r;
+			tile_reader<RD>(r, g, S, off);
+			const uint64_t d = rd_outdegree<DEF>(r, g);
+			uint64_t rf = 0;
+			if (d > 0x7fffffffull) raise(g, ERR_DEGREE);
+			else {
+				dd = (uint32_t)d;
+				if (d && g.window > 0) {
+					rf = rd_reference<DEF>(r, g);
+					if (rf > (uint64_t)g.window || (int64_t)rf > x) { raise(g, ERR_REF_WINDOW); rf = 0; }
+				}
+				if (r.past_end()) raise(g, ERR_OVERRUN);
+			}
+			R.deg_w[i] = dd;
+			R.ref_w[i] = (uint8_t)rf;
+			S.pos[id] = off;
+		}
+		S.nextra[id] = dd;  // (nextra is free until the heads are parsed)
+		__syncwarp();
+	}
+	__syncthreads();
+	// scan in row order: thread t owns rows ERPT * t .. ERPT * t + ERPT - 1 of the tile
+	uint64_t v[ERPT], sum = 0;
+#pragma unroll
+	for (int j = 0; j < ERPT; j++) { v[j] = S.nextra[ERPT * threadIdx.x + j]; sum += v[j]; }
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	uint64_t inc = sum;
+#pragma unroll
+	for (int o = 1; o < 32; o <<= 1) {
+		const uint64_t t = __shfl_up_sync(FULL_MASK, inc, o);
+		if (lane >= o) inc += t;
+	}
+	if (lane == 31) S.warp_sum[warp] = inc;
+	__syncthreads();
+	if (warp == 0) {
+		uint64_t w = lane < TPB / 32 ? S.warp_sum[lane] : 0;
+#pragma unroll
+		for (int o = 1; o < TPB / 32; o <<= 1) {
+			const uint64_t t = __shfl_up_sync(FULL_MASK, w, o);
+			if (lane >= o) w += t;
+		}
+		const uint64_t tile_total = __shfl_sync(FULL_MASK, w, TPB / 32 - 1);
+		if (lane < TPB / 32) S.warp_sum[lane] = w;  // inclusive per warp
+		volatile uint64_t *state = R.tile_state;
+		const uint32_t tile = S.tile;
+		uint64_t exclusive = 0;
+		if (tile == 0) {
+			if (lane == 0) state[0] = FLAG_PFX | tile_total;
+		} else {
+			if (lane == 0) state[tile] = FLAG_AGG | tile_total;
+			int64_t look = (int64_t)tile - 1;
+			for (;;) {
+				const int64_t idx = look - lane;
+				uint64_t st = idx >= 0 ? state[idx] : FLAG_PFX;
+				while (__any_sync(FULL_MASK, (st & FLAG_MASK) == 0))
+					if ((st & FLAG_MASK) == 0) st = state[idx];
+				const unsigned pfx = __ballot_sync(FULL_MASK, (st & FLAG_MASK) == FLAG_PFX);
+				const int first = pfx ? __ffs(pfx) - 1 : 32;
+				uint64_t contrib = (lane <= first && idx >= 0) ? (st & ~FLAG_MASK) : 0;
+#pragma unroll
+				for (int o = 16; o; o >>= 1) contrib += __shfl_xor_sync(FULL_MASK, contrib, o);
+				exclusive += contrib;
+				if (pfx) break;
+				look -= 32;
+			}
+			if (lane == 0) state[tile] = FLAG_PFX | (exclusive + tile_total);
+		}
+		if (lane == 0) S.tile_base = exclusive;
+	}
+	__syncthreads();
+	uint64_t run = S.tile_base + (warp ? S.warp_sum[warp - 1] : 0) + (inc - sum);
+#pragma unroll
+	for (int j = 0; j < ERPT; j++) {
+		const int64_t i = base + ERPT * threadIdx.x + j;
+		if (i < tend) R.rp_w[i] = (int64_t)run;
+		run += v[j];
+	}
+	// rp[tend]: the end of the tile's last row (the next tile writes the same value there; for the last tile, the total)
+	if (threadIdx.x == TPB - 1) R.rp_w[tend] = (int64_t)run;
+	__syncthreads();
+}
+
+template <int DEF, class RD, bool FUSED>
 __device__ __forceinline__ void extras_tile(const GraphDev &g, const RangeDev &R, const HeavyDev &H, ExtrasSmem &S, int64_t base, int64_t count,
                                             int64_t rp_from) {
+	if (FUSED) tile_front_end<DEF, RD>(g, R, S, base, count);
 	// heads of my rows (uniform loop: the warp reconverges at the end of every iteration)
 	int bucket[ERPT];
 #pragma unroll 1
@@ -459,10 +573,11 @@ __device__ __forceinline__ void extras_tile(const GraphDev &g, const RangeDev &R
 			if (x >= R.from && (uint64_t)(R.rp[i + 1] - rp_from) > R.col_capacity) raise(g, ERR_CAPACITY);
 			else {
 				RD r;
-				tile_reader<RD>(r, g, S, ef_get(g, x));
+				tile_reader<RD>(r, g, S, FUSED ? S.pos[id] : ef_get(g, x));
 				RowHead h;
 				const uint32_t rf = R.ref[i];
-				const uint32_t dref = rf ? R.deg[i - rf] : 0;
+				// (front end inside this kernel: rows before the tile belong to another block, their outdegrees are in S.hdeg)
+				const uint32_t dref = !rf ? 0 : (FUSED && i - rf < base) ? hdeg(S)[base - 1 - (i - rf)] : R.deg[i - rf];
 				row_head<DEF>(g, r, dref, h);
 				if (rf && R.info) {
 					RowInfo ri;
@@ -522,13 +637,17 @@ __device__ __forceinline__ void extras_tile(const GraphDev &g, const RangeDev &R
 	}
 }
 
-template <int DEF>
+template <int DEF, bool FUSED>
 __global__ void __launch_bounds__(TPB) k_extras(GraphDev g, RangeDev R, HeavyDev H) {
 	extern __shared__ __align__(16) unsigned char smem_raw[];
 	ExtrasSmem &S = *reinterpret_cast<ExtrasSmem *>(smem_raw);
-	const int64_t base = (int64_t)blockIdx.x * ETILE;
+	if (FUSED) {
+		if (threadIdx.x == 0) S.tile = atomicAdd(R.tile_ticket, 1u);
+		__syncthreads();
+	}
+	const int64_t base = (int64_t)(FUSED ? S.tile : blockIdx.x) * ETILE;
 	const int64_t count = R.hi - R.lo;
-	const int64_t rp_from = R.rp[R.from - R.lo];
+	const int64_t rp_from = FUSED ? 0 : R.rp[R.from - R.lo];  // (front end inside this kernel: no halo, rp[0] = 0)
 	const int64_t tend = base + ETILE < count ? base + ETILE : count;
 	if (threadIdx.x == 0) S.span[0] = ef_get(g, R.lo + base);
 	if (threadIdx.x == 32) S.span[1] = ef_get(g, R.lo + tend);
@@ -537,12 +656,14 @@ __global__ void __launch_bounds__(TPB) k_extras(GraphDev g, RangeDev R, HeavyDev
 	{
 		const char *p;
 		const int t = threadIdx.x;
-		p = (const char *)(R.deg + base) + (size_t)t * 128;
-		if (p < (const char *)(R.deg + tend)) prefetch_l1(p);
-		p = (const char *)(R.rp + base) + (size_t)t * 128;
-		if (p < (const char *)(R.rp + tend + 1)) prefetch_l1(p);
-		p = (const char *)(R.ref + base) + (size_t)t * 128;
-		if (p < (const char *)(R.ref + tend)) prefetch_l1(p);
+		if (!FUSED) {
+			p = (const char *)(R.deg + base) + (size_t)t * 128;
+			if (p < (const char *)(R.deg + tend)) prefetch_l1(p);
+			p = (const char *)(R.rp + base) + (size_t)t * 128;
+			if (p < (const char *)(R.rp + tend + 1)) prefetch_l1(p);
+			p = (const char *)(R.ref + base) + (size_t)t * 128;
+			if (p < (const char *)(R.ref + tend)) prefetch_l1(p);
+		}
 		const uint64_t e0 = (uint64_t)(R.lo + base - g.ef_first), e1 = (uint64_t)(R.lo + tend - g.ef_first);
 		p = (const char *)(g.ef_lower + (e0 * (uint64_t)g.ef_l >> 6)) + (size_t)t * 128;
 		if (p <= (const char *)(g.ef_lower + (e1 * (uint64_t)g.ef_l >> 6))) prefetch_l1(p);
@@ -573,9 +694,11 @@ __global__ void __launch_bounds__(TPB) k_extras(GraphDev g, RangeDev R, HeavyDev
 		if (threadIdx.x == 0) { S.wbase = w0; S.nw = (uint32_t)nw; }
 	}
 	__syncthreads();
-	if (staged) extras_tile<DEF, TileReader>(g, R, H, S, base, count, rp_from);
-	else extras_tile<DEF, BitReader>(g, R, H, S, base, count, rp_from);
+	if (staged) extras_tile<DEF, TileReader, FUSED>(g, R, H, S, base, count, rp_from);
+	else extras_tile<DEF, BitReader, FUSED>(g, R, H, S, base, count, rp_from);
 }
+
+uint32_t extras_tiles(int64_t count) { return grid_for(count, ETILE); }
 
 // class starts of the global heavy list: counters[1..64] = counts -> counters[65..128] = running cursors
 __global__ void k_heavy_offsets(HeavyDev H) {
@@ -734,19 +857,30 @@ void launch_extras(const Launch &L, const GraphDev &g, int def, const RangeDev &
 	if (count <= 0) return;
 	if (h.rows) cudaMemsetAsync(h.counters, 0, 129 * sizeof(unsigned long long), L.stream);
 	const size_t smem = sizeof(ExtrasSmem);
+#define WGBV_LAUNCH_EXTRAS(D, F)                                                                              \
+	do {                                                                                                     \
+		cudaFuncSetAttribute(k_extras<D, F>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);        \
+		k_extras<D, F><<<grid_for(count, ETILE), TPB, smem, L.stream>>>(g, r, h);                            \
+	} while (0)
+	const bool front = r.rp_w != nullptr;  // stages 1 and 2 inside the kernel
+	if (front) {
+		cudaMemsetAsync(r.tile_state, 0, (size_t)extras_tiles(count) * sizeof(uint64_t), L.stream);
+		cudaMemsetAsync(r.tile_ticket, 0, sizeof(uint32_t), L.stream);
+	}
 	switch (def) {
 	case 2:
-		cudaFuncSetAttribute(k_extras<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-		k_extras<2><<<grid_for(count, ETILE), TPB, smem, L.stream>>>(g, r, h);
+		if (front) WGBV_LAUNCH_EXTRAS(2, true);
+		else WGBV_LAUNCH_EXTRAS(2, false);
 		break;
 	case 1:
-		cudaFuncSetAttribute(k_extras<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-		k_extras<1><<<grid_for(count, ETILE), TPB, smem, L.stream>>>(g, r, h);
+		if (front) WGBV_LAUNCH_EXTRAS(1, true);
+		else WGBV_LAUNCH_EXTRAS(1, false);
 		break;
 	default:
-		cudaFuncSetAttribute(k_extras<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-		k_extras<0><<<grid_for(count, ETILE), TPB, smem, L.stream>>>(g, r, h);
+		if (front) WGBV_LAUNCH_EXTRAS(0, true);
+		else WGBV_LAUNCH_EXTRAS(0, false);
 	}
+#undef WGBV_LAUNCH_EXTRAS
 	WGBV_LAUNCHED(L);
 	if (!h.rows) return;
 	k_heavy_offsets<<<1, 32, 0, L.stream>>>(h);

@@ -41,6 +41,15 @@ struct RangeDev {
 	uint32_t *depth_out = nullptr;
 	uint32_t walk_levels = 0;
 	uint32_t *deep = nullptr;
+	// One-launch front end (no halo, lo == from): k_extras itself reads outdegree and reference of its rows (stage 1),
+	// scans the outdegrees across tiles by decoupled look-back (stage 2) and writes deg_w / ref_w / rp_w -- the very
+	// arrays deg / ref / rp point to -- before it parses the rest.  tile_state: one zeroed word per tile; tile_ticket:
+	// one zeroed word.  All unused when rp_w is nullptr.
+	uint32_t *deg_w = nullptr;
+	uint8_t *ref_w = nullptr;
+	int64_t *rp_w = nullptr;
+	uint64_t *tile_state = nullptr;
+	uint32_t *tile_ticket = nullptr;
 };
 
 // One random-access job list: `rows` chain rows, each decoded into its own slot.
@@ -97,6 +106,7 @@ void launch_level_lists(const Launch &L, const GraphDev &g, const uint8_t *ref, 
                         uint32_t *deep);
 // stage 3a: intervals + residuals of every row (whole row when it has no reference)
 void launch_extras(const Launch &L, const GraphDev &g, int def, const RangeDev &r, const HeavyDev &h);
+uint32_t extras_tiles(int64_t count);
 // stage 3b: copy-block resolution of the rows at one depth level; list == nullptr: every node is inspected
 // all levels of shallow chains in one launch (see k_copy_fused); ticket and flags[tiles] must be zero
 uint32_t copy_fused_tiles(int64_t count);

@@ -73,6 +73,7 @@ struct wgbv_stream {
 	DevBuf deg, ref, depth, rp, scan_state, ticket, halo, levels, list, col, rowptr, ids, batch;
 	DevBuf t_pairs[2], t_indeg, t_counts, t_pos;  // wgbv_transpose_csr
 	DevBuf heavy_rows, heavy_sorted, heavy_cls, heavy_counters, tile_scratch, level_pos, row_info;
+	bool front_in_extras = true;  // false: always run header and scan as their own launches (WGBV_SPLIT_FRONT=1)
 	bool fused_levels = false;  // true: all levels of shallow chains in one launch, k_copy_fused (WGBV_FUSED_LEVELS=1)
 	bool force_levels = true;   // false: use the fused tile kernel where it applies (WGBV_TILE=1)
 	DevBuf c_node, c_dst, c_parent, c_deg, c_isq, c_level, c_len, c_arcs, c_row0, c_soff, c_store;
@@ -379,6 +380,8 @@ extern "C" int wgbv_stream_create(wgbv_graph *g, void *cuda_stream, wgbv_stream 
 	// the level-synchronous kernels on graphs with long rows, so it is opt-in for now.
 	const char *tl = getenv("WGBV_TILE");
 	s->force_levels = !(tl && tl[0] == '1');
+	const char *sf = getenv("WGBV_SPLIT_FRONT");
+	s->front_in_extras = !(sf && sf[0] == '1');
 	const char *fl = getenv("WGBV_FUSED_LEVELS");
 	s->fused_levels = fl && fl[0] == '1';
 	g->streams++;
@@ -469,6 +472,7 @@ struct Prepared {
 	uint32_t max_depth = 0;
 	bool have_depth = false;
 	const int64_t *rp = nullptr;
+	int64_t *front_rp = nullptr;  // not null: stages 1 and 2 have NOT run; k_extras does them itself and writes the row pointers here
 };
 
 // Stages 1, 2 and 2b for [from, to): degrees, row pointers and depth levels.  Leaves the row pointers of
@@ -614,9 +618,17 @@ static int decode_rows(wgbv_stream *s, int64_t from, int64_t to, Prepared &P, in
 			R.deep = deep;
 		}
 	}
+	if (P.front_rp) {
+		R.deg_w = s->deg.as<uint32_t>();
+		R.ref_w = s->ref.as<uint8_t>();
+		R.rp_w = P.front_rp;
+		R.tile_state = s->scan_state.as<uint64_t>();
+		R.tile_ticket = s->ticket.as<uint32_t>();
+	}
 	launch_extras(L, s->dev, g->def_codes, R, H);
 	R.depth = s->depth.as<uint32_t>();
 	R.depth_out = nullptr;
+	R.rp_w = nullptr;
 	if (fused) {
 		const uint32_t tiles = copy_fused_tiles(P.cnt);
 		if ((rc = s->levels.ensure((size_t)tiles * 4))) return rc;
@@ -701,6 +713,26 @@ extern "C" int wgbv_decode_csr(wgbv_stream *s, int64_t from, int64_t to, int64_t
 	int rc = check_range(s->g, from, to);
 	if (rc) return rc;
 	Prepared P;
+	wgbv_graph *g = s->g;
+	// The usual case -- bounded, shallow reference chains and a range that needs no halo -- runs without the separate
+	// header and scan launches and without the read-back of the arc count: k_extras does stages 1 and 2 for its own
+	// tiles (RangeDev::rp_w) and the capacity is checked on the device.  WGBV_SPLIT_FRONT=1 keeps the separate stages.
+	if (s->front_in_extras && to > from && halo_start(g, from) == from && g->halo_nodes >= 0 && g->props.max_ref_count <= 8 &&
+	    s->force_levels && !s->fused_levels && to - from < (int64_t)0xfffffff0ll) {
+		P.lo = from;
+		P.cnt = to - from;
+		P.halo_n = 0;
+		P.halo_arcs = 0;
+		P.arcs = (int64_t)std::min<uint64_t>(col_capacity, (uint64_t)INT64_MAX / 16);  // an upper bound: sizes the scratch
+		P.rp = d_rowptr;
+		P.front_rp = d_rowptr;
+		const size_t c = (size_t)P.cnt;
+		if ((rc = s->deg.ensure(c * 4)) || (rc = s->ref.ensure(c)) || (rc = s->scan_state.ensure(((c + 1) / 2048 + (size_t)extras_tiles(P.cnt) + 2) * 8)) ||
+		    (rc = s->ticket.ensure(64)))
+			return rc;
+		for (int i = 0; i < 4; i++) cudaEventRecord(s->ev[i], s->stream);  // (stages 1-2 have no time of their own here)
+		return decode_rows(s, from, to, P, d_col, col_capacity);
+	}
 	if ((rc = prepare(s, from, to, d_rowptr, P))) return rc;
 	return decode_rows(s, from, to, P, d_col, col_capacity);
 }

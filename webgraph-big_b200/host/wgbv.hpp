@@ -159,6 +159,12 @@ public:
 		while ((int)res.size() < howMany) res.push_back(NodeIterator(shared_from_this(), n, n));
 		return res;
 	}
+	// Transform.transpose on a CSR that already lives in device memory (Transform.java:1098-1144); all four are device pointers
+	void transposeDevice(int64_t n, const int64_t *d_rowptr, const int64_t *d_col, int64_t *d_t_rowptr, int64_t *d_t_col) {
+		check(wgbv_transpose_csr(st_, n, d_rowptr, d_col, d_t_rowptr, d_t_col));
+	}
+	// host-side scans of this copy deliver successors as uint32 (graphs of at most 2^32 nodes): half the PCIe bytes
+	void setNarrowScan(bool on) { check(wgbv_scan_set_narrow(st_, on ? 1 : 0)); }
 	wgbv_stream *stream() const { return st_; }
 };
 
