@@ -463,3 +463,39 @@ def test_transpose_equals_oracle_and_is_an_involution(cnr, cnr_golden):
     assert trp[7] == 0 and trp[8] == 50000 and np.array_equal(tcol, np.arange(50000))
     with pytest.raises(wg.IllegalArgumentException):
         _transpose_on_gpu(cnr, 10, np.array([0, 1] + [1] * 9, dtype=np.int64), np.array([10], dtype=np.int64))
+
+
+def test_offsets_decoded_on_the_device(monkeypatch, cnr_basename, cnr_golden):
+    """the .offsets stream decoded and turned into the Elias-Fano list on the device (forced here for small
+    graphs with WGBV_DEVICE_OFFSETS=1) must open the same graph as the host decoder: the reference's own .offsets file,
+    graphs with giant records (sparse Elias-Fano blocks, codes longer than a machine word apart), zero-degree runs, a
+    slice, and a truncated stream."""
+    monkeypatch.setenv("WGBV_DEVICE_OFFSETS", "1")
+    deg, rowptr, col = cnr_golden
+    with wg.GpuBVGraph.load(cnr_basename) as g:
+        rp, c = g.decodeToCSR()
+        assert np.array_equal(rp, rowptr) and np.array_equal(c, col)
+        ids = np.array([0, 1, 325556, 100000, 77, 200001], dtype=np.int64)
+        rp2, c2 = g.successorsBatch(ids)
+        assert np.array_equal(c2, np.concatenate([col[rowptr[x]:rowptr[x + 1]] for x in ids]))
+    graphs = [bg.copy_model(50000, seed=31, mean_degree=9, nsplits=1),
+              bg.erdos_renyi(3000, 0.01, seed=4),
+              bg.big_graph(2000, giant_every=300, giant_degree=40000, nsplits=1)]
+    rowptr2, col2 = _similar_rows_graph(3000, (256, 1000, 1536), 12, 40000, 40000)
+    graphs.append(bg.encode_csr(rowptr2, col2, bg.make_params(window=7, maxref=3, minint=4)))
+    empty_rp = np.zeros(5001, dtype=np.int64)
+    empty_rp[2500:] = 3
+    graphs.append(bg.encode_csr(empty_rp, np.array([1, 2, 4999], dtype=np.int64), bg.make_params()))
+    for e in graphs:
+        if e is None:
+            continue
+        odeg, ocol = oracle_of(e).decode_range()
+        with gpu_of(e) as g:
+            rp, c = g.decodeToCSR()
+            assert np.array_equal(rp, rowptr_of(odeg)) and np.array_equal(c, ocol)
+            n = odeg.size
+            ids = np.array([0, n - 1, n // 2, n // 3], dtype=np.int64)
+            assert np.array_equal(g.outdegrees(ids), odeg[ids])
+    e = graphs[0]
+    with pytest.raises(wg.IOException):
+        wg.GpuBVGraph.load_mem(e.properties_text(), e.graph, e.offsets_stream[: e.offsets_stream.size // 2])

@@ -144,6 +144,13 @@ void launch_transpose_pack(const Launch &L, const GraphDev &g, int64_t n, const 
                            uint64_t *pairs, uint32_t *indeg);
 void launch_radix_hist(const Launch &L, const uint64_t *in, uint64_t count, int pass, uint32_t *counts);
 void launch_radix_scatter(const Launch &L, const uint64_t *in, uint64_t count, int pass, const int64_t *pos, uint64_t *out, int64_t *t_col);
+// .offsets on the device (bv_offsets.cu): h_stream holds `count` gamma-coded differences; *d_off_out (cudaMalloc'ed, the
+// caller frees it) receives their running sums.  device_ef_build turns off[0 .. n) - base into the Elias-Fano arrays
+// ef_get reads, leaves them on the device and copies them into `ef`.
+struct EliasFano;
+int device_decode_offsets(const uint8_t *h_stream, uint64_t nbytes, int64_t count, uint64_t **d_off_out);
+int device_ef_build(const uint64_t *d_off, uint64_t n, uint64_t base, uint64_t last_value, EliasFano &ef, uint64_t **d_lower,
+                    uint64_t **d_upper, uint64_t **d_hints, uint64_t **d_sparse, uint64_t *device_bytes);
 // byte-swap the uploaded stream into big-endian 64-bit words, in place
 void launch_bswap(const Launch &L, uint64_t *words, uint64_t nwords);
 // A handful of device scalars for the host, written by a kernel straight into mapped pinned host memory: unlike a small

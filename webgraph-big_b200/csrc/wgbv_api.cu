@@ -5,6 +5,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <chrono>
 #include <new>
 #include <string>
 #include <vector>
@@ -157,9 +158,23 @@ extern "C" void wgbv_close(wgbv_graph *g) {
 
 // Builds the device-resident graph for nodes [avail_lo, shard_hi) from `off`, the absolute bit offsets (inside
 // `graph`) of nodes [off_first, off_first + off.size() - 1].
+// WGBV_TIMING=1: the phases of an open, on stderr
+struct LoadTimer {
+	bool on;
+	std::chrono::steady_clock::time_point t;
+	LoadTimer() : on(getenv("WGBV_TIMING") != nullptr), t(std::chrono::steady_clock::now()) {}
+	void lap(const char *what) {
+		if (!on) return;
+		const auto now = std::chrono::steady_clock::now();
+		fprintf(stderr, "[wgbv] %-28s %8.1f ms\n", what, std::chrono::duration<double, std::milli>(now - t).count());
+		t = now;
+	}
+};
+
+// The offsets come either as a host vector (`off`) or, decoded on the device, as `d_off` (then `off` is empty).
 static int build_graph(const wgbv_props *props, const uint8_t *graph, uint64_t graph_bytes, const std::vector<uint64_t> &off,
-                       int64_t off_first, int64_t avail_lo, int64_t shard_lo, int64_t shard_hi, int64_t halo_nodes, int device,
-                       wgbv_graph **out) {
+                       const uint64_t *d_off, int64_t off_first, int64_t avail_lo, int64_t shard_lo, int64_t shard_hi, int64_t halo_nodes,
+                       int device, wgbv_graph **out) {
 	wgbv_graph *g = new (std::nothrow) wgbv_graph();
 	if (!g) return fail(WGBV_EARG, "out of host memory");
 	g->props = *props;
@@ -175,8 +190,19 @@ static int build_graph(const wgbv_props *props, const uint8_t *graph, uint64_t g
 	int rc;
 
 	// the slice of the bit stream that holds [avail_lo, shard_hi), starting on a 64-bit word of the file
-	const uint64_t bit0 = off[(size_t)(avail_lo - off_first)] & ~63ull;
-	const uint64_t bit1 = off[(size_t)(shard_hi - off_first)];
+	uint64_t first_off, last_off;
+	if (d_off) {
+		if (cudaMemcpy(&first_off, d_off + (avail_lo - off_first), 8, cudaMemcpyDeviceToHost) != cudaSuccess ||
+		    cudaMemcpy(&last_off, d_off + (shard_hi - off_first), 8, cudaMemcpyDeviceToHost) != cudaSuccess) {
+			delete g;
+			return fail(WGBV_ECUDA, "reading the decoded offsets failed: %s", cudaGetErrorString(cudaGetLastError()));
+		}
+	} else {
+		first_off = off[(size_t)(avail_lo - off_first)];
+		last_off = off[(size_t)(shard_hi - off_first)];
+	}
+	const uint64_t bit0 = first_off & ~63ull;
+	const uint64_t bit1 = last_off;
 	const uint64_t byte0 = bit0 >> 3;
 	const uint64_t byte1 = std::min<uint64_t>((bit1 + 7) >> 3, graph_bytes);
 	const uint64_t data_words = (byte1 > byte0 ? byte1 - byte0 + 7 : 0) / 8;
@@ -185,6 +211,7 @@ static int build_graph(const wgbv_props *props, const uint8_t *graph, uint64_t g
 	g->byte1 = byte1;
 	g->data_words = data_words;
 	auto cleanup = [&](int code) { wgbv_close(g); return code; };
+	LoadTimer lt;
 	if (cudaMalloc((void **)&g->d_words, nwords * 8) != cudaSuccess) return cleanup(fail(WGBV_ECUDA, "cudaMalloc of the bit stream (%llu bytes) failed", (unsigned long long)nwords * 8));
 	g->device_bytes += nwords * 8;
 	if (cudaMemset(g->d_words, 0, nwords * 8) != cudaSuccess) return cleanup(fail(WGBV_ECUDA, "cudaMemset failed"));
@@ -192,14 +219,24 @@ static int build_graph(const wgbv_props *props, const uint8_t *graph, uint64_t g
 		return cleanup(fail(WGBV_ECUDA, "upload of the bit stream failed"));
 	Launch L{nullptr, nullptr};
 	launch_bswap(L, g->d_words, data_words);
+	lt.lap("upload of the bit stream");
 
 	// Elias-Fano list of the offsets of [avail_lo, shard_hi] relative to bit0
-	g->ef.build(off.data() + (avail_lo - off_first), (uint64_t)(shard_hi - avail_lo + 1), bit0);
-	if ((rc = upload(&g->d_lower, g->ef.lower, &g->device_bytes))) return cleanup(rc);
-	if ((rc = upload(&g->d_upper, g->ef.upper, &g->device_bytes))) return cleanup(rc);
-	if ((rc = upload(&g->d_hints, g->ef.hints, &g->device_bytes))) return cleanup(rc);
-	if ((rc = upload(&g->d_sparse, g->ef.sparse, &g->device_bytes))) return cleanup(rc);
+	if (d_off) {
+		if ((rc = device_ef_build(d_off + (avail_lo - off_first), (uint64_t)(shard_hi - avail_lo + 1), bit0, last_off, g->ef, &g->d_lower,
+		                          &g->d_upper, &g->d_hints, &g->d_sparse, &g->device_bytes)))
+			return cleanup(rc);
+		lt.lap("Elias-Fano on the device");
+	} else {
+		g->ef.build(off.data() + (avail_lo - off_first), (uint64_t)(shard_hi - avail_lo + 1), bit0);
+		lt.lap("Elias-Fano construction");
+		if ((rc = upload(&g->d_lower, g->ef.lower, &g->device_bytes))) return cleanup(rc);
+		if ((rc = upload(&g->d_upper, g->ef.upper, &g->device_bytes))) return cleanup(rc);
+		if ((rc = upload(&g->d_hints, g->ef.hints, &g->device_bytes))) return cleanup(rc);
+		if ((rc = upload(&g->d_sparse, g->ef.sparse, &g->device_bytes))) return cleanup(rc);
+	}
 	if (cudaDeviceSynchronize() != cudaSuccess) return cleanup(fail(WGBV_ECUDA, "device error while loading: %s", cudaGetErrorString(cudaGetLastError())));
+	lt.lap("upload of the offsets list");
 
 	GraphDev &d = g->dev;
 	d.words = g->d_words;
@@ -234,6 +271,40 @@ static int64_t halo_of(const wgbv_props *props) {
 	return (int64_t)props->window_size * (int64_t)props->max_ref_count;
 }
 
+// .offsets on the device (bv_offsets.cu): gamma-coded streams of at least 2^20 entries; WGBV_DEVICE_OFFSETS=1 forces it
+// for any size, =0 keeps the host decoder.
+static bool offsets_on_device(const wgbv_props *props, int64_t count) {
+	if (props->offset_coding != WGBV_GAMMA || count < 1) return false;
+	const char *e = getenv("WGBV_DEVICE_OFFSETS");
+	if (e && e[0] == '0') return false;
+	if (e && e[0] == '1') return true;
+	return count >= (1 << 20);
+}
+
+// Decodes the stream on the device and opens [shard_lo, shard_hi) of it (no sharding decision is taken from the offsets).
+static int open_with_device_offsets(const wgbv_props *props, const uint8_t *graph, uint64_t graph_bytes, const uint8_t *offsets,
+                                    uint64_t offsets_bytes, int64_t off_first, int64_t count, int64_t avail_lo, int64_t shard_lo,
+                                    int64_t shard_hi, int device, wgbv_graph **out) {
+	uint64_t *d_off = nullptr;
+	LoadTimer lt;
+	int rc = device_decode_offsets(offsets, offsets_bytes, count, &d_off);
+	if (rc) return rc;
+	lt.lap(".offsets on the device");
+	uint64_t last = 0;
+	if (cudaMemcpy(&last, d_off + (count - 1), 8, cudaMemcpyDeviceToHost) != cudaSuccess) {
+		cudaFree(d_off);
+		return fail(WGBV_ECUDA, "reading the decoded offsets failed: %s", cudaGetErrorString(cudaGetLastError()));
+	}
+	if (last > graph_bytes * 8) {
+		cudaFree(d_off);
+		return fail(WGBV_EIO, "the last offset (%llu) lies beyond the end of the bit stream (%llu bits)", (unsigned long long)last, (unsigned long long)graph_bytes * 8);
+	}
+	static const std::vector<uint64_t> none;
+	rc = build_graph(props, graph, graph_bytes, none, d_off, off_first, avail_lo, shard_lo, shard_hi, halo_of(props), device, out);
+	cudaFree(d_off);
+	return rc;
+}
+
 static int check_offsets(const std::vector<uint64_t> &off, uint64_t graph_bytes) {
 	if (off.back() > graph_bytes * 8) return fail(WGBV_EIO, "the last offset (%llu) lies beyond the end of the bit stream (%llu bits)", (unsigned long long)off.back(), (unsigned long long)graph_bytes * 8);
 	for (size_t i = 0; i + 1 < off.size(); i++)
@@ -250,6 +321,8 @@ extern "C" int wgbv_open_mem(const wgbv_props *props, const uint8_t *graph, uint
 	int rc = check_codings(*props);
 	if (rc) return rc;
 	if ((rc = select_device(device))) return rc;
+	if (shard_count == 1 && offsets_on_device(props, props->nodes + 1))
+		return open_with_device_offsets(props, graph, graph_bytes, offsets, offsets_bytes, 0, props->nodes + 1, 0, 0, props->nodes, device, out);
 	std::vector<uint64_t> off;
 	if ((rc = decode_offsets(*props, offsets, offsets_bytes, props->nodes + 1, off))) return rc;
 	if ((rc = check_offsets(off, graph_bytes))) return rc;
@@ -260,7 +333,7 @@ extern "C" int wgbv_open_mem(const wgbv_props *props, const uint8_t *graph, uint
 	plan_shards(off, shard_count, bounds);
 	const int64_t lo = bounds[(size_t)shard_index], hi = bounds[(size_t)shard_index + 1];
 	const int64_t avail_lo = halo < 0 ? 0 : std::max<int64_t>(0, lo - halo);
-	return build_graph(props, graph, graph_bytes, off, 0, avail_lo, lo, hi, halo, device, out);
+	return build_graph(props, graph, graph_bytes, off, nullptr, 0, avail_lo, lo, hi, halo, device, out);
 }
 
 extern "C" int wgbv_plan_shards(const wgbv_props *props, const uint8_t *offsets, uint64_t offsets_bytes, int shard_count,
@@ -292,10 +365,15 @@ extern "C" int wgbv_open_slice(const wgbv_props *props, int64_t first_node, int6
 	int rc = check_codings(*props);
 	if (rc) return rc;
 	if ((rc = select_device(device))) return rc;
+	if (offsets_on_device(props, node_count + 1))
+		return open_with_device_offsets(props, bits, nbytes, offsets, offsets_bytes, first_node, node_count + 1, first_node,
+		                                first_node + halo_nodes, first_node + node_count, device, out);
 	std::vector<uint64_t> off;
+	LoadTimer lt;
 	if ((rc = decode_offsets(*props, offsets, offsets_bytes, node_count + 1, off))) return rc;
+	lt.lap("decoding of .offsets");
 	if ((rc = check_offsets(off, nbytes))) return rc;
-	return build_graph(props, bits, nbytes, off, first_node, first_node, first_node + halo_nodes, first_node + node_count, halo_of(props), device, out);
+	return build_graph(props, bits, nbytes, off, nullptr, first_node, first_node, first_node + halo_nodes, first_node + node_count, halo_of(props), device, out);
 }
 
 extern "C" int wgbv_upload_stream(wgbv_stream *s, const uint8_t *graph, uint64_t graph_bytes) {
