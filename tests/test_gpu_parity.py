@@ -499,3 +499,36 @@ def test_offsets_decoded_on_the_device(monkeypatch, cnr_basename, cnr_golden):
     e = graphs[0]
     with pytest.raises(wg.IOException):
         wg.GpuBVGraph.load_mem(e.properties_text(), e.graph, e.offsets_stream[: e.offsets_stream.size // 2])
+
+
+def test_randomized_parity_sweep():
+    """Many small graphs with random shapes and random format parameters (window, maxrefcount, minintervallength,
+    degrees up to a few thousand, how much is copied): bulk decode, a decode that starts in the middle (halo), batched
+    random access and the transpose involution against the oracle."""
+    rng = np.random.default_rng(20241)
+    for trial in range(36):
+        n = int(rng.integers(500, 40000))
+        window = int(rng.choice([1, 2, 3, 7, 7, 7, 12, 16]))
+        maxref = int(rng.choice([1, 2, 3, 3, 3, 5, 8, 2147483647]))
+        minint = int(rng.choice([0, 2, 3, 4, 4, 8]))
+        md = float(rng.choice([2, 5, 12, 20, 20, 45, 90]))
+        e = bg.copy_model(n, seed=int(rng.integers(1, 1 << 30)), mean_degree=md, p_ref=float(rng.uniform(0.2, 0.95)),
+                          p_keep=float(rng.uniform(0.3, 0.97)), p_run=float(rng.uniform(0.0, 0.6)), max_degree=int(rng.choice([50, 300, 3000])),
+                          params=bg.make_params(window=window, maxref=maxref, minint=minint), nsplits=int(rng.choice([1, 3])))
+        odeg, ocol = oracle_of(e).decode_range()
+        orp = rowptr_of(odeg)
+        tag = (trial, n, window, maxref, minint, md)
+        with gpu_of(e) as g:
+            rp, c = g.decodeToCSR()
+            assert np.array_equal(rp, orp) and np.array_equal(c, ocol), tag
+            a = int(rng.integers(0, n))
+            b = int(rng.integers(a, n + 1))
+            rp2, c2 = g.decodeToCSR(a, b)
+            assert np.array_equal(rp2, orp[a:b + 1] - orp[a]) and np.array_equal(c2, ocol[orp[a]:orp[b]]), tag
+            ids = rng.integers(0, n, 200).astype(np.int64)
+            rp3, c3 = g.successorsBatch(ids)
+            assert np.array_equal(c3, np.concatenate([ocol[orp[x]:orp[x + 1]] for x in ids])), tag
+            if trial % 6 == 0:
+                trp, tcol = _transpose_on_gpu(g, n, orp, ocol)
+                brp, bcol = _transpose_on_gpu(g, n, trp, tcol)
+                assert np.array_equal(brp, orp) and np.array_equal(bcol, ocol), tag
