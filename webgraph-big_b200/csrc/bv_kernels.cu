@@ -1394,15 +1394,7 @@ __global__ void __launch_bounds__(TPB) k_chain_copy(GraphDev g, ChainDev c, uint
 	row_head<DEF>(g, r, dref, h);
 	r.seek(h.blocks_pos);
 	__syncwarp(mask);
-	// reference rows of at most 128 successors: merge from the mask of copied positions the head parse has just built
-	// (one emitted successor per iteration); the others from the block codes.  Both loops are warp-synchronous: every
-	// lane of `mask` calls both, with no work in the one that is not its own.
-	const bool masked = dref <= 128;
-	const int64_t *src = chain_slot(c, (uint64_t)p);
-	int64_t *dst = chain_slot(c, row);
-	row_copy_masked(g, src, masked ? h.cmask[0] : 0, masked ? h.cmask[1] : 0, dst + h.ncopied, dst, h.d - h.ncopied, mask);
-	if (__any_sync(mask, !masked))
-		row_copy<DEF>(g, r, src, dref, dst + h.ncopied, dst, h.d, h.bc, masked ? 0u : h.ncopied, mask);
+	row_copy<DEF>(g, r, chain_slot(c, (uint64_t)p), dref, chain_slot(c, row) + h.ncopied, chain_slot(c, row), h.d, h.bc, h.ncopied, mask);
 }
 void launch_chain_copy(const Launch &L, const GraphDev &g, int def, const ChainDev &c, uint64_t rows, const uint32_t *level,
                        uint32_t this_level) {
