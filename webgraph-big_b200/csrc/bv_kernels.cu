@@ -475,7 +475,7 @@ __device__ __forceinline__ void tile_front_end(const GraphDev &g, const RangeDev
 			}
 			R.deg_w[i] = dd;
 			R.ref_w[i] = (uint8_t)rf;
-			S.pos[id] = off;
+			S.pos[id] = r.tell() + (RD::IS_GLOBAL ? 0ull : (S.wbase << 5));  // after the reference: where the head loop resumes
 		}
 		S.nextra[id] = dd;  // (nextra is free until the heads are parsed)
 		__syncwarp();
@@ -576,9 +576,11 @@ __device__ __forceinline__ void extras_tile(const GraphDev &g, const RangeDev &R
 				tile_reader<RD>(r, g, S, FUSED ? S.pos[id] : ef_get(g, x));
 				RowHead h;
 				const uint32_t rf = R.ref[i];
-				// (front end inside this kernel: rows before the tile belong to another block, their outdegrees are in S.hdeg)
+				// (front end inside this kernel: rows before the tile belong to another block, their outdegrees are in S.hdeg;
+				// outdegree and reference have been read already and the reader resumes after them)
 				const uint32_t dref = !rf ? 0 : (FUSED && i - rf < base) ? hdeg(S)[base - 1 - (i - rf)] : R.deg[i - rf];
-				row_head<DEF>(g, r, dref, h);
+				if (FUSED) row_blocks<DEF>(g, r, R.deg[i], rf, dref, h);
+				else row_head<DEF>(g, r, dref, h);
 				if (rf && R.info) {
 					RowInfo ri;
 					if (row_is_masked(h.d, dref)) {

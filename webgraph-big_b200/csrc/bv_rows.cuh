@@ -55,19 +55,18 @@ struct RowHead {
 	bool ok;           // false: inconsistent counts (an error bit has been raised); d and ncopied are zeroed
 };
 
-// Reads outdegree, reference, block count and sums the blocks; leaves the reader after the last block (at the
-// interval section).  dref = outdegree of the reference row (only used when rf > 0).  BVG:1010-1033.
+// The part of a row's head that follows the reference: block count and blocks (summed, and turned into the mask of
+// copied positions); leaves the reader after the last block (at the interval section).  d and rf are the row's
+// outdegree and reference, dref the outdegree of the reference row (only used when rf > 0).  BVG:1017-1033.
 template <int DEF, class RD>
-__device__ __forceinline__ void row_head(const GraphDev &g, RD &r, uint32_t dref, RowHead &h) {
-	const uint64_t d = rd_outdegree<DEF>(r, g);
-	h.d = (uint32_t)d;
-	h.rf = 0;
+__device__ __forceinline__ void row_blocks(const GraphDev &g, RD &r, uint32_t d, uint32_t rf, uint32_t dref, RowHead &h) {
+	h.d = d;
+	h.rf = rf;
 	h.bc = 0;
 	h.ncopied = 0;
 	h.blocks_pos = 0;
 	h.cmask[0] = h.cmask[1] = 0;
 	h.ok = true;
-	if (d != 0 && g.window > 0) h.rf = (uint32_t)rd_reference<DEF>(r, g);
 	if (h.rf > 0) {
 		uint64_t bc = rd_blockcount<DEF>(r, g);
 		if (bc > (uint64_t)dref + 1) { h.ok = false; bc = 0; }
@@ -97,6 +96,16 @@ __device__ __forceinline__ void row_head(const GraphDev &g, RD &r, uint32_t dref
 		h.bc = 0;
 		h.cmask[0] = h.cmask[1] = 0;
 	}
+}
+
+// Reads outdegree, reference, block count and sums the blocks; leaves the reader after the last block (at the
+// interval section).  dref = outdegree of the reference row (only used when rf > 0).  BVG:1010-1033.
+template <int DEF, class RD>
+__device__ __forceinline__ void row_head(const GraphDev &g, RD &r, uint32_t dref, RowHead &h) {
+	const uint64_t d = rd_outdegree<DEF>(r, g);
+	uint32_t rf = 0;
+	if (d != 0 && g.window > 0) rf = (uint32_t)rd_reference<DEF>(r, g);
+	row_blocks<DEF>(g, r, (uint32_t)d, rf, dref, h);
 }
 
 // No-op window policy of row_extras_core: the residual reader needs no refilling.
