@@ -386,7 +386,10 @@ static constexpr int TILE = TPB * RPT;   // rows per block: the sort domain (see
 // different lengths, and whichever warp gets them runs nearly empty.  They are appended to a global list, sorted
 // by class over the whole range (k_heavy_scatter), and decoded by k_extras_heavy where every warp finds 32 rows of
 // one class.
-static constexpr uint32_t HEAVY = 128;
+#ifndef WGBV_HEAVY
+#define WGBV_HEAVY 128
+#endif
+static constexpr uint32_t HEAVY = WGBV_HEAVY;
 
 // stage 3a: one block per ETILE consecutive nodes.  Rows without a reference come out complete.
 // The records of consecutive rows are contiguous in the bit stream, so the block first copies the tile's whole span
@@ -901,7 +904,10 @@ void launch_extras(const Launch &L, const GraphDev &g, int def, const RangeDev &
 // stage 3b: the rows of one depth level.  With a list, a block takes CTILE list entries; without, it inspects CTILE
 // consecutive nodes and keeps those at this level.  Long rows are merged by a whole warp each (row_copy_warp),
 // short ones by one lane each, 32 rows of one class per warp (row_copy_masked).
-static constexpr int CRPT = 4;
+#ifndef WGBV_CRPT
+#define WGBV_CRPT 2
+#endif
+static constexpr int CRPT = WGBV_CRPT;  // 512 rows per block measured best (256: +0.45 ms, 768: +0.1 ms, 1024: +0.3 ms, 2048: +2.9 ms per 10^8 nodes)
 static constexpr int CTILE = TPB * CRPT;
 
 __device__ __forceinline__ void cp_async8(void *smem_dst, const void *gmem_src) {
