@@ -251,34 +251,6 @@ void launch_depth(const Launch &L, const GraphDev &g, const uint8_t *ref, uint32
 	WGBV_LAUNCHED(L);
 }
 
-// Level lists (only used when chains are deep): histogram of depths, then a scatter of node indices by level.
-__global__ void __launch_bounds__(TPB) k_level_count(const uint32_t *__restrict__ depth, int64_t count, uint32_t nlevels,
-                                                     unsigned long long *level_count) {
-	const int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
-	if (i >= count) return;
-	const uint32_t d = depth[i];
-	if (d == 0 || d >= nlevels) return;
-	atomicAdd(&level_count[d], 1ull);
-}
-__global__ void __launch_bounds__(TPB) k_level_scatter(const uint32_t *__restrict__ depth, int64_t count, uint32_t nlevels,
-                                                       unsigned long long *level_cursor, uint32_t *__restrict__ list) {
-	const int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
-	if (i >= count) return;
-	const uint32_t d = depth[i];
-	if (d == 0 || d >= nlevels) return;
-	const unsigned long long p = atomicAdd(&level_cursor[d], 1ull);
-	list[p] = (uint32_t)i;
-}
-void launch_level_count(const Launch &L, const uint32_t *depth, int64_t count, uint32_t nlevels, unsigned long long *level_count) {
-	k_level_count<<<grid_for(count, TPB), TPB, 0, L.stream>>>(depth, count, nlevels, level_count);
-	WGBV_LAUNCHED(L);
-}
-void launch_level_scatter(const Launch &L, const uint32_t *depth, int64_t count, uint32_t nlevels,
-                          unsigned long long *level_cursor, uint32_t *list) {
-	k_level_scatter<<<grid_for(count, TPB), TPB, 0, L.stream>>>(depth, count, nlevels, level_cursor, list);
-	WGBV_LAUNCHED(L);
-}
-
 // ------------------------------------------------------------------------------------------------ stage 3
 // Ordered level lists for shallow chains (at most LEVELS_MAX levels): rows of one level, in node order, so that the
 // copy kernels find dense, memory-ordered work.  k_level_block_counts counts the rows of every level in blocks of

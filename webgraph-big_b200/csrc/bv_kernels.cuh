@@ -94,11 +94,7 @@ void launch_emit_rowptr(const Launch &L, const int64_t *rp, int64_t skip, int64_
 // stage 2b: reference-chain depths.  stats[0] = nodes still unresolved after this pass, stats[1] = max depth seen
 void launch_depth(const Launch &L, const GraphDev &g, const uint8_t *ref, uint32_t *depth, int64_t lo, int64_t from,
                   int64_t count, int first_pass, uint32_t *stats);
-// level lists for deep chains: count per level, then scatter node indices (relative to lo) by level
-void launch_level_count(const Launch &L, const uint32_t *depth, int64_t count, uint32_t nlevels, unsigned long long *level_count);
-void launch_level_scatter(const Launch &L, const uint32_t *depth, int64_t count, uint32_t nlevels,
-                          unsigned long long *level_cursor, uint32_t *list);
-// ordered level lists for shallow chains (nlevels <= 8): counts and pos hold nlevels * ceil(count / 2048) entries (+1 for pos);
+// ordered level lists, at most 8 levels per pass (nlevels <= 8; deeper chains take several passes): counts and pos hold nlevels * ceil(count / 2048) entries (+1 for pos);
 // the pass lists levels level0+1 .. level0+nlevels; level level0+l (l 1-based) occupies list[pos[(l-1) * nblocks] .. pos[l * nblocks]).  With ref != nullptr the depths are computed
 // on the way (bounded walk, *deep set if a chain is longer than nlevels) and stored to depth[]; with ref == nullptr depth[] is input.
 void launch_level_lists(const Launch &L, const GraphDev &g, const uint8_t *ref, uint32_t *depth, int64_t lo, int64_t from, int64_t count,
