@@ -621,6 +621,29 @@ uint64_t bvg_csr_checksum(int64_t first_node, int64_t n, const int64_t *rowptr, 
 	return acc;
 }
 
+/* Arc labels as BitStreamArcLabelledImmutableGraph.store writes them (labelling/BitStreamArcLabelledImmutableGraph.java:
+ * 654-681): the labels of every node's arcs one after the other in `out`; node_bits[x] = bits taken by node x (what
+ * the .labeloffsets stream gamma-codes after a leading gamma(0)).  kind 0: `width`-bit integers (FixedWidthIntLabel),
+ * kind 1: gamma-coded naturals (GammaCodedIntLabel).  Returns the bits written (nothing is copied if out_cap is short). */
+uint64_t bvg_write_labels(int kind, int width, int64_t n, const int64_t *rowptr, const int64_t *values, uint8_t *out, uint64_t out_cap,
+                          uint64_t *node_bits) {
+	obs_t o; memset(&o, 0, sizeof o);
+	for (int64_t x = 0; x < n; x++) {
+		const uint64_t before = o.bits;
+		for (int64_t j = rowptr[x]; j < rowptr[x + 1]; j++) {
+			if (kind == 0) obs_put_long(&o, (uint64_t)values[j], width);
+			else put_gamma(&o, (uint64_t)values[j]);
+		}
+		node_bits[x] = o.bits - before;
+	}
+	obs_finish(&o);
+	const uint64_t bytes = (o.bits + 7) >> 3;
+	if (bytes <= out_cap) memcpy(out, o.buf, bytes);
+	const uint64_t bits = o.bits;
+	free(o.buf);
+	return bits;
+}
+
 /* Single-code writer exposed so that tests can round-trip every code through the oracle's readers. */
 uint64_t bvg_write_codes(int coding, int k, const uint64_t *vals, int64_t n, uint8_t *out, uint64_t out_cap) {
 	obs_t o; memset(&o, 0, sizeof o);

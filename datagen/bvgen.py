@@ -65,6 +65,8 @@ def lib():
         L.bvg_free.restype = None
         L.bvg_csr_checksum.argtypes = [C.c_int64, C.c_int64, C.c_void_p, C.c_void_p]
         L.bvg_csr_checksum.restype = C.c_uint64
+        L.bvg_write_labels.argtypes = [C.c_int, C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
+        L.bvg_write_labels.restype = C.c_uint64
         L.bvg_write_codes.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_uint64]
         L.bvg_write_codes.restype = C.c_uint64
         _LIB = L
@@ -187,3 +189,22 @@ def write_codes(coding, values, k=3):
     out = np.zeros(vals.size * per + 64, dtype=np.uint8)
     bits = lib().bvg_write_codes(coding, k, vals.ctypes.data, vals.size, out.ctypes.data, out.size)
     return out[: (bits + 7) // 8].copy(), bits
+
+
+LABEL_FIXED_INT, LABEL_GAMMA_INT = 0, 1
+
+
+def write_labels(kind, width, rowptr, values):
+    """The .labels and .labeloffsets streams of a labelled graph whose arcs (in CSR order) carry `values`
+    (BitStreamArcLabelledImmutableGraph.store restated, see bvg_write_labels).  Returns (labels bytes, labeloffsets bytes)."""
+    rowptr = np.ascontiguousarray(rowptr, dtype=np.int64)
+    values = np.ascontiguousarray(values, dtype=np.int64)
+    n = rowptr.size - 1
+    per = width if kind == LABEL_FIXED_INT else 2 * max(int(values.max()) if values.size else 0, 1).bit_length() + 1
+    out = np.zeros(values.size * per // 8 + 64, dtype=np.uint8)
+    node_bits = np.zeros(max(n, 1), dtype=np.uint64)
+    bits = lib().bvg_write_labels(kind, width, n, rowptr.ctypes.data, values.ctypes.data if values.size else None, out.ctypes.data, out.size,
+                                  node_bits.ctypes.data)
+    assert (bits + 7) // 8 <= out.size
+    offs, _ = write_codes(GAMMA, np.concatenate([np.zeros(1, dtype=np.uint64), node_bits[:n]]))
+    return out[: (bits + 7) // 8].copy(), offs

@@ -208,6 +208,29 @@ WGBV_API int wgbv_scan_set_narrow(wgbv_stream *s, int on);
  */
 WGBV_API int wgbv_transpose_csr(wgbv_stream *s, int64_t n, const int64_t *d_rowptr, const int64_t *d_col, int64_t *d_t_rowptr, int64_t *d_t_col);
 
+/*
+ * Arc labels: the `.labels` / `.labeloffsets` pair of a BitStreamArcLabelledImmutableGraph
+ * (labelling/BitStreamArcLabelledImmutableGraph.java:65-100; offsets :339-363; what its node iterator reads per arc
+ * :487-560) decoded into an int64 array parallel to the CSR successors of the underlying graph.  kind selects the
+ * label prototype: WGBV_LABEL_FIXED_INT = FixedWidthIntLabel(key, width), width 0..32 (FixedWidthIntLabel.java:70-73);
+ * WGBV_LABEL_GAMMA_INT = GammaCodedIntLabel(key) (GammaCodedIntLabel.java:60-64).  `nodes` is the node count of the
+ * underlying graph; labeloffsets holds nodes + 1 gamma-coded differences.
+ *   wgbv_labels_decode       d_rowptr[0 .. to-from] (device; what wgbv_decode_csr / wgbv_decode_degrees wrote for the
+ *                            same range) gives every node's outdegree and the place of its labels in d_labels
+ *                            (device, `capacity` elements).  Asynchronous on the stream; errors at wgbv_stream_sync.
+ *   wgbv_labels_decode_host  the same with host arrays (synchronous).
+ * A stream, offsets and outdegrees that do not belong together give WGBV_ESTATE (the reference would return garbage).
+ */
+typedef struct wgbv_labels wgbv_labels;
+enum { WGBV_LABEL_FIXED_INT = 0, WGBV_LABEL_GAMMA_INT = 1 };
+WGBV_API int wgbv_labels_open_mem(int device, int64_t nodes, int kind, int width, const uint8_t *labels, uint64_t labels_bytes,
+                                  const uint8_t *labeloffsets, uint64_t labeloffsets_bytes, wgbv_labels **out);
+WGBV_API void wgbv_labels_close(wgbv_labels *l);
+WGBV_API int wgbv_labels_decode(wgbv_stream *s, const wgbv_labels *l, int64_t from, int64_t to, const int64_t *d_rowptr,
+                                int64_t *d_labels, uint64_t capacity);
+WGBV_API int wgbv_labels_decode_host(wgbv_stream *s, const wgbv_labels *l, int64_t from, int64_t to, const int64_t *h_rowptr,
+                                     int64_t *h_labels, uint64_t capacity);
+
 /* outdegree(x) for a batch of arbitrary nodes (BVG:821-851): h_out[i] = outdegree(h_ids[i]).  Host buffers. */
 WGBV_API int wgbv_outdegrees(wgbv_stream *s, const int64_t *h_ids, uint64_t k, int64_t *h_out);
 

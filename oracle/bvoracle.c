@@ -487,6 +487,27 @@ int64_t bvo_decode_split(const bvo_params *g, const uint8_t *graph, uint64_t gra
 }
 
 /* Exposed single-code readers so that the tests can pin each code on hand-made vectors. */
+/* Arc labels stored as a bit stream: what BitStreamArcLabelledNodeIterator does for every node of [lo, hi)
+ * (labelling/BitStreamArcLabelledImmutableGraph.java:487-560: position the label stream at the node's label offset,
+ * then one label.fromBitStream() per successor, in successor order).  kind 0 = FixedWidthIntLabel (readInt(width),
+ * FixedWidthIntLabel.java:70-73), kind 1 = GammaCodedIntLabel (readGamma, GammaCodedIntLabel.java:60-64).
+ * label_offsets: the n+1 running sums of the .labeloffsets stream (same gamma-delta format as .offsets,
+ * LabelOffsetsLongIterator :339-363, read with bvo_read_offsets).  degrees[i] = outdegree of node lo+i.
+ * Returns the number of labels written to out, or -1 if a node's labels do not end where the next node's begin. */
+int64_t bvo_decode_labels(int kind, int width, const uint8_t *labels, uint64_t labels_bytes, const uint64_t *label_offsets,
+                          int64_t lo, int64_t hi, const int64_t *degrees, int64_t *out) {
+	int64_t w = 0;
+	for (int64_t x = lo; x < hi; x++) {
+		ibs_t s; ibs_init(&s, labels, labels_bytes, label_offsets[x]);
+		for (int64_t j = 0; j < degrees[x - lo]; j++) {
+			const uint64_t v = kind == 0 ? (width ? ibs_bits(&s, width) : 0) : ibs_gamma(&s);
+			out[w++] = (int64_t)(int32_t)(uint32_t)v;  /* the Java field is an int */
+		}
+		if (s.pos != label_offsets[x + 1]) return -1;
+	}
+	return w;
+}
+
 uint64_t bvo_read_code(const uint8_t *p, uint64_t nbytes, uint64_t *bitpos, int coding, int k) {
 	ibs_t s; ibs_init(&s, p, nbytes, *bitpos);
 	uint64_t v;

@@ -532,3 +532,32 @@ def test_randomized_parity_sweep():
                 trp, tcol = _transpose_on_gpu(g, n, orp, ocol)
                 brp, bcol = _transpose_on_gpu(g, n, trp, tcol)
                 assert np.array_equal(brp, orp) and np.array_equal(bcol, ocol), tag
+
+
+def test_arc_labels_equal_oracle(cnr, cnr_golden):
+    """.labels / .labeloffsets of a BitStreamArcLabelledImmutableGraph decoded on the device, against the
+    CPU restatement: fixed-width labels of several widths (0, 1, 10, 31, 32 bits: the last one exercises the int sign),
+    gamma-coded labels, ranges that start in the middle, and a label stream that does not match the graph."""
+    deg, rowptr, col = cnr_golden
+    n = deg.size
+    rng = np.random.default_rng(11)
+    for kind, width, hi in ((wg.LABEL_FIXED_INT, 10, 1 << 10), (wg.LABEL_FIXED_INT, 1, 2), (wg.LABEL_FIXED_INT, 0, 1),
+                            (wg.LABEL_FIXED_INT, 31, 1 << 31), (wg.LABEL_FIXED_INT, 32, 1 << 32), (wg.LABEL_GAMMA_INT, 0, 1 << 18)):
+        values = rng.integers(0, hi, col.size).astype(np.int64)
+        lab, off = bg.write_labels(kind, width, rowptr, values)
+        expect = bo.decode_labels(kind, width, lab, off, deg)
+        assert np.array_equal(expect.astype(np.uint32), values.astype(np.uint32))
+        with wg.GpuArcLabels(kind, width, lab, off, n) as L:
+            got = L.decode(cnr, rowptr)
+            assert np.array_equal(got, expect), (kind, width)
+            a, b = 123456, 200001
+            rp, _ = cnr.decodeToCSR(a, b)
+            assert np.array_equal(L.decode(cnr, rp, a, b), expect[rowptr[a]:rowptr[b]])
+            assert L.decode(cnr, np.zeros(1, dtype=np.int64), 5, 5).size == 0
+            wrong = rowptr.copy()
+            wrong[1:] += 1  # node 0 claims one more arc than its labels hold
+            if not (kind == wg.LABEL_FIXED_INT and width == 0):  # (labels of no bits end where they should, whatever their number)
+                with pytest.raises(wg.IllegalStateException):
+                    L.decode(cnr, wrong[:1001], 0, 1000)
+            with pytest.raises(wg.IllegalArgumentException):
+                L.decode(cnr, rowptr[:3], n - 1, n + 1)

@@ -375,6 +375,57 @@ class GpuBVGraph:
         return True
 
 
+LABEL_FIXED_INT, LABEL_GAMMA_INT = 0, 1
+
+
+class GpuArcLabels:
+    """The `.labels` / `.labeloffsets` pair of a BitStreamArcLabelledImmutableGraph on the device
+    (labelling/BitStreamArcLabelledImmutableGraph.java:65-100): labels come back as an int64 array parallel to the
+    successors of the underlying graph.  kind: LABEL_FIXED_INT (FixedWidthIntLabel, `width` bits) or LABEL_GAMMA_INT."""
+
+    def __init__(self, kind, width, labels_bytes, labeloffsets_bytes, nodes, device=0):
+        lab = np.ascontiguousarray(np.frombuffer(labels_bytes, dtype=np.uint8)) if not isinstance(labels_bytes, np.ndarray) else np.ascontiguousarray(labels_bytes)
+        off = np.ascontiguousarray(np.frombuffer(labeloffsets_bytes, dtype=np.uint8)) if not isinstance(labeloffsets_bytes, np.ndarray) else np.ascontiguousarray(labeloffsets_bytes)
+        h = C.c_void_p()
+        _lib.check(_lib.lib().wgbv_labels_open_mem(device, nodes, kind, width, lab.ctypes.data if lab.size else None, lab.size,
+                                                   off.ctypes.data, off.size, C.byref(h)))
+        self.h = h
+        self.nodes = nodes
+
+    def close(self):
+        if self.h is not None:
+            _lib.lib().wgbv_labels_close(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def decode(self, graph, rowptr, from_=0, to=None):
+        """Labels of the arcs of nodes [from, to) (host arrays): rowptr[0 .. to-from] are the row pointers of that range,
+        e.g. from graph.decodeToCSR(from, to); `graph` lends its stream."""
+        to = self.nodes if to is None else to
+        rowptr = np.ascontiguousarray(rowptr, dtype=np.int64)
+        if rowptr.size != to - from_ + 1:
+            raise IllegalArgumentException("rowptr must have to - from + 1 entries")
+        arcs = int(rowptr[-1] - rowptr[0])
+        out = np.empty(arcs, dtype=np.int64)
+        _lib.check(_lib.lib().wgbv_labels_decode_host(graph._st.h, self.h, from_, to, rowptr.ctypes.data, out.ctypes.data if arcs else None, arcs))
+        return out
+
+    def decodeDevice(self, graph, from_, to, d_rowptr, d_labels, capacity):
+        """Device buffers (int pointers), asynchronous on the graph copy's stream."""
+        _lib.check(_lib.lib().wgbv_labels_decode(graph._st.h, self.h, from_, to, C.c_void_p(d_rowptr), C.c_void_p(d_labels), capacity))
+
+
 class NodeIterator:
     """BVGraphNodeIterator (BVG:1100-1245) over chunked GPU decodes; arrays returned are valid until the next
     nextLong() (the reference's window-slot rule, BVG:1171-1172)."""

@@ -74,6 +74,10 @@ SYMBOLS = [
     ("wgbv_scan_end", None, [_P]),
     ("wgbv_scan_set_narrow", C.c_int, [_P, C.c_int]),
     ("wgbv_transpose_csr", C.c_int, [_P, C.c_int64, _P, _P, _P, _P]),
+    ("wgbv_labels_open_mem", C.c_int, [C.c_int, C.c_int64, C.c_int, C.c_int, _P, C.c_uint64, _P, C.c_uint64, C.POINTER(_P)]),
+    ("wgbv_labels_close", None, [_P]),
+    ("wgbv_labels_decode", C.c_int, [_P, _P, C.c_int64, C.c_int64, _P, _P, C.c_uint64]),
+    ("wgbv_labels_decode_host", C.c_int, [_P, _P, C.c_int64, C.c_int64, _P, _P, C.c_uint64]),
     ("wgbv_outdegrees", C.c_int, [_P, _P, C.c_uint64, _P]),
     ("wgbv_successors_batch_degrees", C.c_int, [_P, _P, C.c_uint64, _P, C.POINTER(C.c_int64)]),
     ("wgbv_successors_batch", C.c_int, [_P, _P, C.c_uint64, _P, _P, C.c_uint64]),

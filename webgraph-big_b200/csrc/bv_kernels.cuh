@@ -147,6 +147,10 @@ struct EliasFano;
 int device_decode_offsets(const uint8_t *h_stream, uint64_t nbytes, int64_t count, uint64_t **d_off_out);
 int device_ef_build(const uint64_t *d_off, uint64_t n, uint64_t base, uint64_t last_value, EliasFano &ef, uint64_t **d_lower,
                     uint64_t **d_upper, uint64_t **d_hints, uint64_t **d_sparse, uint64_t *device_bytes);
+// arc labels (bv_labels.cu): `lab` holds the label stream and its offsets the way a graph handle holds the graph's;
+// rowptr[0 .. count] are the row pointers of nodes [from, from + count); out is parallel to their successors
+void launch_labels(const Launch &L, const GraphDev &lab, int kind, int width, int64_t from, int64_t count, const int64_t *rowptr,
+                   int64_t *out, uint64_t capacity);
 // byte-swap the uploaded stream into big-endian 64-bit words, in place
 void launch_bswap(const Launch &L, uint64_t *words, uint64_t nwords);
 // A handful of device scalars for the host, written by a kernel straight into mapped pinned host memory: unlike a small

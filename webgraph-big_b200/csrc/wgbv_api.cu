@@ -1066,6 +1066,80 @@ extern "C" int wgbv_transpose_csr(wgbv_stream *s, int64_t n, const int64_t *d_ro
 	return collect_errors(s);
 }
 
+// ------------------------------------------------------------------------------------------------ arc labels
+// A label stream with its offsets is held exactly like a graph's bit stream with its offsets: the handle wraps a
+// wgbv_graph opened over (.labels, .labeloffsets) with neutral format parameters.
+struct wgbv_labels {
+	wgbv_graph *g = nullptr;
+	int kind = 0, width = 0;
+};
+
+extern "C" int wgbv_labels_open_mem(int device, int64_t nodes, int kind, int width, const uint8_t *labels, uint64_t labels_bytes,
+                                    const uint8_t *labeloffsets, uint64_t labeloffsets_bytes, wgbv_labels **out) {
+	clear_error();
+	if (!out || (!labels && labels_bytes) || !labeloffsets || nodes < 0) return fail(WGBV_EARG, "null argument or negative node count");
+	*out = nullptr;
+	if (kind != WGBV_LABEL_FIXED_INT && kind != WGBV_LABEL_GAMMA_INT) return fail(WGBV_EUNSUPPORTED, "unknown label kind %d", kind);
+	if (kind == WGBV_LABEL_FIXED_INT && (width < 0 || width > 32)) return fail(WGBV_EARG, "a fixed-width int label has 0 to 32 bits, not %d", width);
+	wgbv_props p{};
+	p.nodes = nodes;
+	p.window_size = 0;
+	p.max_ref_count = 0;
+	p.zeta_k = 3;
+	p.outdegree_coding = p.block_coding = p.block_count_coding = p.offset_coding = WGBV_GAMMA;
+	p.residual_coding = WGBV_ZETA;
+	p.reference_coding = WGBV_UNARY;
+	wgbv_graph *g = nullptr;
+	const int rc = wgbv_open_mem(&p, labels, labels_bytes, labeloffsets, labeloffsets_bytes, device, 0, 1, &g);
+	if (rc) return rc;
+	wgbv_labels *l = new (std::nothrow) wgbv_labels();
+	if (!l) { wgbv_close(g); return fail(WGBV_EARG, "out of host memory"); }
+	l->g = g;
+	l->kind = kind;
+	l->width = width;
+	*out = l;
+	return WGBV_OK;
+}
+
+extern "C" void wgbv_labels_close(wgbv_labels *l) {
+	if (!l) return;
+	wgbv_close(l->g);
+	delete l;
+}
+
+extern "C" int wgbv_labels_decode(wgbv_stream *s, const wgbv_labels *l, int64_t from, int64_t to, const int64_t *d_rowptr,
+                                  int64_t *d_labels, uint64_t capacity) {
+	clear_error();
+	if (!s || !l || !d_rowptr || (!d_labels && capacity)) return fail(WGBV_EARG, "null argument");
+	if (from < 0 || to < from || to > l->g->props.nodes) return fail(WGBV_EINDEX, "Node index out of range: [%lld, %lld)", (long long)from, (long long)to);
+	if (l->g->device != s->g->device) return fail(WGBV_EARG, "the labels and the stream live on different devices");
+	CU(cudaSetDevice(s->g->device));
+	GraphDev lab = l->g->dev;
+	lab.err = s->d_err;
+	launch_labels(s->launch(), lab, l->kind, l->width, from, to - from, d_rowptr, d_labels, capacity);
+	const cudaError_t e = cudaGetLastError();
+	if (e != cudaSuccess) return fail(WGBV_ECUDA, "kernel launch failed: %s", cudaGetErrorString(e));
+	return WGBV_OK;
+}
+
+extern "C" int wgbv_labels_decode_host(wgbv_stream *s, const wgbv_labels *l, int64_t from, int64_t to, const int64_t *h_rowptr,
+                                       int64_t *h_labels, uint64_t capacity) {
+	clear_error();
+	if (!s || !l || !h_rowptr) return fail(WGBV_EARG, "null argument");
+	if (from < 0 || to < from || to > l->g->props.nodes) return fail(WGBV_EINDEX, "Node index out of range: [%lld, %lld)", (long long)from, (long long)to);
+	const int64_t cnt = to - from, arcs = h_rowptr[cnt] - h_rowptr[0];
+	if (arcs < 0) return fail(WGBV_EARG, "row pointers are not increasing");
+	if ((uint64_t)arcs > capacity) return fail(WGBV_EARG, "capacity (%llu) is smaller than the %lld arcs of the range", (unsigned long long)capacity, (long long)arcs);
+	if (arcs && !h_labels) return fail(WGBV_EARG, "null argument");
+	CU(cudaSetDevice(s->g->device));
+	int rc;
+	if ((rc = s->rowptr.ensure((size_t)(cnt + 1) * 8)) || (rc = s->col.ensure((size_t)std::max<int64_t>(arcs, 1) * 8))) return rc;
+	CU(cudaMemcpyAsync(s->rowptr.as<int64_t>(), h_rowptr, (size_t)(cnt + 1) * 8, cudaMemcpyHostToDevice, s->stream));
+	if ((rc = wgbv_labels_decode(s, l, from, to, s->rowptr.as<int64_t>(), s->col.as<int64_t>(), (uint64_t)arcs))) return rc;
+	if (arcs) CU(cudaMemcpyAsync(h_labels, s->col.as<int64_t>(), (size_t)arcs * 8, cudaMemcpyDeviceToHost, s->stream));
+	return collect_errors(s);
+}
+
 // ------------------------------------------------------------------------------------------------ random access
 static int batch_degrees(wgbv_stream *s, const int64_t *d_ids, uint64_t k, int64_t *d_rowptr, int64_t *arcs_out) {
 	wgbv_graph *g = s->g;
