@@ -46,6 +46,7 @@ def parse_args():
     ap.add_argument("--cpu-sample-nodes", type=int, default=0, help="0: sized from the core count")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-labels", action="store_true", help="skip the arc-label decode (SURVEY 8f-3, N=1 only)")
     ap.add_argument("--no-transpose", action="store_true", help="skip the transpose of the decoded CSR (SURVEY 8f-1, N=1 only)")
     ap.add_argument("--e2e-trace", action="store_true", help="print the arrival time of every chunk of the last e2e step to stderr")
     ap.add_argument("--seed", type=int, default=2)
@@ -207,7 +208,10 @@ def main():
 
     props_text = e.properties_text().replace(f"nodes={n}", f"nodes={world * n}")
     t0 = time.time()
-    stream = torch.cuda.current_stream()
+    # one explicit stream for everything: the library launches on it and torch's events are recorded on it (the default
+    # stream has handle 0, which the library takes as "create your own")
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(stream)
     # pinned copy of the compressed stream: the source of the per-step upload of the end-to-end measurement
     h_graph = torch.empty(e.graph.size + 16, dtype=torch.uint8, pin_memory=True)
     h_graph[: e.graph.size] = torch.from_numpy(e.graph)
@@ -296,6 +300,44 @@ def main():
         if not t_ok:
             raise SystemExit("transpose(transpose(CSR)) does not hash to the generator's checksum")
 
+    # 10-bit labels on every arc of the graph just decoded (synthetic: arc j carries a hash of j), stored as a
+    # BitStreamArcLabelledImmutableGraph stores them and decoded into an array parallel to the successors.
+    labels = None
+    if world == 1 and not args.no_labels:
+        import bvgen
+        width = 10
+        t0 = time.time()
+        h_rp = d_rowptr.cpu().numpy()
+        lab, off = bvgen.write_labels_synthetic(width, h_rp)
+        lab_gen_s = time.time() - t0
+        L = wg.GpuArcLabels(wg.LABEL_FIXED_INT, width, lab, off, n, device=local_rank)
+        d_lab = torch.empty(max(arcs, 1), dtype=torch.int64, device=dev)
+        L.decodeDevice(g, first, first + n, d_rowptr.data_ptr(), d_lab.data_ptr(), arcs)
+        g.sync()
+        reps = 3
+        lv0, lv1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        lv0.record()
+        for _ in range(reps):
+            L.decodeDevice(g, first, first + n, d_rowptr.data_ptr(), d_lab.data_ptr(), arcs)
+        lv1.record()
+        g.sync()
+        l_ms = lv0.elapsed_time(lv1) / reps
+        mult = bvgen.LABEL_HASH_MULTIPLIER - (1 << 64)  # the same multiplier as a signed 64-bit number
+        l_ok = True
+        for a in range(0, arcs, 1 << 27):
+            j = torch.arange(a, min(arcs, a + (1 << 27)), dtype=torch.int64, device=dev)
+            l_ok = l_ok and bool(torch.equal(((j * mult) >> 20) & ((1 << width) - 1), d_lab[a:a + j.numel()]))
+            del j
+        l_bytes = int(lab.size) + int(off.size) + 8 * arcs + 8 * (n + 1)
+        labels = {"metric": "decoded arc labels/s (.labels -> int64 array parallel to the CSR)", "value": arcs / (l_ms * 1e-3), "unit": "labels/s",
+                  "ms": l_ms, "label": f"FixedWidthIntLabel, {width} bits", "verified": bool(l_ok), "generation_s": lab_gen_s,
+                  "roofline": {"bound": "hbm", "achieved": l_bytes / (l_ms * 1e-3) / 1e9, "unit": "GB/s",
+                               "frac": l_bytes / (l_ms * 1e-3) / 1e9 / peaks()[0], "algorithmic_bytes": l_bytes}}
+        L.close()
+        del d_lab, lab, off, h_rp
+        if not l_ok:
+            raise SystemExit("decoded labels differ from the generator's")
+
     total_arcs = torch.tensor([arcs], dtype=torch.int64, device=dev)
     if world > 1:
         dist.all_reduce(total_arcs)
@@ -383,7 +425,7 @@ def main():
                        "compressed_bytes_rank0": int(e.graph.size), "bits_per_arc": e.graph_bits / max(arcs, 1),
                        "l2": "inputs and outputs exceed L2 (compressed stream and 8 B/arc output are GBs per step)",
                        "parallelism": f"{world} contiguous shard(s), no data-path collective; all-gather of arc counts"},
-            "roofline": roofline, "e2e": e2e, "e2e_narrow": e2e_narrow, "transpose": transpose, "cpu_baseline": cpu, "gpu_launches": int(launches), "clocks": clocks,
+            "roofline": roofline, "e2e": e2e, "e2e_narrow": e2e_narrow, "transpose": transpose, "labels": labels, "cpu_baseline": cpu, "gpu_launches": int(launches), "clocks": clocks,
             "verified": bool(verified), "global_row_base_rank0": global_base, "generation_s": gen_s, "load_s": load_s,
         }
         print(json.dumps(line))

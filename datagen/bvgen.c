@@ -644,6 +644,29 @@ uint64_t bvg_write_labels(int kind, int width, int64_t n, const int64_t *rowptr,
 	return bits;
 }
 
+/* The same for synthetic labels that need no value array (benchmark scale): arc number j (in CSR order) carries
+ * label_of_arc(j, width) = the low `width` bits of j * 0x9E3779B97F4A7C15 >> 20.  Fixed-width labels only. */
+static inline uint64_t label_of_arc(uint64_t j, int width) {
+	const uint64_t h = (j * 0x9E3779B97F4A7C15ull) >> 20;
+	return width >= 64 ? h : h & ((1ull << width) - 1);
+}
+uint64_t bvg_write_labels_synthetic(int width, int64_t n, const int64_t *rowptr, uint8_t *out, uint64_t out_cap, uint64_t *node_bits) {
+	const uint64_t arcs = (uint64_t)(rowptr[n] - rowptr[0]);
+	const uint64_t bytes = (arcs * (uint64_t)width + 7) >> 3;
+	if (bytes + 16 > out_cap) return arcs * (uint64_t)width;
+	obs_t o; memset(&o, 0, sizeof o);
+	o.buf = out;             /* written in place: the caller's buffer is large enough, obs_reserve never grows it */
+	o.cap = out_cap;
+	uint64_t j = 0;
+	for (int64_t x = 0; x < n; x++) {
+		const int64_t d = rowptr[x + 1] - rowptr[x];
+		for (int64_t k = 0; k < d; k++, j++) obs_put_long(&o, label_of_arc(j, width), width);
+		node_bits[x] = (uint64_t)d * (uint64_t)width;
+	}
+	if (o.nacc) o.buf[(o.bits - o.nacc) >> 3] = (uint8_t)(o.acc << (8 - o.nacc));
+	return o.bits;
+}
+
 /* Single-code writer exposed so that tests can round-trip every code through the oracle's readers. */
 uint64_t bvg_write_codes(int coding, int k, const uint64_t *vals, int64_t n, uint8_t *out, uint64_t out_cap) {
 	obs_t o; memset(&o, 0, sizeof o);

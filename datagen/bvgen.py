@@ -67,6 +67,8 @@ def lib():
         L.bvg_csr_checksum.restype = C.c_uint64
         L.bvg_write_labels.argtypes = [C.c_int, C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
         L.bvg_write_labels.restype = C.c_uint64
+        L.bvg_write_labels_synthetic.argtypes = [C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
+        L.bvg_write_labels_synthetic.restype = C.c_uint64
         L.bvg_write_codes.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_uint64]
         L.bvg_write_codes.restype = C.c_uint64
         _LIB = L
@@ -208,3 +210,20 @@ def write_labels(kind, width, rowptr, values):
     assert (bits + 7) // 8 <= out.size
     offs, _ = write_codes(GAMMA, np.concatenate([np.zeros(1, dtype=np.uint64), node_bits[:n]]))
     return out[: (bits + 7) // 8].copy(), offs
+
+
+LABEL_HASH_MULTIPLIER = 0x9E3779B97F4A7C15
+
+
+def write_labels_synthetic(width, rowptr):
+    """Fixed-width labels for a benchmark-size graph without a value array: arc j (CSR order) carries the low `width`
+    bits of (j * LABEL_HASH_MULTIPLIER mod 2^64) >> 20.  Returns (labels bytes, labeloffsets bytes)."""
+    rowptr = np.ascontiguousarray(rowptr, dtype=np.int64)
+    n = rowptr.size - 1
+    arcs = int(rowptr[-1] - rowptr[0])
+    out = np.zeros((arcs * width + 7) // 8 + 64, dtype=np.uint8)
+    node_bits = np.zeros(max(n, 1), dtype=np.uint64)
+    bits = lib().bvg_write_labels_synthetic(width, n, rowptr.ctypes.data, out.ctypes.data, out.size, node_bits.ctypes.data)
+    assert bits == arcs * width
+    offs, _ = write_codes(GAMMA, np.concatenate([np.zeros(1, dtype=np.uint64), node_bits[:n]]))
+    return out[: (bits + 7) // 8], offs

@@ -25,7 +25,7 @@ for spec in args:
         env["WGBV_LIBRARY"] = os.path.join(ROOT, path) if not os.path.isabs(path) else path
     else:
         env.pop("WGBV_LIBRARY", None)
-    cmd = [sys.executable, os.path.join(ROOT, "bench.py"), "--warmup", "3", "--no-e2e", "--no-cpu-baseline"] + extra
+    cmd = [sys.executable, os.path.join(ROOT, "bench.py"), "--warmup", "3", "--no-e2e", "--no-cpu-baseline", "--no-labels", "--no-transpose"] + extra
     res = subprocess.run(cmd, env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=600)
     try:
         j = json.loads(res.stdout.strip().splitlines()[-1])

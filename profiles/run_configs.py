@@ -27,6 +27,7 @@ def main():
 
     import webgraph_big_b200 as wg
     threads = len(os.sched_getaffinity(0))
+    torch.cuda.set_stream(torch.cuda.Stream())  # an explicit stream: the library launches on it, the events below are recorded on it
 
     if "c1" not in args.skip:
         e = bvgen.erdos_renyi(1_000_000, 1.6e-5, seed=1, params=bvgen.make_params(7, 3, 4, 3))
