@@ -149,8 +149,10 @@ int device_ef_build(const uint64_t *d_off, uint64_t n, uint64_t base, uint64_t l
                     uint64_t **d_upper, uint64_t **d_hints, uint64_t **d_sparse, uint64_t *device_bytes);
 // arc labels (bv_labels.cu): `lab` holds the label stream and its offsets the way a graph handle holds the graph's;
 // rowptr[0 .. count] are the row pointers of nodes [from, from + count); out is parallel to their successors
+// arcs_bound: an upper bound on the labels of the range (sizes the grid of the fixed-width kernel; the kernel reads the
+// exact number from rowptr)
 void launch_labels(const Launch &L, const GraphDev &lab, int kind, int width, int64_t from, int64_t count, const int64_t *rowptr,
-                   int64_t *out, uint64_t capacity);
+                   int64_t *out, uint64_t capacity, uint64_t arcs_bound);
 // byte-swap the uploaded stream into big-endian 64-bit words, in place
 void launch_bswap(const Launch &L, uint64_t *words, uint64_t nwords);
 // A handful of device scalars for the host, written by a kernel straight into mapped pinned host memory: unlike a small

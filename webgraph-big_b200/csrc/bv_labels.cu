@@ -5,7 +5,8 @@
 // `.labeloffsets`, gamma-coded differences exactly like `.offsets` (labelling/BitStreamArcLabelledImmutableGraph.java:
 // 65-100, 339-363, 654-681).  Its node iterator positions the stream at the node's offset and calls
 // label.fromBitStream() once per successor (:487-560).  Here the stream is held like the graph's (32-bit MSB-first
-// words + Elias-Fano offsets, both built by the loader the graph uses) and one lane reads one node's labels:
+// words + Elias-Fano offsets, both built by the loader the graph uses); gamma-coded labels are read one node per lane,
+// fixed-width ones one label per thread (see k_labels_fixed):
 //   kind WGBV_LABEL_FIXED_INT  FixedWidthIntLabel: readInt(width)   (FixedWidthIntLabel.java:70-73)
 //   kind WGBV_LABEL_GAMMA_INT  GammaCodedIntLabel: readGamma()      (GammaCodedIntLabel.java:60-64)
 // A node whose labels do not end where the next node's begin raises ERR_DEGREE (the stream, the offsets and the
@@ -32,12 +33,56 @@ __global__ void __launch_bounds__(TPB) k_labels(GraphDev lab, int64_t from, int6
 	if (r.tell() != end) raise(lab, ERR_DEGREE);
 }
 
+// Fixed-width labels need no per-node work: the labels of consecutive nodes are consecutive in the stream, so label j of
+// the range sits at (offset of node `from`) + j * width.  One thread per label, coalesced 8-byte stores; the offsets are
+// only used to check, one thread per node, that they say the same (k_labels_check).
+__device__ __forceinline__ int64_t fixed_label(const uint32_t *__restrict__ words, uint64_t nw, uint64_t bit, int width) {
+	const uint64_t w = bit >> 5;
+	const uint32_t a = w < nw ? __ldg(words + w) : 0u, b = w + 1 < nw ? __ldg(words + w + 1) : 0u;
+	const uint64_t two = (uint64_t)a << 32 | b;  // bits [32w, 32w + 64) of the stream, first bit on top
+	const uint32_t v = width ? (uint32_t)((two << (bit & 31u)) >> (64 - width)) : 0u;
+	return (int64_t)(int32_t)v;  // the Java field is an int
+}
+
+__global__ void __launch_bounds__(TPB) k_labels_fixed(GraphDev lab, int64_t from, int64_t count, const int64_t *__restrict__ rp, int width,
+                                                      int64_t *__restrict__ out, uint64_t capacity) {
+	__shared__ uint64_t s_base;
+	if (threadIdx.x == 0) s_base = ef_get(lab, from);
+	__syncthreads();
+	const uint64_t arcs = (uint64_t)(rp[count] - rp[0]);
+	const uint64_t j = ((uint64_t)blockIdx.x * TPB + threadIdx.x) * 2;  // two labels per thread, one 16-byte store
+	if (j >= arcs) return;
+	if (arcs > capacity) { if (j == 0) raise(lab, ERR_CAPACITY); return; }
+	const uint32_t *words = (const uint32_t *)lab.words;
+	const uint64_t nw = lab.nwords * 2, bit = s_base + j * (uint64_t)width;
+	const int64_t v0 = fixed_label(words, nw, bit, width);
+	if (j + 1 < arcs) {
+		const int64_t v1 = fixed_label(words, nw, bit + (uint64_t)width, width);
+		if ((reinterpret_cast<uintptr_t>(out) & 15u) == 0) *reinterpret_cast<longlong2 *>(out + j) = make_longlong2(v0, v1);
+		else { out[j] = v0; out[j + 1] = v1; }
+	} else out[j] = v0;
+}
+
+__global__ void __launch_bounds__(TPB) k_labels_check(GraphDev lab, int64_t from, int64_t count, const int64_t *__restrict__ rp, int width) {
+	const int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
+	if (i >= count) return;
+	if (ef_get(lab, from + i + 1) - ef_get(lab, from + i) != (uint64_t)(rp[i + 1] - rp[i]) * (uint64_t)width) raise(lab, ERR_DEGREE);
+}
+
 void launch_labels(const Launch &L, const GraphDev &lab, int kind, int width, int64_t from, int64_t count, const int64_t *rowptr,
-                   int64_t *out, uint64_t capacity) {
+                   int64_t *out, uint64_t capacity, uint64_t arcs_bound) {
 	if (count <= 0) return;
-	if (kind == 0) k_labels<0><<<grid_for(count, TPB), TPB, 0, L.stream>>>(lab, from, count, rowptr, width, out, capacity);
-	else k_labels<1><<<grid_for(count, TPB), TPB, 0, L.stream>>>(lab, from, count, rowptr, width, out, capacity);
-	WGBV_LAUNCHED(L);
+	if (kind == 0) {
+		k_labels_check<<<grid_for(count, TPB), TPB, 0, L.stream>>>(lab, from, count, rowptr, width);
+		WGBV_LAUNCHED(L);
+		if (arcs_bound) {
+			k_labels_fixed<<<grid_for((int64_t)((arcs_bound + 1) / 2), TPB), TPB, 0, L.stream>>>(lab, from, count, rowptr, width, out, capacity);
+			WGBV_LAUNCHED(L);
+		}
+	} else {
+		k_labels<1><<<grid_for(count, TPB), TPB, 0, L.stream>>>(lab, from, count, rowptr, width, out, capacity);
+		WGBV_LAUNCHED(L);
+	}
 }
 
 }  // namespace wgbv

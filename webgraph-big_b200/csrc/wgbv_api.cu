@@ -1116,7 +1116,10 @@ extern "C" int wgbv_labels_decode(wgbv_stream *s, const wgbv_labels *l, int64_t 
 	CU(cudaSetDevice(s->g->device));
 	GraphDev lab = l->g->dev;
 	lab.err = s->d_err;
-	launch_labels(s->launch(), lab, l->kind, l->width, from, to - from, d_rowptr, d_labels, capacity);
+	// (the device knows the exact number of labels; `capacity` bounds it, and so does the length of the stream)
+	const uint64_t stream_bits = l->g->dev.bit_end;
+	const uint64_t bound = l->kind == WGBV_LABEL_FIXED_INT && l->width > 0 ? std::min<uint64_t>(capacity, stream_bits / (uint64_t)l->width) : capacity;
+	launch_labels(s->launch(), lab, l->kind, l->width, from, to - from, d_rowptr, d_labels, capacity, bound);
 	const cudaError_t e = cudaGetLastError();
 	if (e != cudaSuccess) return fail(WGBV_ECUDA, "kernel launch failed: %s", cudaGetErrorString(e));
 	return WGBV_OK;
