@@ -168,6 +168,26 @@ public:
 	wgbv_stream *stream() const { return st_; }
 };
 
+// The labels of a BitStreamArcLabelledImmutableGraph (labelling/BitStreamArcLabelledImmutableGraph.java:65-100) on the
+// device: decode() returns them parallel to the successors that Graph::decodeToCSR returns for the same range.
+class ArcLabels {
+	wgbv_labels *h_ = nullptr;
+
+public:
+	ArcLabels(int device, int64_t nodes, int kind, int width, const std::vector<uint8_t> &labels, const std::vector<uint8_t> &labeloffsets) {
+		check(wgbv_labels_open_mem(device, nodes, kind, width, labels.data(), labels.size(), labeloffsets.data(), labeloffsets.size(), &h_));
+	}
+	ArcLabels(const ArcLabels &) = delete;
+	ArcLabels &operator=(const ArcLabels &) = delete;
+	~ArcLabels() { wgbv_labels_close(h_); }
+	std::vector<int64_t> decode(Graph &g, int64_t from, int64_t to, const std::vector<int64_t> &rowptr) {
+		if ((int64_t)rowptr.size() != to - from + 1) throw IllegalArgumentException("rowptr must have to - from + 1 entries");
+		std::vector<int64_t> out((size_t)(rowptr.back() - rowptr.front()));
+		check(wgbv_labels_decode_host(g.stream(), h_, from, to, rowptr.data(), out.data(), out.size()));
+		return out;
+	}
+};
+
 inline NodeIterator::NodeIterator(std::shared_ptr<Graph> g, int64_t from, int64_t upper)
     : g_(std::move(g)), from_(from), curr_(from - 1), limit_((upper < g_->numNodes() ? upper : g_->numNodes()) - 1), c0_(from), c1_(from) {}
 
