@@ -6,7 +6,8 @@
 // y in successors(x) -- is a stable sort of the arcs by target: the arcs of a CSR come in increasing source order, so
 // a STABLE sort by target alone leaves every target's sources increasing.
 //
-//   k_t_pack      arc j -> one 64-bit word  target << 32 | source   (node ids below 2^32), counts in-degrees
+//   k_t_pack      arc j -> one 64-bit word  target << 32 | source   (node ids below 2^32), counts in-degrees and the
+//                 digits of the first pass (its blocks cover the same tiles as the radix kernels)
 //   k_rs_hist     per pass: digit histogram of every tile of RS_TILE words
 //   (k_scan)      digit-major scan of the tile histograms = first output position of every (digit, tile)
 //   k_rs_scatter  per pass: stable scatter of the tile's words; the last pass writes the sources straight to t_col
@@ -38,8 +39,8 @@ int transpose_passes(uint64_t nodes) {
 
 // One block per PACK_TILE consecutive arcs; the rows that hold them are found by binary search in the row pointers
 // (first the block's range of rows, then every arc inside that range: a handful of steps that hit L1).
-static constexpr int PACK_ITEMS = 8;
-static constexpr int PACK_TILE = TPB * PACK_ITEMS;
+static constexpr int PACK_ITEMS = RS_ITEMS;
+static constexpr int PACK_TILE = TPB * PACK_ITEMS;  // = RS_TILE: the block also counts the digits of the first pass for its tile
 
 __device__ __forceinline__ int64_t row_of(const int64_t *__restrict__ rp, int64_t lo, int64_t hi, int64_t a) {
 	// the last row r in [lo, hi] with rp[r] <= a
@@ -52,8 +53,11 @@ __device__ __forceinline__ int64_t row_of(const int64_t *__restrict__ rp, int64_
 }
 
 __global__ void __launch_bounds__(TPB) k_t_pack(GraphDev g, int64_t n, const int64_t *__restrict__ rp, const int64_t *__restrict__ col,
-                                                uint64_t arcs, uint64_t *__restrict__ pairs, uint32_t *indeg) {
+                                                uint64_t arcs, uint64_t *__restrict__ pairs, uint32_t *indeg, uint32_t nblocks,
+                                                uint32_t *__restrict__ counts) {
 	__shared__ int64_t s_row[2];
+	__shared__ uint32_t hist[RS_DIGITS];  // digits of radix pass 0 (bits 32 .. 32 + RS_BITS of the packed word)
+	for (int d = threadIdx.x; d < RS_DIGITS; d += TPB) hist[d] = 0;
 	const uint64_t j0 = (uint64_t)blockIdx.x * PACK_TILE;
 	const uint64_t j1 = j0 + PACK_TILE < arcs ? j0 + PACK_TILE : arcs;
 	const int64_t base = rp[0];
@@ -70,12 +74,16 @@ __global__ void __launch_bounds__(TPB) k_t_pack(GraphDev g, int64_t n, const int
 			if (y < 0 || y >= n) {
 				raise(g, ERR_INDEX);
 				pairs[j] = (uint64_t)x;  // keeps the sort well defined; the call fails anyway
+				atomicAdd(&hist[0], 1u);
 			} else {
 				pairs[j] = (uint64_t)y << 32 | (uint64_t)x;
 				atomicAdd(&indeg[y], 1u);
+				atomicAdd(&hist[(uint32_t)y & (RS_DIGITS - 1)], 1u);
 			}
 		}
 	}
+	__syncthreads();
+	for (int d = threadIdx.x; d < RS_DIGITS; d += TPB) counts[(size_t)d * nblocks + blockIdx.x] = hist[d];
 }
 
 __global__ void __launch_bounds__(TPB) k_rs_hist(const uint64_t *__restrict__ in, uint64_t count, int shift, uint32_t nblocks,
@@ -184,9 +192,10 @@ __global__ void __launch_bounds__(TPB, 4) k_rs_scatter(const uint64_t *__restric
 }
 
 void launch_transpose_pack(const Launch &L, const GraphDev &g, int64_t n, const int64_t *rowptr, const int64_t *col, uint64_t arcs,
-                           uint64_t *pairs, uint32_t *indeg) {
+                           uint64_t *pairs, uint32_t *indeg, uint32_t *counts) {
 	if (!arcs) return;
-	k_t_pack<<<grid_for((int64_t)arcs, PACK_TILE), TPB, 0, L.stream>>>(g, n, rowptr, col, arcs, pairs, indeg);
+	const uint32_t nblocks = (uint32_t)transpose_tiles(arcs);
+	k_t_pack<<<nblocks, TPB, 0, L.stream>>>(g, n, rowptr, col, arcs, pairs, indeg, nblocks, counts);
 	WGBV_LAUNCHED(L);
 }
 

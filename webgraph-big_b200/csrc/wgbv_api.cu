@@ -1049,13 +1049,13 @@ extern "C" int wgbv_transpose_csr(wgbv_stream *s, int64_t n, const int64_t *d_ro
 	const int passes = arcs ? transpose_passes((uint64_t)n) : 0;
 	if (passes > 1 && (rc = s->t_pairs[1].ensure(na * 8))) return rc;
 	CU(cudaMemsetAsync(s->t_indeg.as<uint32_t>(), 0, nn * 4, s->stream));
-	launch_transpose_pack(L, s->dev, n, d_rowptr, d_col, (uint64_t)arcs, s->t_pairs[0].as<uint64_t>(), s->t_indeg.as<uint32_t>());
+	launch_transpose_pack(L, s->dev, n, d_rowptr, d_col, (uint64_t)arcs, s->t_pairs[0].as<uint64_t>(), s->t_indeg.as<uint32_t>(), s->t_counts.as<uint32_t>());
 	// in-degrees -> row pointers of the transpose
 	launch_scan(L, s->t_indeg.as<uint32_t>(), d_t_rowptr, n, s->scan_state.as<uint64_t>(), s->ticket.as<uint32_t>());
 	int cur = 0;
 	for (int p = 0; p < passes; p++) {
 		const uint64_t *in = s->t_pairs[cur].as<uint64_t>();
-		launch_radix_hist(L, in, (uint64_t)arcs, p, s->t_counts.as<uint32_t>());
+		if (p > 0) launch_radix_hist(L, in, (uint64_t)arcs, p, s->t_counts.as<uint32_t>());  // (pass 0: counted by the pack kernel)
 		launch_scan(L, s->t_counts.as<uint32_t>(), s->t_pos.as<int64_t>(), (int64_t)ncounts, s->scan_state.as<uint64_t>(), s->ticket.as<uint32_t>());
 		const bool last = p == passes - 1;
 		launch_radix_scatter(L, in, (uint64_t)arcs, p, s->t_pos.as<int64_t>(), last ? nullptr : s->t_pairs[cur ^ 1].as<uint64_t>(), last ? d_t_col : nullptr);
