@@ -113,3 +113,8 @@ def test_label_streams_round_trip():
         got = bo.decode_labels(kind, width, lab, off, deg)
         assert np.array_equal(got.astype(np.uint32), vals.astype(np.uint32))
         assert np.array_equal(bo.decode_labels(kind, width, lab, off, deg, 500, 1500), got[rp[500]:rp[1500]])
+    # the benchmark's labels: arc j carries the low `width` bits of (j * multiplier mod 2^64) >> 20
+    lab, off = bg.write_labels_synthetic(10, rp)
+    j = np.arange(rp[-1], dtype=np.uint64)
+    expect = ((j * np.uint64(bg.LABEL_HASH_MULTIPLIER)) >> np.uint64(20)) & np.uint64(1023)
+    assert np.array_equal(bo.decode_labels(0, 10, lab, off, deg).astype(np.uint64), expect)
