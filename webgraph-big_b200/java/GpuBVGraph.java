@@ -51,6 +51,12 @@ public class GpuBVGraph extends ImmutableGraph {
 		static final MethodHandle SUCCESSORS_BATCH_HOST = h("wgbv_successors_batch_host",
 				FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_LONG, ADDRESS, ADDRESS, JAVA_LONG, ADDRESS));
 		static final MethodHandle LAST_ERROR = h("wgbv_last_error", FunctionDescriptor.of(ADDRESS));
+		// arc labels (labelling/BitStreamArcLabelledImmutableGraph.java:65-100): an array parallel to the successors
+		static final MethodHandle LABELS_OPEN_MEM = h("wgbv_labels_open_mem",
+				FunctionDescriptor.of(JAVA_INT, JAVA_INT, JAVA_LONG, JAVA_INT, JAVA_INT, ADDRESS, JAVA_LONG, ADDRESS, JAVA_LONG, ADDRESS));
+		static final MethodHandle LABELS_DECODE_HOST = h("wgbv_labels_decode_host",
+				FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_LONG, JAVA_LONG, ADDRESS, ADDRESS, JAVA_LONG));
+		static final MethodHandle LABELS_CLOSE = h("wgbv_labels_close", FunctionDescriptor.ofVoid(ADDRESS));
 
 		/** Status code to the exception the reference throws at the same place (include/wgbv.h). */
 		static void check(final int rc) {
@@ -191,6 +197,22 @@ public class GpuBVGraph extends ImmutableGraph {
 	}
 
 	@Override
+	/** Labels of the arcs of [from, to), parallel to the successors that {@link #decodeToCSR} returns for the same range:
+	 *  labels = handle from wgbv_labels_open_mem over the .labels / .labeloffsets of a BitStreamArcLabelledImmutableGraph
+	 *  whose underlying graph is this one; rowptr = first segment returned by decodeToCSR(from, to, a). */
+	public MemorySegment decodeLabels(final MemorySegment labels, final long from, final long to, final MemorySegment rowptr, final Arena a) {
+		final long arcs = rowptr.getAtIndex(JAVA_LONG, to - from) - rowptr.getAtIndex(JAVA_LONG, 0);
+		final MemorySegment out = a.allocate(Math.max(arcs, 1) * 8, 8);
+		try {
+			Wgbv.check((int)Wgbv.LABELS_DECODE_HOST.invokeExact(stream, labels, from, to, rowptr, out, arcs));
+		} catch (final RuntimeException e) {
+			throw e;
+		} catch (final Throwable t) {
+			throw new RuntimeException(t);
+		}
+		return out;
+	}
+
 	public NodeIterator nodeIterator(final long from) {
 		if (from < 0 || from > shared.n) throw new IllegalArgumentException("Node index out of range: " + from);
 		return new GpuNodeIterator(this, from, Long.MAX_VALUE);
