@@ -254,6 +254,7 @@ def main():
     clocks = sampler.stop()
     g.sync()
     launches = g.kernelLaunches() - launches0
+    fused_stats = g.fusedStats()
     ms = ev0.elapsed_time(ev1)
     t = torch.tensor([ms], dtype=torch.float64, device=dev)
     if world > 1:
@@ -426,7 +427,7 @@ def main():
                        "l2": "inputs and outputs exceed L2 (compressed stream and 8 B/arc output are GBs per step)",
                        "parallelism": f"{world} contiguous shard(s), no data-path collective; all-gather of arc counts"},
             "roofline": roofline, "e2e": e2e, "e2e_narrow": e2e_narrow, "transpose": transpose, "labels": labels, "cpu_baseline": cpu, "gpu_launches": int(launches), "clocks": clocks,
-            "verified": bool(verified), "global_row_base_rank0": global_base, "generation_s": gen_s, "load_s": load_s,
+            "verified": bool(verified), "fused": fused_stats, "global_row_base_rank0": global_base, "generation_s": gen_s, "load_s": load_s,
         }
         print(json.dumps(line))
     g.close()

@@ -30,6 +30,11 @@ typedef struct {
 } bvg_params;
 
 enum { BVG_MODEL_CSR = 0, BVG_MODEL_ER = 1, BVG_MODEL_COPY = 2, BVG_MODEL_BIG = 3 };
+/* encoder statistics: copied / intervalised / residual arcs, rows with a reference, blocks, intervals, and the bits
+ * spent on outdegrees, references, blocks (counts included), intervals (count included) and residuals; rows whose
+ * reference row has more than 128 successors; sum of reference-chain lengths; rows with a chain of length 1, 2, 3, >3 */
+enum { ST_COPIED = 0, ST_INTERVAL, ST_RESIDUAL, ST_REFROWS, ST_BLOCKS, ST_INTERVALS, ST_BITS_OUTDEG, ST_BITS_REF, ST_BITS_BLOCKS,
+       ST_BITS_INTERVALS, ST_BITS_RESIDUALS, ST_BIGREF, ST_CHAIN_SUM, ST_CHAIN1, ST_CHAIN2, ST_CHAIN3, ST_CHAIN4, BVG_NSTATS = 20 };
 
 typedef struct {
 	int32_t model;
@@ -189,6 +194,8 @@ static inline void lv_need(lvec *v, int64_t n) {
 typedef struct {
 	const bvg_params *g;
 	lvec blocks, extras, left, len, residuals;
+	/* what the reference's compressor reports in .properties (BVG:2490-2567), accumulated while emitting */
+	int64_t stats[BVG_NSTATS];
 } enc_t;
 
 /* The reference's differential compressor: emits (or, with o == NULL, only prices) everything after
@@ -217,16 +224,24 @@ static uint64_t diff_comp(enc_t *e, obs_t *o, int64_t x, int ref, const int64_t 
 
 	if (g->window > 0) {
 		bits += len_code(g->reference_coding, (uint64_t)ref, 0);
-		if (o) put_code(o, g->reference_coding, (uint64_t)ref, 0);
+		if (o) { put_code(o, g->reference_coding, (uint64_t)ref, 0); e->stats[ST_BITS_REF] += (int64_t)bits; }
 	}
 	if (ref != 0) {
 		const int64_t bc = e->blocks.n;
+		const uint64_t before = bits;
 		bits += len_code(g->blockcount_coding, (uint64_t)bc, 0);
 		if (o) put_code(o, g->blockcount_coding, (uint64_t)bc, 0);
 		for (int64_t i = 0; i < bc; i++) {
 			const uint64_t v = (uint64_t)(e->blocks.a[i] - (i ? 1 : 0));
 			bits += len_code(g->block_coding, v, 0);
 			if (o) put_code(o, g->block_coding, v, 0);
+		}
+		if (o) {
+			e->stats[ST_REFROWS]++;
+			e->stats[ST_BLOCKS] += bc;
+			e->stats[ST_BITS_BLOCKS] += (int64_t)(bits - before);
+			e->stats[ST_COPIED] += curlen - e->extras.n;
+			if (reflen > 128) e->stats[ST_BIGREF]++;
 		}
 	}
 	if (e->extras.n > 0) {
@@ -246,6 +261,7 @@ static uint64_t diff_comp(enc_t *e, obs_t *o, int64_t x, int ref, const int64_t 
 				if (r < g->minint) lv_push(&e->residuals, v[i]);
 			}
 			const int64_t ic = e->left.n;
+			const uint64_t before = bits;
 			bits += len_gamma((uint64_t)ic);
 			if (o) put_gamma(o, (uint64_t)ic);
 			int64_t prev = 0;
@@ -254,10 +270,13 @@ static uint64_t diff_comp(enc_t *e, obs_t *o, int64_t x, int ref, const int64_t 
 				const uint64_t b = (uint64_t)(e->len.a[i] - g->minint);
 				prev = e->left.a[i] + e->len.a[i];
 				bits += len_gamma(a) + len_gamma(b);
-				if (o) { put_gamma(o, a); put_gamma(o, b); }
+				if (o) { put_gamma(o, a); put_gamma(o, b); e->stats[ST_INTERVAL] += e->len.a[i]; }
 			}
+			if (o) { e->stats[ST_INTERVALS] += ic; e->stats[ST_BITS_INTERVALS] += (int64_t)(bits - before); }
 			res = e->residuals.a; nres = e->residuals.n;
 		}
+		if (o) e->stats[ST_RESIDUAL] += nres;
+		const uint64_t before_res = bits;
 		if (nres != 0) {
 			int64_t prev = res[0];
 			uint64_t a = int2nat(prev - x);
@@ -270,6 +289,7 @@ static uint64_t diff_comp(enc_t *e, obs_t *o, int64_t x, int ref, const int64_t 
 				prev = res[i];
 			}
 		}
+		if (o) e->stats[ST_BITS_RESIDUALS] += (int64_t)(bits - before_res);
 	}
 	return bits;
 }
@@ -403,6 +423,7 @@ typedef struct {
 	int error;          /* a record longer than 2^32-1 bits */
 	int64_t arcs;
 	uint64_t checksum;
+	int64_t stats[BVG_NSTATS];
 } split_t;
 
 typedef struct {
@@ -419,6 +440,7 @@ typedef struct {
 	uint64_t checksum;
 	uint64_t *seg_checksum; int64_t seg_nodes, nseg;
 	int error;
+	int64_t stats[BVG_NSTATS];
 } bvg_job;
 
 /* Order-sensitive hash of one successor list and its mix into a commutative graph checksum.  The CUDA side
@@ -457,6 +479,7 @@ static void encode_split(bvg_job *J, split_t *sp) {
 		const uint64_t start = o->bits;
 		const int64_t d = cur->n;
 		put_code(o, g->outdegree_coding, (uint64_t)d, 0);
+		e.stats[ST_BITS_OUTDEG] += (int64_t)(o->bits - start);
 		if (d > 0) {
 			uint64_t best = ~0ull; int bestref = -1, bestcand = -1;
 			refcount[ci] = -1;
@@ -470,6 +493,11 @@ static void encode_split(bvg_job *J, split_t *sp) {
 			}
 			refcount[ci] = refcount[bestcand] + 1;
 			diff_comp(&e, o, x, bestref, lists[bestcand].a, lists[bestcand].n, cur->a, d);
+			if (bestref) {
+				const int c = refcount[ci];
+				e.stats[ST_CHAIN_SUM] += c;
+				e.stats[c >= 4 ? ST_CHAIN4 : ST_CHAIN1 + c - 1]++;
+			}
 		}
 		if (o->bits - start > 0xffffffffull) sp->error = 1;
 		sp->bitlen[x - sp->from] = (uint32_t)(o->bits - start);
@@ -481,6 +509,7 @@ static void encode_split(bvg_job *J, split_t *sp) {
 		}
 	}
 	obs_finish(o);
+	memcpy(sp->stats, e.stats, sizeof sp->stats);
 	for (int i = 0; i < cyc; i++) free(lists[i].a);
 	free(lists); free(ring); free(refcount);
 	free(e.blocks.a); free(e.extras.a); free(e.left.a); free(e.len.a); free(e.residuals.a);
@@ -571,6 +600,7 @@ bvg_job *bvg_run(const bvg_params *g, const bvg_model *m, int nsplits, int threa
 	for (int k = 0; k < nsplits; k++) {
 		dst[k + 1] = dst[k] + J->splits[k].obs.bits;
 		J->arcs += J->splits[k].arcs;
+		for (int q = 0; q < BVG_NSTATS; q++) J->stats[q] += J->splits[k].stats[q];
 		J->checksum += J->splits[k].checksum;
 		J->error |= J->splits[k].error;
 	}
@@ -603,6 +633,8 @@ const uint8_t *bvg_graph(bvg_job *J, uint64_t *bytes, uint64_t *bits) { *bytes =
 const uint64_t *bvg_offsets(bvg_job *J) { return J->offsets; }
 const uint8_t *bvg_offsets_stream(bvg_job *J, uint64_t *bytes) { build_offstream(J); *bytes = J->offstream_bytes; return J->offstream; }
 int64_t bvg_arcs(bvg_job *J) { return J->arcs; }
+/* out[BVG_NSTATS]: the encoder statistics (see the ST_ enumeration) */
+void bvg_stats(bvg_job *J, int64_t *out) { memcpy(out, J->stats, sizeof J->stats); }
 int bvg_error(bvg_job *J) { return J->error; }
 uint64_t bvg_checksum(bvg_job *J) { return J->checksum; }
 const uint64_t *bvg_seg_checksums(bvg_job *J, int64_t *nseg) { *nseg = J->nseg; return J->seg_checksum; }

@@ -55,6 +55,8 @@ def lib():
         L.bvg_offsets_stream.restype = C.c_void_p
         L.bvg_arcs.argtypes = [C.c_void_p]
         L.bvg_arcs.restype = C.c_int64
+        L.bvg_stats.argtypes = [C.c_void_p, C.c_void_p]
+        L.bvg_stats.restype = None
         L.bvg_error.argtypes = [C.c_void_p]
         L.bvg_error.restype = C.c_int
         L.bvg_checksum.argtypes = [C.c_void_p]
@@ -92,11 +94,18 @@ def flags_string(p):
     return " | ".join(out)
 
 
+# what the reference's compressor writes to .properties (BVGraph.java:2490-2567), plus a few shape figures of our own
+STAT_NAMES = ("copiedarcs", "intervalisedarcs", "residualarcs", "rows_with_reference", "blocks", "intervals", "bitsforoutdegrees",
+              "bitsforreferences", "bitsforblocks", "bitsforintervals", "bitsforresiduals", "rows_with_reference_row_over_128",
+              "refchain_length_sum", "rows_chain1", "rows_chain2", "rows_chain3", "rows_chain4plus")
+
+
 class Encoded:
     """An encoded graph held in host memory (numpy arrays own the bytes)."""
 
-    def __init__(self, params, n, arcs, graph, graph_bits, offsets, offsets_stream, checksum, seg_checksums, seg_nodes):
+    def __init__(self, params, n, arcs, graph, graph_bits, offsets, offsets_stream, checksum, seg_checksums, seg_nodes, stats=None):
         self.params, self.n, self.arcs = params, n, arcs
+        self.stats = stats or {}
         self.graph, self.graph_bits = graph, graph_bits
         self.offsets, self.offsets_stream = offsets, offsets_stream
         self.checksum, self.seg_checksums, self.seg_nodes = checksum, seg_checksums, seg_nodes
@@ -139,7 +148,10 @@ def _collect(job, params, n, seg_nodes, want_offsets_stream=True):
             ns = C.c_int64()
             sp = L.bvg_seg_checksums(job, C.byref(ns))
             segs = np.ctypeslib.as_array(C.cast(sp, C.POINTER(C.c_uint64)), shape=(max(ns.value, 1),))[:ns.value].copy()
-        return Encoded(params, n, L.bvg_arcs(job), graph, nbits.value, offsets, ostream, L.bvg_checksum(job), segs, seg_nodes)
+        st = np.zeros(20, dtype=np.int64)
+        L.bvg_stats(job, st.ctypes.data)
+        stats = {k: int(v) for k, v in zip(STAT_NAMES, st)}
+        return Encoded(params, n, L.bvg_arcs(job), graph, nbits.value, offsets, ostream, L.bvg_checksum(job), segs, seg_nodes, stats)
     finally:
         L.bvg_free(job)
 

@@ -236,6 +236,10 @@ static void scratch_free(scratch_t *t) {
 
 /* Header part shared by sequential and random access: everything after the outdegree.
  * `dref` is the outdegree of x-ref, consulted only when the block count is even (BVG:1030). */
+/* Optional per-row shape figures for analysis (bvo_row_shapes): ncopied, block count, interval count, interval
+ * elements, residual count.  Not part of the decode. */
+static __thread int64_t *tl_shape = NULL;
+
 static int decode_tail(const bvo_params *g, ibs_t *s, int64_t x, int64_t d, int ref,
                        const int64_t *ref_list, int64_t dref, scratch_t *t, int64_t *out, int64_t *len_out) {
 	int err = 0;
@@ -288,6 +292,11 @@ static int decode_tail(const bvo_params *g, ibs_t *s, int64_t x, int64_t d, int 
 	}
 	const int64_t residual_count = extra_count;
 	if (residual_count < 0) return BVO_ESTATE; /* malformed: the reference would misbehave here */
+	if (tl_shape) {
+		int64_t ti = 0;
+		for (int64_t i = 0; i < interval_count; i++) ti += t->len.a[i];
+		tl_shape[0] = ncopied; tl_shape[1] = block_count; tl_shape[2] = interval_count; tl_shape[3] = ti; tl_shape[4] = residual_count;
+	}
 
 	/* extras = Merged(IntervalSequence, Residuals), BVG:1067-1073: a plain merge with duplicates dropped. */
 	{
@@ -419,10 +428,12 @@ int64_t bvo_decode_range(const bvo_params *g, const uint8_t *graph, uint64_t gra
 		if (s.overrun) { rc = BVO_EIO; goto done; }
 		outd[cur] = d;
 		if (deg_out) deg_out[x - from] = d;
+		if (tl_shape) { tl_shape += 6; tl_shape[0] = tl_shape[1] = tl_shape[2] = tl_shape[3] = tl_shape[4] = 0; tl_shape[5] = 0; }
 		if (vec_need(&win[cur], d)) { rc = BVO_ECAPACITY; goto done; }
 		int64_t len = 0;
 		if (d != 0) {
 			const int ref = g->window > 0 ? (int)rd_reference(&s, g, &err) : -1; /* BVG:1015 */
+			if (tl_shape) tl_shape[5] = ref > 0 ? ref : 0;
 			if (err) { rc = err; goto done; }
 			if (ref > 0 && x - ref < 0) { rc = BVO_ESTATE; goto done; }
 			const int ri = (int)((x - ref + cyc) % cyc); /* BVG:1018 */
@@ -441,6 +452,16 @@ done:
 	for (int i = 0; i < cyc; i++) free(win[i].a);
 	free(win); free(outd);
 	scratch_free(&t);
+	return rc;
+}
+
+/* Analysis helper: shape[6 * (x - from) ..] = ncopied, blocks, intervals, interval elements, residuals, reference of
+ * every node of [from, to) (sequential scan).  shape must hold 6 * (to - from + 1) entries. */
+int64_t bvo_row_shapes(const bvo_params *g, const uint8_t *graph, uint64_t graph_bytes, const uint64_t *offsets,
+                       int64_t from, int64_t to, int64_t *deg_out, int64_t *shape) {
+	tl_shape = shape - 6;
+	const int64_t rc = bvo_decode_range(g, graph, graph_bytes, offsets, from, to, deg_out, NULL, 0);
+	tl_shape = NULL;
 	return rc;
 }
 

@@ -266,10 +266,9 @@ def _similar_rows_graph(n, centers, width, size, seed):
     return rowptr, np.concatenate(rows)
 
 
-def test_tiles_that_do_not_fit_shared_memory(monkeypatch):
-    """The fused tile kernel's slower modes: rows in global scratch (tile larger than shared memory, halo rows a few
-    thousand successors long) and the hand-over to the level-synchronous kernels (halo larger than the scratch)."""
-    monkeypatch.setenv("WGBV_TILE", "1")
+def test_tiles_that_do_not_fit_shared_memory():
+    """The one-pass tile kernel's slow tiles: rows a few thousand (or tens of thousands of) successors long that reference
+    each other across tile boundaries are decoded by k_slow in global memory; ranges that start next to them."""
     for size, centers in ((4000, (256, 1000, 1536)), (40000, (512, 2048 + 256))):
         n = 3000
         rowptr, col = _similar_rows_graph(n, centers, 12, size, size)
@@ -279,24 +278,48 @@ def test_tiles_that_do_not_fit_shared_memory(monkeypatch):
         with gpu_of(e) as g:
             rp, c = g.decodeToCSR()
             assert np.array_equal(rp, rowptr) and np.array_equal(c, col)
-            rp2, c2 = g.decodeToCSR(centers[0] + 3, n)
-            assert np.array_equal(c2, col[rowptr[centers[0] + 3]:])
+            st = g.fusedStats()
+            assert st["enabled"] and st["slow_tiles"] > 0 and st["reruns"] == 0
+            # ranges that start inside the run of long rows (the first tile is slow and its rows reference rows before the range)
+            for lo in (centers[0] + 3, centers[0] - 5, centers[1] + 1):
+                rp2, c2 = g.decodeToCSR(lo, n)
+                assert np.array_equal(rp2, rowptr[lo:] - rowptr[lo]) and np.array_equal(c2, col[rowptr[lo]:])
 
 
-def test_fused_tile_kernel_equals_oracle(monkeypatch, cnr_basename, cnr_golden):
-    """The opt-in fused tile kernel (WGBV_TILE=1) on the golden fixture and on a synthetic graph."""
-    monkeypatch.setenv("WGBV_TILE", "1")
+def test_fused_and_general_paths_agree(monkeypatch, cnr_basename, cnr_golden):
+    """The one-pass tile kernel (default) and the level-synchronous kernels (WGBV_FUSED=0) on the golden fixture, on
+    ranges that start inside a tile, and on synthetic graphs with 1..8 levels and rows on both merge paths."""
     deg, rowptr, col = cnr_golden
-    with wg.GpuBVGraph.load(cnr_basename) as g:
-        rp, c = g.decodeToCSR()
-        assert np.array_equal(rp, rowptr) and np.array_equal(c, col)
-        rp, c = g.decodeToCSR(100000, 200000)
-        assert np.array_equal(c, col[rowptr[100000]:rowptr[200000]])
-    e = bg.copy_model(30000, seed=123, mean_degree=25, params=bg.make_params(window=7, maxref=3, minint=4), nsplits=2)
+    graphs = [bg.copy_model(60000, seed=7 + maxref, mean_degree=md, params=bg.make_params(window=window, maxref=maxref, minint=4), nsplits=2)
+              for maxref, window, md in ((1, 1, 12), (3, 7, 25), (4, 7, 60), (8, 8, 25))]
+    oracles = [oracle_of(e).decode_range() for e in graphs]
+    for fused in ("1", "0"):
+        monkeypatch.setenv("WGBV_FUSED", fused)
+        with wg.GpuBVGraph.load(cnr_basename) as g:
+            assert g.fusedStats()["enabled"] == (fused == "1")
+            rp, c = g.decodeToCSR()
+            assert np.array_equal(rp, rowptr) and np.array_equal(c, col)
+            for lo, hi in ((100001, 200003), (1, 2), (325000, 325557), (0, 0), (5, 5)):
+                rp, c = g.decodeToCSR(lo, hi)
+                assert np.array_equal(rp, rowptr[lo:hi + 1] - rowptr[lo]) and np.array_equal(c, col[rowptr[lo]:rowptr[hi]])
+        for e, (odeg, ocol) in zip(graphs, oracles):
+            with gpu_of(e) as g:
+                rp, c = g.decodeToCSR()
+                assert np.array_equal(rp, rowptr_of(odeg)) and np.array_equal(c, ocol)
+                assert g.fusedStats()["reruns"] == 0
+
+
+def test_chains_longer_than_the_properties_promise():
+    """A file whose maxrefcount understates its chains (the reference's decoder never looks at maxrefcount): the tile
+    kernel notices, and the decode is rerun on the general path without trusting the property."""
+    e = bg.copy_model(20000, seed=99, mean_degree=20, params=bg.make_params(window=7, maxref=6, minint=4), nsplits=1)
     odeg, ocol = oracle_of(e).decode_range()
-    with gpu_of(e) as g:
-        rp, c = g.decodeToCSR()
-        assert np.array_equal(rp, rowptr_of(odeg)) and np.array_equal(c, ocol)
+    for lie in (1, 0):
+        text = e.properties_text().replace("maxrefcount=6", f"maxrefcount={lie}")
+        with wg.GpuBVGraph.load_mem(text, e.graph, e.offsets_stream) as g:
+            rp, c = g.decodeToCSR()
+            assert np.array_equal(rp, rowptr_of(odeg)) and np.array_equal(c, ocol)
+            assert g.fusedStats()["reruns"] >= 1
 
 
 def test_narrow_scan_delivers_the_same_successors(cnr, cnr_golden):
@@ -312,29 +335,6 @@ def test_narrow_scan_delivers_the_same_successors(cnr, cnr_golden):
         assert np.array_equal(np.concatenate(got) if got else np.zeros(0, np.int64), col[rowptr[lo]:rowptr[hi]])
     for a, b, rp, c in cnr.scan(0, 1000, 1000):
         assert c.dtype == np.int64 and np.array_equal(c, col[:rowptr[1000]])
-
-
-def test_fused_levels_kernel_equals_oracle(monkeypatch, cnr_basename, cnr_golden):
-    """The opt-in single-launch copy stage (WGBV_FUSED_LEVELS=1: task queue + per-row dependency flags) on the golden
-    fixture, on ranges that start inside a tile, and on synthetic graphs with 1..8 levels and rows on both merge paths."""
-    monkeypatch.setenv("WGBV_FUSED_LEVELS", "1")
-    deg, rowptr, col = cnr_golden
-    with wg.GpuBVGraph.load(cnr_basename) as g:
-        rp, c = g.decodeToCSR()
-        assert np.array_equal(rp, rowptr) and np.array_equal(c, col)
-        rp, c = g.decodeToCSR(100001, 200003)
-        assert np.array_equal(c, col[rowptr[100001]:rowptr[200003]])
-    for maxref, window, md in ((1, 1, 12), (3, 7, 25), (4, 7, 60), (8, 16, 25)):
-        e = bg.copy_model(60000, seed=7 + maxref, mean_degree=md, params=bg.make_params(window=window, maxref=maxref, minint=4), nsplits=2)
-        odeg, ocol = oracle_of(e).decode_range()
-        with gpu_of(e) as g:
-            rp, c = g.decodeToCSR()
-            assert np.array_equal(rp, rowptr_of(odeg)) and np.array_equal(c, ocol)
-    rowptr2, col2 = _similar_rows_graph(3000, (256, 1000, 1536), 12, 4000, 4000)
-    e = bg.encode_csr(rowptr2, col2, bg.make_params(window=7, maxref=3, minint=4))
-    with gpu_of(e) as g:
-        rp, c = g.decodeToCSR()
-        assert np.array_equal(rp, rowptr2) and np.array_equal(c, col2)
 
 
 def test_streaming_scan_equals_golden(cnr, cnr_golden):

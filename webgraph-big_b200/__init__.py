@@ -353,6 +353,13 @@ class GpuBVGraph:
     def kernelLaunches(self):
         return _lib.lib().wgbv_kernel_launches(self._st.h)
 
+    def fusedStats(self):
+        """(tiles of the last bulk decode, tiles among them left to the slow-tile kernel, decodes rerun on the general
+        path, whether this handle's decodes take the one-pass tile kernel); call after sync()."""
+        out = (C.c_uint64 * 4)()
+        _lib.check(_lib.lib().wgbv_fused_stats(self._st.h, C.byref(out)))
+        return {"tiles": int(out[0]), "slow_tiles": int(out[1]), "reruns": int(out[2]), "enabled": bool(out[3])}
+
     def algorithmicBytes(self, from_, to, arcs):
         return _lib.lib().wgbv_algorithmic_bytes(self._sh.handle, from_, to, arcs)
 

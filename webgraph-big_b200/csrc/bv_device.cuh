@@ -22,6 +22,8 @@ enum : uint32_t {
 	ERR_NOT_SORTED = 16u,     // duplicate between copied successors and extras (malformed file)
 	ERR_CAPACITY = 32u,       // output capacity exceeded
 	ERR_INDEX = 64u,          // a queried node id is outside the range the handle can decode (BVG:863)
+	ERR_FUSED_FALLBACK = 128u,  // not an error: the fused tile kernel met something only the general path handles (the host reruns the decode)
+	ERR_FUSED_DEEP = 256u,      // same, for a reference chain longer than the properties promise: the rerun must not trust them either
 };
 
 // Everything a kernel needs to know about an opened graph; passed by value.
@@ -60,8 +62,9 @@ __device__ __forceinline__ void raise(const GraphDev &g, uint32_t bit) { atomicO
 // LDG = true: the words are in global memory and read through the read-only path; false: plain (generic) loads, so
 // that the same decoder runs on a tile of the stream staged in shared memory.
 template <bool LDG>
-struct BitReaderT {
+struct WordCore {
 	static constexpr bool IS_GLOBAL = LDG;
+	using pos_t = uint64_t;
 	const uint32_t *base;  // address of the word the last seek() started from
 	uint64_t j0;    // stream index of that word
 	uint32_t lim;   // words that may be loaded from base (saturated)
@@ -132,7 +135,7 @@ struct BitReaderT {
 		} else {
 			// words in shared memory: load the candidate unconditionally (cheap, uniform) and select, so that the lanes
 			// of a warp -- which cross word boundaries at different times -- do not split into two instruction streams
-			const uint32_t cand = base[idx + 1 < lim ? idx + 1 : lim - 1];
+			const uint32_t cand = lim ? base[idx + 1 < lim ? idx + 1 : lim - 1] : 0u;  // (lim == 0: a position at the very end)
 			const bool adv = sh >= 32;
 			sh = adv ? sh - 32 : sh;
 			hi = adv ? lo : hi;
@@ -141,80 +144,110 @@ struct BitReaderT {
 			idx += adv ? 1u : 0u;
 		}
 	}
+};
 
+// A reader that keeps nothing but its bit position: every peek loads the two words under the position again.  Meant for
+// streams staged in shared memory, where a load costs about as much as the register shuffling it replaces: fewer
+// instructions per code and one live register instead of six.  `words` must be followed by at least one loadable
+// word past the last one holding data (the staging code pads); positions beyond the staged span read the last pair.
+struct PosCore {
+	static constexpr bool IS_GLOBAL = false;
+	using pos_t = uint32_t;
+	const uint32_t *base;
+	uint32_t last;  // index of the last word that may be the first of a loaded pair
+	uint32_t p;     // bit position relative to base[0]
+	__device__ __forceinline__ void init_words(const uint32_t *words, uint32_t nwords, uint32_t rel_pos) {
+		base = words;
+		last = nwords >= 2 ? nwords - 2 : 0;
+		p = rel_pos;
+	}
+	__device__ __forceinline__ void seek(uint64_t pos) { p = (uint32_t)pos; }
+	__device__ __forceinline__ uint64_t tell() const { return p; }
+	__device__ __forceinline__ bool past_end() const { return (p >> 5) > last + 1; }
+	__device__ __forceinline__ uint32_t peek() const {
+		uint32_t w = p >> 5;
+		w = w < last ? w : last;
+		return __funnelshift_l(base[w + 1], base[w], p);
+	}
+	__device__ __forceinline__ void consume(uint32_t n) { p += n; }
+};
+
+// The instantaneous codes on top of a core that provides peek() / consume() / past_end().
+template <class Core>
+struct CodesT : Core {
 	__device__ __forceinline__ uint64_t bits(unsigned n) {  // n in [0, 64]
 		uint64_t v = 0;
 		if (n > 32) {
-			v = peek();
-			consume(32);
+			v = this->peek();
+			this->consume(32);
 			n -= 32;
 		}
 		if (n) {
-			v = (v << n) | (peek() >> (32u - n));
-			consume(n);
+			v = (v << n) | (this->peek() >> (32u - n));
+			this->consume(n);
 		}
 		return v;
 	}
 
 	__device__ __forceinline__ uint64_t unary() {
-		uint32_t t = peek();
+		uint32_t t = this->peek();
 		uint64_t total = 0;
 		while (t == 0) {
 			total += 32;
-			consume(32);
-			if (past_end()) return total;  // the kernels raise ERR_OVERRUN on their own checks
-			t = peek();
+			this->consume(32);
+			if (this->past_end()) return total;  // the kernels raise ERR_OVERRUN on their own checks
+			t = this->peek();
 		}
 		const unsigned z = (unsigned)__clz((int)t);
-		consume(z + 1);
+		this->consume(z + 1);
 		return total + z;
 	}
 
 	__device__ __forceinline__ uint64_t gamma() {
-		const uint32_t t = peek();
+		const uint32_t t = this->peek();
 		if (t >> 16) {  // at most 15 leading zeros: the whole code (<= 31 bits) is in the window
 			const unsigned z = (unsigned)__clz((int)t);
 			const uint32_t v = (t << z) >> (31u - z);
-			consume(2 * z + 1);
+			this->consume(2 * z + 1);
 			return (uint64_t)v - 1;
 		}
-		const uint64_t m = unary();
+		const uint64_t m = this->unary();
 		if (m > 63) return 0;
-		return ((1ull << m) | bits((unsigned)m)) - 1;
+		return ((1ull << m) | this->bits((unsigned)m)) - 1;
 	}
 
 	__device__ __forceinline__ uint64_t delta() {
-		const uint64_t m = gamma();
+		const uint64_t m = this->gamma();
 		if (m > 63) return 0;
-		return ((1ull << m) | bits((unsigned)m)) - 1;
+		return ((1ull << m) | this->bits((unsigned)m)) - 1;
 	}
 
 	__device__ __forceinline__ uint64_t zeta(int k) {
-		const uint32_t t = peek();
-		const int h = t ? __clz((int)t) : 32;
-		const int pb = h * k + k - 1;  // payload bits before the optional extra one
-		if (h + 2 + pb <= 32) {
+		const uint32_t t = this->peek();
+		const int h = __clz((int)t);  // (32 for t == 0)
+		const int hk = h * k;
+		if (hk + h + k + 1 <= 32) {
+			// unary part (h + 1 bits), then hk + k - 1 payload bits m and possibly one more bit b: m2 = m:b
 			const uint32_t x = t << (h + 1);
-			const uint32_t left = 1u << (h * k);
-			const uint32_t m = pb ? x >> (32 - pb) : 0u;
-			const bool shorter = m < left;
-			const uint32_t b = (x >> (31 - pb)) & 1u;
-			consume((uint32_t)(h + 1 + pb) + (shorter ? 0u : 1u));
-			return (uint64_t)(shorter ? m + left - 1 : ((m << 1) | b) - 1);
+			const uint32_t m2 = x >> (32 - (hk + k));
+			const uint32_t two_left = 2u << hk;
+			const bool shorter = m2 < two_left;  // m < left = 2^hk
+			this->consume((uint32_t)(hk + h + k) + (shorter ? 0u : 1u));
+			return (uint64_t)(shorter ? (m2 >> 1) + (two_left >> 1) - 1u : m2 - 1u);
 		}
-		const uint64_t hh = unary();
+		const uint64_t hh = this->unary();
 		if (hh * (uint64_t)k + (uint64_t)k > 64) return 0;
 		const uint64_t left = 1ull << (hh * k);
-		const uint64_t m = bits((unsigned)(hh * k + k - 1));
+		const uint64_t m = this->bits((unsigned)(hh * k + k - 1));
 		if (m < left) return m + left - 1;
-		return ((m << 1) | bits(1)) - 1;
+		return ((m << 1) | this->bits(1)) - 1;
 	}
 
 	__device__ __forceinline__ uint64_t nibble() {
 		uint64_t x = 0, stop;
 		int guard = 0;
 		do {
-			const uint64_t q = bits(4);
+			const uint64_t q = this->bits(4);
 			stop = q >> 3;
 			x = (x << 3) | (q & 7);
 		} while (!stop && ++guard < 22);
@@ -223,34 +256,36 @@ struct BitReaderT {
 
 	__device__ __forceinline__ uint64_t golomb(int b) {
 		if (b == 0) return 0;
-		const uint64_t q = unary();
+		const uint64_t q = this->unary();
 		const int s = 31 - __clz(b);
 		const uint64_t M = (1ull << (s + 1)) - (uint64_t)b;
-		uint64_t x = bits((unsigned)s);
-		if (x >= M) x = ((x << 1) | bits(1)) - M;
+		uint64_t x = this->bits((unsigned)s);
+		if (x >= M) x = ((x << 1) | this->bits(1)) - M;
 		return q * (uint64_t)b + x;
 	}
 
 	// gamma | delta | unary switchboard used by outdegrees, references, block counts and blocks
 	__device__ __forceinline__ uint64_t code(int coding) {
 		switch (coding) {
-		case C_GAMMA: return gamma();
-		case C_DELTA: return delta();
-		default: return unary();
+		case C_GAMMA: return this->gamma();
+		case C_DELTA: return this->delta();
+		default: return this->unary();
 		}
 	}
 	__device__ __forceinline__ uint64_t residual(int coding, int k) {
 		switch (coding) {
-		case C_ZETA: return zeta(k);
-		case C_GAMMA: return gamma();
-		case C_DELTA: return delta();
-		case C_NIBBLE: return nibble();
-		default: return golomb(k);
+		case C_ZETA: return this->zeta(k);
+		case C_GAMMA: return this->gamma();
+		case C_DELTA: return this->delta();
+		case C_NIBBLE: return this->nibble();
+		default: return this->golomb(k);
 		}
 	}
 };
+template <bool LDG> using BitReaderT = CodesT<WordCore<LDG>>;
 using BitReader = BitReaderT<true>;
 using TileReader = BitReaderT<false>;
+using PosReader = CodesT<PosCore>;
 
 // Fast.nat2int
 __device__ __forceinline__ int64_t nat2int(uint64_t x) { return (x & 1) ? -(int64_t)((x + 1) >> 1) : (int64_t)(x >> 1); }

@@ -528,20 +528,6 @@ __device__ __forceinline__ void extras_tile(const GraphDev &g, const RangeDev &R
 		const int id = q * TPB + threadIdx.x;
 		const int64_t i = base + id;
 		bucket[q] = -1;
-		if (R.depth_out && i < count) {
-			// depth of the row's reference chain: a bounded walk over the reference array stage 1 left in memory
-			uint32_t dp = 0;
-			for (int64_t y = i;;) {
-				const uint32_t rf = R.ref[y];
-				if (rf == 0) break;
-				if (y < (int64_t)rf) { dp = DEPTH_INVALID; break; }
-				if (dp == R.walk_levels) { dp = DEPTH_UNRESOLVED; atomicExch(R.deep, 1u); break; }
-				y -= rf;
-				dp++;
-			}
-			if (dp == DEPTH_INVALID && R.lo + i >= R.from) raise(g, ERR_REF_UNRESOLVED);
-			R.depth_out[i] = dp;
-		}
 		// a halo row whose reference lies before the decoded range is never needed (and cannot be decoded): skip it
 		if (i < count && R.deg[i] != 0 && (R.depth ? R.depth[i] < DEPTH_INVALID : (int64_t)R.ref[i] <= i)) {
 			const int64_t x = R.lo + i;
@@ -967,199 +953,6 @@ __global__ void __launch_bounds__(TPB) k_copy_level(GraphDev g, RangeDev R, uint
 			row_copy_masked(g, row_slot(R, k - rf, rp_from), m0, m1, dst + ncopied, dst, R.deg[k] - ncopied, mask);
 		}
 	}
-}
-
-// stage 3b for shallow chains, ALL levels in one launch.  A block takes a tile of FTILE consecutive nodes (tiles are
-// handed out in node order by a ticket) and runs all the levels on it, so that what level l wrote is still in L2
-// (often in L1) when level l+1 reads it, and no per-level lists are needed.
-//
-// There is no barrier between the levels.  The tile's rows are sorted by (level, work class) into a list of tasks -- a
-// long row for a whole warp, or 32 short rows of one class, one per lane -- which the warps take IN ORDER from a shared
-// counter.  Before it starts, a task waits for exactly what it depends on: the `done` byte of each reference row
-// (shared memory), or, for a reference row that lies in the previous tile, that tile's published level (a global
-// flag; those rows are then read with ld.cg, past this SM's L1).  Everything a task can wait for belongs to a task
-// with a smaller number or to a tile with a smaller ticket, i.e. to something already running: no deadlock.
-// With at most four levels the tile is split in two halves whose levels alternate in the task order (A1 B1 A2 B2 ...):
-// when the warps reach A2 the tasks still in flight are B1's, which A2 does not depend on, so the waits are short.
-static constexpr int FRPT = 4;
-static constexpr int FTILE = TPB * FRPT;
-static constexpr int FCLS = 16;      // sort classes per level: 2 for warp rows, 14 for lane rows
-static constexpr int FCLS_WARP = 2;
-static_assert(LEVELS_MAX * FCLS <= NBUCKETS, "level x class must fit the sort buckets");
-
-struct FusedSmem {
-	uint64_t a[FTILE], b[FTILE];  // the rows' RowInfo
-	uint32_t hist[NBUCKETS + 1];
-	uint16_t order[FTILE];
-	uint8_t far[FTILE];   // bit 0: the reference row belongs to the previous tile; bit 1: masked row
-	uint8_t done[FTILE];  // 1: the row is complete
-	uint32_t tstart[LEVELS_MAX + 1];     // first task of segment s = (level - 1) * halves + half; tstart[segments] = number of tasks
-	uint32_t remaining[LEVELS_MAX + 1];  // unfinished tasks of level l
-	uint32_t levels_done;                // bit l-1: level l has no unfinished task
-	uint32_t next;                       // next task to hand out
-	uint32_t tile;
-};
-
-__device__ __forceinline__ uint32_t ld_acquire(const uint32_t *p) {
-	uint32_t v;
-	asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-	return v;
-}
-
-__device__ __forceinline__ int fused_class(uint32_t d, bool warp_row) {
-	if (warp_row) return d >= 512 ? 0 : 1;
-	int c;
-	if (d >= 48) c = d >= 96 ? 0 : d >= 64 ? 1 : 2;
-	else if (d >= 24) c = d >= 40 ? 3 : d >= 32 ? 4 : 5;
-	else if (d >= 8) c = d >= 20 ? 6 : d >= 16 ? 7 : d >= 12 ? 8 : 9;
-	else c = d >= 6 ? 10 : d >= 4 ? 11 : d == 3 ? 12 : 13;
-	return FCLS_WARP + c;
-}
-
-// the levels 1..k of this tile are complete (k = trailing ones of levels_done): tell the next tile
-__device__ __forceinline__ void fused_publish(const FusedSmem &S, uint32_t levels_done, uint32_t *flags) {
-	const uint32_t k = (uint32_t)__ffs((int)~levels_done) - 1u;
-	if (k) {
-		__threadfence();
-		atomicMax(flags + S.tile, k);
-	}
-}
-
-template <int DEF>
-__global__ void __launch_bounds__(TPB, 6) k_copy_fused(GraphDev g, RangeDev R, uint32_t nlevels, uint32_t *ticket, uint32_t *flags,
-                                                    const uint32_t *__restrict__ deep) {
-	extern __shared__ __align__(16) unsigned char smem_raw[];
-	FusedSmem &S = *reinterpret_cast<FusedSmem *>(smem_raw);
-	if (*deep) return;  // some chain is longer than nlevels: the host takes the general route
-	if (threadIdx.x == 0) {
-		S.tile = atomicAdd(ticket, 1u);
-		S.next = 0;
-	}
-	__syncthreads();
-	const uint32_t tile = S.tile;
-	const int64_t base = (int64_t)tile * FTILE;
-	const int64_t count = R.hi - R.lo;
-	const int64_t rp_from = R.rp[R.from - R.lo];
-	const uint32_t halves = nlevels * 2 <= LEVELS_MAX ? 2 : 1, nseg = nlevels * halves;
-	int bucket[FRPT];
-#pragma unroll
-	for (int q = 0; q < FRPT; q++) {
-		const int id = q * TPB + threadIdx.x;
-		const int64_t i = base + id;
-		bucket[q] = -1;
-		if (i < count) {
-			const uint32_t dp = R.depth[i], d = R.deg[i];
-			if (dp >= 1 && dp <= nlevels && d != 0 && !(R.lo + i >= R.from && (uint64_t)(R.rp[i + 1] - rp_from) > R.col_capacity)) {
-				const RowInfo ri = R.info[i];
-				const uint32_t rf = R.ref[i];
-				const bool masked = row_is_masked(d, R.deg[i - rf]);
-				if (masked ? (ri.a | ri.b) != 0 : (uint32_t)ri.b != 0) {
-					bucket[q] = (int)((dp - 1) * halves + (halves == 2 && q >= FRPT / 2 ? 1 : 0)) * FCLS + fused_class(d, !masked);
-					S.a[id] = ri.a;
-					S.b[id] = ri.b;
-					S.far[id] = ((int64_t)rf > i - base ? 1 : 0) | (masked ? 2 : 0);
-				}
-			}
-		}
-		S.done[id] = bucket[q] < 0;
-	}
-	uint32_t total;
-	block_bin_sort<FRPT>(bucket, S.hist, S.order, &total);
-	if (threadIdx.x == 0) {
-		uint32_t t = 0, dm = 0;
-		for (uint32_t l = 1; l <= nlevels; l++) S.remaining[l] = 0;
-		for (uint32_t sg = 0; sg < nseg; sg++) {
-			const uint32_t w0 = S.hist[sg * FCLS], w1 = S.hist[sg * FCLS + FCLS_WARP], e1 = S.hist[(sg + 1) * FCLS];
-			const uint32_t nt = (w1 - w0) + (e1 - w1 + 31) / 32;
-			S.tstart[sg] = t;
-			S.remaining[sg / halves + 1] += nt;
-			t += nt;
-		}
-		for (uint32_t l = 1; l <= nlevels; l++)
-			if (S.remaining[l] == 0) dm |= 1u << (l - 1);
-		S.tstart[nseg] = t;
-		S.levels_done = dm;
-		fused_publish(S, dm, flags);
-	}
-	__syncthreads();
-	const unsigned lane = threadIdx.x & 31u;
-	const uint32_t ntasks = S.tstart[nseg];
-	const volatile uint8_t *done = S.done;
-#pragma unroll 1
-	for (;;) {
-		uint32_t t = 0;
-		if (lane == 0) t = atomicAdd(&S.next, 1u);
-		t = __shfl_sync(FULL_MASK, t, 0);
-		if (t >= ntasks) break;
-		uint32_t sg = 0;
-		while (sg + 1 < nseg && t >= S.tstart[sg + 1]) sg++;
-		const uint32_t l = sg / halves + 1;
-		const uint32_t rel = t - S.tstart[sg];
-		const uint32_t w0 = S.hist[sg * FCLS], w1 = S.hist[sg * FCLS + FCLS_WARP], e1 = S.hist[(sg + 1) * FCLS];
-		const bool warp_row = rel < w1 - w0;
-		const uint32_t idx = warp_row ? w0 + rel : w1 + (rel - (w1 - w0)) * 32 + lane;
-		const bool active = idx < e1;
-		const unsigned mask = __ballot_sync(FULL_MASK, active);
-		const int id = active ? S.order[idx] : 0;
-		const int64_t k = base + id;
-		const uint32_t rf = active ? R.ref[k] : 0;
-		const bool far = active && (S.far[id] & 1) != 0;
-		// wait for the reference rows
-		if (__any_sync(FULL_MASK, far) && l >= 2) {
-			if (lane == 0)
-				while (ld_acquire(flags + tile - 1) < l - 1) __nanosleep(100);
-			__syncwarp();
-		}
-		while (!__all_sync(FULL_MASK, !active || far || done[id - (int)rf] != 0)) __nanosleep(40);
-		__threadfence_block();
-		const bool cg = __any_sync(FULL_MASK, far);
-		if (warp_row) {
-			const uint32_t ncopied = (uint32_t)S.b[id];
-			int64_t *dst = row_slot(R, k, rp_from);
-			BitReader r;
-			r.init(g, S.a[id]);
-			row_copy_warp<DEF>(g, r, row_slot(R, k - rf, rp_from), R.deg[k - rf], dst + ncopied, dst, R.deg[k], (uint32_t)(S.b[id] >> 32), ncopied, cg);
-		} else if (active) {
-			const uint64_t m0 = S.a[id], m1 = S.b[id];
-			const uint32_t ncopied = (uint32_t)(__popcll(m0) + __popcll(m1));
-			int64_t *dst = row_slot(R, k, rp_from);
-			row_copy_masked(g, row_slot(R, k - rf, rp_from), m0, m1, dst + ncopied, dst, R.deg[k] - ncopied, mask, cg);
-		}
-		// rows near the end of the tile may be read by the next tile's block: their data must be visible device-wide
-		// before the level is published; for the others the block is enough
-		if (__any_sync(FULL_MASK, active && id >= FTILE - (int)g.window)) __threadfence();
-		else __threadfence_block();
-		__syncwarp();
-		if (active && (!warp_row || lane == 0)) S.done[id] = 1;
-		if (lane == 0 && atomicSub(&S.remaining[l], 1u) == 1u) {
-			__threadfence();
-			fused_publish(S, atomicOr(&S.levels_done, 1u << (l - 1)) | (1u << (l - 1)), flags);
-		}
-	}
-}
-
-uint32_t copy_fused_tiles(int64_t count) { return grid_for(count, FTILE); }
-
-void launch_copy_fused(const Launch &L, const GraphDev &g, int def, const RangeDev &r, uint32_t nlevels, uint32_t *ticket, uint32_t *flags,
-                       const uint32_t *deep) {
-	const int64_t count = r.hi - r.lo;
-	if (count <= 0 || nlevels == 0) return;
-	const size_t smem = sizeof(FusedSmem);
-	const unsigned grid = copy_fused_tiles(count);
-	switch (def) {
-	case 2:
-		cudaFuncSetAttribute(k_copy_fused<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-		k_copy_fused<2><<<grid, TPB, smem, L.stream>>>(g, r, nlevels, ticket, flags, deep);
-		break;
-	case 1:
-		cudaFuncSetAttribute(k_copy_fused<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-		k_copy_fused<1><<<grid, TPB, smem, L.stream>>>(g, r, nlevels, ticket, flags, deep);
-		break;
-	default:
-		cudaFuncSetAttribute(k_copy_fused<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-		k_copy_fused<0><<<grid, TPB, smem, L.stream>>>(g, r, nlevels, ticket, flags, deep);
-	}
-	WGBV_LAUNCHED(L);
 }
 
 void launch_copy_level(const Launch &L, const GraphDev &g, int def, const RangeDev &r, uint32_t level, const uint32_t *list,

@@ -36,11 +36,6 @@ struct RangeDev {
 	int64_t *halo;          // successors of [lo, from): row x starts at halo + rp[x-lo]
 	uint64_t col_capacity;  // elements available at col
 	RowInfo *info;          // written by k_extras for every row with a reference, read by k_copy_level (may be nullptr)
-	// shallow chains without a depth pass: k_extras walks the reference array itself (at most walk_levels hops),
-	// stores the depths here and sets *deep if some chain is longer (all three unused when depth_out is nullptr)
-	uint32_t *depth_out = nullptr;
-	uint32_t walk_levels = 0;
-	uint32_t *deep = nullptr;
 	// One-launch front end (no halo, lo == from): k_extras itself reads outdegree and reference of its rows (stage 1),
 	// scans the outdegrees across tiles by decoupled look-back (stage 2) and writes deg_w / ref_w / rp_w -- the very
 	// arrays deg / ref / rp point to -- before it parses the rest.  tile_state: one zeroed word per tile; tile_ticket:
@@ -71,13 +66,20 @@ struct HeavyDev {
 	unsigned long long *counters;  // [0] entries, [1..64] per-class counts, [65..128] per-class cursors
 };
 
-// The fused tile kernel (bv_tile.cu): per-block scratch for tiles that do not fit shared memory.
-static constexpr int TILE_MAX_HALO = 64;  // largest window_size * max_ref_count the tile kernel handles
-struct TileDev {
-	int64_t *scratch;        // blocks * scratch_cap successors
-	uint32_t scratch_cap;    // per block
+// The fused tile kernel (bv_fused.cu): one pass over the bit stream, a tile of rows per block, everything on chip.
+static constexpr int TILE_MAX_HALO = 64;  // largest window_size * max_ref_count the fused kernel handles
+struct FusedDev {
+	int64_t from, to;        // nodes to decode; rows before `from` (down to the first row the handle holds) serve as halo
 	int32_t halo;            // window_size * max_ref_count of the graph
-	uint32_t *fallback;      // set to 1 when some tile has to be left to the level-synchronous kernels
+	int32_t tile_rows;       // rows per tile: 256 - halo
+	uint32_t ntiles;
+	int64_t *rowptr;         // to - from + 1 entries, rowptr[0] = 0
+	int64_t *col;
+	uint64_t col_capacity;
+	uint64_t *tile_state;    // ntiles zeroed words: look-back state of the arc-count scan
+	uint32_t *ticket;        // zeroed: [0] tiles handed out, [1] chunks of k_slow handed out
+	uint32_t *slow_count;    // zeroed: tiles left to k_slow
+	uint32_t *tile_done;     // ntiles words, written by the kernels: 1 = the tile's successors are complete
 };
 
 struct Launch {
@@ -104,10 +106,6 @@ void launch_level_lists(const Launch &L, const GraphDev &g, const uint8_t *ref, 
 void launch_extras(const Launch &L, const GraphDev &g, int def, const RangeDev &r, const HeavyDev &h);
 uint32_t extras_tiles(int64_t count);
 // stage 3b: copy-block resolution of the rows at one depth level; list == nullptr: every node is inspected
-// all levels of shallow chains in one launch (see k_copy_fused); ticket and flags[tiles] must be zero
-uint32_t copy_fused_tiles(int64_t count);
-void launch_copy_fused(const Launch &L, const GraphDev &g, int def, const RangeDev &r, uint32_t nlevels, uint32_t *ticket, uint32_t *flags,
-                       const uint32_t *deep);
 void launch_copy_level(const Launch &L, const GraphDev &g, int def, const RangeDev &r, uint32_t level,
                        const uint32_t *list, uint64_t list_count);
 // checksum of a CSR
@@ -127,9 +125,10 @@ void launch_chain_extras(const Launch &L, const GraphDev &g, int def, const Chai
 void launch_chain_copy(const Launch &L, const GraphDev &g, int def, const ChainDev &c, uint64_t rows,
                        const uint32_t *level, uint32_t this_level);
 void launch_scan64(const Launch &L, const unsigned long long *in, int64_t *out, int64_t count, uint64_t *state, uint32_t *ticket);
-// stage 3, fused: one block decodes a tile of rows completely in shared memory (bounded reference chains only)
-size_t tile_smem_bytes();
-int launch_tile(const Launch &L, const GraphDev &g, int def, const RangeDev &r, const TileDev &t, int blocks);
+// the whole decode of [F.from, F.to) in one pass (k_fused) plus the tiles that do not fit shared memory (k_slow);
+// returns a cudaError_t as int
+int launch_fused(const Launch &L, const GraphDev &g, int def, const FusedDev &F, int sm_count);
+int fused_tile_rows(int halo, double mean_degree, double mean_record_bits);
 // transpose of a device CSR (bv_transpose.cu): pack arcs into target << 32 | source words and count in-degrees, then
 // LSD radix passes over the target half (hist -> scan of counts[digit * tiles + tile] -> stable scatter; the last
 // scatter writes the sources to t_col)

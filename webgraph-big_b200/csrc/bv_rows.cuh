@@ -137,16 +137,32 @@ __device__ __forceinline__ void row_intervals(const GraphDev &g, RD &r, uint32_t
 	}
 }
 
+// Element types of a row store.  Successors are int64 at the C ABI; the fused tile kernel keeps rows of graphs with
+// fewer than 2^32 - 1 nodes as uint32 in shared memory (half the bytes, 32-bit arithmetic in the serial loops) and
+// widens them on the way out.  ElemMax<E> is a sentinel larger than every node id representable in E's mode.
+template <class E> struct ElemTraits;
+template <> struct ElemTraits<int64_t> {
+	using V = int64_t;
+	static constexpr int64_t MAX = INT64_MAX;
+};
+template <> struct ElemTraits<uint32_t> {
+	using V = uint32_t;
+	static constexpr uint32_t MAX = 0xffffffffu;
+};
+
 // The merge of intervals (cursor ri, `ic` of them) and residuals (cursor r, `nres` of them) into out[0..nextra).
-// Warp-synchronous: every lane of `mask` must call it (nextra == 0: no work).  Two loops: a merging one that runs
-// while some lane of the warp still has interval material, then a tight one for pure gap decoding (the kernels sort
-// rows so that most warps never enter the first).  WIN lets the residual reader run on a small window of the stream
-// that the warp refills together (see k_extras_heavy); with NoWindow that code vanishes.
-template <int DEF, class RDI, class RDR, class WIN>
+// Warp-synchronous: every lane of `mask` must call it (nextra == 0: no work).  Three parts: a merging loop that runs
+// while some lane of the warp still has interval material, then (one site, all lanes together) the first residual of
+// rows that have not decoded any yet -- its code is a signed offset from x and may need 64 bits even when node ids fit
+// 32 -- and then a tight loop of pure gap decoding in E's arithmetic (the kernels sort rows so that most warps never
+// enter the first loop).  WIN lets the residual reader run on a small window of the stream that the warp refills
+// together (see k_extras_heavy); with NoWindow that code vanishes.
+template <int DEF, class RDI, class RDR, class WIN, class E = int64_t>
 __device__ __forceinline__ void row_extras_core(const GraphDev &g, RDI &ri, RDR &r, int64_t x, uint32_t nextra, uint32_t ic, uint32_t nres,
-                                                int64_t *out, unsigned mask, WIN &win) {
-	int64_t cur = 0, end = 0;  // current interval [cur, end)
-	int64_t res = x;           // last residual decoded; pending (not yet written) iff have_res
+                                                E *out, unsigned mask, WIN &win) {
+	using V = typename ElemTraits<E>::V;
+	V cur = 0, end = 0;  // current interval [cur, end)
+	V res = (V)x;        // last residual decoded; pending (not yet written) iff have_res
 	bool have_res = false, first_res = true, first_int = true;
 	uint32_t o = 0;
 	for (; __any_sync(mask, o < nextra && (cur != end || ic != 0)); o++) {
@@ -154,32 +170,37 @@ __device__ __forceinline__ void row_extras_core(const GraphDev &g, RDI &ri, RDR 
 		if (o < nextra) {
 			if (cur == end && ic) {  // next interval (rare: once per interval)
 				const uint64_t gap = ri.gamma();
-				cur = first_int ? x + nat2int(gap) : end + 1 + (int64_t)gap;
+				cur = first_int ? (V)(x + nat2int(gap)) : (V)(end + 1 + (V)gap);
 				first_int = false;
-				end = cur + (int64_t)ri.gamma() + g.min_interval;
+				end = (V)(cur + (V)ri.gamma() + (V)g.min_interval);
 				ic--;
 			}
 			if (!have_res && nres) {
 				const uint64_t code = rd_residual<DEF>(r, g);
-				res = first_res ? x + nat2int(code) : res + 1 + (int64_t)code;
+				res = first_res ? (V)(x + nat2int(code)) : (V)(res + 1 + (V)code);
 				first_res = false;
 				have_res = true;
 				nres--;
 			}
-			const bool take_int = cur < end && (!have_res || cur < res);
-			out[o] = take_int ? cur : res;
+			const bool take_int = cur != end && (!have_res || cur < res);
+			out[o] = (E)(take_int ? cur : res);
 			if (take_int) cur++;
 			else have_res = false;
 		}
 	}
-	if (have_res && o < nextra) out[o++] = res;  // a residual decoded above but not written yet
+	if (have_res && o < nextra) out[o++] = (E)res;  // a residual decoded above but not written yet
+	if (__any_sync(mask, first_res && o < nextra)) {
+		if (WIN::enabled && __any_sync(mask, win.low(r))) win.refill(r, mask);
+		if (first_res && o < nextra) {
+			res = (V)(x + nat2int(rd_residual<DEF>(r, g)));
+			out[o++] = (E)res;
+		}
+	}
 	for (; __any_sync(mask, o < nextra); o++) {
 		if (WIN::enabled && __any_sync(mask, win.low(r))) win.refill(r, mask);
 		if (o < nextra) {
-			const uint64_t code = rd_residual<DEF>(r, g);
-			res = first_res ? x + nat2int(code) : res + 1 + (int64_t)code;
-			first_res = false;
-			out[o] = res;
+			res = (V)(res + 1 + (V)rd_residual<DEF>(r, g));
+			out[o] = (E)res;
 		}
 	}
 }
@@ -187,8 +208,8 @@ __device__ __forceinline__ void row_extras_core(const GraphDev &g, RDI &ri, RDR 
 // Decodes the interval section and the residuals of row x (reader positioned at the interval count, i.e. right
 // after the blocks) and writes the `nextra` merged values, in increasing order, to out[0..nextra).
 // BVG:1037-1073, 902-954.  Warp-synchronous: every lane of `mask` must call it (nextra == 0: no work).
-template <int DEF, class RD>
-__device__ __forceinline__ void row_extras(const GraphDev &g, RD &r, int64_t x, uint32_t nextra, int64_t *out, unsigned mask) {
+template <int DEF, class RD, class E = int64_t>
+__device__ __forceinline__ void row_extras(const GraphDev &g, RD &r, int64_t x, uint32_t nextra, E *out, unsigned mask) {
 	uint32_t ic, nres;
 	uint64_t int_pos;
 	row_intervals(g, r, nextra, ic, int_pos, nres);
@@ -253,13 +274,16 @@ __device__ __forceinline__ void row_copy(const GraphDev &g, RD &r, const int64_t
 // copied element -- through one instruction stream.  ext[0..ne) are the extras; in place operation as in row_copy.
 // Warp-synchronous: every lane of `mask` must call it (m == 0 for lanes without work).
 // cg (warp-uniform): read the reference row past the L1 (it was written by another block of the running kernel).
-__device__ __forceinline__ void row_copy_masked(const GraphDev &g, const int64_t *src, uint64_t m, uint64_t m1, const int64_t *ext,
-                                                int64_t *dst, uint32_t ne, unsigned mask, bool cg = false) {
+template <class E = int64_t>
+__device__ __forceinline__ void row_copy_masked(const GraphDev &g, const E *src, uint64_t m, uint64_t m1, const E *ext, E *dst, uint32_t ne,
+                                                unsigned mask, bool cg = false) {
+	constexpr bool GLOBAL = sizeof(E) == 8;  // int64 rows live in global memory (prefetches, optional ld.cg); uint32 rows in shared memory
+	const E EMAX = ElemTraits<E>::MAX;
 	uint32_t ei = 0;
 	if (!m) { m = m1; m1 = 0; src += 64; }
 	int pos = m ? __ffsll((long long)m) - 1 : 0;
-	int64_t e = (m && ne) ? ext[0] : INT64_MAX;
-	int64_t c = m ? (cg ? __ldcg(src + pos) : src[pos]) : 0;
+	E e = (m && ne) ? ext[0] : EMAX;
+	E c = m ? ((GLOBAL && cg) ? __ldcg(src + pos) : src[pos]) : 0;
 	while (__any_sync(mask, m != 0)) {
 		if (m) {
 			const bool take_e = e < c;
@@ -267,16 +291,16 @@ __device__ __forceinline__ void row_copy_masked(const GraphDev &g, const int64_t
 			*dst++ = take_e ? e : c;
 			if (take_e) {
 				// each new 32-byte sector of a stream would cost a memory round trip: ask for the one two ahead
-				if ((ei & 3u) == 0 && ei + 8 < ne) prefetch_l1(ext + ei + 8);
-				e = ++ei < ne ? ext[ei] : INT64_MAX;
+				if (GLOBAL && (ei & 3u) == 0 && ei + 8 < ne) prefetch_l1(ext + ei + 8);
+				e = ++ei < ne ? ext[ei] : EMAX;
 			} else {
 				m &= m - 1;
 				if (!m && m1) { m = m1; m1 = 0; src += 64; pos -= 64; }
 				if (m) {
 					const int q = __ffsll((long long)m) - 1;
-					if (!cg && (q >> 2) != (pos >> 2)) prefetch_l1(src + (q & ~3) + 8);
+					if (GLOBAL && !cg && (q >> 2) != (pos >> 2)) prefetch_l1(src + (q & ~3) + 8);
 					pos = q;
-					c = cg ? __ldcg(src + q) : src[q];
+					c = (GLOBAL && cg) ? __ldcg(src + q) : src[q];
 				}
 			}
 		}
@@ -305,9 +329,11 @@ __device__ __forceinline__ uint32_t nth_set_bit(uint32_t m, uint32_t n) {
 // (rank among its own kind + rank among the other kind), so the serial dependency of the one-lane merge -- and with
 // it the long tail of very long rows -- disappears.  In place operation (ext == dst + ncopied) is safe for the same
 // reason as in row_copy: a round writes below the position of the first extra it has not loaded yet.
-template <int DEF, class RD>
-__device__ __forceinline__ void row_copy_warp(const GraphDev &g, RD &r, const int64_t *src, uint32_t dref, const int64_t *ext,
-                                              int64_t *dst, uint32_t d, uint32_t bc, uint32_t ncopied, bool cg = false) {
+template <int DEF, class RD, class E = int64_t>
+__device__ __forceinline__ void row_copy_warp(const GraphDev &g, RD &r, const E *src, uint32_t dref, const E *ext, E *dst, uint32_t d,
+                                              uint32_t bc, uint32_t ncopied, bool cg = false) {
+	constexpr bool GLOBAL = sizeof(E) == 8;
+	const E EMAX = ElemTraits<E>::MAX;
 	const unsigned lane = threadIdx.x & 31u;
 	const uint32_t ne = d - ncopied;
 	uint32_t kb = 0;           // first position of the current window of the reference row
@@ -317,12 +343,12 @@ __device__ __forceinline__ void row_copy_warp(const GraphDev &g, RD &r, const in
 	uint32_t bs = 0, be = 0, blk = 0;
 	bool bcopy = false;
 	unsigned cmask = 0;        // copied positions of the current window not emitted yet
-	int64_t c = 0;             // my reference element of the current window
+	E c = 0;                   // my reference element of the current window
 	bool fresh = true;         // the window at kb has not been loaded yet
 	while (done < ncopied) {
 		if (fresh) {
 			const uint32_t p = kb + lane;
-			c = p < dref ? (cg ? __ldcg(src + p) : src[p]) : INT64_MAX;
+			c = p < dref ? ((GLOBAL && cg) ? __ldcg(src + p) : src[p]) : EMAX;
 			bool f = false;
 			// walk the blocks that overlap [kb, kb + 32)
 			for (;;) {
@@ -342,24 +368,24 @@ __device__ __forceinline__ void row_copy_warp(const GraphDev &g, RD &r, const in
 		// A: the copied elements of the window still to emit, compacted to lanes 0..nA-1
 		const unsigned nA = (unsigned)__popc(cmask);
 		const int srcl = lane < nA ? (int)nth_set_bit(cmask, lane) : 0;
-		int64_t A = __shfl_sync(FULL_MASK, c, srcl);
-		if (lane >= nA) A = INT64_MAX;
+		E A = __shfl_sync(FULL_MASK, c, srcl);
+		if (lane >= nA) A = EMAX;
 		// B: the next extras
 		const uint32_t nB = ne - ei < 32u ? ne - ei : 32u;
-		const int64_t B = lane < nB ? ext[ei + lane] : INT64_MAX;
+		const E B = lane < nB ? ext[ei + lane] : EMAX;
 		const bool src_last = kb + 32 >= dref;   // nothing copied follows this window
 		const bool ext_last = ei + nB >= ne;     // no extra follows this window
-		const int64_t a_last = __shfl_sync(FULL_MASK, A, (int)nA - 1);
-		const int64_t b_last = nB ? __shfl_sync(FULL_MASK, B, (int)nB - 1) : INT64_MIN;
-		const int64_t lim_a = src_last ? INT64_MAX : a_last;
-		const int64_t lim_b = ext_last ? INT64_MAX : b_last;
-		const int64_t limit = lim_a < lim_b ? lim_a : lim_b;
+		const E a_last = __shfl_sync(FULL_MASK, A, (int)nA - 1);
+		const E b_last = nB ? __shfl_sync(FULL_MASK, B, (int)nB - 1) : (E)0;
+		const E lim_a = src_last ? EMAX : a_last;
+		const E lim_b = ext_last ? EMAX : b_last;  // (no extras at all: ext_last holds, the limit is not used)
+		const E limit = lim_a < lim_b ? lim_a : lim_b;
 		// ranks in the other window by binary search over lanes (both windows are sorted, padded with +inf)
 		uint32_t a_in_b = 0, b_in_a = 0;  // #B < A_lane, #A < B_lane
 #pragma unroll
 		for (int step = 16; step; step >>= 1) {
-			const int64_t vb = __shfl_sync(FULL_MASK, B, (int)(a_in_b + step - 1));
-			const int64_t va = __shfl_sync(FULL_MASK, A, (int)(b_in_a + step - 1));
+			const E vb = __shfl_sync(FULL_MASK, B, (int)(a_in_b + step - 1));
+			const E va = __shfl_sync(FULL_MASK, A, (int)(b_in_a + step - 1));
 			if (vb < A) a_in_b += step;
 			if (va < B) b_in_a += step;
 		}
@@ -380,6 +406,193 @@ __device__ __forceinline__ void row_copy_warp(const GraphDev &g, RD &r, const in
 		if (cmask == 0) { kb += 32; fresh = true; }
 		__syncwarp();
 	}
+}
+
+
+// ------------------------------------------------------------------------------------------------ whole-warp rows
+// A long residual list decoded by a whole warp.  The codes of a row are a serial chain -- where a code starts is only
+// known once the one before it has been read -- and a row of hundreds (or, in the reference's slow test,
+// BVGraphSlowTest.java:30-96, a billion) residuals would keep one lane busy while everything that depends on the
+// row waits.  But the bit range of the list is known exactly (it ends where the next record starts), and the codes
+// resynchronise: a parse started at a wrong position falls in step with the true one within a few codes.  So the
+// range is cut into segments of COOP_SEG bits, one per lane.  Every lane parses its segment from a guessed entry
+// (the segment's first bit; lane 0 knows the truth) and reports where its parse leaves the segment; that exit is
+// the next lane's entry, so lanes whose entry changed parse again, until no entry changes (two or three rounds in
+// practice, lane i is certainly right after round i + 1).  A scan over the lanes' code counts and gap sums then gives
+// every lane the index and the value its first code starts from, and a last parse writes the successors.  All 32
+// lanes pass the same arguments; proto is a reader on the stream (any position), [p0, p1) the bit range of the n codes.
+// BVG:902-954 (ResidualLongIterator) is what this replaces.
+static constexpr uint32_t COOP_SEG_MIN = 128, COOP_SEG_MAX = 4096;
+// rows of at least this many residuals are decoded by a whole warp (rows with intervals only if they have at most 32)
+static constexpr uint32_t COOP_LONG = 64;
+
+template <int DEF, class RD, class E>
+__device__ __forceinline__ void coop_residuals(const GraphDev &g, const RD &proto, typename RD::pos_t p0, typename RD::pos_t p1, uint32_t n,
+                                               int64_t x, E *out) {
+	using V = typename ElemTraits<E>::V;
+	using P = typename RD::pos_t;
+	const unsigned lane = threadIdx.x & 31u;
+	P wstart = p0;      // true position of the first code not written yet
+	uint32_t done = 0;  // codes written
+	V base = (V)x;      // value the next code's gap is added to (set up by the first code, which is a signed offset from x)
+	// segment length: the whole list in one window when it is short, long segments (fewer rounds per bit) when it is huge
+	const uint64_t span = p1 > p0 ? (uint64_t)(p1 - p0) : 0;
+	uint64_t sg = (span + 31) / 32;
+	sg = (sg + 31) & ~31ull;
+	const P seg = (P)(sg < COOP_SEG_MIN ? COOP_SEG_MIN : sg > COOP_SEG_MAX ? COOP_SEG_MAX : sg);
+	while (done < n && wstart < p1) {
+		const P seg_lo = wstart + seg * lane, seg_hi = seg_lo + seg;
+		const bool active = seg_lo < p1;
+		const P lim = seg_hi < p1 ? seg_hi : p1;
+		P entry = seg_lo, exit = seg_lo;
+		uint32_t cnt = 0;
+		V total = 0;  // sum of (gap + 1) over my codes
+		bool dirty = active;
+		for (int round = 0; round < 34; round++) {
+			if (dirty) {
+				RD r = proto;
+				r.seek(entry);
+				P p = entry;
+				cnt = 0;
+				total = 0;
+				while (p < lim) {
+					const uint64_t code = rd_residual<DEF>(r, g);
+					total += (V)code + 1;
+					cnt++;
+					const P q = (P)r.tell();
+					if (q <= p) { p = lim; break; }  // (cannot happen: every code has at least one bit)
+					p = q;
+				}
+				exit = p > entry ? p : entry;
+			}
+			P prev = __shfl_up_sync(FULL_MASK, exit, 1);
+			if (lane == 0) prev = wstart;
+			dirty = active && prev != entry;
+			if (dirty) entry = prev;
+			if (!__any_sync(FULL_MASK, dirty)) break;
+		}
+		if (!active) { cnt = 0; total = 0; }
+		// The row's first residual is a signed offset from x (BVG:917), the others are gaps (BVG:929).  The scans below
+		// treat every code as a gap; the starting value is chosen so that the first one comes out right all the same.
+		if (done == 0) {
+			V b0 = 0;
+			if (lane == 0) {
+				RD r = proto;
+				r.seek(wstart);
+				const uint64_t code = rd_residual<DEF>(r, g);
+				b0 = (V)(x + nat2int(code)) - ((V)code + 1);
+			}
+			base = __shfl_sync(FULL_MASK, b0, 0);
+		}
+		// index and value every lane starts from (inclusive scans over the lanes)
+		uint32_t ci = cnt;
+		V ti = total;
+#pragma unroll
+		for (int o = 1; o < 32; o <<= 1) {
+			const uint32_t c2 = __shfl_up_sync(FULL_MASK, ci, o);
+			const V t2 = __shfl_up_sync(FULL_MASK, ti, o);
+			if ((int)lane >= o) { ci += c2; ti += t2; }
+		}
+		const uint32_t wcount = __shfl_sync(FULL_MASK, ci, 31);
+		const V wtotal = __shfl_sync(FULL_MASK, ti, 31);
+		// the last parse: write
+		if (cnt) {
+			uint32_t idx = done + ci - cnt;
+			V val = base + (ti - total);
+			RD r = proto;
+			r.seek(entry);
+			for (uint32_t k = 0; k < cnt; k++) {
+				val += (V)rd_residual<DEF>(r, g) + 1;
+				if (idx < n) out[idx] = (E)val;
+				idx++;
+			}
+		}
+		base += wtotal;
+		done += wcount;
+		// the window ends where its last active lane's parse ended
+		const unsigned am = __ballot_sync(FULL_MASK, active);
+		const int last = 31 - __clz((int)am);
+		const P wend = __shfl_sync(FULL_MASK, exit, last);
+		if (wcount == 0 || wend <= wstart) break;  // malformed: no progress
+		wstart = wend;
+	}
+	if (done < n) raise(g, ERR_DEGREE);  // the record holds fewer codes than announced
+}
+
+// The intervals of a row merged into its residuals by a whole warp (all lanes pass the same arguments).  ext[0..ne) is
+// the extras part of the row's slot; its last nres entries hold the residuals, in increasing order; the reader is
+// positioned at the interval count and the row has at most 32 intervals.  Lane k keeps interval k.  Residuals move
+// down to their final places first (in chunks, in increasing order: a target never lies above its source), then the
+// interval elements fill the holes.  In files the reference writes no residual lies inside an interval
+// (intervalize, BVG:1595-1618), so an interval goes in as one piece.  BVG:1037-1073, LongIntervalSequenceIterator.java:57-77.
+template <class RD, class E>
+__device__ __forceinline__ void coop_intervals_merge(const GraphDev &g, const RD &proto, typename RD::pos_t ipos, int64_t x, E *ext, uint32_t ne,
+                                                     uint32_t nres) {
+	using V = typename ElemTraits<E>::V;
+	const unsigned lane = threadIdx.x & 31u;
+	RD r = proto;
+	r.seek(ipos);
+	uint64_t ic64 = r.gamma();
+	const uint32_t ic = ic64 > 32 ? 32u : (uint32_t)ic64;
+	V left = 0, prev_end = 0;
+	uint32_t len = 0;
+	for (uint32_t i = 0; i < ic; i++) {  // every lane reads the same codes; lane i keeps interval i
+		const uint64_t gap = r.gamma();
+		const V l = i == 0 ? (V)(x + nat2int(gap)) : (V)(prev_end + 1 + (V)gap);
+		const uint32_t ln = (uint32_t)r.gamma() + (uint32_t)g.min_interval;
+		prev_end = l + (V)ln;
+		if (i == lane) { left = l; len = ln; }
+	}
+	// s: interval elements before mine
+	uint32_t s = len;
+#pragma unroll
+	for (int o = 1; o < 32; o <<= 1) {
+		const uint32_t t = __shfl_up_sync(FULL_MASK, s, o);
+		if ((int)lane >= o) s += t;
+	}
+	const uint32_t total = __shfl_sync(FULL_MASK, s, 31);
+	s -= len;
+	if (total != ne - nres) { raise(g, ERR_DEGREE); return; }
+	E *res = ext + total;
+	// c: residuals smaller than my interval
+	uint32_t c = 0;
+	if (lane < ic) {
+		uint32_t lo = 0, hi = nres;
+		while (lo < hi) {
+			const uint32_t mid = (lo + hi) >> 1;
+			if ((V)res[mid] < left) lo = mid + 1;
+			else hi = mid;
+		}
+		c = lo;
+	}
+	__syncwarp();
+	for (uint32_t u0 = 0; u0 < nres; u0 += 32) {
+		const uint32_t u = u0 + lane;
+		const bool a = u < nres;
+		const V rv = a ? (V)res[u] : 0;
+		uint32_t below = 0;
+		for (uint32_t k = 0; k < ic; k++) {
+			const V lk = __shfl_sync(FULL_MASK, left, k);
+			const uint32_t nk = __shfl_sync(FULL_MASK, len, k);
+			if (lk < rv) below += nk;
+		}
+		__syncwarp();
+		if (a) ext[u + below] = (E)rv;
+		__syncwarp();
+	}
+	for (uint32_t e0 = 0; e0 < total; e0 += 32) {
+		const uint32_t e = e0 + lane;
+		int kk = 0;
+		for (uint32_t k = 1; k < ic; k++) {
+			const uint32_t sk = __shfl_sync(FULL_MASK, s, k);
+			if (sk <= e) kk = (int)k;
+		}
+		const V lk = __shfl_sync(FULL_MASK, left, kk);
+		const uint32_t sk = __shfl_sync(FULL_MASK, s, kk);
+		const uint32_t ck = __shfl_sync(FULL_MASK, c, kk);
+		if (e < total) ext[e + ck] = (E)(lk + (V)(e - sk));
+	}
+	__syncwarp();
 }
 
 }  // namespace wgbv

@@ -36,6 +36,7 @@ struct wgbv_graph {
 	EliasFano ef;  // host copy, for accounting
 	int streams = 0;
 	int sm_count = 148;
+	int fused_rows = 0;  // rows per tile of the one-pass kernel for this graph (0: not used)
 };
 
 // A grow-only device buffer.
@@ -73,10 +74,20 @@ struct wgbv_stream {
 	uint64_t launches = 0;
 	DevBuf deg, ref, depth, rp, scan_state, ticket, halo, levels, list, col, rowptr, ids, batch;
 	DevBuf t_pairs[2], t_indeg, t_counts, t_pos;  // wgbv_transpose_csr
-	DevBuf heavy_rows, heavy_sorted, heavy_cls, heavy_counters, tile_scratch, level_pos, row_info;
+	DevBuf heavy_rows, heavy_sorted, heavy_cls, heavy_counters, level_pos, row_info, tile_done;
 	bool front_in_extras = true;  // false: always run header and scan as their own launches (WGBV_SPLIT_FRONT=1)
-	bool fused_levels = false;  // true: all levels of shallow chains in one launch, k_copy_fused (WGBV_FUSED_LEVELS=1)
-	bool force_levels = true;   // false: use the fused tile kernel where it applies (WGBV_TILE=1)
+	bool use_fused = true;        // false: never use the one-pass tile kernel (WGBV_FUSED=0): the level-synchronous path only
+	// The decodes of the fused kernel whose outcome has not been read yet: if one of them reported ERR_FUSED_FALLBACK
+	// (something only the general path handles), the call that collects the errors reruns them on the general path
+	// (the error word does not say which one it was; rerunning a good one gives the same result).
+	struct FusedCall {
+		int64_t from, to;
+		int64_t *d_rowptr, *d_col;
+		uint64_t col_capacity;
+	};
+	std::vector<FusedCall> fused_pending;
+	uint64_t fused_fallbacks = 0;  // decodes that were rerun
+	uint32_t last_slow_tiles = 0, last_tiles = 0;
 	DevBuf c_node, c_dst, c_parent, c_deg, c_isq, c_level, c_len, c_arcs, c_row0, c_soff, c_store;
 	cudaEvent_t ev[6]{};
 	bool ev_valid = false;
@@ -260,6 +271,14 @@ static int build_graph(const wgbv_props *props, const uint8_t *graph, uint64_t g
 	d.reference_coding = props->reference_coding;
 	d.block_count_coding = props->block_count_coding;
 	d.err = nullptr;
+	{
+		// the one-pass tile kernel: bounded chains, node ids that fit 32 bits, and a density its tiles can hold
+		const int64_t held = shard_hi - avail_lo;
+		const double rec_bits = held > 0 ? (double)(bit1 - bit0) / (double)held : 0.0;
+		const double mean_deg = props->nodes > 0 && props->arcs > 0 ? (double)props->arcs / (double)props->nodes : rec_bits / 12.0;
+		if (halo_nodes >= 0 && halo_nodes <= TILE_MAX_HALO && props->max_ref_count <= 8 && (uint64_t)props->nodes < 0xffffffffull)
+			g->fused_rows = fused_tile_rows((int)halo_nodes, mean_deg, rec_bits);
+	}
 	*out = g;
 	return WGBV_OK;
 }
@@ -453,15 +472,12 @@ extern "C" int wgbv_stream_create(wgbv_graph *g, void *cuda_stream, wgbv_stream 
 	for (auto &e : s->ev) cudaEventCreate(&e);
 	s->dev = g->dev;
 	s->dev.err = s->d_err;
-	// WGBV_TILE=1 selects the fused tile kernel (bv_tile.cu) for graphs with bounded reference chains.  It moves the
-	// algorithmic minimum of bytes but, as measured on B200 (profiles/), its block-wide barriers make it slower than
-	// the level-synchronous kernels on graphs with long rows, so it is opt-in for now.
-	const char *tl = getenv("WGBV_TILE");
-	s->force_levels = !(tl && tl[0] == '1');
+	// WGBV_FUSED=0 keeps every decode on the level-synchronous kernels (the general path: unbounded chains, node ids
+	// beyond 32 bits); by default graphs with bounded chains take the one-pass tile kernel (bv_fused.cu).
+	const char *fu = getenv("WGBV_FUSED");
+	s->use_fused = !(fu && fu[0] == '0');
 	const char *sf = getenv("WGBV_SPLIT_FRONT");
 	s->front_in_extras = !(sf && sf[0] == '1');
-	const char *fl = getenv("WGBV_FUSED_LEVELS");
-	s->fused_levels = fl && fl[0] == '1';
 	g->streams++;
 	*out = s;
 	return WGBV_OK;
@@ -473,7 +489,7 @@ extern "C" void wgbv_stream_destroy(wgbv_stream *s) {
 	if (s->stream) cudaStreamSynchronize(s->stream);
 	for (DevBuf *b : {&s->t_pairs[0], &s->t_pairs[1], &s->t_indeg, &s->t_counts, &s->t_pos}) b->release();
 	for (DevBuf *b : {&s->deg, &s->ref, &s->depth, &s->rp, &s->scan_state, &s->ticket, &s->halo, &s->levels, &s->list, &s->col,
-	                  &s->rowptr, &s->ids, &s->batch, &s->heavy_rows, &s->heavy_sorted, &s->heavy_cls, &s->heavy_counters, &s->tile_scratch, &s->level_pos, &s->row_info, &s->c_node, &s->c_dst, &s->c_parent, &s->c_deg, &s->c_isq, &s->c_level,
+	                  &s->rowptr, &s->ids, &s->batch, &s->heavy_rows, &s->heavy_sorted, &s->heavy_cls, &s->heavy_counters, &s->tile_done, &s->level_pos, &s->row_info, &s->c_node, &s->c_dst, &s->c_parent, &s->c_deg, &s->c_isq, &s->c_level,
 	                  &s->c_len, &s->c_arcs, &s->c_row0, &s->c_soff, &s->c_store})
 		b->release();
 	for (auto &sl : s->slot) {
@@ -498,15 +514,33 @@ extern "C" void wgbv_stream_destroy(wgbv_stream *s) {
 
 static int error_from_bits(wgbv_stream *s, uint32_t e);
 
-// Reads and clears the sticky error word; maps it onto a status code.
+static int decode_general(wgbv_stream *s, int64_t from, int64_t to, int64_t *d_rowptr, int64_t *d_col, uint64_t col_capacity, bool trust_maxref);
+
+// Reads and clears the sticky error word; maps it onto a status code.  A decode of the fused kernel that met something
+// only the general path handles (ERR_FUSED_FALLBACK: a reference chain longer than the properties promise, a slow
+// tile at the start of a range that needs halo rows) is rerun here, on the general path, before anything is reported.
 static int collect_errors(wgbv_stream *s) {
 	uint32_t *h = (uint32_t *)(s->h_pin + 8);
-	CU(cudaMemcpyAsync(h, s->d_err, 4, cudaMemcpyDeviceToHost, s->stream));
-	CU(cudaStreamSynchronize(s->stream));
-	const uint32_t e = h[0];
-	if (!e) return WGBV_OK;
-	CU(cudaMemsetAsync(s->d_err, 0, 4, s->stream));
-	return error_from_bits(s, e);
+	for (int attempt = 0;; attempt++) {
+		CU(cudaMemcpyAsync(h, s->d_err, 12, cudaMemcpyDeviceToHost, s->stream));
+		CU(cudaStreamSynchronize(s->stream));
+		const uint32_t e = h[0];
+		if (!s->fused_pending.empty()) s->last_slow_tiles = h[2];
+		if (!e) { s->fused_pending.clear(); return WGBV_OK; }
+		CU(cudaMemsetAsync(s->d_err, 0, 4, s->stream));
+		if ((e & (ERR_FUSED_FALLBACK | ERR_FUSED_DEEP)) && !s->fused_pending.empty() && attempt == 0) {
+			const std::vector<wgbv_stream::FusedCall> calls = s->fused_pending;
+			s->fused_pending.clear();
+			for (const auto &c : calls) {
+				s->fused_fallbacks++;
+				const int rc = decode_general(s, c.from, c.to, c.d_rowptr, c.d_col, c.col_capacity, !(e & ERR_FUSED_DEEP));
+				if (rc) return rc;
+			}
+			continue;
+		}
+		s->fused_pending.clear();
+		return error_from_bits(s, e & ~(ERR_FUSED_FALLBACK | ERR_FUSED_DEEP));
+	}
 }
 
 static int error_from_bits(wgbv_stream *s, uint32_t e) {
@@ -550,6 +584,7 @@ struct Prepared {
 	uint32_t max_depth = 0;
 	bool have_depth = false;
 	const int64_t *rp = nullptr;
+	bool no_walk = false;         // true: the depths come from k_depth whatever the properties say
 	int64_t *front_rp = nullptr;  // not null: stages 1 and 2 have NOT run; k_extras does them itself and writes the row pointers here
 };
 
@@ -574,10 +609,12 @@ static int compute_depth(wgbv_stream *s, int64_t from, Prepared &P) {
 	return WGBV_OK;
 }
 
-static int prepare(wgbv_stream *s, int64_t from, int64_t to, int64_t *d_rowptr, Prepared &P) {
+static int prepare(wgbv_stream *s, int64_t from, int64_t to, int64_t *d_rowptr, Prepared &P, bool trust_maxref = true) {
 	wgbv_graph *g = s->g;
 	const Launch L = s->launch();
-	P.lo = halo_start(g, from);
+	// (a file whose chains are longer than its properties say: every row the handle holds may be needed)
+	P.lo = trust_maxref ? halo_start(g, from) : g->avail_lo;
+	P.no_walk = !trust_maxref;
 	P.cnt = to - P.lo;
 	P.halo_n = from - P.lo;
 	if (P.cnt >= (int64_t)0xfffffff0ll) return fail(WGBV_EARG, "a single decode call is limited to 2^32-16 nodes; split the range");
@@ -632,6 +669,7 @@ static int decode_rows(wgbv_stream *s, int64_t from, int64_t to, Prepared &P, in
 	const Launch L = s->launch();
 	int rc;
 	if ((uint64_t)P.arcs > col_capacity) return fail(WGBV_EARG, "col_capacity (%llu) is smaller than the %lld arcs of [%lld, %lld)", (unsigned long long)col_capacity, (long long)P.arcs, (long long)from, (long long)to);
+	if (P.cnt <= 0 || to <= from) return WGBV_OK;  // nothing to decode (the row pointers have been written)
 	RangeDev R;
 	R.lo = P.lo;
 	R.from = from;
@@ -644,35 +682,18 @@ static int decode_rows(wgbv_stream *s, int64_t from, int64_t to, Prepared &P, in
 	R.halo = s->halo.as<int64_t>();
 	R.col_capacity = col_capacity;
 	R.info = nullptr;
-	// Bounded reference chains: the fused tile kernel decodes everything on chip in one launch.  The
-	// level-synchronous kernels below remain the general path (unbounded chains, tiles that fit nowhere).
-	if (g->halo_nodes >= 0 && g->halo_nodes <= TILE_MAX_HALO && !s->force_levels) {
-		TileDev T;
-		const int blocks = g->sm_count * 3;
-		T.scratch_cap = 1u << 16;
-		if ((rc = s->tile_scratch.ensure((size_t)blocks * T.scratch_cap * 8))) return rc;
-		T.scratch = s->tile_scratch.as<int64_t>();
-		T.halo = (int32_t)g->halo_nodes;
-		T.fallback = s->d_err + 2;
-		CU(cudaMemsetAsync(T.fallback, 0, 4, s->stream));
-		if (launch_tile(L, s->dev, g->def_codes, R, T, blocks)) return fail(WGBV_ECUDA, "launch of the tile kernel failed: %s", cudaGetErrorString(cudaGetLastError()));
-		uint32_t *hf = (uint32_t *)(s->h_pin + 9);
-		CU(cudaMemcpyAsync(hf, T.fallback, 4, cudaMemcpyDeviceToHost, s->stream));
-		cudaEventRecord(s->ev[4], s->stream);
-		s->ev_valid = true;
-		CU(cudaStreamSynchronize(s->stream));
-		if (!*hf) return WGBV_OK;
-	}
 	// Shallow chains (max_ref_count <= 8, the usual case): no separate depth pass -- the level-list kernels walk the
 	// chains themselves.  Otherwise (or if a chain turns out longer than the properties promise) k_depth runs first.
-	bool walk = !P.have_depth && g->halo_nodes >= 0 && g->props.max_ref_count <= 8;
+	bool walk = !P.have_depth && !P.no_walk && g->halo_nodes >= 0 && g->props.max_ref_count <= 8;
+	// (max_ref_count <= 0 promises that no row has a reference; with a window the stream may still hold some: check)
+	if (walk && g->props.window_size > 0 && g->props.max_ref_count <= 0) walk = false;
 	if (!walk && !P.have_depth && (rc = compute_depth(s, from, P))) return rc;
 	if ((rc = s->halo.ensure((size_t)std::max<int64_t>(P.halo_arcs, 1) * 8)) || (rc = s->depth.ensure((size_t)std::max<int64_t>(P.cnt, 1) * 4))) return rc;
 	R.depth = walk ? nullptr : s->depth.as<uint32_t>();
 	R.halo = s->halo.as<int64_t>();
 	if ((rc = s->row_info.ensure((size_t)std::max<int64_t>(P.cnt, 1) * sizeof(RowInfo)))) return rc;
 	R.info = s->row_info.as<RowInfo>();
-	// rows with >= 64 extras go through a global, class-sorted list: at most total_arcs / 64 of them
+	// rows with >= 128 extras go through a global, class-sorted list: at most total_arcs / 128 of them (sized for 64)
 	HeavyDev H;
 	const size_t hcap = (size_t)((P.arcs + P.halo_arcs) / 64 + 1);
 	if ((rc = s->heavy_rows.ensure(hcap * 4)) || (rc = s->heavy_sorted.ensure(hcap * 4)) || (rc = s->heavy_cls.ensure(hcap)) ||
@@ -684,18 +705,6 @@ static int decode_rows(wgbv_stream *s, int64_t from, int64_t to, Prepared &P, in
 	H.counters = s->heavy_counters.as<unsigned long long>();
 	uint32_t nlev = walk ? (uint32_t)std::max(g->props.max_ref_count, 0) : P.max_depth;
 	uint32_t *deep = s->d_err + 3;
-	// Shallow chains, opt-in (WGBV_FUSED_LEVELS=1): all levels in one launch (k_copy_fused), with the depths from
-	// k_extras' own walk when there was no depth pass.  It moves a third of the DRAM bytes of the per-level launches
-	// over ordered lists below but is not faster yet (profiles/r01_notes.md), so the lists remain the default.
-	const bool fused = nlev > 0 && nlev <= 8 && s->fused_levels;
-	if (fused) {
-		CU(cudaMemsetAsync(deep, 0, 4, s->stream));
-		if (walk) {
-			R.depth_out = s->depth.as<uint32_t>();
-			R.walk_levels = nlev;
-			R.deep = deep;
-		}
-	}
 	if (P.front_rp) {
 		R.deg_w = s->deg.as<uint32_t>();
 		R.ref_w = s->ref.as<uint8_t>();
@@ -705,28 +714,7 @@ static int decode_rows(wgbv_stream *s, int64_t from, int64_t to, Prepared &P, in
 	}
 	launch_extras(L, s->dev, g->def_codes, R, H);
 	R.depth = s->depth.as<uint32_t>();
-	R.depth_out = nullptr;
 	R.rp_w = nullptr;
-	if (fused) {
-		const uint32_t tiles = copy_fused_tiles(P.cnt);
-		if ((rc = s->levels.ensure((size_t)tiles * 4))) return rc;
-		CU(cudaMemsetAsync(s->levels.as<uint32_t>(), 0, (size_t)tiles * 4, s->stream));
-		CU(cudaMemsetAsync(s->ticket.as<uint32_t>(), 0, 4, s->stream));
-		launch_copy_fused(L, s->dev, g->def_codes, R, nlev, s->ticket.as<uint32_t>(), s->levels.as<uint32_t>(), deep);
-		if (walk) {
-			PeekArgs pk;
-			pk.add(deep, 4);
-			launch_peek(L, pk, s->d_pin + 10);
-			CU(cudaStreamSynchronize(s->stream));
-			if (s->h_pin[10]) {
-				// a chain longer than max_ref_count: the properties lied (or the file is malformed) and the fused kernel has
-				// done nothing; take the general route
-				walk = false;
-				if ((rc = compute_depth(s, from, P))) return rc;
-				nlev = P.max_depth;
-			} else nlev = 0;
-		} else nlev = 0;
-	}
 	for (int attempt = 0; attempt < 2 && nlev > 0 && nlev <= 8; attempt++) {
 		// shallow chains: ordered lists of the rows of every level
 		const size_t nblocks = (size_t)((P.cnt + 2047) / 2048);
@@ -784,24 +772,22 @@ static int decode_rows(wgbv_stream *s, int64_t from, int64_t to, Prepared &P, in
 	return WGBV_OK;
 }
 
-extern "C" int wgbv_decode_csr(wgbv_stream *s, int64_t from, int64_t to, int64_t *d_rowptr, int64_t *d_col, uint64_t col_capacity) {
-	clear_error();
-	if (!s || !d_rowptr || (!d_col && col_capacity)) return fail(WGBV_EARG, "null argument");
-	CU(cudaSetDevice(s->g->device));
-	int rc = check_range(s->g, from, to);
-	if (rc) return rc;
+// The level-synchronous path for [from, to): valid for every graph the library opens.
+static int decode_general(wgbv_stream *s, int64_t from, int64_t to, int64_t *d_rowptr, int64_t *d_col, uint64_t col_capacity, bool trust_maxref) {
+	int rc;
 	Prepared P;
 	wgbv_graph *g = s->g;
-	// The usual case -- bounded, shallow reference chains and a range that needs no halo -- runs without the separate
-	// header and scan launches and without the read-back of the arc count: k_extras does stages 1 and 2 for its own
-	// tiles (RangeDev::rp_w) and the capacity is checked on the device.  WGBV_SPLIT_FRONT=1 keeps the separate stages.
-	if (s->front_in_extras && to > from && halo_start(g, from) == from && g->halo_nodes >= 0 && g->props.max_ref_count <= 8 &&
-	    s->force_levels && !s->fused_levels && to - from < (int64_t)0xfffffff0ll) {
+	// Bounded, shallow reference chains and a range that needs no halo run without the separate header and scan
+	// launches and without the read-back of the arc count: k_extras does stages 1 and 2 for its own tiles
+	// (RangeDev::rp_w) and the capacity is checked on the device.  WGBV_SPLIT_FRONT=1 keeps the separate stages.
+	if (trust_maxref && s->front_in_extras && to > from && halo_start(g, from) == from && g->halo_nodes >= 0 && g->props.max_ref_count <= 8 &&
+	    !(g->props.window_size > 0 && g->props.max_ref_count <= 0) && to - from < (int64_t)0xfffffff0ll) {
 		P.lo = from;
 		P.cnt = to - from;
 		P.halo_n = 0;
 		P.halo_arcs = 0;
-		P.arcs = (int64_t)std::min<uint64_t>(col_capacity, (uint64_t)INT64_MAX / 16);  // an upper bound: sizes the scratch
+		// an upper bound on the arcs of the range: sizes the scratch of the heavy rows (never more than the whole graph has)
+		P.arcs = (int64_t)std::min<uint64_t>(col_capacity, (uint64_t)std::max<int64_t>(g->props.arcs, 0));
 		P.rp = d_rowptr;
 		P.front_rp = d_rowptr;
 		const size_t c = (size_t)P.cnt;
@@ -811,8 +797,76 @@ extern "C" int wgbv_decode_csr(wgbv_stream *s, int64_t from, int64_t to, int64_t
 		for (int i = 0; i < 4; i++) cudaEventRecord(s->ev[i], s->stream);  // (stages 1-2 have no time of their own here)
 		return decode_rows(s, from, to, P, d_col, col_capacity);
 	}
-	if ((rc = prepare(s, from, to, d_rowptr, P))) return rc;
+	if ((rc = prepare(s, from, to, d_rowptr, P, trust_maxref))) return rc;
 	return decode_rows(s, from, to, P, d_col, col_capacity);
+}
+
+// One pass of the fused tile kernel over [from, to) (bv_fused.cu); asynchronous, no read-back.
+static bool fused_applies(const wgbv_stream *s) {
+	const wgbv_graph *g = s->g;
+	return s->use_fused && g->fused_rows > 0;
+}
+
+static int decode_fused(wgbv_stream *s, int64_t from, int64_t to, int64_t *d_rowptr, int64_t *d_col, uint64_t col_capacity) {
+	wgbv_graph *g = s->g;
+	int rc;
+	FusedDev F;
+	F.from = from;
+	F.to = to;
+	F.halo = (int32_t)g->halo_nodes;
+	F.tile_rows = g->fused_rows;
+	const int64_t ntiles = (to - from + F.tile_rows - 1) / F.tile_rows;
+	if (ntiles >= (int64_t)0x7fffffff) return fail(WGBV_EARG, "a single decode call is limited to 2^31 tiles; split the range");
+	F.ntiles = (uint32_t)ntiles;
+	if ((rc = s->scan_state.ensure((size_t)ntiles * 8)) || (rc = s->ticket.ensure(64)) || (rc = s->tile_done.ensure((size_t)ntiles * 4))) return rc;
+	F.rowptr = d_rowptr;
+	F.col = d_col;
+	F.col_capacity = col_capacity;
+	F.tile_state = s->scan_state.as<uint64_t>();
+	F.ticket = s->ticket.as<uint32_t>();
+	F.slow_count = s->d_err + 2;
+	F.tile_done = s->tile_done.as<uint32_t>();
+	for (int i = 0; i < 4; i++) cudaEventRecord(s->ev[i], s->stream);
+	CU(cudaMemsetAsync(F.tile_state, 0, (size_t)ntiles * 8, s->stream));
+	CU(cudaMemsetAsync(F.ticket, 0, 64, s->stream));
+	CU(cudaMemsetAsync(F.slow_count, 0, 4, s->stream));
+	const int e = launch_fused(s->launch(), s->dev, g->def_codes, F, g->sm_count);
+	if (e) return fail(WGBV_ECUDA, "launch of the fused tile kernel failed: %s", cudaGetErrorString((cudaError_t)e));
+	cudaEventRecord(s->ev[4], s->stream);
+	s->ev_valid = true;
+	s->fused_pending.push_back({from, to, d_rowptr, d_col, col_capacity});
+	s->last_tiles = F.ntiles;
+	const cudaError_t le = cudaGetLastError();
+	if (le != cudaSuccess) return fail(WGBV_ECUDA, "kernel launch failed: %s", cudaGetErrorString(le));
+	return WGBV_OK;
+}
+
+extern "C" int wgbv_decode_csr(wgbv_stream *s, int64_t from, int64_t to, int64_t *d_rowptr, int64_t *d_col, uint64_t col_capacity) {
+	clear_error();
+	if (!s || !d_rowptr || (!d_col && col_capacity)) return fail(WGBV_EARG, "null argument");
+	CU(cudaSetDevice(s->g->device));
+	int rc = check_range(s->g, from, to);
+	if (rc) return rc;
+	if (s->fused_pending.size() >= 16) {
+		// many decodes in flight whose outcome nobody has asked for: read it before the list of possible reruns grows
+		if ((rc = collect_errors(s))) return rc;
+	}
+	if (to == from) {
+		CU(cudaMemsetAsync(d_rowptr, 0, 8, s->stream));  // rowptr[0] = 0: an empty range has no other output
+		return WGBV_OK;
+	}
+	if (fused_applies(s)) return decode_fused(s, from, to, d_rowptr, d_col, col_capacity);
+	return decode_general(s, from, to, d_rowptr, d_col, col_capacity, true);
+}
+
+extern "C" int wgbv_fused_stats(wgbv_stream *s, uint64_t out[4]) {
+	clear_error();
+	if (!s || !out) return fail(WGBV_EARG, "null argument");
+	out[0] = s->last_tiles;
+	out[1] = s->last_slow_tiles;
+	out[2] = s->fused_fallbacks;
+	out[3] = fused_applies(s) ? 1 : 0;
+	return WGBV_OK;
 }
 
 extern "C" int wgbv_last_stage_ms(wgbv_stream *s, float out[5]) {
@@ -834,6 +888,21 @@ extern "C" int wgbv_decode_csr_host(wgbv_stream *s, int64_t from, int64_t to, in
 	if (rc) return rc;
 	const int64_t cnt = to - from;
 	if ((rc = s->rowptr.ensure((size_t)(cnt + 1) * 8))) return rc;
+	if (h_col && cnt > 0 && fused_applies(s)) {
+		// one pass of the tile kernel into a device buffer of the caller's capacity; the arc count comes back with the row pointers
+		if ((rc = s->col.ensure((size_t)std::max<uint64_t>(col_capacity, 1) * 8))) return rc;
+		if ((rc = decode_fused(s, from, to, s->rowptr.as<int64_t>(), s->col.as<int64_t>(), col_capacity))) return rc;
+		if ((rc = collect_errors(s))) return rc;
+		CU(cudaMemcpyAsync(h_rowptr, s->rowptr.as<int64_t>(), (size_t)(cnt + 1) * 8, cudaMemcpyDeviceToHost, s->stream));
+		CU(cudaStreamSynchronize(s->stream));
+		const int64_t arcs = h_rowptr[cnt];
+		if (arcs_out) *arcs_out = arcs;
+		if (arcs > 0) {
+			CU(cudaMemcpyAsync(h_col, s->col.as<int64_t>(), (size_t)arcs * 8, cudaMemcpyDeviceToHost, s->stream));
+			CU(cudaStreamSynchronize(s->stream));
+		}
+		return WGBV_OK;
+	}
 	Prepared P;
 	if ((rc = prepare(s, from, to, s->rowptr.as<int64_t>(), P))) return rc;
 	if (arcs_out) *arcs_out = P.arcs;
