@@ -46,15 +46,10 @@ static_assert(FTH == TPB, "block_bin_sort numbers items by TPB");
 #ifndef WGBV_FBLOCKS
 #define WGBV_FBLOCKS 4  // resident blocks per SM the register allocation aims at
 #endif
-#ifndef WGBV_FWARP
-#define WGBV_FWARP 32  // rows of at least this many successors are merged by a whole warp (measured: 128 -> 14.3 ms, 48 -> 12.6 ms, 32 -> 12.0 ms per 2e7 nodes)
-#endif
-static constexpr uint32_t FWARP = WGBV_FWARP;
 static constexpr int FRC = WGBV_FRC;
 static constexpr int FBW = WGBV_FBW;
 static constexpr uint32_t FLEVELS = 8;  // longest reference chain the kernel follows
-static constexpr int FCLS = 16;         // sort classes per level: 2 for warp rows, 14 for lane rows
-static constexpr int FCLS_WARP = 2;
+static constexpr int FCLS = 16;         // sort classes per level, see fused_class()
 static_assert(FLEVELS * FCLS <= NBUCKETS, "level x class must fit the sort buckets");
 static_assert(FRC < 65536, "copied / extra counts of a tile row are kept in 16 bits");
 
@@ -85,14 +80,17 @@ __device__ __forceinline__ void cp_async16_f(void *smem_dst, const void *gmem_sr
 	asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gmem_src));
 }
 
-__device__ __forceinline__ int fused_class(uint32_t d, bool warp_row) {
-	if (warp_row) return d >= 512 ? 0 : 1;
-	int c;
-	if (d >= 48) c = d >= 96 ? 0 : d >= 64 ? 1 : 2;
-	else if (d >= 24) c = d >= 40 ? 3 : d >= 32 ? 4 : 5;
-	else if (d >= 8) c = d >= 20 ? 6 : d >= 16 ? 7 : d >= 12 ? 8 : 9;
-	else c = d >= 6 ? 10 : d >= 4 ? 11 : d == 3 ? 12 : 13;
-	return FCLS_WARP + c;
+// How a row with a reference is merged, by its outdegree d (masked: its reference row has at most 128 successors and
+// d <= 256, so the copy blocks are held as a mask of copied positions):
+//   class 0       not masked: a whole warp, from the block codes (row_copy_warp)
+//   class 1       64 <= d <= 256: 32 lanes by merge path (group_merge<32>)
+//   class 2       16 <= d < 64: 8 lanes by merge path (group_merge<8>), four rows per warp
+//   classes 3..15 d < 16: one lane per row, rows of (nearly) one length per warp (row_merge_lean)
+__device__ __forceinline__ int fused_class(uint32_t d, bool masked) {
+	if (!masked) return 0;
+	if (d >= 64) return 1;
+	if (d >= 16) return 2;
+	return 3 + (d >= 3 ? 15 - (int)d : 12);
 }
 
 // Outdegree and reference of row x (readOutdegree / readReference, BVG:654-661, 692-703) with k_header's checks.
@@ -313,7 +311,7 @@ __global__ void __launch_bounds__(FTH, WGBV_FBLOCKS) k_fused(GraphDev g, FusedDe
 		ncop = h.ncopied;
 		nextra = h.d - h.ncopied;
 		if (rf) {
-			masked = d < FWARP && dref <= 128;
+			masked = d <= 256 && dref <= 128;
 			S.m0[tid] = masked ? h.cmask[0] : h.blocks_pos;
 			S.m1[tid] = masked ? h.cmask[1] : ((uint64_t)h.ncopied | (uint64_t)h.bc << 32);
 		}
@@ -375,17 +373,18 @@ __global__ void __launch_bounds__(FTH, WGBV_FBLOCKS) k_fused(GraphDev g, FusedDe
 	// ---- copy blocks, one depth level after the other (rows sorted by level, then work class)
 	bucket[0] = -1;
 	if (needed && rf && ncop) {
-		bucket[0] = (int)(depth - 1) * FCLS + fused_class(d, !masked);
+		bucket[0] = (int)(depth - 1) * FCLS + fused_class(d, masked);
 		atomicMax(&S.max_depth, depth);
 	}
 	uint32_t ncopy;
 	block_bin_sort<1>(bucket, S.hist, S.order, &ncopy);  // (its first barrier also ends the extras phase)
 	const uint32_t max_depth = S.max_depth;
 	for (uint32_t l = 1; l <= max_depth; l++) {
-		const uint32_t s0 = S.hist[(l - 1) * FCLS], sw = S.hist[(l - 1) * FCLS + FCLS_WARP], s1 = S.hist[l * FCLS];
-		// long rows and rows without a mask: one warp per row
+		const uint32_t *hb = S.hist + (l - 1) * FCLS;
+		const uint32_t c0 = hb[0], c1 = hb[1], c2 = hb[2], c3 = hb[3], c16 = hb[FCLS];
+		// rows without a mask: one warp per row, from the block codes
 #pragma unroll 1
-		for (uint32_t t = s0 + warp; t < sw; t += FTH / 32) {
+		for (uint32_t t = c0 + warp; t < c1; t += FTH / 32) {
 			const int id = S.order[t];
 			const int y = id - (int)S.ref[id];
 			const uint32_t nc = (uint32_t)S.m1[id];
@@ -395,18 +394,34 @@ __global__ void __launch_bounds__(FTH, WGBV_FBLOCKS) k_fused(GraphDev g, FusedDe
 			row_copy_warp<DEF>(g, r, (const E *)(S.rows + S.rowoff[y]), S.deg[y], (const E *)(dst + nc), dst, S.deg[id], (uint32_t)(S.m1[id] >> 32), nc);
 		}
 		__syncwarp();
-		// the others: one lane per row, 32 rows of one class per warp, merged from the mask
+		// long masked rows: 32 lanes per row
 #pragma unroll 1
-		for (uint32_t tb = sw + (tid & ~31u); tb < s1; tb += FTH) {
+		for (uint32_t t = c1 + warp; t < c2; t += FTH / 32) {
+			const int id = S.order[t];
+			const int y = id - (int)S.ref[id];
+			group_merge<32, E>(g, true, (const E *)(S.rows + S.rowoff[y]), S.m0[id], S.m1[id], S.rows + S.rowoff[id], S.deg[id], S.ncopied[id], lane);
+		}
+		// medium rows: 8 lanes per row, four rows per warp
+#pragma unroll 1
+		for (uint32_t tb = c2 + warp * 4; tb < c3; tb += (FTH / 32) * 4) {
+			const uint32_t t = tb + (lane >> 3);
+			const bool active = t < c3;
+			const int id = active ? S.order[t] : 0;
+			const int y = id - (int)S.ref[id];
+			group_merge<8, E>(g, active, (const E *)(S.rows + S.rowoff[y]), S.m0[id], S.m1[id], S.rows + S.rowoff[id], S.deg[id], S.ncopied[id], lane & 7u);
+		}
+		// short rows: one lane per row
+#pragma unroll 1
+		for (uint32_t tb = c3 + (tid & ~31u); tb < c16; tb += FTH) {
 			const uint32_t t = tb + lane;
-			const bool active = t < s1;
+			const bool active = t < c16;
 			const unsigned mask = __ballot_sync(FULL_MASK, active);
 			if (active) {
 				const int id = S.order[t];
 				const int y = id - (int)S.ref[id];
 				const uint32_t nc = S.ncopied[id];
 				E *dst = S.rows + S.rowoff[id];
-				row_copy_masked<E>(g, (const E *)(S.rows + S.rowoff[y]), S.m0[id], S.m1[id], (const E *)(dst + nc), dst, S.deg[id] - nc, mask);
+				row_merge_lean<E>(g, (const E *)(S.rows + S.rowoff[y]), S.m0[id], S.m1[id], (const E *)(dst + nc), dst, S.deg[id] - nc, mask);
 			}
 		}
 		__syncthreads();

@@ -28,23 +28,6 @@ static constexpr unsigned FULL_MASK = 0xffffffffu;
 // a prefetch may name any address: it never faults
 __device__ __forceinline__ void prefetch_l1(const void *p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
 
-// bits [from, from + len) of a 64-bit mask (what falls beyond bit 63 is dropped)
-__device__ __forceinline__ uint64_t bit_span(uint64_t from, uint64_t len) {
-	if (from >= 64 || len == 0) return 0;
-	return (len >= 64 ? ~0ull : (1ull << len) - 1ull) << from;
-}
-
-// sets bits [from, from + len) of a 128-bit mask (what falls beyond bit 127 is dropped)
-__device__ __forceinline__ void mask_span(uint64_t (&m)[2], uint64_t from, uint64_t len) {
-	m[0] |= bit_span(from, len);
-	if (len > 128) len = 128;
-	const uint64_t end = from + len;
-	if (end > 64 && from < 128) {
-		const uint64_t hf = from > 64 ? from - 64 : 0;
-		m[1] |= bit_span(hf, end - 64 - hf);
-	}
-}
-
 struct RowHead {
 	uint32_t d;        // outdegree
 	uint32_t rf;       // reference (0: none)
@@ -55,9 +38,18 @@ struct RowHead {
 	bool ok;           // false: inconsistent counts (an error bit has been raised); d and ncopied are zeroed
 };
 
+// bits [0, t) of a 128-bit mask
+__device__ __forceinline__ void mask_prefix(uint64_t t, uint64_t &lo, uint64_t &hi) {
+	lo = t >= 64 ? ~0ull : (1ull << t) - 1ull;
+	hi = t <= 64 ? 0ull : t >= 128 ? ~0ull : (1ull << (t - 64)) - 1ull;
+}
+
 // The part of a row's head that follows the reference: block count and blocks (summed, and turned into the mask of
 // copied positions); leaves the reader after the last block (at the interval section).  d and rf are the row's
 // outdegree and reference, dref the outdegree of the reference row (only used when rf > 0).  BVG:1017-1033.
+// The blocks alternate copy / skip starting with copy, so the copied positions are the XOR of the prefixes [0, c_k)
+// over the running block ends c_k -- plus [0, dref) when the count is even, i.e. when the tail after the last block
+// is copied too.  (Positions from 128 on are dropped: the mask is complete only when dref <= 128.)
 template <int DEF, class RD>
 __device__ __forceinline__ void row_blocks(const GraphDev &g, RD &r, uint32_t d, uint32_t rf, uint32_t dref, RowHead &h) {
 	h.d = d;
@@ -72,22 +64,28 @@ __device__ __forceinline__ void row_blocks(const GraphDev &g, RD &r, uint32_t d,
 		if (bc > (uint64_t)dref + 1) { h.ok = false; bc = 0; }
 		h.bc = (uint32_t)bc;
 		h.blocks_pos = r.tell();
-		uint64_t copied = 0, total = 0;
+		uint64_t copied = 0, total = 0, m0 = 0, m1 = 0;
 		for (uint32_t i = 0; i < h.bc; i++) {
 			const uint64_t b = rd_block<DEF>(r, g) + (i ? 1 : 0);
-			if (!(i & 1)) {
-				copied += b;
-				mask_span(h.cmask, total, b);
-			}
+			if (!(i & 1)) copied += b;
 			total += b;
+			uint64_t lo, hi;
+			mask_prefix(total, lo, hi);
+			m0 ^= lo;
+			m1 ^= hi;
 		}
 		if (total > dref) h.ok = false;
 		else if (!(h.bc & 1)) {
 			copied += dref - total;
-			mask_span(h.cmask, total, dref - total);
+			uint64_t lo, hi;
+			mask_prefix(dref, lo, hi);
+			m0 ^= lo;
+			m1 ^= hi;
 		}
 		if (copied > d) h.ok = false;
 		h.ncopied = (uint32_t)copied;
+		h.cmask[0] = m0;
+		h.cmask[1] = m1;
 	}
 	if (!h.ok) {
 		raise(g, ERR_DEGREE);
@@ -150,6 +148,62 @@ template <> struct ElemTraits<uint32_t> {
 	static constexpr uint32_t MAX = 0xffffffffu;
 };
 
+template <class T> struct IsPosReader { static constexpr bool value = false; };
+template <> struct IsPosReader<PosReader> { static constexpr bool value = true; };
+
+// The pure gap loop of row_extras_core for zeta_3 codes in staged words: the stream runs through a 64-bit register
+// window (the next 32..63 bits, left-aligned), so the chain from one code to the next is count-leading-zeros, two
+// shifts, an add and the window shift -- no load on it -- and the word that tops the window up is loaded ahead.
+// Codes of more than 32 bits (gaps of 2^24 and more) leave through the generic reader.  Lock step as the loop it
+// replaces: every lane of `mask` calls it; on return r stands after the last code read.  (Measured: four codes per
+// vote instead of one made the step slower, 8.9 -> 11.4 ms per 2e7 nodes: the lanes of a warp stop at different counts.)
+template <class V, class E>
+__device__ __forceinline__ void gap_loop_zeta3(PosReader &r, V &res, uint32_t &o, uint32_t nextra, E *out, unsigned mask) {
+	const uint32_t *w = r.base;
+	const uint32_t lastw = r.last + 1;
+	uint32_t idx = r.p >> 5;
+	idx = idx < r.last ? idx : r.last;
+	uint32_t sh = r.p & 31u;
+	uint64_t win = (((uint64_t)w[idx] << 32) | w[idx + 1]) << sh;
+	uint32_t have = 64u - sh;  // valid bits in win: 32..64 at the top of every iteration
+	uint32_t nx = idx + 2;     // next word to load
+	for (; __any_sync(mask, o < nextra); o++) {
+		if (o < nextra) {
+			const uint32_t t = (uint32_t)(win >> 32);
+			const int h = __clz((int)t);
+			if (h <= 7) {
+				const uint32_t x1 = t << (h + 1);
+				const bool longer = (x1 >> 30) != 0;  // the two leading payload bits: not both zero = one more bit follows
+				const uint32_t m2 = x1 >> (29 - 3 * h);
+				const uint32_t val = longer ? m2 - 1u : (m2 >> 1) + (1u << (3 * h)) - 1u;
+				const uint32_t len = 4u * (uint32_t)h + 3u + (longer ? 1u : 0u);
+				res = (V)(res + 1 + (V)val);
+				out[o] = (E)res;
+				win <<= len;
+				have -= len;
+				const uint32_t wi = nx < lastw ? nx : lastw;
+				const uint32_t nw32 = w[wi];
+				if (have < 32u) {
+					win |= (uint64_t)nw32 << (32u - have);
+					have += 32u;
+					nx++;
+				}
+			} else {
+				r.p = nx * 32u - have;
+				res = (V)(res + 1 + (V)r.zeta(3));
+				out[o] = (E)res;
+				idx = r.p >> 5;
+				idx = idx < r.last ? idx : r.last;
+				sh = r.p & 31u;
+				win = (((uint64_t)w[idx] << 32) | w[idx + 1]) << sh;
+				have = 64u - sh;
+				nx = idx + 2;
+			}
+		}
+	}
+	r.p = nx * 32u - have;
+}
+
 // The merge of intervals (cursor ri, `ic` of them) and residuals (cursor r, `nres` of them) into out[0..nextra).
 // Warp-synchronous: every lane of `mask` must call it (nextra == 0: no work).  Three parts: a merging loop that runs
 // while some lane of the warp still has interval material, then (one site, all lanes together) the first residual of
@@ -196,11 +250,15 @@ __device__ __forceinline__ void row_extras_core(const GraphDev &g, RDI &ri, RDR 
 			out[o++] = (E)res;
 		}
 	}
-	for (; __any_sync(mask, o < nextra); o++) {
-		if (WIN::enabled && __any_sync(mask, win.low(r))) win.refill(r, mask);
-		if (o < nextra) {
-			res = (V)(res + 1 + (V)rd_residual<DEF>(r, g));
-			out[o] = (E)res;
+	if constexpr (DEF == 2 && IsPosReader<RDR>::value && !WIN::enabled) {
+		gap_loop_zeta3(r, res, o, nextra, out, mask);
+	} else {
+		for (; __any_sync(mask, o < nextra); o++) {
+			if (WIN::enabled && __any_sync(mask, win.low(r))) win.refill(r, mask);
+			if (o < nextra) {
+				res = (V)(res + 1 + (V)rd_residual<DEF>(r, g));
+				out[o] = (E)res;
+			}
 		}
 	}
 }
@@ -305,6 +363,107 @@ __device__ __forceinline__ void row_copy_masked(const GraphDev &g, const E *src,
 			}
 		}
 	}
+}
+
+// The same merge for rows kept in shared memory, written so that an iteration is one straight instruction stream:
+// both candidates are loaded (a shared-memory load costs less than a divergent branch), the smaller one is stored,
+// and the cursor that supplied it advances by predication.  Ends when the copied successors are exhausted: extras
+// after the last copied one are in place already.  Every lane of `mask` must call it (m == m1 == 0: no work).
+template <class E>
+__device__ __forceinline__ void row_merge_lean(const GraphDev &g, const E *src, uint64_t m, uint64_t m1, const E *ext, E *dst, uint32_t ne,
+                                               unsigned mask) {
+	const E EMAX = ElemTraits<E>::MAX;
+	uint32_t ei = 0, base = 0;
+	if (!m) { m = m1; m1 = 0; base = 64; }
+	bool dup = false;
+	while (__any_sync(mask, m != 0)) {
+		if (m) {
+			const uint32_t pos = base + (uint32_t)__ffsll((long long)m) - 1u;
+			const E c = src[pos];
+			const E e = ei < ne ? ext[ei] : EMAX;
+			const bool take_e = e < c;
+			dup |= e == c;
+			*dst++ = take_e ? e : c;
+			ei += take_e ? 1u : 0u;
+			const uint64_t mn = take_e ? m : (m & (m - 1));
+			const bool sw = mn == 0;
+			m = sw ? m1 : mn;
+			m1 = sw ? 0ull : m1;
+			base = sw ? 64u : base;
+		}
+	}
+	if (dup) raise(g, ERR_NOT_SORTED);
+}
+
+// The merge of a row's copied successors with its extras by G lanes (G = 8 or 32) through merge path: no lane walks
+// the whole row.  The row lives in shared memory: src is the finished reference row (at most 128 successors, (m0, m1) the
+// mask of its copied positions), dst[0..d) the row's slot with the extras waiting in its tail dst[nc..d).
+//   1. the copied successors are compacted into dst[0..nc), every lane taking 128 / G positions of the mask;
+//   2. lane `part` produces outputs [part * q, part * q + q), q = ceil(d / G) <= 8: a binary search finds how many of
+//      the first part * q outputs come from the copied run, a short serial merge fills the lane's registers;
+//   3. after all lanes have read, they store.
+// The whole warp must call it together (lanes without a row: active = false); rows of different groups do not interact.
+// MaskedLongIterator.java:67-100 + MergedLongIterator.java:54-92 of the reference, as one data-parallel step.
+template <int G, class E>
+__device__ __forceinline__ void group_merge(const GraphDev &g, bool active, const E *src, uint64_t m0, uint64_t m1, E *dst, uint32_t d, uint32_t nc,
+                                            uint32_t part) {
+	static_assert(G == 8 || G == 32, "group sizes with 128 / G positions inside one mask word");
+	constexpr uint32_t W = 128 / G;
+	const E EMAX = ElemTraits<E>::MAX;
+	if (active) {
+		const uint32_t lo_bit = part * W;
+		const uint64_t word = lo_bit < 64 ? m0 : m1;
+		uint32_t slice = (uint32_t)(word >> (lo_bit & 63u)) & ((1u << W) - 1u);
+		const uint32_t before = lo_bit < 64 ? (uint32_t)__popcll(m0 & ((1ull << lo_bit) - 1ull))
+		                                    : (uint32_t)(__popcll(m0) + __popcll(m1 & ((1ull << (lo_bit - 64)) - 1ull)));
+		E *o = dst + before;
+		while (slice) {
+			const uint32_t b = (uint32_t)__ffs((int)slice) - 1u;
+			slice &= slice - 1u;
+			*o++ = src[lo_bit + b];
+		}
+	}
+	__syncwarp();
+	E outv[8];
+	uint32_t k0 = 0, cnt = 0;
+	if (active) {
+		const uint32_t q = (d + G - 1) / G;
+		const uint32_t ne = d - nc;
+		k0 = part * q;
+		if (k0 < d) {
+			cnt = d - k0 < q ? d - k0 : q;
+			const E *A = dst, *B = dst + nc;
+			// i: outputs before k0 that come from A
+			uint32_t lo = k0 > ne ? k0 - ne : 0u, hi = k0 < nc ? k0 : nc;
+			while (lo < hi) {
+				const uint32_t i = (lo + hi) >> 1, j = k0 - i;
+				if (j > 0 && B[j - 1] > A[i]) lo = i + 1;
+				else hi = i;
+			}
+			uint32_t i = lo, j = k0 - lo;
+			E a = i < nc ? A[i] : EMAX, b = j < ne ? B[j] : EMAX;
+			bool dup = false;
+#pragma unroll
+			for (int t = 0; t < 8; t++) {
+				if ((uint32_t)t < cnt) {
+					const bool ta = a < b;
+					dup |= a == b;
+					outv[t] = ta ? a : b;
+					i += ta ? 1u : 0u;
+					j += ta ? 0u : 1u;
+					const E na = i < nc ? A[i] : EMAX, nb = j < ne ? B[j] : EMAX;
+					a = ta ? na : a;
+					b = ta ? b : nb;
+				}
+			}
+			if (dup) raise(g, ERR_NOT_SORTED);
+		}
+	}
+	__syncwarp();
+#pragma unroll
+	for (int t = 0; t < 8; t++)
+		if ((uint32_t)t < cnt) dst[k0 + t] = outv[t];
+	__syncwarp();
 }
 
 // position of the n-th (0-based) set bit of m; n < popc(m)
@@ -422,9 +581,18 @@ __device__ __forceinline__ void row_copy_warp(const GraphDev &g, RD &r, const E 
 // every lane the index and the value its first code starts from, and a last parse writes the successors.  All 32
 // lanes pass the same arguments; proto is a reader on the stream (any position), [p0, p1) the bit range of the n codes.
 // BVG:902-954 (ResidualLongIterator) is what this replaces.
-static constexpr uint32_t COOP_SEG_MIN = 128, COOP_SEG_MAX = 4096;
+#ifndef WGBV_COOP_SEG
+#define WGBV_COOP_SEG 512
+#endif
+#ifndef WGBV_COOP_LONG
+#define WGBV_COOP_LONG 128
+#endif
+// Shortest segment: a misaligned zeta_3 parse of 16-bit codes falls in step after 112 bits on average (90 % within 260,
+// 99 % within 500: measured on the benchmark graph), and a lane that does not resynchronise inside its segment costs
+// the lanes after it another round.
+static constexpr uint32_t COOP_SEG_MIN = WGBV_COOP_SEG, COOP_SEG_MAX = 4096;
 // rows of at least this many residuals are decoded by a whole warp (rows with intervals only if they have at most 32)
-static constexpr uint32_t COOP_LONG = 64;
+static constexpr uint32_t COOP_LONG = WGBV_COOP_LONG;
 
 template <int DEF, class RD, class E>
 __device__ __forceinline__ void coop_residuals(const GraphDev &g, const RD &proto, typename RD::pos_t p0, typename RD::pos_t p1, uint32_t n,
