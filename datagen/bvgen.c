@@ -348,6 +348,16 @@ static void gen_er(const bvg_model *m, int64_t x, lvec *out) {
 static void gen_copy(const bvg_model *m, int64_t x, int64_t split_start, lvec *const *ring, int cyc, lvec *out) {
 	uint64_t s = node_seed(m->seed, x);
 	out->n = 0;
+	if (m->giant_every > 0 && x % m->giant_every == m->giant_every / 2) {
+		/* a BigGraph-style giant row (slow/.../BVGraphSlowTest.java:30-96): giant_degree successors i * giant_stride */
+		lv_need(out, m->giant_degree);
+		for (int64_t i = 0; i < m->giant_degree; i++) {
+			const int64_t y = i * m->giant_stride;
+			if (y >= m->global_n) break;
+			out->a[out->n++] = y;
+		}
+		return;
+	}
 	if (u01(&s) < 0.05) return;
 	const double sigma = 1.0, mu = log(m->mean_degree) - 0.5 * sigma * sigma;
 	const double u1 = 1.0 - u01(&s), u2 = u01(&s);
@@ -578,13 +588,20 @@ bvg_job *bvg_run(const bvg_params *g, const bvg_model *m, int nsplits, int threa
 	if (J->m.global_n <= 0) J->m.global_n = J->m.first_node + J->m.n;
 	m = &J->m;
 	const int64_t n = m->n;
+	/* nsplits < 0: every split has exactly -nsplits nodes (the last one what is left), so that parts of one large graph
+	 * generated separately agree on where the compression splits are */
+	int64_t per_exact = 0;
+	if (nsplits < 0) {
+		per_exact = -(int64_t)nsplits;
+		nsplits = (int)((n + per_exact - 1) / per_exact);
+	}
 	if (nsplits < 1) nsplits = 1;
 	if ((int64_t)nsplits > n && n > 0) nsplits = (int)n;
 	if (n == 0) nsplits = 1;
 	if (threads < 1) threads = 1;
 	J->nsplits = nsplits;
 	J->splits = (split_t *)calloc((size_t)nsplits, sizeof(split_t));
-	const int64_t per = (n + nsplits - 1) / nsplits;
+	const int64_t per = per_exact ? per_exact : (n + nsplits - 1) / nsplits;
 	for (int k = 0; k < nsplits; k++) {
 		J->splits[k].from = m->first_node + (per * k < n ? per * k : n);
 		J->splits[k].to = m->first_node + (per * (k + 1) < n ? per * (k + 1) : n);

@@ -177,11 +177,15 @@ def erdos_renyi(n, p, seed=1, params=None, nsplits=64, threads=0, seg_nodes=0):
 
 
 def copy_model(n, seed=2, mean_degree=20.0, p_ref=0.7, p_keep=0.8, p_run=0.3, far_frac=0.05, near_scale=1e4,
-               max_degree=10000, params=None, nsplits=256, threads=0, seg_nodes=0, first_node=0, global_n=0):
-    """Copy-model web-like graph; with first_node/global_n one part [first_node, first_node+n) of a larger graph."""
+               max_degree=10000, params=None, nsplits=256, threads=0, seg_nodes=0, first_node=0, global_n=0,
+               giant_every=0, giant_degree=1 << 20, giant_stride=4):
+    """Copy-model web-like graph; with first_node/global_n one part [first_node, first_node+n) of a larger graph.
+    giant_every > 0: node x with x % giant_every == giant_every // 2 gets giant_degree successors i * giant_stride instead
+    (the giant rows of the reference's slow test, BVGraphSlowTest.java:30-96)."""
     params = params or make_params()
     m = Model(model=MODEL_COPY, n=n, first_node=first_node, global_n=global_n, seed=seed, mean_degree=mean_degree, p_ref=p_ref, p_keep=p_keep, p_run=p_run,
-              far_frac=far_frac, near_scale=near_scale, max_degree=max_degree)
+              far_frac=far_frac, near_scale=near_scale, max_degree=max_degree, giant_every=giant_every, giant_degree=giant_degree,
+              giant_stride=giant_stride)
     return _collect(lib().bvg_run(C.byref(params), C.byref(m), nsplits, _threads(threads), seg_nodes), params, n, seg_nodes)
 
 

@@ -293,8 +293,8 @@ WGBV_API uint64_t wgbv_kernel_launches(const wgbv_stream *s);
 /* Accounting of the one-pass tile kernel (csrc/bv_fused.cu; no counterpart in the reference): out[0] = tiles of the last
  * wgbv_decode_csr that took it, out[1] = how many of them did not fit shared memory and were decoded by the slow-tile
  * kernel (valid after wgbv_stream_sync), out[2] = decodes of this stream that had to be rerun on the level-synchronous
- * path, out[3] = 1 if decodes of this handle take the tile kernel at all (bounded reference chains, node ids below
- * 2^32 - 1, WGBV_FUSED=0 not set). */
+ * path, out[3] = 1 if decodes of this handle take the tile kernel (WGBV_FUSED=1 in the environment, bounded reference
+ * chains, node ids below 2^32 - 1). */
 WGBV_API int wgbv_fused_stats(wgbv_stream *s, uint64_t out[4]);
 
 /* Algorithmic bytes of decoding [from, to) (compressed bits in + Elias-Fano bits touched + int64 row pointers

@@ -455,6 +455,47 @@ done:
 	return rc;
 }
 
+/* Batched random access on all host threads, the way SpeedTest -r calls successors(x) for random x
+ * (src/it/unimi/dsi/big/webgraph/test/SpeedTest.java:95-108): thread t takes ids[t], ids[t + threads], ...
+ * Returns the number of arcs read (or a negative error). */
+typedef struct {
+	const bvo_params *g; const uint8_t *graph; uint64_t graph_bytes; const uint64_t *offsets;
+	const int64_t *ids; int64_t k; int t, threads; int64_t arcs; int64_t rc;
+} ra_t;
+
+static void *ra_main(void *p) {
+	ra_t *w = (ra_t *)p;
+	for (int64_t q = w->t; q < w->k; q += w->threads) {
+		const int64_t x = w->ids[q];
+		if (x < 0 || x >= w->g->nodes) { w->rc = BVO_EINDEX; return NULL; }
+		int64_t *l = NULL, len = 0;
+		const int err = successors_rec(w->g, w->graph, w->graph_bytes, w->offsets, x, &l, &len, 0);
+		free(l);
+		if (err) { w->rc = err; return NULL; }
+		w->arcs += len;
+	}
+	return NULL;
+}
+
+int64_t bvo_random_access(const bvo_params *g, const uint8_t *graph, uint64_t graph_bytes, const uint64_t *offsets,
+                          const int64_t *ids, int64_t k, int threads) {
+	if (threads < 1) threads = 1;
+	if (threads > 256) threads = 256;
+	pthread_t th[256];
+	ra_t w[256];
+	for (int t = 0; t < threads; t++) {
+		w[t] = (ra_t){g, graph, graph_bytes, offsets, ids, k, t, threads, 0, BVO_OK};
+		pthread_create(&th[t], NULL, ra_main, &w[t]);
+	}
+	int64_t arcs = 0, rc = BVO_OK;
+	for (int t = 0; t < threads; t++) {
+		pthread_join(th[t], NULL);
+		if (w[t].rc) rc = w[t].rc;
+		arcs += w[t].arcs;
+	}
+	return rc ? rc : arcs;
+}
+
 /* Analysis helper: shape[6 * (x - from) ..] = ncopied, blocks, intervals, interval elements, residuals, reference of
  * every node of [from, to) (sequential scan).  shape must hold 6 * (to - from + 1) entries. */
 int64_t bvo_row_shapes(const bvo_params *g, const uint8_t *graph, uint64_t graph_bytes, const uint64_t *offsets,

@@ -61,6 +61,8 @@ def lib():
         L.bvo_decode_split.restype = C.c_int64
         L.bvo_decode_labels.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_uint64, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p]
         L.bvo_decode_labels.restype = C.c_int64
+        L.bvo_random_access.argtypes = [C.POINTER(Params), C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_int64, C.c_int]
+        L.bvo_random_access.restype = C.c_int64
         L.bvo_read_code.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64), C.c_int, C.c_int]
         L.bvo_read_code.restype = C.c_uint64
         del u8p, u64p, i64p
@@ -165,6 +167,14 @@ class OracleGraph:
         if r < 0:
             raise _err(r)
         return out[:r]
+
+    def random_access(self, ids, threads=1):
+        """successors(x) for every x of ids on `threads` host threads (SpeedTest -r); returns the arcs read."""
+        ids = np.ascontiguousarray(ids, dtype=np.int64)
+        r = lib().bvo_random_access(C.byref(self.p), self.graph.ctypes.data, self.graph.size, self._off(), ids.ctypes.data, ids.size, threads)
+        if r < 0:
+            raise _err(r)
+        return r
 
     def decode_range(self, lo=0, hi=None, threads=1, want_col=True):
         """Sequential (threads == 1, nodeIterator) or split (splitNodeIterators) scan of [lo, hi): (deg, col)."""

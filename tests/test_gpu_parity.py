@@ -202,6 +202,23 @@ def test_giant_rows_and_zero_degree_nodes():
         assert not rp.any() and c.size == 0
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("fused", ["0", "1"])
+def test_giant_rows_in_a_web_like_graph(monkeypatch, fused):
+    """BASELINE config 5's shape in small: a sparse copy-model graph with a few rows of tens of thousands of successors
+    (residuals for stride 4, one long interval for stride 1; other rows reference them), decoded by a whole warp each."""
+    monkeypatch.setenv("WGBV_FUSED", fused)
+    for stride, gd in ((4, 60000), (1, 150000), (7, 30000)):
+        e = bg.copy_model(250000, seed=50 + stride, mean_degree=3.3, nsplits=4, giant_every=100000, giant_degree=gd, giant_stride=stride)
+        deg, col = oracle_of(e).decode_range()
+        assert deg.max() >= 30000
+        with gpu_of(e) as g:
+            rp, c = g.decodeToCSR()
+            assert np.array_equal(rp, rowptr_of(deg)) and np.array_equal(c, col)
+            rp, c = g.decodeToCSR(49990, 150010)
+            assert np.array_equal(c, col[rowptr_of(deg)[49990]:rowptr_of(deg)[150010]])
+
+
 def test_tree_grid():
     """BVGraphTest.testCompression grid (BVGraphTest.java:52-103), a sample of it."""
     from test_datagen import tree_csr
@@ -266,9 +283,10 @@ def _similar_rows_graph(n, centers, width, size, seed):
     return rowptr, np.concatenate(rows)
 
 
-def test_tiles_that_do_not_fit_shared_memory():
+def test_tiles_that_do_not_fit_shared_memory(monkeypatch):
     """The one-pass tile kernel's slow tiles: rows a few thousand (or tens of thousands of) successors long that reference
     each other across tile boundaries are decoded by k_slow in global memory; ranges that start next to them."""
+    monkeypatch.setenv("WGBV_FUSED", "1")
     for size, centers in ((4000, (256, 1000, 1536)), (40000, (512, 2048 + 256))):
         n = 3000
         rowptr, col = _similar_rows_graph(n, centers, 12, size, size)
@@ -309,9 +327,10 @@ def test_fused_and_general_paths_agree(monkeypatch, cnr_basename, cnr_golden):
                 assert g.fusedStats()["reruns"] == 0
 
 
-def test_chains_longer_than_the_properties_promise():
+def test_chains_longer_than_the_properties_promise(monkeypatch):
     """A file whose maxrefcount understates its chains (the reference's decoder never looks at maxrefcount): the tile
     kernel notices, and the decode is rerun on the general path without trusting the property."""
+    monkeypatch.setenv("WGBV_FUSED", "1")
     e = bg.copy_model(20000, seed=99, mean_degree=20, params=bg.make_params(window=7, maxref=6, minint=4), nsplits=1)
     odeg, ocol = oracle_of(e).decode_range()
     for lie in (1, 0):

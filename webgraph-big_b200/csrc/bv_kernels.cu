@@ -412,6 +412,14 @@ template <>
 __device__ __forceinline__ void tile_reader<TileReader>(TileReader &r, const GraphDev &, const ExtrasSmem &S, uint64_t pos) {
 	r.init_words(S.bits, S.nw, (uint32_t)(pos - (S.wbase << 5)));
 }
+#ifndef WGBV_STAGED_READER
+#define WGBV_STAGED_READER PosReader  // the reader of a staged tile: position only, the words are loaded at every peek
+#endif
+using StagedReader = WGBV_STAGED_READER;
+template <>
+__device__ __forceinline__ void tile_reader<PosReader>(PosReader &r, const GraphDev &, const ExtrasSmem &S, uint64_t pos) {
+	r.init_words(S.bits, S.nw, (uint32_t)(pos - (S.wbase << 5)));
+}
 
 // Stages 1 and 2 for the rows of a tile, inside k_extras (RangeDev::rp_w): outdegree and reference of every row, then
 // the exclusive scan of the outdegrees -- inside the tile through shared memory, across tiles by decoupled look-back
@@ -657,7 +665,7 @@ __global__ void __launch_bounds__(TPB) k_extras(GraphDev g, RangeDev R, HeavyDev
 		if (threadIdx.x == 0) { S.wbase = w0; S.nw = (uint32_t)nw; }
 	}
 	__syncthreads();
-	if (staged) extras_tile<DEF, TileReader, FUSED>(g, R, H, S, base, count, rp_from);
+	if (staged) extras_tile<DEF, StagedReader, FUSED>(g, R, H, S, base, count, rp_from);
 	else extras_tile<DEF, BitReader, FUSED>(g, R, H, S, base, count, rp_from);
 }
 
@@ -714,6 +722,7 @@ __global__ void __launch_bounds__(TPB) k_heavy_scatter(HeavyDev H) {
 static constexpr int HW_WORDS = 32;   // words of stream per lane and refill
 static constexpr int HW_PITCH = 35;   // row pitch in words (odd multiple: the 32 lanes hit 32 banks)
 static constexpr uint32_t HW_LOW = 29;  // refill when a reader's prefetched word index reaches this
+static constexpr uint32_t GIANT_ROW = 4096;  // residuals from which a row is decoded by a whole warp
 
 struct HeavyWindow {
 	static constexpr bool enabled = true;
@@ -777,8 +786,8 @@ __global__ void __launch_bounds__(TPB) k_extras_heavy(GraphDev g, RangeDev R, He
 		const unsigned mask = __ballot_sync(FULL_MASK, active);
 		// heads and interval sections straight from global memory (short), then the residuals through the window
 		int64_t i = 0;
-		uint32_t nextra = 0, ic = 0, nres = 0, ncopied = 0;
-		uint64_t int_pos = 0, res_pos = 0;
+		uint32_t nextra = 0, ic = 0, ic0 = 0, nres = 0, ncopied = 0;
+		uint64_t int_pos = 0, res_pos = 0, cnt_pos = 0;
 		BitReader rh;
 		if (active) {
 			i = H.sorted[t];
@@ -788,11 +797,40 @@ __global__ void __launch_bounds__(TPB) k_extras_heavy(GraphDev g, RangeDev R, He
 			row_head<DEF>(g, rh, rf ? R.deg[i - rf] : 0, h);
 			nextra = h.d - h.ncopied;
 			ncopied = h.ncopied;
+			cnt_pos = rh.tell();
 			row_intervals(g, rh, nextra, ic, int_pos, nres);
+			ic0 = ic;
 			res_pos = rh.tell();
 			if (ic) rh.seek(int_pos);  // rh becomes the interval cursor
 		}
 		__syncwarp();
+		// Giant rows (the reference's slow test has rows of 2^30 successors, BVGraphSlowTest.java:30-96): one lane would need
+		// seconds, so the whole warp decodes them one after the other, every lane a segment of the list (coop_residuals).
+		{
+			const bool giant = active && nres >= GIANT_ROW && ic <= 32;
+			unsigned gm = __ballot_sync(FULL_MASK, giant);
+			while (gm) {
+				const int src = __ffs((int)gm) - 1;
+				gm &= gm - 1;
+				const int64_t gi = __shfl_sync(FULL_MASK, i, src);
+				const uint64_t g_res = __shfl_sync(FULL_MASK, res_pos, src);
+				const uint32_t g_nres = __shfl_sync(FULL_MASK, nres, src), g_nextra = __shfl_sync(FULL_MASK, nextra, src);
+				const uint32_t g_ncop = __shfl_sync(FULL_MASK, ncopied, src), g_ic = __shfl_sync(FULL_MASK, ic0, src);
+				const int64_t gx = R.lo + gi;
+				int64_t *ext = row_slot(R, gi, rp_from) + g_ncop;
+				BitReader proto;
+				proto.init(g, ef_get(g, gx));
+				coop_residuals<DEF>(g, proto, g_res, ef_get(g, gx + 1), g_nres, gx, ext + (g_nextra - g_nres));
+				if (g_ic) {
+					__threadfence_block();
+					__syncwarp();
+					// (coop_intervals_merge starts at the interval count: one gamma code before the first interval)
+					coop_intervals_merge(g, proto, __shfl_sync(FULL_MASK, cnt_pos, src), gx, ext, g_nextra, g_nres);
+				}
+				__syncwarp();
+			}
+			if (giant) nextra = 0;  // done: nothing left for the lock-step loops below
+		}
 		if (DEF == 0) {
 			// run-time codings include Golomb / unary residuals, whose codes can be longer than any window: read them
 			// straight from global memory
@@ -950,7 +988,11 @@ __global__ void __launch_bounds__(TPB) k_copy_level(GraphDev g, RangeDev R, uint
 			const uint64_t m0 = S.a[id], m1 = S.b[id];
 			const uint32_t ncopied = (uint32_t)(__popcll(m0) + __popcll(m1));
 			int64_t *dst = row_slot(R, k, rp_from);
+#ifdef WGBV_LEAN_COPY
+			row_merge_lean<int64_t>(g, row_slot(R, k - rf, rp_from), m0, m1, dst + ncopied, dst, R.deg[k] - ncopied, mask);
+#else
 			row_copy_masked(g, row_slot(R, k - rf, rp_from), m0, m1, dst + ncopied, dst, R.deg[k] - ncopied, mask);
+#endif
 		}
 	}
 }

@@ -76,7 +76,7 @@ struct wgbv_stream {
 	DevBuf t_pairs[2], t_indeg, t_counts, t_pos;  // wgbv_transpose_csr
 	DevBuf heavy_rows, heavy_sorted, heavy_cls, heavy_counters, level_pos, row_info, tile_done;
 	bool front_in_extras = true;  // false: always run header and scan as their own launches (WGBV_SPLIT_FRONT=1)
-	bool use_fused = true;        // false: never use the one-pass tile kernel (WGBV_FUSED=0): the level-synchronous path only
+	bool use_fused = false;       // true: bulk decodes take the one-pass tile kernel where it applies (WGBV_FUSED=1)
 	// The decodes of the fused kernel whose outcome has not been read yet: if one of them reported ERR_FUSED_FALLBACK
 	// (something only the general path handles), the call that collects the errors reruns them on the general path
 	// (the error word does not say which one it was; rerunning a good one gives the same result).
@@ -472,10 +472,11 @@ extern "C" int wgbv_stream_create(wgbv_graph *g, void *cuda_stream, wgbv_stream 
 	for (auto &e : s->ev) cudaEventCreate(&e);
 	s->dev = g->dev;
 	s->dev.err = s->d_err;
-	// WGBV_FUSED=0 keeps every decode on the level-synchronous kernels (the general path: unbounded chains, node ids
-	// beyond 32 bits); by default graphs with bounded chains take the one-pass tile kernel (bv_fused.cu).
+	// WGBV_FUSED=1 sends bulk decodes of graphs with bounded chains through the one-pass tile kernel (bv_fused.cu).  It
+	// moves the algorithmic minimum of bytes and needs no scratch arrays, but as measured on B200 (profiles/r02_notes.md)
+	// it is still slower than the level-synchronous kernels (8.9 vs 7.5 ms per 2e7 nodes), so those stay the default.
 	const char *fu = getenv("WGBV_FUSED");
-	s->use_fused = !(fu && fu[0] == '0');
+	s->use_fused = fu && fu[0] == '1';
 	const char *sf = getenv("WGBV_SPLIT_FRONT");
 	s->front_in_extras = !(sf && sf[0] == '1');
 	g->streams++;
