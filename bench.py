@@ -481,6 +481,15 @@ def run_config(args, torch, dist, wg, rank, local_rank, world, dev, stream, thre
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_per_step = float(t.item()) / args.steps
     stage_ms = stage_acc / args.steps
+    # per rank: device ms per step, halo rows decoded redundantly, nodes of the shard (rank 0 has no halo: the cost of the
+    # halo path shows as the difference between its time and the others')
+    mine_info = torch.tensor([ms / args.steps, float(sh.halo), float(n)], dtype=torch.float64, device=dev)
+    info = torch.zeros(world * 3, dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_gather_into_tensor(info, mine_info)
+    else:
+        info.copy_(mine_info)
+    info = info.cpu().reshape(world, 3).tolist()
 
     # parity at full size: the checksum of the decoded CSR must equal the one the generator took before encoding
     arcs = int(d_rowptr[n].item())
@@ -663,10 +672,11 @@ def run_config(args, torch, dist, wg, rank, local_rank, world, dev, stream, thre
                        "compressed_bytes_rank0": int(sh.graph.size), "bits_per_arc": e.graph_bits / max(e.arcs, 1),
                        "encoder_statistics_rank0": stats_of(e),
                        "l2": "inputs and outputs exceed L2 (compressed stream and 8 B/arc output are GBs per step)",
-                       "parallelism": (f"{world} contiguous shards of one graph, boundaries inside compression splits; every rank decodes the "
-                                       f"{sh.halo} rows before its shard as halo (no data-path collective); all-gather of arc counts") if world > 1
+                       "parallelism": (f"{world} contiguous shards of one graph, boundaries inside compression splits; every rank but the first decodes the "
+                                       f"{int(max(r[1] for r in info))} rows before its shard as halo (no data-path collective); all-gather of arc counts") if world > 1
                        else "1 shard; no collective",
-                       "halo_nodes": sh.halo, "shard_first_node_rank0": first},
+                       "halo_nodes": int(max(r[1] for r in info)), "halo_nodes_by_rank": [int(r[1]) for r in info],
+                       "ms_per_step_by_rank": [r[0] for r in info], "nodes_by_rank": [int(r[2]) for r in info]},
             "roofline": roofline, "e2e": e2e, "e2e_narrow": e2e_narrow, "transpose": transpose, "labels": labels, "c1": c1, "c3": c3, "c4": c4,
             "cpu_baseline": cpu, "gpu_launches": int(launches), "clocks": clocks,
             "verified": bool(verified), "fused": fused_stats, "global_row_base_rank0": global_base, "generation_s": sh.gen_s, "load_s": load_s,
