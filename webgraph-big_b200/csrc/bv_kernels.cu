@@ -722,7 +722,8 @@ __global__ void __launch_bounds__(TPB) k_heavy_scatter(HeavyDev H) {
 static constexpr int HW_WORDS = 32;   // words of stream per lane and refill
 static constexpr int HW_PITCH = 35;   // row pitch in words (odd multiple: the 32 lanes hit 32 banks)
 static constexpr uint32_t HW_LOW = 29;  // refill when a reader's prefetched word index reaches this
-static constexpr uint32_t GIANT_ROW = 4096;  // residuals from which a row is decoded by a whole warp
+static constexpr uint32_t GIANT_ROW = 4096;   // residuals from which a row is decoded by a whole warp
+static constexpr uint32_t GIANT_ROW2 = 32768;  // ... and from which by GIANT_CHUNKS warps (k_giant_*)
 
 struct HeavyWindow {
 	static constexpr bool enabled = true;
@@ -807,7 +808,26 @@ __global__ void __launch_bounds__(TPB) k_extras_heavy(GraphDev g, RangeDev R, He
 		// Giant rows (the reference's slow test has rows of 2^30 successors, BVGraphSlowTest.java:30-96): one lane would need
 		// seconds, so the whole warp decodes them one after the other, every lane a segment of the list (coop_residuals).
 		{
-			const bool giant = active && nres >= GIANT_ROW && ic <= 32;
+			bool giant = active && nres >= GIANT_ROW && ic <= 32;
+			if (giant && nres >= GIANT_ROW2 && H.giants) {
+				// the largest ones: many warps each, after this kernel
+				const unsigned long long slot = atomicAdd(&H.counters[129], 1ull);
+				if (slot < (unsigned long long)GIANT_MAX) {
+					GiantRow gr;
+					gr.x = R.lo + i;
+					gr.p0 = res_pos;
+					gr.p1 = ef_get(g, R.lo + i + 1);
+					gr.cnt_pos = cnt_pos;
+					gr.ext = row_slot(R, i, rp_from) + ncopied;
+					gr.nres = nres;
+					gr.ne = nextra;
+					gr.ic = ic0;
+					gr.pad = 0;
+					H.giants[slot] = gr;
+					giant = false;
+					nextra = 0;
+				}
+			}
 			unsigned gm = __ballot_sync(FULL_MASK, giant);
 			while (gm) {
 				const int src = __ffs((int)gm) - 1;
@@ -853,10 +873,139 @@ __global__ void __launch_bounds__(TPB) k_extras_heavy(GraphDev g, RangeDev R, He
 	}
 }
 
+// ---- giant rows: GIANT_CHUNKS warps per row (see GiantRow)
+__device__ __forceinline__ void giant_chunk_range(const GiantRow &gr, int c, uint64_t &cs, uint64_t &ce) {
+	const uint64_t span = gr.p1 - gr.p0;
+	const uint64_t cb = ((span + GIANT_CHUNKS - 1) / GIANT_CHUNKS + 63) & ~63ull;
+	cs = gr.p0 + cb * (uint64_t)c;
+	ce = cs + cb;
+	if (cs > gr.p1) cs = gr.p1;
+	if (ce > gr.p1) ce = gr.p1;
+}
+
+template <int DEF>
+__global__ void __launch_bounds__(TPB) k_giant_scan(GraphDev g, HeavyDev H) {
+	const unsigned long long total = H.counters[129] < (unsigned long long)GIANT_MAX ? H.counters[129] : (unsigned long long)GIANT_MAX;
+	const int c = (int)(blockIdx.x * (TPB / 32) + (threadIdx.x >> 5));
+	for (unsigned long long gi = blockIdx.y; gi < total; gi += gridDim.y) {
+		const GiantRow gr = H.giants[gi];
+		uint64_t cs, ce;
+		giant_chunk_range(gr, c, cs, ce);
+		GiantChunk ch;
+		ch.entry = ch.exit = cs;
+		ch.total = ch.base = 0;
+		ch.count = ch.idx0 = 0;
+		if (cs < ce) {
+			BitReader proto;
+			proto.init(g, gr.p0);
+			// a code start at or after cs: parse from GIANT_LEAD bits before it (every lane the same codes)
+			uint64_t p = cs - gr.p0 > (uint64_t)GIANT_LEAD ? cs - GIANT_LEAD : gr.p0;
+			if (c != 0) {
+				BitReader r = proto;
+				r.seek(p);
+				while (p < cs) {
+					rd_residual<DEF>(r, g);
+					const uint64_t q = r.tell();
+					if (q <= p) break;
+					p = q;
+				}
+			} else p = gr.p0;
+			ch.entry = p;
+			uint32_t count;
+			int64_t tot;
+			uint64_t ex;
+			coop_residuals_ex<DEF, false>(g, proto, p, ce, 0xffffffffu, gr.x, (int64_t *)nullptr, 0u, (int64_t)0, false, count, tot, ex);
+			ch.count = count;
+			ch.total = tot;
+			ch.exit = ex > p ? ex : p;
+		}
+		if ((threadIdx.x & 31) == 0) H.gchunks[gi * GIANT_CHUNKS + c] = ch;
+	}
+}
+
+template <int DEF>
+__global__ void k_giant_fix(GraphDev g, HeavyDev H) {
+	const unsigned long long total = H.counters[129] < (unsigned long long)GIANT_MAX ? H.counters[129] : (unsigned long long)GIANT_MAX;
+	const unsigned lane = threadIdx.x & 31u;
+	for (unsigned long long gi = blockIdx.x; gi < total; gi += gridDim.x) {
+		const GiantRow gr = H.giants[gi];
+		BitReader proto;
+		proto.init(g, gr.p0);
+		// value the first gap builds on: the first code is a signed offset from x (BVG:917)
+		int64_t base;
+		{
+			BitReader r = proto;
+			const uint64_t code = rd_residual<DEF>(r, g);
+			base = gr.x + nat2int(code) - ((int64_t)code + 1);
+		}
+		uint64_t expect = gr.p0;
+		uint32_t idx = 0;
+		for (int c = 0; c < GIANT_CHUNKS; c++) {
+			GiantChunk ch = H.gchunks[gi * GIANT_CHUNKS + c];
+			uint64_t cs, ce;
+			giant_chunk_range(gr, c, cs, ce);
+			if (expect >= ce) {
+				// (nothing starts in this chunk)
+				ch.entry = ch.exit = expect;
+				ch.count = 0;
+				ch.total = 0;
+			} else if (ch.entry != expect || cs >= ce) {
+				// the lead-in had not fallen in step (or the chunk before ended late): scan again from the true start
+				uint32_t count;
+				int64_t tot;
+				uint64_t ex;
+				coop_residuals_ex<DEF, false>(g, proto, expect, ce, 0xffffffffu, gr.x, (int64_t *)nullptr, 0u, (int64_t)0, false, count, tot, ex);
+				ch.entry = expect;
+				ch.count = count;
+				ch.total = tot;
+				ch.exit = ex > expect ? ex : expect;
+			}
+			ch.idx0 = idx;
+			ch.base = base;
+			idx += ch.count;
+			base += ch.total;
+			expect = ch.exit;
+			if (lane == 0) H.gchunks[gi * GIANT_CHUNKS + c] = ch;
+		}
+		if (lane == 0 && idx != gr.nres) raise(g, ERR_DEGREE);
+	}
+}
+
+template <int DEF>
+__global__ void __launch_bounds__(TPB) k_giant_write(GraphDev g, HeavyDev H) {
+	const unsigned long long total = H.counters[129] < (unsigned long long)GIANT_MAX ? H.counters[129] : (unsigned long long)GIANT_MAX;
+	const int c = (int)(blockIdx.x * (TPB / 32) + (threadIdx.x >> 5));
+	for (unsigned long long gi = blockIdx.y; gi < total; gi += gridDim.y) {
+		const GiantRow gr = H.giants[gi];
+		const GiantChunk ch = H.gchunks[gi * GIANT_CHUNKS + c];
+		if (ch.count == 0) continue;
+		uint64_t cs, ce;
+		giant_chunk_range(gr, c, cs, ce);
+		BitReader proto;
+		proto.init(g, gr.p0);
+		uint32_t count;
+		int64_t tot;
+		uint64_t ex;
+		coop_residuals_ex<DEF, true>(g, proto, ch.entry, ce, gr.nres, gr.x, gr.ext + (gr.ne - gr.nres), ch.idx0, ch.base, false, count, tot, ex);
+	}
+}
+
+// the intervals of giant rows that have both (rare): one warp per row
+__global__ void k_giant_merge(GraphDev g, HeavyDev H) {
+	const unsigned long long total = H.counters[129] < (unsigned long long)GIANT_MAX ? H.counters[129] : (unsigned long long)GIANT_MAX;
+	for (unsigned long long gi = blockIdx.x; gi < total; gi += gridDim.x) {
+		const GiantRow gr = H.giants[gi];
+		if (!gr.ic) continue;
+		BitReader proto;
+		proto.init(g, gr.cnt_pos);
+		coop_intervals_merge(g, proto, gr.cnt_pos, gr.x, gr.ext, gr.ne, gr.nres);
+	}
+}
+
 void launch_extras(const Launch &L, const GraphDev &g, int def, const RangeDev &r, const HeavyDev &h) {
 	const int64_t count = r.hi - r.lo;
 	if (count <= 0) return;
-	if (h.rows) cudaMemsetAsync(h.counters, 0, 129 * sizeof(unsigned long long), L.stream);
+	if (h.rows) cudaMemsetAsync(h.counters, 0, 130 * sizeof(unsigned long long), L.stream);
 	const size_t smem = sizeof(ExtrasSmem);
 #define WGBV_LAUNCH_EXTRAS(D, F)                                                                              \
 	do {                                                                                                     \
@@ -895,6 +1044,16 @@ void launch_extras(const Launch &L, const GraphDev &g, int def, const RangeDev &
 	default: k_extras_heavy<0><<<148 * 8, TPB, 0, L.stream>>>(g, r, h);
 	}
 	WGBV_LAUNCHED(L);
+	if (!h.giants) return;
+	// giant rows, if any (the kernels read the count on the device and leave at once when there is none)
+	const dim3 gg(GIANT_CHUNKS / (TPB / 32), 32);
+	switch (def) {
+	case 2: k_giant_scan<2><<<gg, TPB, 0, L.stream>>>(g, h); k_giant_fix<2><<<32, 32, 0, L.stream>>>(g, h); k_giant_write<2><<<gg, TPB, 0, L.stream>>>(g, h); break;
+	case 1: k_giant_scan<1><<<gg, TPB, 0, L.stream>>>(g, h); k_giant_fix<1><<<32, 32, 0, L.stream>>>(g, h); k_giant_write<1><<<gg, TPB, 0, L.stream>>>(g, h); break;
+	default: k_giant_scan<0><<<gg, TPB, 0, L.stream>>>(g, h); k_giant_fix<0><<<32, 32, 0, L.stream>>>(g, h); k_giant_write<0><<<gg, TPB, 0, L.stream>>>(g, h);
+	}
+	k_giant_merge<<<32, 32, 0, L.stream>>>(g, h);
+	for (int q = 0; q < 4; q++) WGBV_LAUNCHED(L);
 }
 
 // stage 3b: the rows of one depth level.  With a list, a block takes CTILE list entries; without, it inspects CTILE

@@ -59,11 +59,35 @@ struct ChainDev {
 };
 
 // The global list of rows whose extras are too long to be decoded inside their tile (see bv_kernels.cu).
+// A giant row (tens of thousands of residuals and more: BVGraphSlowTest.java:30-96 has a row of 2^30 successors) is not
+// decoded by one warp but by GIANT_CHUNKS warps side by side: the bit range of its residuals is cut into that many
+// chunks, every warp finds a code start at the head of its chunk (a parse started GIANT_LEAD bits earlier has fallen in
+// step by then), counts its codes and sums their gaps (k_giant_scan); one warp per row checks that every chunk starts
+// where the one before it ended -- rescanning it if not -- and turns counts and sums into starting indices and values
+// (k_giant_fix); then the warps write (k_giant_write).
+struct GiantRow {
+	int64_t x;              // node id
+	uint64_t p0, p1;        // bit range of the residuals (relative to GraphDev::bit_base)
+	uint64_t cnt_pos;       // position of the interval count (only used when ic != 0)
+	int64_t *ext;           // the extras part of the row's slot (ne entries; the residuals go to its tail)
+	uint32_t nres, ne, ic, pad;
+};
+struct GiantChunk {
+	uint64_t entry, exit;   // first code starting in the chunk; first code starting after it
+	int64_t total, base;    // sum of (gap + 1) over the chunk's codes; value its first code builds on
+	uint32_t count, idx0;   // codes in the chunk; index of the first one
+};
+static constexpr int GIANT_MAX = 1024;     // giant rows per decode handled this way (more: decoded by one warp each)
+static constexpr int GIANT_CHUNKS = 256;
+static constexpr uint32_t GIANT_LEAD = 4096;
+
 struct HeavyDev {
 	uint32_t *rows;    // row indices (relative to RangeDev.lo) in arrival order; nullptr disables the heavy path
 	uint8_t *cls;      // class of each entry
 	uint32_t *sorted;  // row indices sorted by class, heaviest first
-	unsigned long long *counters;  // [0] entries, [1..64] per-class counts, [65..128] per-class cursors
+	unsigned long long *counters;  // [0] entries, [1..64] per-class counts, [65..128] per-class cursors, [129] giant rows
+	GiantRow *giants;      // GIANT_MAX entries (nullptr: giant rows are decoded by one warp each)
+	GiantChunk *gchunks;   // GIANT_MAX * GIANT_CHUNKS entries
 };
 
 // The fused tile kernel (bv_fused.cu): one pass over the bit stream, a tile of rows per block, everything on chip.

@@ -522,7 +522,13 @@ __device__ __forceinline__ void row_copy_warp(const GraphDev &g, RD &r, const E 
 			cmask = __ballot_sync(FULL_MASK, f && p < dref);
 			fresh = false;
 			if (kb + 32 >= dref && cmask == 0) break;  // malformed: announced copies that do not exist
-			if (cmask == 0) { kb += 32; fresh = true; continue; }
+			if (cmask == 0) {
+				// nothing copied in this window; a skip block that reaches far beyond it (a few successors taken from a giant
+				// reference row) is jumped over in one step
+				kb = (!bcopy && be > kb + 32) ? (be & ~31u) : kb + 32;
+				fresh = true;
+				continue;
+			}
 		}
 		// A: the copied elements of the window still to emit, compacted to lanes 0..nA-1
 		const unsigned nA = (unsigned)__popc(cmask);
@@ -594,21 +600,27 @@ static constexpr uint32_t COOP_SEG_MIN = WGBV_COOP_SEG, COOP_SEG_MAX = 4096;
 // rows of at least this many residuals are decoded by a whole warp (rows with intervals only if they have at most 32)
 static constexpr uint32_t COOP_LONG = WGBV_COOP_LONG;
 
-template <int DEF, class RD, class E>
-__device__ __forceinline__ void coop_residuals(const GraphDev &g, const RD &proto, typename RD::pos_t p0, typename RD::pos_t p1, uint32_t n,
-                                               int64_t x, E *out) {
+// The general form: decodes the codes that START in [p0, p1) -- p0 a true code start -- as the codes idx0, idx0 + 1, ... of
+// the row, the first of them building on the value `base` (first_code: p0 is the start of the whole list, whose
+// first code is a signed offset from x; base is then worked out here).  WRITE = false only counts: `count` codes, the
+// sum `total` of (gap + 1) over them, and `exit`, the start of the first code at or after p1.  nmax bounds the indices
+// written.  Giant rows are cut into chunks that whole warps scan, and later write, side by side (k_giant_*).
+template <int DEF, bool WRITE, class RD, class E>
+__device__ __forceinline__ void coop_residuals_ex(const GraphDev &g, const RD &proto, typename RD::pos_t p0, typename RD::pos_t p1, uint32_t nmax,
+                                                  int64_t x, E *out, uint32_t idx0, typename ElemTraits<E>::V base, bool first_code, uint32_t &count,
+                                                  typename ElemTraits<E>::V &total_out, typename RD::pos_t &exit_out) {
 	using V = typename ElemTraits<E>::V;
 	using P = typename RD::pos_t;
 	const unsigned lane = threadIdx.x & 31u;
-	P wstart = p0;      // true position of the first code not written yet
-	uint32_t done = 0;  // codes written
-	V base = (V)x;      // value the next code's gap is added to (set up by the first code, which is a signed offset from x)
-	// segment length: the whole list in one window when it is short, long segments (fewer rounds per bit) when it is huge
+	P wstart = p0;         // true position of the first code not handled yet
+	uint32_t done = idx0;  // index of that code
+	V acc = 0;
+	// segment length: the whole range in one window when it is short, long segments (fewer rounds per bit) when it is huge
 	const uint64_t span = p1 > p0 ? (uint64_t)(p1 - p0) : 0;
 	uint64_t sg = (span + 31) / 32;
 	sg = (sg + 31) & ~31ull;
 	const P seg = (P)(sg < COOP_SEG_MIN ? COOP_SEG_MIN : sg > COOP_SEG_MAX ? COOP_SEG_MAX : sg);
-	while (done < n && wstart < p1) {
+	while (wstart < p1 && (!WRITE || done < nmax)) {
 		const P seg_lo = wstart + seg * lane, seg_hi = seg_lo + seg;
 		const bool active = seg_lo < p1;
 		const P lim = seg_hi < p1 ? seg_hi : p1;
@@ -642,7 +654,7 @@ __device__ __forceinline__ void coop_residuals(const GraphDev &g, const RD &prot
 		if (!active) { cnt = 0; total = 0; }
 		// The row's first residual is a signed offset from x (BVG:917), the others are gaps (BVG:929).  The scans below
 		// treat every code as a gap; the starting value is chosen so that the first one comes out right all the same.
-		if (done == 0) {
+		if (first_code && done == 0) {
 			V b0 = 0;
 			if (lane == 0) {
 				RD r = proto;
@@ -664,27 +676,40 @@ __device__ __forceinline__ void coop_residuals(const GraphDev &g, const RD &prot
 		const uint32_t wcount = __shfl_sync(FULL_MASK, ci, 31);
 		const V wtotal = __shfl_sync(FULL_MASK, ti, 31);
 		// the last parse: write
-		if (cnt) {
+		if (WRITE && cnt) {
 			uint32_t idx = done + ci - cnt;
 			V val = base + (ti - total);
 			RD r = proto;
 			r.seek(entry);
 			for (uint32_t k = 0; k < cnt; k++) {
 				val += (V)rd_residual<DEF>(r, g) + 1;
-				if (idx < n) out[idx] = (E)val;
+				if (idx < nmax) out[idx] = (E)val;
 				idx++;
 			}
 		}
 		base += wtotal;
+		acc += wtotal;
 		done += wcount;
 		// the window ends where its last active lane's parse ended
 		const unsigned am = __ballot_sync(FULL_MASK, active);
 		const int last = 31 - __clz((int)am);
 		const P wend = __shfl_sync(FULL_MASK, exit, last);
-		if (wcount == 0 || wend <= wstart) break;  // malformed: no progress
+		if (wcount == 0 || wend <= wstart) { wstart = p1; break; }  // malformed: no progress
 		wstart = wend;
 	}
-	if (done < n) raise(g, ERR_DEGREE);  // the record holds fewer codes than announced
+	count = done - idx0;
+	total_out = acc;
+	exit_out = wstart;
+}
+
+template <int DEF, class RD, class E>
+__device__ __forceinline__ void coop_residuals(const GraphDev &g, const RD &proto, typename RD::pos_t p0, typename RD::pos_t p1, uint32_t n,
+                                               int64_t x, E *out) {
+	uint32_t count;
+	typename ElemTraits<E>::V total;
+	typename RD::pos_t exit;
+	coop_residuals_ex<DEF, true>(g, proto, p0, p1, n, x, out, 0u, (typename ElemTraits<E>::V)x, true, count, total, exit);
+	if (count < n) raise(g, ERR_DEGREE);  // the record holds fewer codes than announced
 }
 
 // The intervals of a row merged into its residuals by a whole warp (all lanes pass the same arguments).  ext[0..ne) is

@@ -74,7 +74,7 @@ struct wgbv_stream {
 	uint64_t launches = 0;
 	DevBuf deg, ref, depth, rp, scan_state, ticket, halo, levels, list, col, rowptr, ids, batch;
 	DevBuf t_pairs[2], t_indeg, t_counts, t_pos;  // wgbv_transpose_csr
-	DevBuf heavy_rows, heavy_sorted, heavy_cls, heavy_counters, level_pos, row_info, tile_done;
+	DevBuf heavy_rows, heavy_sorted, heavy_cls, heavy_counters, giants, gchunks, level_pos, row_info, tile_done;
 	bool front_in_extras = true;  // false: always run header and scan as their own launches (WGBV_SPLIT_FRONT=1)
 	bool use_fused = false;       // true: bulk decodes take the one-pass tile kernel where it applies (WGBV_FUSED=1)
 	// The decodes of the fused kernel whose outcome has not been read yet: if one of them reported ERR_FUSED_FALLBACK
@@ -490,7 +490,7 @@ extern "C" void wgbv_stream_destroy(wgbv_stream *s) {
 	if (s->stream) cudaStreamSynchronize(s->stream);
 	for (DevBuf *b : {&s->t_pairs[0], &s->t_pairs[1], &s->t_indeg, &s->t_counts, &s->t_pos}) b->release();
 	for (DevBuf *b : {&s->deg, &s->ref, &s->depth, &s->rp, &s->scan_state, &s->ticket, &s->halo, &s->levels, &s->list, &s->col,
-	                  &s->rowptr, &s->ids, &s->batch, &s->heavy_rows, &s->heavy_sorted, &s->heavy_cls, &s->heavy_counters, &s->tile_done, &s->level_pos, &s->row_info, &s->c_node, &s->c_dst, &s->c_parent, &s->c_deg, &s->c_isq, &s->c_level,
+	                  &s->rowptr, &s->ids, &s->batch, &s->heavy_rows, &s->heavy_sorted, &s->heavy_cls, &s->heavy_counters, &s->giants, &s->gchunks, &s->tile_done, &s->level_pos, &s->row_info, &s->c_node, &s->c_dst, &s->c_parent, &s->c_deg, &s->c_isq, &s->c_level,
 	                  &s->c_len, &s->c_arcs, &s->c_row0, &s->c_soff, &s->c_store})
 		b->release();
 	for (auto &sl : s->slot) {
@@ -698,12 +698,15 @@ static int decode_rows(wgbv_stream *s, int64_t from, int64_t to, Prepared &P, in
 	HeavyDev H;
 	const size_t hcap = (size_t)((P.arcs + P.halo_arcs) / 64 + 1);
 	if ((rc = s->heavy_rows.ensure(hcap * 4)) || (rc = s->heavy_sorted.ensure(hcap * 4)) || (rc = s->heavy_cls.ensure(hcap)) ||
-	    (rc = s->heavy_counters.ensure(129 * 8)))
+	    (rc = s->heavy_counters.ensure(130 * 8)) || (rc = s->giants.ensure(sizeof(GiantRow) * GIANT_MAX)) ||
+	    (rc = s->gchunks.ensure(sizeof(GiantChunk) * (size_t)GIANT_MAX * GIANT_CHUNKS)))
 		return rc;
 	H.rows = s->heavy_rows.as<uint32_t>();
 	H.sorted = s->heavy_sorted.as<uint32_t>();
 	H.cls = s->heavy_cls.as<uint8_t>();
 	H.counters = s->heavy_counters.as<unsigned long long>();
+	H.giants = s->giants.as<GiantRow>();
+	H.gchunks = s->gchunks.as<GiantChunk>();
 	uint32_t nlev = walk ? (uint32_t)std::max(g->props.max_ref_count, 0) : P.max_depth;
 	uint32_t *deep = s->d_err + 3;
 	if (P.front_rp) {
