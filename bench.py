@@ -280,6 +280,42 @@ def time_decode(torch, g, first, last, d_rowptr, d_col, cap, steps, warmup, extr
     return ev0.elapsed_time(ev1) / steps
 
 
+def pcie_probe(torch, dist, dev, world):
+    """What bounds the end-to-end leg: pinned device->host copies of 1 GiB on every rank AT THE SAME TIME (and the same
+    with a host->device copy beside each); GB/s per rank (slowest) and in total."""
+    nbytes = 1 << 30
+    d = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    h = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
+    d2 = torch.empty(nbytes // 4, dtype=torch.uint8, device=dev)
+    h2 = torch.empty(nbytes // 4, dtype=torch.uint8, pin_memory=True)
+    s2 = torch.cuda.Stream(device=dev)
+
+    def run(with_h2d, reps=3):
+        h.copy_(d, non_blocking=True)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            if with_h2d:
+                with torch.cuda.stream(s2):
+                    for _ in range(4):
+                        d2.copy_(h2, non_blocking=True)
+            h.copy_(d, non_blocking=True)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        t = torch.tensor([dt], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return reps * nbytes / float(t.item()) / 1e9
+
+    a, b = run(False), run(True)
+    del d, h, d2, h2
+    return {"d2h_gbs_per_rank_all_ranks_at_once": a, "d2h_gbs_total": a * world, "d2h_gbs_per_rank_with_h2d_beside": b,
+            "what": "1 GiB pinned device-to-host copies on all ranks at the same time (slowest rank); the e2e leg moves 8 B per arc this way"}
+
+
 def config_c1(torch, wg, dev, local_rank, stream):
     """BASELINE.json configs[0]: Erdos-Renyi 1M nodes / ~16M arcs, w=7 maxRef=3 minInt=4 zeta3, full nodeIterator decode on
     the CPU (the oracle's sequential scan, one thread) -- with the GPU decode of the same file beside it, compared in full."""
@@ -647,6 +683,10 @@ def run_config(args, torch, dist, wg, rank, local_rank, world, dev, stream, thre
         if nodes_total <= 1 << 32:
             e2e_narrow = run_e2e(True)
 
+    pcie = None
+    if not args.no_e2e and config == "c2":
+        pcie = pcie_probe(torch, dist, dev, world)
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         th = cpu_threads()
@@ -677,7 +717,7 @@ def run_config(args, torch, dist, wg, rank, local_rank, world, dev, stream, thre
                        else "1 shard; no collective",
                        "halo_nodes": int(max(r[1] for r in info)), "halo_nodes_by_rank": [int(r[1]) for r in info],
                        "ms_per_step_by_rank": [r[0] for r in info], "nodes_by_rank": [int(r[2]) for r in info]},
-            "roofline": roofline, "e2e": e2e, "e2e_narrow": e2e_narrow, "transpose": transpose, "labels": labels, "c1": c1, "c3": c3, "c4": c4,
+            "roofline": roofline, "e2e": e2e, "e2e_narrow": e2e_narrow, "pcie_probe": pcie, "transpose": transpose, "labels": labels, "c1": c1, "c3": c3, "c4": c4,
             "cpu_baseline": cpu, "gpu_launches": int(launches), "clocks": clocks,
             "verified": bool(verified), "fused": fused_stats, "global_row_base_rank0": global_base, "generation_s": sh.gen_s, "load_s": load_s,
         }

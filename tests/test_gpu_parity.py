@@ -219,6 +219,46 @@ def test_giant_rows_in_a_web_like_graph(monkeypatch, fused):
             assert np.array_equal(c, col[rowptr_of(deg)[49990]:rowptr_of(deg)[150010]])
 
 
+@pytest.mark.parametrize("fused", ["0", "1"])
+def test_repeated_and_concurrent_decodes_are_identical(monkeypatch, cnr_basename, cnr_golden, fused):
+    """The kernels hand work out by tickets and pass prefix sums, level lists and row data between blocks through global
+    memory (decoupled look-back, in-place merges).  compute-sanitizer is closed on the pool these tests run on, so the
+    protocols are stressed instead: the same decodes many times over, on two streams of one graph at the same time and on
+    ranges that cut tiles at odd places -- every result must equal the golden, bit for bit, every time."""
+    import threading
+    monkeypatch.setenv("WGBV_FUSED", fused)
+    deg, rowptr, col = cnr_golden
+    n = deg.size
+    e = bg.copy_model(120000, seed=4242, mean_degree=18, nsplits=3)
+    odeg, ocol = oracle_of(e).decode_range()
+    orp = rowptr_of(odeg)
+    errors = []
+
+    def work(g, want_rp, want_col, ranges, reps):
+        try:
+            for k in range(reps):
+                for lo, hi in ranges:
+                    rp, c = g.decodeToCSR(lo, hi)
+                    if not (np.array_equal(rp, want_rp[lo:hi + 1] - want_rp[lo]) and np.array_equal(c, want_col[want_rp[lo]:want_rp[hi]])):
+                        errors.append((k, lo, hi))
+        except Exception as ex:  # noqa: BLE001
+            errors.append(repr(ex))
+
+    with wg.GpuBVGraph.load(cnr_basename) as g1, gpu_of(e) as g2:
+        c1, c2 = g1.copy(), g2.copy()
+        ths = [threading.Thread(target=work, args=(g1, rowptr, col, [(0, n), (1017, 250001)], 8)),
+               threading.Thread(target=work, args=(c1, rowptr, col, [(300000, n), (0, 99999), (5, 4101)], 8)),
+               threading.Thread(target=work, args=(g2, orp, ocol, [(0, e.n), (33, 77777)], 10)),
+               threading.Thread(target=work, args=(c2, orp, ocol, [(100000, e.n), (0, 60001)], 10))]
+        for t in ths:
+            t.start()
+        for t in ths:
+            t.join()
+        c1.close()
+        c2.close()
+    assert not errors, errors[:5]
+
+
 def test_tree_grid():
     """BVGraphTest.testCompression grid (BVGraphTest.java:52-103), a sample of it."""
     from test_datagen import tree_csr
