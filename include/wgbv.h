@@ -209,6 +209,21 @@ WGBV_API int wgbv_scan_set_narrow(wgbv_stream *s, int on);
 WGBV_API int wgbv_transpose_csr(wgbv_stream *s, int64_t n, const int64_t *d_rowptr, const int64_t *d_col, int64_t *d_t_rowptr, int64_t *d_t_col);
 
 /*
+ * BVGraph compression of a CSR in device memory: what BVGraph.store / storeInternal write to the .graph
+ * file (BVGraph.java:2163-2327; per node: the candidate loop over the window with refCount < maxRefCount, BVG:2249-2270,
+ * diffComp BVG:1977-2159, intervalize BVG:1595-1618).  props gives windowsize, maxrefcount, minintervallength, zetak and
+ * the codings (nodes / arcs are not read); d_rowptr[0 .. n] / d_col are device pointers to the successor lists (sorted,
+ * without duplicates) of nodes first_node .. first_node + n - 1.  split_nodes = 0 compresses in one run, exactly as a
+ * single-threaded store; split_nodes = k > 0 starts every k nodes with an empty window, as the threads of the reference's
+ * parallel compressor do (BVG:2408-2457) -- the streams of the splits are already concatenated bit-exactly.
+ * Outputs (host memory): graph_out[0 .. ceil(*graph_bits / 8)) the bytes of the .graph file (capacity in bytes:
+ * WGBV_EARG with the size needed in *graph_bits if it is too small); node_bits_out, if not NULL, the n record lengths
+ * in bits, whose gamma-coded differences are the .offsets file (BVG:2228, 2311).
+ */
+WGBV_API int wgbv_encode_csr(int device, const wgbv_props *props, int64_t first_node, int64_t n, const int64_t *d_rowptr, const int64_t *d_col,
+                             int64_t split_nodes, uint8_t *graph_out, uint64_t graph_capacity, uint64_t *graph_bits, uint64_t *node_bits_out);
+
+/*
  * Arc labels: the `.labels` / `.labeloffsets` pair of a BitStreamArcLabelledImmutableGraph
  * (labelling/BitStreamArcLabelledImmutableGraph.java:65-100; offsets :339-363; what its node iterator reads per arc
  * :487-560) decoded into an int64 array parallel to the CSR successors of the underlying graph.  kind selects the

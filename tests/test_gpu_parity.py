@@ -620,3 +620,31 @@ def test_arc_labels_equal_oracle(cnr, cnr_golden):
                     L.decode(cnr, wrong[:1001], 0, 1000)
             with pytest.raises(wg.IllegalArgumentException):
                 L.decode(cnr, rowptr[:3], n - 1, n + 1)
+
+
+def test_device_compressor_reproduces_the_reference_fixture(cnr_basename, cnr_golden):
+    """the device compressor (wgbv_encode_csr) given the golden successor lists and the fixture's parameters
+    (w=7, maxRef=3, minInt=3, zeta_3; one run, as the fixture was stored) writes the reference's own cnr-2000.graph byte
+    for byte, and record lengths whose gamma-coded differences are cnr-2000.offsets."""
+    deg, rowptr, col = cnr_golden
+    graph, offsets, props = wg.store_csr(rowptr, col, window_size=7, max_ref_count=3, min_interval_length=3, zeta_k=3)
+    want = np.fromfile(cnr_basename + ".graph", dtype=np.uint8)
+    assert graph.size == want.size and np.array_equal(graph, want)
+    want_off = np.fromfile(cnr_basename + ".offsets", dtype=np.uint8)
+    assert np.array_equal(offsets, want_off)
+
+
+@pytest.mark.parametrize("window,maxref,minint,split", [(7, 3, 4, 0), (7, 3, 4, 7000), (1, 1, 0, 0), (0, 3, 2, 0), (16, 8, 1, 5000), (3, 0, 3, 0)])
+def test_device_compressor_equals_the_generator_and_round_trips(window, maxref, minint, split):
+    """The device compressor against the CPU restatement of the reference's compressor (datagen/bvgen.c, bit-exact on the
+    fixture) for other parameters and for compression splits; what it writes decodes back to the same lists."""
+    e0 = bg.copy_model(40000, seed=900 + window, mean_degree=14, nsplits=1)
+    odeg, ocol = oracle_of(e0).decode_range()
+    rp = rowptr_of(odeg)
+    e = bg.encode_csr(rp, ocol, bg.make_params(window=window, maxref=maxref, minint=minint), nsplits=-split if split else 1)
+    graph, offsets, props = wg.store_csr(rp, ocol, window_size=window, max_ref_count=maxref, min_interval_length=minint, split_nodes=split)
+    assert np.array_equal(graph, e.graph)
+    assert np.array_equal(offsets, e.offsets_stream)
+    with wg.GpuBVGraph.load_mem(props, graph, offsets) as g:
+        rp2, c2 = g.decodeToCSR()
+        assert np.array_equal(rp2, rp) and np.array_equal(c2, ocol)

@@ -382,6 +382,74 @@ class GpuBVGraph:
         return True
 
 
+# coding ids of wgbv_props (CompressionFlags.java of the reference)
+DELTA, GAMMA, GOLOMB, SKEWED_GOLOMB, UNARY, ZETA, NIBBLE = 1, 2, 3, 4, 5, 6, 7
+
+
+def _gamma_stream(values):
+    """The bytes of a gamma-coded stream of naturals (host side: the .offsets file of a stored graph)."""
+    v = np.ascontiguousarray(values, dtype=np.uint64) + np.uint64(1)
+    msb = np.zeros(v.size, dtype=np.int64)
+    t = v.copy()
+    for sh in (32, 16, 8, 4, 2, 1):
+        big = t >= (np.uint64(1) << np.uint64(sh))
+        msb[big] += sh
+        t[big] >>= np.uint64(sh)
+    ends = np.cumsum(2 * msb + 1)
+    total = int(ends[-1]) if v.size else 0
+    bits = np.zeros(total + 8, dtype=np.uint8)
+    starts = ends - (2 * msb + 1)
+    # code = msb zeros, then the msb + 1 significant bits of v
+    for b in range(int(msb.max()) + 1 if v.size else 0):
+        sel = msb >= b
+        bits[(starts + msb + (msb - b))[sel]] = ((v[sel] >> np.uint64(b)) & np.uint64(1)).astype(np.uint8)
+    return np.packbits(bits[: (total + 7) // 8 * 8]), total
+
+
+def store_csr(rowptr, col, basename=None, window_size=7, max_ref_count=3, min_interval_length=4, zeta_k=3, residual_coding=ZETA,
+              first_node=0, split_nodes=0, device=0):
+    """BVGraph.store for successor lists given as a CSR (BVGraph.java:2329-2590): compresses on the device
+    (wgbv_encode_csr) and returns (graph bytes, offsets bytes, properties text); with a basename the three files are
+    written as well.  rowptr / col: numpy arrays, or device pointers given as (ptr, n) / (ptr,).  split_nodes > 0 starts
+    every that many nodes with an empty window, like the threads of the reference's parallel compressor."""
+    import torch
+    L = _lib.lib()
+    dev = torch.device("cuda", device)
+    rp = torch.from_numpy(np.ascontiguousarray(rowptr, dtype=np.int64)).to(dev)
+    cl = torch.from_numpy(np.ascontiguousarray(col, dtype=np.int64)).to(dev)
+    n = rp.numel() - 1
+    arcs = int(rowptr[-1] - rowptr[0])
+    p = _lib.Props(nodes=n, arcs=arcs, window_size=window_size, max_ref_count=max_ref_count, min_interval_length=min_interval_length, zeta_k=zeta_k,
+                   outdegree_coding=GAMMA, block_coding=GAMMA, residual_coding=residual_coding, reference_coding=UNARY, block_count_coding=GAMMA,
+                   offset_coding=GAMMA)
+    cap = max(64, arcs * 10 + n * 4 + 64)
+    for _ in range(2):
+        out = np.zeros(cap, dtype=np.uint8)
+        node_bits = np.zeros(max(n, 1), dtype=np.uint64)
+        bits = C.c_uint64()
+        rc = L.wgbv_encode_csr(device, C.byref(p), first_node, n, C.c_void_p(rp.data_ptr()), C.c_void_p(cl.data_ptr() if cl.numel() else 0), split_nodes,
+                               out.ctypes.data, out.size, C.byref(bits), node_bits.ctypes.data)
+        if rc and bits.value // 8 + 1 > cap:
+            cap = bits.value // 8 + 64
+            continue
+        _lib.check(rc)
+        break
+    graph = out[: (bits.value + 7) // 8].copy()
+    offsets, _ = _gamma_stream(np.concatenate([np.zeros(1, dtype=np.uint64), node_bits[:n]]))
+    flags = "" if residual_coding == ZETA else "RESIDUALS_" + {GAMMA: "GAMMA", DELTA: "DELTA", NIBBLE: "NIBBLE", GOLOMB: "GOLOMB"}[residual_coding]
+    props = ("#BVGraph properties\ngraphclass=it.unimi.dsi.big.webgraph.BVGraph\nversion=0\n"
+             f"nodes={n}\narcs={arcs}\nwindowsize={window_size}\nmaxrefcount={max_ref_count}\nminintervallength={min_interval_length}\n"
+             f"zetak={zeta_k}\ncompressionflags={flags}\nbitsperlink={bits.value / max(arcs, 1):.4g}\nbitspernode={bits.value / max(n, 1):.4g}\n")
+    if basename:
+        with open(basename + ".graph", "wb") as f:
+            f.write(graph.tobytes())
+        with open(basename + ".offsets", "wb") as f:
+            f.write(offsets.tobytes())
+        with open(basename + ".properties", "w") as f:
+            f.write(props)
+    return graph, offsets, props
+
+
 LABEL_FIXED_INT, LABEL_GAMMA_INT = 0, 1
 
 

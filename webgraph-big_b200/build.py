@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libwgbv.so")
-SOURCES = ["wgbv_api.cu", "bv_kernels.cu", "bv_fused.cu", "bv_transpose.cu", "bv_offsets.cu", "bv_labels.cu", "bv_noalloc.cu", "bv_loader.cpp"]
+SOURCES = ["wgbv_api.cu", "bv_kernels.cu", "bv_fused.cu", "bv_encode.cu", "bv_transpose.cu", "bv_offsets.cu", "bv_labels.cu", "bv_noalloc.cu", "bv_loader.cpp"]
 HEADERS = ["bv_device.cuh", "bv_rows.cuh", "bv_kernels.cuh", "bv_block.cuh", "bv_loader.h", os.path.join("..", "..", "include", "wgbv.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC,-Wall,-Wextra,-Wno-parentheses,-fvisibility=hidden", "-shared", "-cudart", "static"]

@@ -106,6 +106,19 @@ struct FusedDev {
 	uint32_t *tile_done;     // ntiles words, written by the kernels: 1 = the tile's successors are complete
 };
 
+// BVGraph compression of a device CSR (bv_encode.cu)
+struct EncDev {
+	const int64_t *rowptr, *col;
+	int64_t n;           // rows
+	int64_t first_node;  // node id of row 0 (successors are coded relative to the node id)
+	int64_t split;       // nodes per compression split (>= 1)
+	int32_t window, maxref, minint, zetak;
+	int32_t outdegree_coding, block_coding, residual_coding, reference_coding, blockcount_coding;
+};
+// prices, chooses and writes; returns 0, -1 (CUDA error) or -2 (words_capacity too small: *total_bits_out says how much is needed)
+int encode_csr_device(cudaStream_t stream, const EncDev &E, uint32_t *d_cost, uint8_t *d_chosen, unsigned long long *d_bits, int64_t *d_off,
+                      uint64_t *scan_state, uint32_t *ticket, uint32_t *d_words, uint64_t words_capacity, uint64_t *total_bits_out);
+
 struct Launch {
 	cudaStream_t stream;
 	uint64_t *launches;  // incremented once per kernel launched

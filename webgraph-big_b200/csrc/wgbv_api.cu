@@ -1096,6 +1096,64 @@ extern "C" void wgbv_scan_end(wgbv_stream *s) {
 	s->scanning = false;
 }
 
+// ------------------------------------------------------------------------------------------------ compression
+extern "C" int wgbv_encode_csr(int device, const wgbv_props *props, int64_t first_node, int64_t n, const int64_t *d_rowptr, const int64_t *d_col,
+                               int64_t split_nodes, uint8_t *graph_out, uint64_t graph_capacity, uint64_t *graph_bits, uint64_t *node_bits_out) {
+	clear_error();
+	if (!props || !d_rowptr || !graph_bits || n < 0 || split_nodes < 0) return fail(WGBV_EARG, "null argument or negative size");
+	int rc = check_codings(*props);
+	if (rc) return rc;
+	if ((rc = select_device(device))) return rc;
+	*graph_bits = 0;
+	if (n == 0) return WGBV_OK;
+	EncDev E;
+	E.rowptr = d_rowptr;
+	E.col = d_col;
+	E.n = n;
+	E.first_node = first_node;
+	E.split = split_nodes > 0 ? split_nodes : n;
+	E.window = props->window_size;
+	E.maxref = props->max_ref_count;
+	E.minint = props->min_interval_length;
+	E.zetak = props->zeta_k;
+	E.outdegree_coding = props->outdegree_coding;
+	E.block_coding = props->block_coding;
+	E.residual_coding = props->residual_coding;
+	E.reference_coding = props->reference_coding;
+	E.blockcount_coding = props->block_count_coding;
+	cudaStream_t st = nullptr;
+	DevBuf cost, chosen, bits, off, state, ticket, words;
+	auto done = [&](int code) {
+		for (DevBuf *b : {&cost, &chosen, &bits, &off, &state, &ticket, &words}) b->release();
+		if (st) cudaStreamDestroy(st);
+		return code;
+	};
+	if (cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking) != cudaSuccess) return done(fail(WGBV_ECUDA, "cudaStreamCreate failed"));
+	int64_t h_rp[2];
+	if (cudaMemcpy(&h_rp[0], d_rowptr, 8, cudaMemcpyDeviceToHost) != cudaSuccess || cudaMemcpy(&h_rp[1], d_rowptr + n, 8, cudaMemcpyDeviceToHost) != cudaSuccess)
+		return done(fail(WGBV_ECUDA, "reading the row pointers failed: %s", cudaGetErrorString(cudaGetLastError())));
+	const int64_t arcs = h_rp[1] - h_rp[0];
+	if (arcs < 0 || (arcs && !d_col)) return done(fail(WGBV_EARG, "row pointers are not increasing, or no successors given"));
+	const size_t cyc = (size_t)props->window_size + 1;
+	// room for the stream: the caller's capacity bounds what is worth producing
+	const uint64_t words_cap = (graph_capacity / 8 + 2) * 2;
+	if ((rc = cost.ensure((size_t)n * cyc * 4)) || (rc = chosen.ensure((size_t)n)) || (rc = bits.ensure((size_t)n * 8)) || (rc = off.ensure((size_t)(n + 1) * 8)) ||
+	    (rc = state.ensure(((size_t)(n + 1) / 2048 + 2) * 8)) || (rc = ticket.ensure(64)) || (rc = words.ensure((size_t)words_cap * 4)))
+		return done(rc);
+	uint64_t total = 0;
+	const int e = encode_csr_device(st, E, cost.as<uint32_t>(), chosen.as<uint8_t>(), bits.as<unsigned long long>(), off.as<int64_t>(),
+	                                state.as<uint64_t>(), ticket.as<uint32_t>(), words.as<uint32_t>(), words_cap, &total);
+	*graph_bits = total;
+	if (e == -2) return done(fail(WGBV_EARG, "graph_capacity (%llu bytes) is too small for the %llu bits of the stream", (unsigned long long)graph_capacity, (unsigned long long)total));
+	if (e) return done(fail(WGBV_ECUDA, "compression failed on the device: %s", cudaGetErrorString(cudaGetLastError())));
+	const uint64_t nbytes = (total + 7) / 8;
+	if (nbytes > graph_capacity || (!graph_out && nbytes)) return done(fail(WGBV_EARG, "graph_capacity (%llu bytes) is too small for the %llu bits of the stream", (unsigned long long)graph_capacity, (unsigned long long)total));
+	if (nbytes && cudaMemcpyAsync(graph_out, words.p, (size_t)nbytes, cudaMemcpyDeviceToHost, st) != cudaSuccess) return done(fail(WGBV_ECUDA, "copy of the stream failed"));
+	if (node_bits_out && cudaMemcpyAsync(node_bits_out, bits.p, (size_t)n * 8, cudaMemcpyDeviceToHost, st) != cudaSuccess) return done(fail(WGBV_ECUDA, "copy of the record lengths failed"));
+	if (cudaStreamSynchronize(st) != cudaSuccess) return done(fail(WGBV_ECUDA, "device error while compressing: %s", cudaGetErrorString(cudaGetLastError())));
+	return done(WGBV_OK);
+}
+
 // ------------------------------------------------------------------------------------------------ transpose
 extern "C" int wgbv_transpose_csr(wgbv_stream *s, int64_t n, const int64_t *d_rowptr, const int64_t *d_col, int64_t *d_t_rowptr, int64_t *d_t_col) {
 	clear_error();
