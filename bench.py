@@ -568,6 +568,26 @@ def run_config(args, torch, dist, wg, rank, local_rank, world, dev, stream, thre
         if not t_ok:
             raise SystemExit("transpose(transpose(CSR)) does not hash to the generator's checksum")
 
+    # the device compressor on the CSR just decoded, with the generator's own compression splits: it must
+    # write the very stream that was decoded, byte for byte (BVGraph.store -> .graph)
+    encode = None
+    if full and not args.no_configs:
+        P = split_nodes(args.nodes)
+        out = np.zeros(int(sh.graph.size) + 64, dtype=np.uint8)
+        wg.encode_csr_device(min(n, 4 * P), d_rowptr.data_ptr(), d_col.data_ptr(), 0, max_ref_count=args.maxref, split_nodes=P, device=local_rank, out=out)  # warm-up
+        t0 = time.perf_counter()
+        enc, enc_bits, _ = wg.encode_csr_device(n, d_rowptr.data_ptr(), d_col.data_ptr(), arcs, max_ref_count=args.maxref, split_nodes=P, device=local_rank, out=out)
+        enc_s = time.perf_counter() - t0
+        e_ok = enc_bits == e.graph_bits and bool(np.array_equal(enc, e.graph[: enc.size]))
+        encode = {"metric": "compressed arcs/s (device CSR -> .graph bytes in host memory)", "value": arcs / enc_s, "unit": UNIT, "ms": enc_s * 1e3,
+                  "bits_per_arc": enc_bits / max(arcs, 1), "verified": bool(e_ok),
+                  "verified_how": "the stream equals, byte for byte, the one the CPU restatement of the reference's compressor wrote (and that was decoded above)",
+                  "host_encoder_s": sh.gen_s, "what": "wall time of wgbv_encode_csr: pricing of all (node, candidate) pairs, chain-length rule per split, emission, "
+                                                      "copy of the stream to the host; scratch allocated inside the call"}
+        del out
+        if not e_ok:
+            raise SystemExit("the device compressor did not reproduce the generator's stream")
+
     # configs[3] on the graph just decoded (the CSR in d_rowptr / d_col is the check)
     c4 = None
     if full and not args.no_configs:
@@ -717,7 +737,7 @@ def run_config(args, torch, dist, wg, rank, local_rank, world, dev, stream, thre
                        else "1 shard; no collective",
                        "halo_nodes": int(max(r[1] for r in info)), "halo_nodes_by_rank": [int(r[1]) for r in info],
                        "ms_per_step_by_rank": [r[0] for r in info], "nodes_by_rank": [int(r[2]) for r in info]},
-            "roofline": roofline, "e2e": e2e, "e2e_narrow": e2e_narrow, "pcie_probe": pcie, "transpose": transpose, "labels": labels, "c1": c1, "c3": c3, "c4": c4,
+            "roofline": roofline, "e2e": e2e, "e2e_narrow": e2e_narrow, "pcie_probe": pcie, "encode": encode, "transpose": transpose, "labels": labels, "c1": c1, "c3": c3, "c4": c4,
             "cpu_baseline": cpu, "gpu_launches": int(launches), "clocks": clocks,
             "verified": bool(verified), "fused": fused_stats, "global_row_base_rank0": global_base, "generation_s": sh.gen_s, "load_s": load_s,
         }

@@ -209,6 +209,23 @@ WGBV_API int wgbv_scan_set_narrow(wgbv_stream *s, int on);
 WGBV_API int wgbv_transpose_csr(wgbv_stream *s, int64_t n, const int64_t *d_rowptr, const int64_t *d_col, int64_t *d_t_rowptr, int64_t *d_t_col);
 
 /*
+ * Union of two CSRs over the same n nodes, in device memory: for every node the increasing union of its two successor
+ * lists, duplicates dropped -- Transform.union (Transform.java:1659-1663, UnionImmutableGraph) of the reference.  d_u_rowptr gets n + 1 entries,
+ * d_u_col the successors (u_capacity entries available; pass d_u_col = NULL to learn the size only); *arcs_out, if not
+ * NULL, the number of arcs of the union.  WGBV_EARG if u_capacity is too small (*arcs_out says how much is needed).
+ */
+WGBV_API int wgbv_union_csr(wgbv_stream *s, int64_t n, const int64_t *d_a_rowptr, const int64_t *d_a_col, const int64_t *d_b_rowptr,
+                            const int64_t *d_b_col, int64_t *d_u_rowptr, int64_t *d_u_col, uint64_t u_capacity, int64_t *arcs_out);
+
+/*
+ * Symmetrization of a CSR in device memory: the union of the graph and its transpose, Transform.symmetrizeOffline
+ * (Transform.java:573-574: "return union(g, transposeOffline(g, ...))").  The transpose is built in scratch memory of the
+ * stream (as many entries as the graph has arcs).  Arguments as for wgbv_union_csr; n < 2^32 as for wgbv_transpose_csr.
+ */
+WGBV_API int wgbv_symmetrize_csr(wgbv_stream *s, int64_t n, const int64_t *d_rowptr, const int64_t *d_col, int64_t *d_s_rowptr, int64_t *d_s_col,
+                                 uint64_t s_capacity, int64_t *arcs_out);
+
+/*
  * BVGraph compression of a CSR in device memory: what BVGraph.store / storeInternal write to the .graph
  * file (BVGraph.java:2163-2327; per node: the candidate loop over the window with refCount < maxRefCount, BVG:2249-2270,
  * diffComp BVG:1977-2159, intervalize BVG:1595-1618).  props gives windowsize, maxrefcount, minintervallength, zetak and

@@ -234,6 +234,24 @@ def transpose_csr(n, rowptr, col):
     return t_rowptr, src[order]
 
 
+def union_csr(n, a_rowptr, a_col, b_rowptr, b_col):
+    """CPU restatement of Transform.union (Transform.java:1659-1663, UnionImmutableGraph): per node the increasing union of
+    the two successor lists, duplicates dropped.  TEST INFRASTRUCTURE ONLY.  Parity status: unpinned by the reference (no
+    stored fixture of a union); pinned here by this definition."""
+    src = np.concatenate([np.repeat(np.arange(n, dtype=np.int64), np.diff(a_rowptr)), np.repeat(np.arange(n, dtype=np.int64), np.diff(b_rowptr))])
+    dst = np.concatenate([np.asarray(a_col, dtype=np.int64), np.asarray(b_col, dtype=np.int64)])
+    pairs = np.unique(np.stack([src, dst], axis=1), axis=0) if src.size else np.zeros((0, 2), dtype=np.int64)
+    rp = np.zeros(n + 1, dtype=np.int64)
+    np.cumsum(np.bincount(pairs[:, 0], minlength=n)[:n], out=rp[1:])
+    return rp, pairs[:, 1].astype(np.int64)
+
+
+def symmetrize_csr(n, rowptr, col):
+    """Transform.symmetrizeOffline restated (Transform.java:573-574): union(g, transpose(g))."""
+    trp, tcol = transpose_csr(n, rowptr, col)
+    return union_csr(n, rowptr, col, trp, tcol)
+
+
 LABEL_FIXED_INT, LABEL_GAMMA_INT = 0, 1
 
 

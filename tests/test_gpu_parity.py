@@ -524,6 +524,49 @@ def test_transpose_equals_oracle_and_is_an_involution(cnr, cnr_golden):
         _transpose_on_gpu(cnr, 10, np.array([0, 1] + [1] * 9, dtype=np.int64), np.array([10], dtype=np.int64))
 
 
+def test_symmetrize_equals_oracle_and_the_union_with_the_transpose(cnr, cnr_golden):
+    """wgbv_symmetrize_csr (SURVEY 8f-1) against the CPU restatement of Transform.symmetrizeOffline on the golden fixture;
+    the reference's own definition symmetrize(g) == union(g, transpose(g)) (Transform.java:573-574) through the separate
+    entry points; the result is its own transpose; a graph with loops, empty rows and duplicate arcs between g and g^T."""
+    torch = pytest.importorskip("torch")
+    deg, rowptr, col = cnr_golden
+    n = cnr.numNodes()
+
+    def sym(nn, rp, c):
+        d_rp = torch.from_numpy(np.ascontiguousarray(rp, dtype=np.int64)).cuda()
+        d_c = torch.from_numpy(np.ascontiguousarray(c, dtype=np.int64)).cuda() if c.size else torch.zeros(1, dtype=torch.int64, device="cuda")
+        d_srp = torch.empty(nn + 1, dtype=torch.int64, device="cuda")
+        arcs = cnr.symmetrizeCSRDevice(nn, d_rp.data_ptr(), d_c.data_ptr(), d_srp.data_ptr())
+        d_sc = torch.empty(max(arcs, 1), dtype=torch.int64, device="cuda")
+        assert cnr.symmetrizeCSRDevice(nn, d_rp.data_ptr(), d_c.data_ptr(), d_srp.data_ptr(), d_sc.data_ptr(), arcs) == arcs
+        return d_srp.cpu().numpy(), d_sc.cpu().numpy()[:arcs]
+
+    srp, scol = sym(n, rowptr, col)
+    orp, ocol = bo.symmetrize_csr(n, rowptr, col)
+    assert np.array_equal(srp, orp) and np.array_equal(scol, ocol)
+    # union(g, transpose(g)) through the two separate entry points
+    trp, tcol = _transpose_on_gpu(cnr, n, rowptr, col)
+    t = [torch.from_numpy(np.ascontiguousarray(a, dtype=np.int64)).cuda() for a in (rowptr, col, trp, tcol)]
+    d_urp = torch.empty(n + 1, dtype=torch.int64, device="cuda")
+    d_uc = torch.empty(scol.size, dtype=torch.int64, device="cuda")
+    assert cnr.unionCSRDevice(n, t[0].data_ptr(), t[1].data_ptr(), t[2].data_ptr(), t[3].data_ptr(), d_urp.data_ptr(), d_uc.data_ptr(), scol.size) == scol.size
+    assert np.array_equal(d_urp.cpu().numpy(), srp) and np.array_equal(d_uc.cpu().numpy(), scol)
+    with pytest.raises(wg.IllegalArgumentException):
+        cnr.unionCSRDevice(n, t[0].data_ptr(), t[1].data_ptr(), t[2].data_ptr(), t[3].data_ptr(), d_urp.data_ptr(), d_uc.data_ptr(), scol.size - 1)
+    # symmetric: equal to its own transpose
+    s2rp, s2col = _transpose_on_gpu(cnr, n, srp, scol)
+    assert np.array_equal(s2rp, srp) and np.array_equal(s2col, scol)
+    rng = np.random.default_rng(9)
+    for nn, m in ((1, 0), (4, 0), (50, 400), (20000, 90000)):
+        pairs = np.unique(np.stack([rng.integers(0, nn, m), rng.integers(0, nn, m)], axis=1), axis=0) if m else np.zeros((0, 2), np.int64)
+        rp = np.zeros(nn + 1, dtype=np.int64)
+        np.cumsum(np.bincount(pairs[:, 0], minlength=nn), out=rp[1:])
+        c = pairs[:, 1].astype(np.int64)
+        srp, scol = sym(nn, rp, c)
+        orp, ocol = bo.symmetrize_csr(nn, rp, c)
+        assert np.array_equal(srp, orp) and np.array_equal(scol, ocol), (nn, m)
+
+
 def test_offsets_decoded_on_the_device(monkeypatch, cnr_basename, cnr_golden):
     """the .offsets stream decoded and turned into the Elias-Fano list on the device (forced here for small
     graphs with WGBV_DEVICE_OFFSETS=1) must open the same graph as the host decoder: the reference's own .offsets file,

@@ -334,6 +334,21 @@ class GpuBVGraph:
         _lib.check(_lib.lib().wgbv_transpose_csr(self._st.h, n, C.c_void_p(d_rowptr), C.c_void_p(d_col), C.c_void_p(d_t_rowptr),
                                                  C.c_void_p(d_t_col)))
 
+    def symmetrizeCSRDevice(self, n, d_rowptr, d_col, d_s_rowptr, d_s_col=None, capacity=0):
+        """Transform.symmetrizeOffline (union of the graph and its transpose, Transform.java:573-574) of a CSR in device memory;
+        returns the arcs of the result (with d_s_col None only the row pointers and that count are produced)."""
+        arcs = C.c_int64()
+        _lib.check(_lib.lib().wgbv_symmetrize_csr(self._st.h, n, C.c_void_p(d_rowptr), C.c_void_p(d_col), C.c_void_p(d_s_rowptr),
+                                                  C.c_void_p(d_s_col) if d_s_col else None, capacity, C.byref(arcs)))
+        return arcs.value
+
+    def unionCSRDevice(self, n, a_rowptr, a_col, b_rowptr, b_col, u_rowptr, u_col=None, capacity=0):
+        """Transform.union of two CSRs over the same nodes, all in device memory; returns the arcs of the union."""
+        arcs = C.c_int64()
+        _lib.check(_lib.lib().wgbv_union_csr(self._st.h, n, C.c_void_p(a_rowptr), C.c_void_p(a_col), C.c_void_p(b_rowptr), C.c_void_p(b_col),
+                                             C.c_void_p(u_rowptr), C.c_void_p(u_col) if u_col else None, capacity, C.byref(arcs)))
+        return arcs.value
+
     def successorsBatchDevice(self, d_ids, k, d_rowptr, d_col=None, col_capacity=0):
         """Batched random access on device buffers.  With d_col None only the row pointers are produced."""
         L = _lib.lib()
@@ -404,6 +419,23 @@ def _gamma_stream(values):
         sel = msb >= b
         bits[(starts + msb + (msb - b))[sel]] = ((v[sel] >> np.uint64(b)) & np.uint64(1)).astype(np.uint8)
     return np.packbits(bits[: (total + 7) // 8 * 8]), total
+
+
+def encode_csr_device(n, d_rowptr, d_col, arcs, window_size=7, max_ref_count=3, min_interval_length=4, zeta_k=3, residual_coding=ZETA,
+                      first_node=0, split_nodes=0, device=0, out=None, want_node_bits=False):
+    """wgbv_encode_csr on a CSR that is already in device memory (pointers): returns (graph bytes -- a view of `out` if
+    given --, bits, record lengths or None)."""
+    L = _lib.lib()
+    p = _lib.Props(nodes=n, arcs=arcs, window_size=window_size, max_ref_count=max_ref_count, min_interval_length=min_interval_length, zeta_k=zeta_k,
+                   outdegree_coding=GAMMA, block_coding=GAMMA, residual_coding=residual_coding, reference_coding=UNARY, block_count_coding=GAMMA,
+                   offset_coding=GAMMA)
+    if out is None:
+        out = np.zeros(max(64, arcs * 10 + n * 4 + 64), dtype=np.uint8)
+    node_bits = np.zeros(max(n, 1), dtype=np.uint64) if want_node_bits else None
+    bits = C.c_uint64()
+    _lib.check(L.wgbv_encode_csr(device, C.byref(p), first_node, n, C.c_void_p(d_rowptr), C.c_void_p(d_col), split_nodes, out.ctypes.data, out.size,
+                                 C.byref(bits), node_bits.ctypes.data if want_node_bits else None))
+    return out[: (bits.value + 7) // 8], bits.value, node_bits
 
 
 def store_csr(rowptr, col, basename=None, window_size=7, max_ref_count=3, min_interval_length=4, zeta_k=3, residual_coding=ZETA,

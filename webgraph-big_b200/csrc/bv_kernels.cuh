@@ -175,6 +175,11 @@ int transpose_passes(uint64_t nodes);
 // (counts: the tile histograms of radix pass 0, which the pack kernel produces on the way)
 void launch_transpose_pack(const Launch &L, const GraphDev &g, int64_t n, const int64_t *rowptr, const int64_t *col, uint64_t arcs,
                            uint64_t *pairs, uint32_t *indeg, uint32_t *counts);
+// union of two CSRs over the same nodes (bv_transpose.cu): per-row counts, then (after a scan of the counts) the rows
+void launch_union_count(const Launch &L, int64_t n, const int64_t *arp, const int64_t *acol, const int64_t *brp, const int64_t *bcol, uint32_t *cnt,
+                        uint32_t *err);
+void launch_union_fill(const Launch &L, int64_t n, const int64_t *arp, const int64_t *acol, const int64_t *brp, const int64_t *bcol,
+                       const int64_t *urp, int64_t *ucol, uint64_t capacity, uint32_t *err);
 void launch_radix_hist(const Launch &L, const uint64_t *in, uint64_t count, int pass, uint32_t *counts);
 void launch_radix_scatter(const Launch &L, const uint64_t *in, uint64_t count, int pass, const int64_t *pos, uint64_t *out, int64_t *t_col);
 // .offsets on the device (bv_offsets.cu): h_stream holds `count` gamma-coded differences; *d_off_out (cudaMalloc'ed, the

@@ -220,4 +220,53 @@ void launch_radix_scatter(const Launch &L, const uint64_t *in, uint64_t count, i
 	WGBV_LAUNCHED(L);
 }
 
+// ------------------------------------------------------------------------------------------------ union / symmetrize
+// Transform.union(g0, g1) for two CSRs over the same node set (UnionImmutableGraph: per node the sorted union of the two
+// successor lists, duplicates dropped), which with g1 = transpose(g0) is Transform.symmetrizeOffline
+// (Transform.java:573-574).  One thread per row: count, scan, fill.
+template <bool FILL>
+__global__ void __launch_bounds__(TPB) k_union(int64_t n, const int64_t *__restrict__ arp, const int64_t *__restrict__ acol,
+                                               const int64_t *__restrict__ brp, const int64_t *__restrict__ bcol, uint32_t *__restrict__ cnt,
+                                               const int64_t *__restrict__ urp, int64_t *__restrict__ ucol, uint64_t capacity, uint32_t *err) {
+	const int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
+	if (i >= n) return;
+	const int64_t *a = acol + (arp[i] - arp[0]), *b = bcol + (brp[i] - brp[0]);
+	const int64_t na = arp[i + 1] - arp[i], nb = brp[i + 1] - brp[i];
+	int64_t *out = nullptr;
+	if (FILL) {
+		if ((uint64_t)urp[i + 1] > capacity) { atomicOr(err, ERR_CAPACITY); return; }
+		out = ucol + urp[i];
+	}
+	int64_t j = 0, k = 0, o = 0;
+	while (j < na && k < nb) {
+		const int64_t x = a[j], y = b[k];
+		const int64_t v = x < y ? x : y;
+		if (FILL) out[o] = v;
+		o++;
+		j += x <= y;
+		k += y <= x;
+	}
+	if (FILL) {
+		for (; j < na; j++) out[o++] = a[j];
+		for (; k < nb; k++) out[o++] = b[k];
+	} else {
+		o += (na - j) + (nb - k);
+		if (o > 0x7fffffffll) { atomicOr(err, ERR_DEGREE); o = 0; }
+		cnt[i] = (uint32_t)o;
+	}
+}
+
+void launch_union_count(const Launch &L, int64_t n, const int64_t *arp, const int64_t *acol, const int64_t *brp, const int64_t *bcol, uint32_t *cnt,
+                        uint32_t *err) {
+	if (n <= 0) return;
+	k_union<false><<<grid_for(n, TPB), TPB, 0, L.stream>>>(n, arp, acol, brp, bcol, cnt, nullptr, nullptr, 0, err);
+	WGBV_LAUNCHED(L);
+}
+void launch_union_fill(const Launch &L, int64_t n, const int64_t *arp, const int64_t *acol, const int64_t *brp, const int64_t *bcol,
+                       const int64_t *urp, int64_t *ucol, uint64_t capacity, uint32_t *err) {
+	if (n <= 0) return;
+	k_union<true><<<grid_for(n, TPB), TPB, 0, L.stream>>>(n, arp, acol, brp, bcol, nullptr, urp, ucol, capacity, err);
+	WGBV_LAUNCHED(L);
+}
+
 }  // namespace wgbv

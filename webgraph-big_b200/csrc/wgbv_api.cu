@@ -74,6 +74,7 @@ struct wgbv_stream {
 	uint64_t launches = 0;
 	DevBuf deg, ref, depth, rp, scan_state, ticket, halo, levels, list, col, rowptr, ids, batch;
 	DevBuf t_pairs[2], t_indeg, t_counts, t_pos;  // wgbv_transpose_csr
+	DevBuf sym_rowptr, sym_col;                   // wgbv_symmetrize_csr: the transpose
 	DevBuf heavy_rows, heavy_sorted, heavy_cls, heavy_counters, giants, gchunks, level_pos, row_info, tile_done;
 	bool front_in_extras = true;  // false: always run header and scan as their own launches (WGBV_SPLIT_FRONT=1)
 	bool use_fused = false;       // true: bulk decodes take the one-pass tile kernel where it applies (WGBV_FUSED=1)
@@ -488,7 +489,7 @@ extern "C" void wgbv_stream_destroy(wgbv_stream *s) {
 	if (!s) return;
 	cudaSetDevice(s->g->device);
 	if (s->stream) cudaStreamSynchronize(s->stream);
-	for (DevBuf *b : {&s->t_pairs[0], &s->t_pairs[1], &s->t_indeg, &s->t_counts, &s->t_pos}) b->release();
+	for (DevBuf *b : {&s->t_pairs[0], &s->t_pairs[1], &s->t_indeg, &s->t_counts, &s->t_pos, &s->sym_rowptr, &s->sym_col}) b->release();
 	for (DevBuf *b : {&s->deg, &s->ref, &s->depth, &s->rp, &s->scan_state, &s->ticket, &s->halo, &s->levels, &s->list, &s->col,
 	                  &s->rowptr, &s->ids, &s->batch, &s->heavy_rows, &s->heavy_sorted, &s->heavy_cls, &s->heavy_counters, &s->giants, &s->gchunks, &s->tile_done, &s->level_pos, &s->row_info, &s->c_node, &s->c_dst, &s->c_parent, &s->c_deg, &s->c_isq, &s->c_level,
 	                  &s->c_len, &s->c_arcs, &s->c_row0, &s->c_soff, &s->c_store})
@@ -1094,6 +1095,50 @@ extern "C" void wgbv_scan_end(wgbv_stream *s) {
 	}
 	s->up_graph = nullptr;
 	s->scanning = false;
+}
+
+// ------------------------------------------------------------------------------------------------ union / symmetrize
+extern "C" int wgbv_union_csr(wgbv_stream *s, int64_t n, const int64_t *d_a_rowptr, const int64_t *d_a_col, const int64_t *d_b_rowptr,
+                              const int64_t *d_b_col, int64_t *d_u_rowptr, int64_t *d_u_col, uint64_t u_capacity, int64_t *arcs_out) {
+	clear_error();
+	if (!s || !d_a_rowptr || !d_b_rowptr || !d_u_rowptr || n < 0) return fail(WGBV_EARG, "null argument or negative node count");
+	CU(cudaSetDevice(s->g->device));
+	const Launch L = s->launch();
+	int rc;
+	const size_t nn = (size_t)std::max<int64_t>(n, 1);
+	if ((rc = s->t_indeg.ensure(nn * 4)) || (rc = s->scan_state.ensure(((nn + 1) / 2048 + 2) * 8)) || (rc = s->ticket.ensure(64))) return rc;
+	launch_union_count(L, n, d_a_rowptr, d_a_col, d_b_rowptr, d_b_col, s->t_indeg.as<uint32_t>(), s->d_err);
+	launch_scan(L, s->t_indeg.as<uint32_t>(), d_u_rowptr, n, s->scan_state.as<uint64_t>(), s->ticket.as<uint32_t>());
+	PeekArgs pk;
+	pk.add(d_u_rowptr + n, 8);
+	launch_peek(L, pk, s->d_pin);
+	CU(cudaStreamSynchronize(s->stream));
+	const int64_t arcs = (int64_t)s->h_pin[0];
+	if (arcs_out) *arcs_out = arcs;
+	if (d_u_col) {
+		if ((uint64_t)arcs > u_capacity) return fail(WGBV_EARG, "u_capacity (%llu) is smaller than the %lld arcs of the union", (unsigned long long)u_capacity, (long long)arcs);
+		launch_union_fill(L, n, d_a_rowptr, d_a_col, d_b_rowptr, d_b_col, d_u_rowptr, d_u_col, u_capacity, s->d_err);
+	}
+	const cudaError_t e = cudaGetLastError();
+	if (e != cudaSuccess) return fail(WGBV_ECUDA, "kernel launch failed: %s", cudaGetErrorString(e));
+	return collect_errors(s);
+}
+
+extern "C" int wgbv_symmetrize_csr(wgbv_stream *s, int64_t n, const int64_t *d_rowptr, const int64_t *d_col, int64_t *d_s_rowptr, int64_t *d_s_col,
+                                   uint64_t s_capacity, int64_t *arcs_out) {
+	clear_error();
+	if (!s || !d_rowptr || !d_s_rowptr || n < 0) return fail(WGBV_EARG, "null argument or negative node count");
+	CU(cudaSetDevice(s->g->device));
+	int64_t h[2];
+	CU(cudaMemcpyAsync(&h[0], d_rowptr, 8, cudaMemcpyDeviceToHost, s->stream));
+	CU(cudaMemcpyAsync(&h[1], d_rowptr + n, 8, cudaMemcpyDeviceToHost, s->stream));
+	CU(cudaStreamSynchronize(s->stream));
+	const int64_t arcs = h[1] - h[0];
+	if (arcs < 0) return fail(WGBV_EARG, "row pointers are not increasing");
+	int rc;
+	if ((rc = s->sym_rowptr.ensure((size_t)(n + 1) * 8)) || (rc = s->sym_col.ensure((size_t)std::max<int64_t>(arcs, 1) * 8))) return rc;
+	if ((rc = wgbv_transpose_csr(s, n, d_rowptr, d_col, s->sym_rowptr.as<int64_t>(), s->sym_col.as<int64_t>()))) return rc;
+	return wgbv_union_csr(s, n, d_rowptr, d_col, s->sym_rowptr.as<int64_t>(), s->sym_col.as<int64_t>(), d_s_rowptr, d_s_col, s_capacity, arcs_out);
 }
 
 // ------------------------------------------------------------------------------------------------ compression
