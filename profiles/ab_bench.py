@@ -25,11 +25,11 @@ for spec in args:
         env["WGBV_LIBRARY"] = os.path.join(ROOT, path) if not os.path.isabs(path) else path
     else:
         env.pop("WGBV_LIBRARY", None)
-    cmd = [sys.executable, os.path.join(ROOT, "bench.py"), "--warmup", "3", "--no-e2e", "--no-cpu-baseline", "--no-labels", "--no-transpose"] + extra
+    cmd = [sys.executable, os.path.join(ROOT, "bench.py"), "--warmup", "3", "--no-e2e", "--no-cpu-baseline", "--no-labels", "--no-transpose", "--no-configs"] + extra
     res = subprocess.run(cmd, env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=600)
     try:
         j = json.loads(res.stdout.strip().splitlines()[-1])
-        st = {k: round(v, 2) for k, v in j["roofline"]["stage_ms"].items()}
+        st = {k: round(v, 2) for k, v in j["roofline"].get("stage_ms_rank0", {}).items()}
         print(f"{name:12s} {j['ms_per_step']:8.3f} ms/step verified={j.get('verified')} launches={j.get('gpu_launches')} {st}", flush=True)
     except Exception as e:  # noqa: BLE001
         print(f"{name:12s} FAILED rc={res.returncode} {e}\n{res.stderr[-2000:]}", flush=True)
