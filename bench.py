@@ -519,13 +519,13 @@ def run_config(args, torch, dist, wg, rank, local_rank, world, dev, stream, thre
     stage_ms = stage_acc / args.steps
     # per rank: device ms per step, halo rows decoded redundantly, nodes of the shard (rank 0 has no halo: the cost of the
     # halo path shows as the difference between its time and the others')
-    mine_info = torch.tensor([ms / args.steps, float(sh.halo), float(n)], dtype=torch.float64, device=dev)
-    info = torch.zeros(world * 3, dtype=torch.float64, device=dev)
+    mine_info = torch.tensor([ms / args.steps, float(sh.halo), float(n), float(stage_ms[4])], dtype=torch.float64, device=dev)
+    info = torch.zeros(world * 4, dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_gather_into_tensor(info, mine_info)
     else:
         info.copy_(mine_info)
-    info = info.cpu().reshape(world, 3).tolist()
+    info = info.cpu().reshape(world, 4).tolist()
 
     # parity at full size: the checksum of the decoded CSR must equal the one the generator took before encoding
     arcs = int(d_rowptr[n].item())
@@ -736,7 +736,9 @@ def run_config(args, torch, dist, wg, rank, local_rank, world, dev, stream, thre
                                        f"{int(max(r[1] for r in info))} rows before its shard as halo (no data-path collective); all-gather of arc counts") if world > 1
                        else "1 shard; no collective",
                        "halo_nodes": int(max(r[1] for r in info)), "halo_nodes_by_rank": [int(r[1]) for r in info],
-                       "ms_per_step_by_rank": [r[0] for r in info], "nodes_by_rank": [int(r[2]) for r in info]},
+                       "ms_per_step_by_rank": [r[0] for r in info], "decode_ms_by_rank": [r[3] for r in info],
+                       "decode_ms_by_rank_what": "the library's own events around the decode of the shard, without the all-gather: rank 0 has no halo (one-launch front end), the others decode 21 halo rows (separate header and scan launches)",
+                       "nodes_by_rank": [int(r[2]) for r in info]},
             "roofline": roofline, "e2e": e2e, "e2e_narrow": e2e_narrow, "pcie_probe": pcie, "encode": encode, "transpose": transpose, "labels": labels, "c1": c1, "c3": c3, "c4": c4,
             "cpu_baseline": cpu, "gpu_launches": int(launches), "clocks": clocks,
             "verified": bool(verified), "fused": fused_stats, "global_row_base_rank0": global_base, "generation_s": sh.gen_s, "load_s": load_s,
