@@ -163,10 +163,41 @@ public:
 	void transposeDevice(int64_t n, const int64_t *d_rowptr, const int64_t *d_col, int64_t *d_t_rowptr, int64_t *d_t_col) {
 		check(wgbv_transpose_csr(st_, n, d_rowptr, d_col, d_t_rowptr, d_t_col));
 	}
+	// Transform.symmetrizeOffline = union(g, transpose(g)) (Transform.java:573-574) of a device CSR; returns the arcs of the result
+	// (d_s_col == nullptr: only the row pointers and the count)
+	int64_t symmetrizeDevice(int64_t n, const int64_t *d_rowptr, const int64_t *d_col, int64_t *d_s_rowptr, int64_t *d_s_col, uint64_t capacity) {
+		int64_t arcs = 0;
+		check(wgbv_symmetrize_csr(st_, n, d_rowptr, d_col, d_s_rowptr, d_s_col, capacity, &arcs));
+		return arcs;
+	}
+	// Transform.union (Transform.java:1659-1663) of two device CSRs over the same nodes
+	int64_t unionDevice(int64_t n, const int64_t *a_rowptr, const int64_t *a_col, const int64_t *b_rowptr, const int64_t *b_col, int64_t *d_u_rowptr,
+	                    int64_t *d_u_col, uint64_t capacity) {
+		int64_t arcs = 0;
+		check(wgbv_union_csr(st_, n, a_rowptr, a_col, b_rowptr, b_col, d_u_rowptr, d_u_col, capacity, &arcs));
+		return arcs;
+	}
 	// host-side scans of this copy deliver successors as uint32 (graphs of at most 2^32 nodes): half the PCIe bytes
 	void setNarrowScan(bool on) { check(wgbv_scan_set_narrow(st_, on ? 1 : 0)); }
 	wgbv_stream *stream() const { return st_; }
 };
+
+// BVGraph.store (BVGraph.java:2329-2590) for a CSR in device memory: the bytes of the .graph file and the record lengths
+// (whose gamma-coded differences are the .offsets file); split_nodes = 0: one run, as a single-threaded store.
+inline std::vector<uint8_t> storeDevice(int device, const wgbv_props &props, int64_t first_node, int64_t n, const int64_t *d_rowptr, const int64_t *d_col,
+                                        int64_t split_nodes, std::vector<uint64_t> *node_bits = nullptr) {
+	std::vector<uint8_t> out((size_t)(props.arcs > 0 ? props.arcs : 0) * 10 + (size_t)n * 4 + 64);
+	if (node_bits) node_bits->assign((size_t)(n > 0 ? n : 1), 0);
+	uint64_t bits = 0;
+	int rc = wgbv_encode_csr(device, &props, first_node, n, d_rowptr, d_col, split_nodes, out.data(), out.size(), &bits, node_bits ? node_bits->data() : nullptr);
+	if (rc == WGBV_EARG && bits / 8 + 1 > out.size()) {  // (the first guess was too small)
+		out.assign(bits / 8 + 64, 0);
+		rc = wgbv_encode_csr(device, &props, first_node, n, d_rowptr, d_col, split_nodes, out.data(), out.size(), &bits, node_bits ? node_bits->data() : nullptr);
+	}
+	check(rc);
+	out.resize((bits + 7) / 8);
+	return out;
+}
 
 // The labels of a BitStreamArcLabelledImmutableGraph (labelling/BitStreamArcLabelledImmutableGraph.java:65-100) on the
 // device: decode() returns them parallel to the successors that Graph::decodeToCSR returns for the same range.

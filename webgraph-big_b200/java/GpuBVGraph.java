@@ -51,6 +51,13 @@ public class GpuBVGraph extends ImmutableGraph {
 		static final MethodHandle SUCCESSORS_BATCH_HOST = h("wgbv_successors_batch_host",
 				FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_LONG, ADDRESS, ADDRESS, JAVA_LONG, ADDRESS));
 		static final MethodHandle LAST_ERROR = h("wgbv_last_error", FunctionDescriptor.of(ADDRESS));
+		// Transform.symmetrizeOffline / union on device CSRs, and BVGraph.store for a device CSR (include/wgbv.h)
+		static final MethodHandle SYMMETRIZE_CSR = h("wgbv_symmetrize_csr",
+			FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_LONG, ADDRESS, ADDRESS, ADDRESS, ADDRESS, JAVA_LONG, ADDRESS));
+		static final MethodHandle UNION_CSR = h("wgbv_union_csr",
+			FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_LONG, ADDRESS, ADDRESS, ADDRESS, ADDRESS, ADDRESS, ADDRESS, JAVA_LONG, ADDRESS));
+		static final MethodHandle ENCODE_CSR = h("wgbv_encode_csr",
+			FunctionDescriptor.of(JAVA_INT, JAVA_INT, ADDRESS, JAVA_LONG, JAVA_LONG, ADDRESS, ADDRESS, JAVA_LONG, ADDRESS, JAVA_LONG, ADDRESS, ADDRESS));
 		// arc labels (labelling/BitStreamArcLabelledImmutableGraph.java:65-100): an array parallel to the successors
 		static final MethodHandle LABELS_OPEN_MEM = h("wgbv_labels_open_mem",
 				FunctionDescriptor.of(JAVA_INT, JAVA_INT, JAVA_LONG, JAVA_INT, JAVA_INT, ADDRESS, JAVA_LONG, ADDRESS, JAVA_LONG, ADDRESS));
