@@ -16,6 +16,9 @@
 //   k_enc_choose  thread per split: the reference of every node, its record length
 //   k_scan        record lengths -> bit offsets (bv_kernels.cu)
 //   k_enc_emit    thread per node: the record, OR-ed into a zeroed stream of 32-bit words (most significant bit first)
+#include <stdio.h>
+#include <stdlib.h>
+
 #include <algorithm>
 
 #include "bv_block.cuh"
@@ -276,30 +279,50 @@ __global__ void k_enc_choose(EncDev E, const uint32_t *__restrict__ cost, uint8_
 	const int cyc = E.window + 1;
 	int refcount[256];  // (window <= 255)
 	for (int q = 0; q < cyc; q++) refcount[q] = 0;
-	for (int64_t i = lo; i < hi; i++) {
-		const int64_t d = E.rowptr[i + 1] - E.rowptr[i];
-		uint64_t len = e_len(E.outdegree_coding, (uint64_t)d, 0);
-		int best_ref = 0;
-		if (d > 0) {
-			const int ci = (int)(i % cyc);
-			refcount[ci] = -1;
-			uint32_t best = COST_NONE;
-			int best_cand = ci;
-			for (int ref = 0; ref < cyc; ref++) {
-				if (ref > i - lo) break;
-				const int cand = (int)((i - ref) % cyc);
-				const uint32_t c = cost[i * cyc + ref];
-				if (refcount[cand] < E.maxref && c != COST_NONE && c < best) {
-					best = c;
-					best_ref = ref;
-					best_cand = cand;
-				}
+	// The decisions are a serial chain, the loads are not: row pointers and prices of a batch of nodes are fetched
+	// first (independent loads, all in flight together), then the batch is decided from registers / local memory.
+	constexpr int BATCH = 8;
+	for (int64_t b0 = lo; b0 < hi; b0 += BATCH) {
+		int64_t dd[BATCH];
+		uint32_t cc[BATCH][9];
+		const bool small = cyc <= 9;
+#pragma unroll
+		for (int u = 0; u < BATCH; u++) {
+			const int64_t i = b0 + u;
+			dd[u] = i < hi ? E.rowptr[i + 1] - E.rowptr[i] : 0;
+			if (small && i < hi) {
+#pragma unroll
+				for (int r = 0; r < 9; r++) cc[u][r] = r < cyc ? cost[i * cyc + r] : COST_NONE;
 			}
-			refcount[ci] = refcount[best_cand] + 1;
-			len += best;
 		}
-		chosen[i] = (uint8_t)best_ref;
-		bits[i] = len;
+#pragma unroll
+		for (int u = 0; u < BATCH; u++) {
+			const int64_t i = b0 + u;
+			if (i >= hi) break;
+			const int64_t d = dd[u];
+			uint64_t len = e_len(E.outdegree_coding, (uint64_t)d, 0);
+			int best_ref = 0;
+			if (d > 0) {
+				const int ci = (int)(i % cyc);
+				refcount[ci] = -1;
+				uint32_t best = COST_NONE;
+				int best_cand = ci;
+				for (int ref = 0; ref < cyc; ref++) {
+					if (ref > i - lo) break;
+					const int cand = (int)((i - ref) % cyc);
+					const uint32_t c = (small && ref < 9) ? cc[u][ref] : cost[i * cyc + ref];
+					if (refcount[cand] < E.maxref && c != COST_NONE && c < best) {
+						best = c;
+						best_ref = ref;
+						best_cand = cand;
+					}
+				}
+				refcount[ci] = refcount[best_cand] + 1;
+				len += best;
+			}
+			chosen[i] = (uint8_t)best_ref;
+			bits[i] = len;
+		}
 	}
 }
 
@@ -352,9 +375,17 @@ int encode_csr_device(cudaStream_t stream, const EncDev &E, uint32_t *d_cost, ui
 	if (E.n <= 0) { *total_bits_out = 0; return 0; }
 	Launch L{stream, nullptr};
 	const int cyc = E.window + 1;
+	const bool timing = getenv("WGBV_TIMING") != nullptr;
+	cudaEvent_t ev[5];
+	if (timing) {
+		for (auto &e : ev) cudaEventCreate(&e);
+		cudaEventRecord(ev[0], stream);
+	}
 	k_enc_cost<<<grid_for(E.n * cyc, TPB), TPB, 0, stream>>>(E, d_cost);
+	if (timing) cudaEventRecord(ev[1], stream);
 	const int64_t splits = (E.n + E.split - 1) / E.split;
 	k_enc_choose<<<grid_for(splits, 64), 64, 0, stream>>>(E, d_cost, d_chosen, d_bits);
+	if (timing) cudaEventRecord(ev[2], stream);
 	launch_scan64(L, d_bits, d_off, E.n, scan_state, ticket);
 	int64_t total = 0;
 	if (cudaMemcpyAsync(&total, d_off + E.n, 8, cudaMemcpyDeviceToHost, stream) != cudaSuccess || cudaStreamSynchronize(stream) != cudaSuccess) return -1;
@@ -362,9 +393,20 @@ int encode_csr_device(cudaStream_t stream, const EncDev &E, uint32_t *d_cost, ui
 	const uint64_t need = ((uint64_t)total + 63) / 64 * 2;  // 32-bit words, rounded to 64-bit units
 	if (need > words_capacity) return -2;
 	if (cudaMemsetAsync(d_words, 0, need * 4, stream) != cudaSuccess) return -1;
+	if (timing) cudaEventRecord(ev[3], stream);
 	k_enc_emit<<<grid_for(E.n, TPB), TPB, 0, stream>>>(E, d_chosen, d_off, d_words);
 	// words -> bytes of the file: every 32-bit word holds its bits most significant first
 	launch_bswap(L, reinterpret_cast<uint64_t *>(d_words), need / 2);
+	if (timing) {
+		cudaEventRecord(ev[4], stream);
+		cudaStreamSynchronize(stream);
+		float a = 0, b = 0, c = 0;
+		cudaEventElapsedTime(&a, ev[0], ev[1]);
+		cudaEventElapsedTime(&b, ev[1], ev[2]);
+		cudaEventElapsedTime(&c, ev[3], ev[4]);
+		fprintf(stderr, "[wgbv] compress %lld nodes: pricing %.1f ms, reference choice %.1f ms, emission %.1f ms\n", (long long)E.n, a, b, c);
+		for (auto &e : ev) cudaEventDestroy(e);
+	}
 	return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }
 
