@@ -144,7 +144,8 @@ WGBV_API int wgbv_stream_sync(wgbv_stream *s);
 /* Copies the bit stream from host memory to the device again, asynchronously on the stream (the upload half of
  * loadInternal's "read the whole graph into memory", BVG:1520-1528, for callers that keep the compressed graph in
  * pinned host memory and stream it in per pass).  `graph` must be the buffer (or an identical copy) the handle was
- * opened from. */
+ * opened from.  The words are rewritten in place, so this (and wgbv_scan_begin_upload) is only allowed while the
+ * stream is the only one of its graph: WGBV_ESTATE otherwise. */
 WGBV_API int wgbv_upload_stream(wgbv_stream *s, const uint8_t *graph, uint64_t graph_bytes);
 
 /*

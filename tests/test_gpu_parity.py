@@ -115,6 +115,29 @@ def test_index_errors(cnr):
     assert rp.tolist() == [0] and c.size == 0
 
 
+def test_empty_range_on_a_new_handle_and_upload_exclusivity(cnr_basename, cnr_golden):
+    """decodeToCSRDevice(x, x) as the first call of a handle (nothing has sized the stream's scratch yet) leaves
+    rowptr[0] = 0 and touches nothing else; re-uploading the bit stream is refused while a second stream shares the graph."""
+    torch = pytest.importorskip("torch")
+    deg, rowptr, col = cnr_golden
+    with wg.GpuBVGraph.load(cnr_basename) as g:
+        d_rp = torch.full((4,), -7, dtype=torch.int64, device="cuda")
+        d_col = torch.full((4,), -7, dtype=torch.int64, device="cuda")
+        for x in (0, 7, g.numNodes()):
+            g.decodeToCSRDevice(x, x, d_rp.data_ptr(), d_col.data_ptr(), 4)
+            g.sync()
+            assert d_rp.tolist() == [0, -7, -7, -7] and d_col.tolist() == [-7] * 4
+        rp, c = g.decodeToCSR(0, 100)
+        assert np.array_equal(c, col[:rowptr[100]])
+        raw = np.fromfile(cnr_basename + ".graph", dtype=np.uint8)
+        it = g.scan(0, 1000, 500, upload=(raw.ctypes.data, raw.size))
+        assert sum(cc.size for _, _, _, cc in it) == rowptr[1000]
+        other = g.copy()
+        with pytest.raises(wg.IllegalStateException):
+            list(g.scan(0, 1000, 500, upload=(raw.ctypes.data, raw.size)))
+        other.close()
+
+
 def test_checksum_kernel_matches_generator_hash(cnr, cnr_golden):
     torch = pytest.importorskip("torch")
     deg, rowptr, col = cnr_golden

@@ -402,6 +402,9 @@ extern "C" int wgbv_upload_stream(wgbv_stream *s, const uint8_t *graph, uint64_t
 	wgbv_graph *g = s->g;
 	CU(cudaSetDevice(g->device));
 	if (graph_bytes < g->byte1) return fail(WGBV_EARG, "the buffer (%llu bytes) is shorter than the stream that was opened (%llu bytes)", (unsigned long long)graph_bytes, (unsigned long long)g->byte1);
+	// the words are rewritten in place (raw bytes first, byte-swapped afterwards): another stream decoding the same graph
+	// meanwhile would read garbage without any error
+	if (g->streams > 1) return fail(WGBV_ESTATE, "the bit stream can only be uploaded again while this is the graph's only stream (%d exist)", g->streams);
 	if (g->data_words) {
 		CU(cudaMemsetAsync(g->d_words + g->data_words - 1, 0, 8, s->stream));
 		CU(cudaMemcpyAsync(g->d_words, graph + g->byte0, g->byte1 - g->byte0, cudaMemcpyHostToDevice, s->stream));
@@ -1029,6 +1032,7 @@ extern "C" int wgbv_scan_begin_upload(wgbv_stream *s, const uint8_t *graph, uint
 	wgbv_graph *g = s->g;
 	if (graph_bytes < g->byte1) return fail(WGBV_EARG, "the buffer (%llu bytes) is shorter than the stream that was opened (%llu bytes)", (unsigned long long)graph_bytes, (unsigned long long)g->byte1);
 	if (from != g->shard_lo) return fail(WGBV_EARG, "a scan that uploads the stream has to start at the first node of the handle (%lld)", (long long)g->shard_lo);
+	if (g->streams > 1) return fail(WGBV_ESTATE, "the bit stream can only be uploaded again while this is the graph's only stream (%d exist)", g->streams);
 	int rc = wgbv_scan_begin(s, from, to, chunk_nodes);
 	if (rc) return rc;
 	if (!s->upload_stream) {
