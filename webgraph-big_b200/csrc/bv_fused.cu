@@ -321,11 +321,12 @@ __global__ void __launch_bounds__(FTH, WGBV_FBLOCKS) k_fused(GraphDev g, FusedDe
 			uint64_t int_pos;
 			row_intervals(g, r, nextra, ic, int_pos, nres);
 			S.rpos[tid] = (uint32_t)r.tell();
-			// Long residual lists go to a whole warp each (buckets 0 and 1: first in the order); the others are sorted by work,
-			// rows with intervals first inside each class (warps without any skip the merging loop of row_extras_core).
-			// (A tile holds fewer than 8192 successors, so the work classes of its rows start at bucket 16.)
+			// Long residual lists go to a whole warp each (buckets 0 and 1: first in the order); of the others, ALL rows with
+			// intervals come first (buckets 16..63), then the rest (80..127), each part sorted by work: warps without interval
+			// rows never enter the merging loop of row_extras_core.  (A tile holds fewer than 8192 successors, so the work
+			// classes of its rows start at 16.)
 			if (nres >= COOP_LONG && ic <= 32) bucket[0] = ic ? 0 : 1;
-			else if (nextra) bucket[0] = 2 * work_bucket(nextra) + (ic ? 0 : 1);
+			else if (nextra) bucket[0] = (ic ? 0 : BIN_CLASSES) + work_bucket(nextra);
 		}
 	}
 	S.ncopied[tid] = (uint16_t)ncop;

@@ -566,11 +566,13 @@ __device__ __forceinline__ void extras_tile(const GraphDev &g, const RangeDev &R
 					// rows with intervals first inside each class: warps without any skip the merging loop of row_extras
 					bool has_int = false;
 					if (g.min_interval != 0) { RD t = r; has_int = t.gamma() != 0; }
-					bucket[q] = 2 * work_bucket(nextra) + (has_int ? 0 : 1);
+					// sort key: ALL rows with intervals first, then by work -- warps whose rows have no intervals (four out of five)
+					// never enter the merging loop of row_extras_core, which costs twice the plain gap loop per successor
+					bucket[q] = (has_int ? 0 : BIN_CLASSES) + work_bucket(nextra);
 					S.pos[id] = r.tell() + (RD::IS_GLOBAL ? 0ull : (S.wbase << 5));  // absolute: tile_reader() converts back
 					S.nextra[id] = nextra;
 					S.ncopied[id] = h.ncopied;
-					S.cls[id] = (uint8_t)bucket[q];
+					S.cls[id] = (uint8_t)(2 * work_bucket(nextra) + (has_int ? 0 : 1));  // class in the global heavy-row list
 				}
 			}
 		}
@@ -578,28 +580,36 @@ __device__ __forceinline__ void extras_tile(const GraphDev &g, const RangeDev &R
 	}
 	uint32_t total;
 	block_bin_sort<ERPT>(bucket, S.hist, S.order, &total);
-	// after the sort S.hist[b] is the first position of class b; the classes of >= HEAVY extras come first
-	const int first_light = 2 * work_bucket(HEAVY - 1);
-	const uint32_t nheavy = H.rows ? S.hist[first_light] : 0;
+	// after the sort S.hist[b] is the first position of bucket b: rows with intervals in buckets [0, 64), the others in
+	// [64, 128), each half heaviest first; the first fl buckets of either half hold the rows of >= HEAVY extras
+	const int fl = H.rows ? work_bucket(HEAVY - 1) : 0;
+	const uint32_t a0 = S.hist[fl], a1 = S.hist[BIN_CLASSES], b0 = S.hist[BIN_CLASSES + fl];
+	const uint32_t nheavy_a = a0, nheavy = a0 + (b0 - a1);
 	if (nheavy) {
-		if (threadIdx.x < first_light) S.count[threadIdx.x] = S.hist[threadIdx.x + 1] - S.hist[threadIdx.x];
+		// per-class counts of the global list: class 2c (with intervals) = bucket c, class 2c + 1 = bucket 64 + c
+		if ((int)threadIdx.x < 2 * fl) {
+			const int bk = (threadIdx.x & 1 ? BIN_CLASSES : 0) + (int)(threadIdx.x >> 1);
+			S.count[threadIdx.x] = S.hist[bk + 1] - S.hist[bk];
+		}
 		if (threadIdx.x == 0) S.gbase = atomicAdd(&H.counters[0], (unsigned long long)nheavy);
 		__syncthreads();
-		if (threadIdx.x < first_light && S.count[threadIdx.x]) atomicAdd(&H.counters[1 + threadIdx.x], (unsigned long long)S.count[threadIdx.x]);
+		if ((int)threadIdx.x < 2 * fl && S.count[threadIdx.x]) atomicAdd(&H.counters[1 + threadIdx.x], (unsigned long long)S.count[threadIdx.x]);
 		for (uint32_t t = threadIdx.x; t < nheavy; t += TPB) {
-			const int id = S.order[t];
+			const int id = S.order[t < nheavy_a ? t : a1 + (t - nheavy_a)];
 			H.rows[S.gbase + t] = (uint32_t)(base + id);
 			H.cls[S.gbase + t] = S.cls[id];
 		}
 	}
-	// serial part: the lanes of a warp take rows of the same class and run them in lock step
+	// serial part: the lanes of a warp take rows of the same class and run them in lock step (first the light rows with
+	// intervals, positions [a0, a1) of the order, then those without, [b0, total))
+	const uint32_t la = a1 - a0, nlight = la + (total - b0);
 #pragma unroll 1
-	for (uint32_t tb = nheavy + (threadIdx.x & ~31u); tb < total; tb += TPB) {
+	for (uint32_t tb = (threadIdx.x & ~31u); tb < nlight; tb += TPB) {
 		const uint32_t t = tb + (threadIdx.x & 31u);
-		const bool active = t < total;
+		const bool active = t < nlight;
 		const unsigned mask = __ballot_sync(FULL_MASK, active);
 		if (active) {
-			const int id = S.order[t];
+			const int id = S.order[t < la ? a0 + t : b0 + (t - la)];
 			const int64_t k = base + id;
 			RD r;
 			tile_reader<RD>(r, g, S, S.pos[id]);
