@@ -339,26 +339,37 @@ def config_c1(torch, wg, dev, local_rank, stream):
             "roofline": {"bound": "hbm", "achieved": alg / (ms * 1e-3) / 1e9, "unit": "GB/s", "frac": alg / (ms * 1e-3) / 1e9 / peaks()[0], "algorithmic_bytes": alg}}
 
 
-def config_c3(torch, wg, args, dev, local_rank, stream, d_rowptr, d_col, threads):
+def config_c3(torch, wg, args, dev, local_rank, stream, d_rowptr, d_col, n, arcs, checksum, threads):
     """configs[2]: the same graph recompressed with maxrefcount = 2147483647 (what -m -1 writes): unbounded reference chains,
-    level-by-level copy resolution as deep as the longest chain."""
-    sh = Shard(args, 0, 1, threads, maxref=2147483647)
-    e = sh.e
-    n, arcs = e.n, e.arcs
-    g = wg.GpuBVGraph.load_slice(e.properties_text(), 0, n, e.graph, e.offsets_stream, device=local_rank, cuda_stream=stream.cuda_stream)
-    if arcs > d_col.numel():
-        d_col = torch.empty(arcs, dtype=torch.int64, device=dev)
+    level-by-level copy resolution as deep as the longest chain.  The recompression is done by the device compressor
+    (wgbv_encode_csr) from the CSR decoded above, so it is literally the same graph; what is decoded back must hash to the
+    generator's checksum of that graph."""
+    import bvgen
+    P = split_nodes(args.nodes)
+    t0 = time.time()
+    out = np.zeros(arcs * 2 + n + 64, dtype=np.uint8)
+    graph, bits, node_bits = wg.encode_csr_device(n, d_rowptr.data_ptr(), d_col.data_ptr(), arcs, max_ref_count=2147483647, split_nodes=P,
+                                                  device=local_rank, out=out, want_node_bits=True)
+    offsets_stream = bvgen.write_codes(bvgen.GAMMA, np.concatenate([np.zeros(1, dtype=np.uint64), node_bits[:n]]))[0]
+    enc_s = time.time() - t0
+    props = ("graphclass=it.unimi.dsi.big.webgraph.BVGraph\nversion=0\n"
+             f"nodes={n}\narcs={arcs}\nwindowsize=7\nmaxrefcount=2147483647\nminintervallength=4\nzetak=3\ncompressionflags=\n")
+    g = wg.GpuBVGraph.load_slice(props, 0, n, graph, offsets_stream, device=local_rank, cuda_stream=stream.cuda_stream)
+    c_rowptr = torch.empty(n + 1, dtype=torch.int64, device=dev)
+    c_col = torch.empty(max(arcs, 1), dtype=torch.int64, device=dev)
     l0 = g.kernelLaunches()
-    ms = time_decode(torch, g, 0, n, d_rowptr, d_col, arcs, 3, 2)
+    ms = time_decode(torch, g, 0, n, c_rowptr, c_col, arcs, 3, 2)
     launches = (g.kernelLaunches() - l0) // 5
-    ok = g.csrChecksumDevice(0, n, d_rowptr.data_ptr(), d_col.data_ptr()) == e.checksum and int(d_rowptr[n].item()) == arcs
+    ok = g.csrChecksumDevice(0, n, c_rowptr.data_ptr(), c_col.data_ptr()) == checksum and int(c_rowptr[n].item()) == arcs
+    ok = ok and bool(torch.equal(c_rowptr, d_rowptr))
     alg = g.algorithmicBytes(0, n, arcs)
-    st = stats_of(e)
     g.close()
-    return {"workload": f"copy-model graph of the headline, {n} nodes, recompressed with maxrefcount=2147483647", "nodes": n, "arcs": arcs,
-            "bits_per_arc": e.graph_bits / max(arcs, 1), "avg_reference_chain": st["avgref_chain"], "ms": ms, "value": arcs / (ms * 1e-3), "unit": UNIT,
-            "gpu_launches": int(launches), "verified": bool(ok), "verified_how": "checksum of every row against the generator's, taken before encoding",
-            "generation_s": sh.gen_s,
+    del c_rowptr, c_col, out
+    return {"workload": f"the headline graph ({n} nodes) recompressed on the device with maxrefcount=2147483647", "nodes": n, "arcs": arcs,
+            "bits_per_arc": bits / max(arcs, 1), "ms": ms, "value": arcs / (ms * 1e-3), "unit": UNIT,
+            "gpu_launches": int(launches), "verified": bool(ok),
+            "verified_how": "checksum of every decoded row against the generator's checksum of the graph (taken before any encoding); row pointers equal to the headline decode's",
+            "recompression_s": enc_s,
             "roofline": {"bound": "hbm", "achieved": alg / (ms * 1e-3) / 1e9, "unit": "GB/s", "frac": alg / (ms * 1e-3) / 1e9 / peaks()[0], "algorithmic_bytes": alg}}
 
 
@@ -720,7 +731,7 @@ def run_config(args, torch, dist, wg, rank, local_rank, world, dev, stream, thre
         c1 = config_c1(torch, wg, dev, local_rank, stream)
         g.close()
         g = None
-        c3 = config_c3(torch, wg, args, dev, local_rank, stream, d_rowptr, d_col, threads)
+        c3 = config_c3(torch, wg, args, dev, local_rank, stream, d_rowptr, d_col, n, arcs, e.checksum, threads)
 
     line = None
     if rank == 0:
