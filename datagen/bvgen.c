@@ -693,6 +693,29 @@ uint64_t bvg_write_labels(int kind, int width, int64_t n, const int64_t *rowptr,
 	return bits;
 }
 
+/* List-valued labels (FixedWidthIntListLabel.toBitStream, labelling/FixedWidthIntListLabel.java:81-85, and
+ * FixedWidthLongListLabel.java:87-92): per arc gamma(length) and then each element in `width` bits (0..64).
+ * list_ptr[j] .. list_ptr[j + 1] are arc j's elements in `values`. */
+uint64_t bvg_write_label_lists(int width, int64_t n, const int64_t *rowptr, const int64_t *list_ptr, const int64_t *values, uint8_t *out,
+                               uint64_t out_cap, uint64_t *node_bits) {
+	obs_t o; memset(&o, 0, sizeof o);
+	const uint64_t mask = width >= 64 ? ~(uint64_t)0 : ((uint64_t)1 << width) - 1;
+	for (int64_t x = 0; x < n; x++) {
+		const uint64_t before = o.bits;
+		for (int64_t j = rowptr[x]; j < rowptr[x + 1]; j++) {
+			put_gamma(&o, (uint64_t)(list_ptr[j + 1] - list_ptr[j]));
+			for (int64_t t = list_ptr[j]; t < list_ptr[j + 1]; t++) obs_put_long(&o, (uint64_t)values[t] & mask, width);
+		}
+		node_bits[x] = o.bits - before;
+	}
+	obs_finish(&o);
+	const uint64_t bytes = (o.bits + 7) >> 3;
+	if (bytes <= out_cap) memcpy(out, o.buf, bytes);
+	const uint64_t bits = o.bits;
+	free(o.buf);
+	return bits;
+}
+
 /* The same for synthetic labels that need no value array (benchmark scale): arc number j (in CSR order) carries
  * label_of_arc(j, width) = the low `width` bits of j * 0x9E3779B97F4A7C15 >> 20.  Fixed-width labels only. */
 static inline uint64_t label_of_arc(uint64_t j, int width) {

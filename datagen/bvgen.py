@@ -69,6 +69,8 @@ def lib():
         L.bvg_csr_checksum.restype = C.c_uint64
         L.bvg_write_labels.argtypes = [C.c_int, C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
         L.bvg_write_labels.restype = C.c_uint64
+        L.bvg_write_label_lists.argtypes = [C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
+        L.bvg_write_label_lists.restype = C.c_uint64
         L.bvg_write_labels_synthetic.argtypes = [C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
         L.bvg_write_labels_synthetic.restype = C.c_uint64
         L.bvg_write_codes.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_uint64]
@@ -209,7 +211,7 @@ def write_codes(coding, values, k=3):
     return out[: (bits + 7) // 8].copy(), bits
 
 
-LABEL_FIXED_INT, LABEL_GAMMA_INT = 0, 1
+LABEL_FIXED_INT, LABEL_GAMMA_INT, LABEL_FIXED_INT_LIST, LABEL_FIXED_LONG_LIST = 0, 1, 2, 3
 
 
 def write_labels(kind, width, rowptr, values):
@@ -223,6 +225,23 @@ def write_labels(kind, width, rowptr, values):
     node_bits = np.zeros(max(n, 1), dtype=np.uint64)
     bits = lib().bvg_write_labels(kind, width, n, rowptr.ctypes.data, values.ctypes.data if values.size else None, out.ctypes.data, out.size,
                                   node_bits.ctypes.data)
+    assert (bits + 7) // 8 <= out.size
+    offs, _ = write_codes(GAMMA, np.concatenate([np.zeros(1, dtype=np.uint64), node_bits[:n]]))
+    return out[: (bits + 7) // 8].copy(), offs
+
+
+def write_label_lists(width, rowptr, list_ptr, values):
+    """The .labels and .labeloffsets streams of a graph whose arc j (CSR order) carries the list
+    values[list_ptr[j]:list_ptr[j + 1]] of `width`-bit elements (see bvg_write_label_lists)."""
+    rowptr = np.ascontiguousarray(rowptr, dtype=np.int64)
+    list_ptr = np.ascontiguousarray(list_ptr, dtype=np.int64)
+    values = np.ascontiguousarray(values, dtype=np.int64)
+    n = rowptr.size - 1
+    longest = int(np.diff(list_ptr).max()) if list_ptr.size > 1 else 0
+    out = np.zeros((values.size * width + (list_ptr.size - 1) * (2 * (longest + 1).bit_length() + 1)) // 8 + 64, dtype=np.uint8)
+    node_bits = np.zeros(max(n, 1), dtype=np.uint64)
+    bits = lib().bvg_write_label_lists(width, n, rowptr.ctypes.data, list_ptr.ctypes.data, values.ctypes.data if values.size else None,
+                                       out.ctypes.data, out.size, node_bits.ctypes.data)
     assert (bits + 7) // 8 <= out.size
     offs, _ = write_codes(GAMMA, np.concatenate([np.zeros(1, dtype=np.uint64), node_bits[:n]]))
     return out[: (bits + 7) // 8].copy(), offs

@@ -253,9 +253,17 @@ WGBV_API int wgbv_encode_csr(int device, const wgbv_props *props, int64_t first_
  *                            (device, `capacity` elements).  Asynchronous on the stream; errors at wgbv_stream_sync.
  *   wgbv_labels_decode_host  the same with host arrays (synchronous).
  * A stream, offsets and outdegrees that do not belong together give WGBV_ESTATE (the reference would return garbage).
+ * List-valued prototypes -- WGBV_LABEL_FIXED_INT_LIST = FixedWidthIntListLabel(key, width) (width 0..32; per arc
+ * readGamma() elements of readInt(width) each, FixedWidthIntListLabel.java:73-78) and WGBV_LABEL_FIXED_LONG_LIST =
+ * FixedWidthLongListLabel(key, width) (width 0..64, FixedWidthLongListLabel.java:78-84) -- have a ragged result:
+ *   wgbv_labels_decode_lists d_list_ptr (device, arcs + 1 entries) receives the start of every arc's list inside d_values
+ *                            (device, `capacity` elements; NULL: only the starts and *values_out, the total, are produced).
+ *                            Synchronises the stream once to learn the total.  wgbv_labels_decode refuses these kinds.
+ *   wgbv_labels_decode_lists_host  the same with host arrays; call it with h_values NULL to learn *values_out, then again
+ *                            with room for that many elements (or once with a capacity known to suffice).
  */
 typedef struct wgbv_labels wgbv_labels;
-enum { WGBV_LABEL_FIXED_INT = 0, WGBV_LABEL_GAMMA_INT = 1 };
+enum { WGBV_LABEL_FIXED_INT = 0, WGBV_LABEL_GAMMA_INT = 1, WGBV_LABEL_FIXED_INT_LIST = 2, WGBV_LABEL_FIXED_LONG_LIST = 3 };
 WGBV_API int wgbv_labels_open_mem(int device, int64_t nodes, int kind, int width, const uint8_t *labels, uint64_t labels_bytes,
                                   const uint8_t *labeloffsets, uint64_t labeloffsets_bytes, wgbv_labels **out);
 WGBV_API void wgbv_labels_close(wgbv_labels *l);
@@ -263,6 +271,10 @@ WGBV_API int wgbv_labels_decode(wgbv_stream *s, const wgbv_labels *l, int64_t fr
                                 int64_t *d_labels, uint64_t capacity);
 WGBV_API int wgbv_labels_decode_host(wgbv_stream *s, const wgbv_labels *l, int64_t from, int64_t to, const int64_t *h_rowptr,
                                      int64_t *h_labels, uint64_t capacity);
+WGBV_API int wgbv_labels_decode_lists(wgbv_stream *s, const wgbv_labels *l, int64_t from, int64_t to, const int64_t *d_rowptr,
+                                      int64_t *d_list_ptr, int64_t *d_values, uint64_t capacity, int64_t *values_out);
+WGBV_API int wgbv_labels_decode_lists_host(wgbv_stream *s, const wgbv_labels *l, int64_t from, int64_t to, const int64_t *h_rowptr,
+                                           int64_t *h_list_ptr, int64_t *h_values, uint64_t capacity, int64_t *values_out);
 
 /* outdegree(x) for a batch of arbitrary nodes (BVG:821-851): h_out[i] = outdegree(h_ids[i]).  Host buffers. */
 WGBV_API int wgbv_outdegrees(wgbv_stream *s, const int64_t *h_ids, uint64_t k, int64_t *h_out);

@@ -570,6 +570,32 @@ int64_t bvo_decode_labels(int kind, int width, const uint8_t *labels, uint64_t l
 	return w;
 }
 
+/* List-valued labels (FixedWidthIntListLabel.fromBitStream, labelling/FixedWidthIntListLabel.java:73-78; is_long:
+ * FixedWidthLongListLabel.java:78-84): per arc readGamma() elements of readInt(width) / readLong(width).  lens[j] receives
+ * the length of arc j's list; values (may be NULL: lengths only) the elements, `cap` of them at most.  Returns the number
+ * of elements, -1 if a node's labels do not end at the next offset, -2 if cap is too small. */
+int64_t bvo_decode_label_lists(int is_long, int width, const uint8_t *labels, uint64_t labels_bytes, const uint64_t *label_offsets,
+                               int64_t lo, int64_t hi, const int64_t *degrees, int64_t *lens, int64_t *values, int64_t cap) {
+	int64_t arc = 0, w = 0;
+	for (int64_t x = lo; x < hi; x++) {
+		ibs_t s; ibs_init(&s, labels, labels_bytes, label_offsets[x]);
+		for (int64_t j = 0; j < degrees[x - lo]; j++) {
+			const uint64_t len = ibs_gamma(&s);
+			lens[arc++] = (int64_t)len;
+			for (uint64_t t = 0; t < len; t++) {
+				const uint64_t v = ibs_bits(&s, width);
+				if (values) {
+					if (w >= cap) return -2;
+					values[w] = is_long ? (int64_t)v : (int64_t)(int32_t)(uint32_t)v;  /* long[] / int[] */
+				}
+				w++;
+			}
+		}
+		if (s.pos != label_offsets[x + 1]) return -1;
+	}
+	return w;
+}
+
 uint64_t bvo_read_code(const uint8_t *p, uint64_t nbytes, uint64_t *bitpos, int coding, int k) {
 	ibs_t s; ibs_init(&s, p, nbytes, *bitpos);
 	uint64_t v;

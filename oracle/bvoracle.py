@@ -61,6 +61,9 @@ def lib():
         L.bvo_decode_split.restype = C.c_int64
         L.bvo_decode_labels.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_uint64, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p]
         L.bvo_decode_labels.restype = C.c_int64
+        L.bvo_decode_label_lists.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_uint64, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p,
+                                             C.c_void_p, C.c_int64]
+        L.bvo_decode_label_lists.restype = C.c_int64
         L.bvo_random_access.argtypes = [C.POINTER(Params), C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_int64, C.c_int]
         L.bvo_random_access.restype = C.c_int64
         L.bvo_read_code.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64), C.c_int, C.c_int]
@@ -252,7 +255,42 @@ def symmetrize_csr(n, rowptr, col):
     return union_csr(n, rowptr, col, trp, tcol)
 
 
-LABEL_FIXED_INT, LABEL_GAMMA_INT = 0, 1
+LABEL_FIXED_INT, LABEL_GAMMA_INT, LABEL_FIXED_INT_LIST, LABEL_FIXED_LONG_LIST = 0, 1, 2, 3
+
+
+def _label_offsets(labeloffsets_bytes, n):
+    offs = np.ascontiguousarray(np.frombuffer(labeloffsets_bytes, dtype=np.uint8))
+    p = Params()
+    p.nodes = n
+    p.offset_coding = 2  # BVO_GAMMA
+    off = np.zeros(n + 1, dtype=np.uint64)
+    rc = lib().bvo_read_offsets(C.byref(p), offs.ctypes.data, offs.size, off.ctypes.data)
+    if rc:
+        raise _err(rc)
+    return off
+
+
+def decode_label_lists(kind, width, labels_bytes, labeloffsets_bytes, degrees, lo=0, hi=None):
+    """List-valued labels of the arcs of nodes [lo, hi) (see bvo_decode_label_lists): returns (list_ptr, values) with
+    arc j's list = values[list_ptr[j]:list_ptr[j + 1]].  Parity status: unpinned by the reference, like decode_labels."""
+    degrees = np.ascontiguousarray(degrees, dtype=np.int64)
+    n = degrees.size
+    hi = n if hi is None else hi
+    lab = np.ascontiguousarray(np.frombuffer(labels_bytes, dtype=np.uint8))
+    off = _label_offsets(labeloffsets_bytes, n)
+    part = np.ascontiguousarray(degrees[lo:hi])
+    lens = np.zeros(int(part.sum()), dtype=np.int64)
+    is_long = int(kind == LABEL_FIXED_LONG_LIST)
+    total = lib().bvo_decode_label_lists(is_long, width, lab.ctypes.data, lab.size, off.ctypes.data, lo, hi, part.ctypes.data, lens.ctypes.data, None, 0)
+    if total < 0:
+        raise ValueError("label stream and label offsets disagree")
+    values = np.zeros(total, dtype=np.int64)
+    got = lib().bvo_decode_label_lists(is_long, width, lab.ctypes.data, lab.size, off.ctypes.data, lo, hi, part.ctypes.data, lens.ctypes.data,
+                                       values.ctypes.data, total)
+    assert got == total
+    list_ptr = np.zeros(lens.size + 1, dtype=np.int64)
+    np.cumsum(lens, out=list_ptr[1:])
+    return list_ptr, values
 
 
 def decode_labels(kind, width, labels_bytes, labeloffsets_bytes, degrees, lo=0, hi=None):

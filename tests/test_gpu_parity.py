@@ -688,6 +688,45 @@ def test_arc_labels_equal_oracle(cnr, cnr_golden):
                 L.decode(cnr, rowptr[:3], n - 1, n + 1)
 
 
+def test_list_labels_equal_oracle(cnr, cnr_golden):
+    """SURVEY 8f-3, list-valued prototypes (FixedWidthIntListLabel.java:73-78, FixedWidthLongListLabel.java:78-84): per arc
+    a gamma-coded length and that many fixed-width elements; the device returns the list starts and the elements.  Int
+    lists of 0, 7 and 32 bits (sign), long lists of 33, 63 and 64 bits, empty lists, sub-ranges, a mismatched stream."""
+    deg, rowptr, col = cnr_golden
+    n = 60000
+    rp = rowptr[: n + 1]
+    arcs = int(rp[-1])
+    rng = np.random.default_rng(5)
+    for kind, width in ((wg.LABEL_FIXED_INT_LIST, 7), (wg.LABEL_FIXED_INT_LIST, 0), (wg.LABEL_FIXED_INT_LIST, 32),
+                        (wg.LABEL_FIXED_LONG_LIST, 33), (wg.LABEL_FIXED_LONG_LIST, 63), (wg.LABEL_FIXED_LONG_LIST, 64)):
+        lens = rng.integers(0, 6, arcs)
+        lens[rng.integers(0, arcs, 20)] = 300  # a few long lists
+        lp = np.zeros(arcs + 1, dtype=np.int64)
+        np.cumsum(lens, out=lp[1:])
+        raw = rng.integers(0, 1 << 63, int(lp[-1]), dtype=np.uint64) * 2 + rng.integers(0, 2, int(lp[-1]), dtype=np.uint64)
+        values = (raw >> np.uint64(64 - width) if width else raw * np.uint64(0)).view(np.int64)
+        lab, off = bg.write_label_lists(width, rp, lp, values)
+        elp, evals = bo.decode_label_lists(kind, width, lab, off, deg[:n])
+        assert np.array_equal(elp, lp)
+        want = values if kind == wg.LABEL_FIXED_LONG_LIST else values.astype(np.uint32).view(np.int32).astype(np.int64)
+        assert np.array_equal(evals, want)
+        with wg.GpuArcLabels(kind, width, lab, off, n) as L:
+            glp, gv = L.decodeLists(cnr, rp)
+            assert np.array_equal(glp, elp) and np.array_equal(gv, evals), (kind, width)
+            a, b = 12345, 40001
+            r2, _ = cnr.decodeToCSR(a, b)
+            glp, gv = L.decodeLists(cnr, r2, a, b)
+            assert np.array_equal(glp, elp[rp[a]:rp[b] + 1] - elp[rp[a]]) and np.array_equal(gv, evals[elp[rp[a]]:elp[rp[b]]])
+            glp, gv = L.decodeLists(cnr, np.zeros(1, dtype=np.int64), 5, 5)
+            assert glp.tolist() == [0] and gv.size == 0
+            with pytest.raises(wg.UnsupportedOperationException):
+                L.decode(cnr, rp)
+            wrong = rp.copy()
+            wrong[1:] += 1
+            with pytest.raises(wg.IllegalStateException):
+                L.decodeLists(cnr, wrong[:1001], 0, 1000)
+
+
 def test_device_compressor_reproduces_the_reference_fixture(cnr_basename, cnr_golden):
     """the device compressor (wgbv_encode_csr) given the golden successor lists and the fixture's parameters
     (w=7, maxRef=3, minInt=3, zeta_3; one run, as the fixture was stored) writes the reference's own cnr-2000.graph byte

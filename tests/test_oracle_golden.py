@@ -118,3 +118,29 @@ def test_label_streams_round_trip():
     j = np.arange(rp[-1], dtype=np.uint64)
     expect = ((j * np.uint64(bg.LABEL_HASH_MULTIPLIER)) >> np.uint64(20)) & np.uint64(1023)
     assert np.array_equal(bo.decode_labels(0, 10, lab, off, deg).astype(np.uint64), expect)
+
+
+def test_label_list_streams_round_trip():
+    """List-valued labels: datagen.write_label_lists (FixedWidthIntListLabel.toBitStream restated) against
+    oracle.decode_label_lists (fromBitStream restated), and a hand-checked stream: one arc with the list [5, 2] of 3-bit
+    elements = gamma(2) 011, then 101 010."""
+    import bvgen as bg
+    lab, off = bg.write_label_lists(3, np.array([0, 1]), np.array([0, 2]), np.array([5, 2]))
+    assert lab.tolist() == [0b01110101, 0b00000000]
+    lp, vals = bo.decode_label_lists(bo.LABEL_FIXED_INT_LIST, 3, lab, off, np.array([1]))
+    assert lp.tolist() == [0, 2] and vals.tolist() == [5, 2]
+    rng = np.random.default_rng(4)
+    deg = rng.integers(0, 7, 1500)
+    rp = np.concatenate([[0], np.cumsum(deg)]).astype(np.int64)
+    for kind, width in ((bo.LABEL_FIXED_INT_LIST, 0), (bo.LABEL_FIXED_INT_LIST, 13), (bo.LABEL_FIXED_INT_LIST, 32), (bo.LABEL_FIXED_LONG_LIST, 47),
+                        (bo.LABEL_FIXED_LONG_LIST, 64)):
+        lens = rng.integers(0, 9, int(rp[-1]))
+        lp = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+        raw = rng.integers(0, 1 << 63, int(lp[-1]), dtype=np.uint64) * 2 + 1
+        values = (raw >> np.uint64(64 - width) if width else raw * np.uint64(0)).view(np.int64)
+        lab, off = bg.write_label_lists(width, rp, lp, values)
+        glp, gv = bo.decode_label_lists(kind, width, lab, off, deg)
+        want = values if kind == bo.LABEL_FIXED_LONG_LIST else values.astype(np.uint32).view(np.int32).astype(np.int64)
+        assert np.array_equal(glp, lp) and np.array_equal(gv, want)
+        glp, gv = bo.decode_label_lists(kind, width, lab, off, deg, 500, 900)
+        assert np.array_equal(glp, lp[rp[500]:rp[900] + 1] - lp[rp[500]]) and np.array_equal(gv, want[lp[rp[500]]:lp[rp[900]]])

@@ -482,13 +482,14 @@ def store_csr(rowptr, col, basename=None, window_size=7, max_ref_count=3, min_in
     return graph, offsets, props
 
 
-LABEL_FIXED_INT, LABEL_GAMMA_INT = 0, 1
+LABEL_FIXED_INT, LABEL_GAMMA_INT, LABEL_FIXED_INT_LIST, LABEL_FIXED_LONG_LIST = 0, 1, 2, 3
 
 
 class GpuArcLabels:
     """The `.labels` / `.labeloffsets` pair of a BitStreamArcLabelledImmutableGraph on the device
     (labelling/BitStreamArcLabelledImmutableGraph.java:65-100): labels come back as an int64 array parallel to the
-    successors of the underlying graph.  kind: LABEL_FIXED_INT (FixedWidthIntLabel, `width` bits) or LABEL_GAMMA_INT."""
+    successors of the underlying graph.  kind: LABEL_FIXED_INT (FixedWidthIntLabel, `width` bits), LABEL_GAMMA_INT, or the
+    list-valued LABEL_FIXED_INT_LIST / LABEL_FIXED_LONG_LIST (decodeLists)."""
 
     def __init__(self, kind, width, labels_bytes, labeloffsets_bytes, nodes, device=0):
         lab = np.ascontiguousarray(np.frombuffer(labels_bytes, dtype=np.uint8)) if not isinstance(labels_bytes, np.ndarray) else np.ascontiguousarray(labels_bytes)
@@ -531,6 +532,29 @@ class GpuArcLabels:
     def decodeDevice(self, graph, from_, to, d_rowptr, d_labels, capacity):
         """Device buffers (int pointers), asynchronous on the graph copy's stream."""
         _lib.check(_lib.lib().wgbv_labels_decode(graph._st.h, self.h, from_, to, C.c_void_p(d_rowptr), C.c_void_p(d_labels), capacity))
+
+    def decodeLists(self, graph, rowptr, from_=0, to=None):
+        """List-valued labels (FixedWidthIntListLabel / FixedWidthLongListLabel) of the arcs of nodes [from, to): returns
+        (list_ptr, values), arc j's list being values[list_ptr[j]:list_ptr[j + 1]] (host arrays)."""
+        to = self.nodes if to is None else to
+        rowptr = np.ascontiguousarray(rowptr, dtype=np.int64)
+        if rowptr.size != to - from_ + 1:
+            raise IllegalArgumentException("rowptr must have to - from + 1 entries")
+        arcs = int(rowptr[-1] - rowptr[0])
+        list_ptr = np.empty(arcs + 1, dtype=np.int64)
+        total = C.c_int64(0)
+        f = _lib.lib().wgbv_labels_decode_lists_host
+        _lib.check(f(graph._st.h, self.h, from_, to, rowptr.ctypes.data, list_ptr.ctypes.data, None, 0, C.byref(total)))
+        values = np.empty(max(total.value, 1), dtype=np.int64)
+        _lib.check(f(graph._st.h, self.h, from_, to, rowptr.ctypes.data, list_ptr.ctypes.data, values.ctypes.data, total.value, C.byref(total)))
+        return list_ptr, values[: total.value]
+
+    def decodeListsDevice(self, graph, from_, to, d_rowptr, d_list_ptr, d_values, capacity):
+        """Device buffers; d_values 0: only the list starts.  Returns the number of elements of the range."""
+        total = C.c_int64(0)
+        _lib.check(_lib.lib().wgbv_labels_decode_lists(graph._st.h, self.h, from_, to, C.c_void_p(d_rowptr), C.c_void_p(d_list_ptr),
+                                                       C.c_void_p(d_values) if d_values else None, capacity, C.byref(total)))
+        return total.value
 
 
 class NodeIterator:

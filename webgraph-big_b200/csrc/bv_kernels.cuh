@@ -195,6 +195,10 @@ int device_ef_build(const uint64_t *d_off, uint64_t n, uint64_t base, uint64_t l
 // exact number from rowptr)
 void launch_labels(const Launch &L, const GraphDev &lab, int kind, int width, int64_t from, int64_t count, const int64_t *rowptr,
                    int64_t *out, uint64_t capacity, uint64_t arcs_bound);
+// list-valued labels: fill = false writes every arc's list length to lens[arc]; fill = true reads the exclusive prefix sums from
+// lens and writes the elements to values
+void launch_label_lists(const Launch &L, const GraphDev &lab, bool fill, int width, int is_long, int64_t from, int64_t count, const int64_t *rowptr,
+                        int64_t *lens, int64_t *values, uint64_t capacity);
 // byte-swap the uploaded stream into big-endian 64-bit words, in place
 void launch_bswap(const Launch &L, uint64_t *words, uint64_t nwords);
 // A handful of device scalars for the host, written by a kernel straight into mapped pinned host memory: unlike a small

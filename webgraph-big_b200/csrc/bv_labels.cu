@@ -9,6 +9,9 @@
 // fixed-width ones one label per thread (see k_labels_fixed):
 //   kind WGBV_LABEL_FIXED_INT  FixedWidthIntLabel: readInt(width)   (FixedWidthIntLabel.java:70-73)
 //   kind WGBV_LABEL_GAMMA_INT  GammaCodedIntLabel: readGamma()      (GammaCodedIntLabel.java:60-64)
+//   kind WGBV_LABEL_FIXED_INT_LIST / _LONG_LIST  FixedWidthIntListLabel / FixedWidthLongListLabel: readGamma() elements of
+//        readInt(width) / readLong(width) each (FixedWidthIntListLabel.java:73-78, FixedWidthLongListLabel.java:78-84):
+//        a ragged result, list_ptr[arc] .. list_ptr[arc + 1] into a values array (k_label_lists: lengths, scan, values)
 // A node whose labels do not end where the next node's begin raises ERR_DEGREE (the stream, the offsets and the
 // outdegrees do not belong together).
 #include "bv_block.cuh"
@@ -83,6 +86,44 @@ void launch_labels(const Launch &L, const GraphDev &lab, int kind, int width, in
 		k_labels<1><<<grid_for(count, TPB), TPB, 0, L.stream>>>(lab, from, count, rowptr, width, out, capacity);
 		WGBV_LAUNCHED(L);
 	}
+}
+
+// List-valued labels.  FILL = false: the number of elements of every arc's list goes to lens[arc]; FILL = true: lens holds
+// the exclusive prefix sums and the elements go to values.  One lane per node (the lists of a node's arcs follow one
+// another in the stream and each starts with its own length).
+template <bool FILL>
+__global__ void __launch_bounds__(TPB) k_label_lists(GraphDev lab, int64_t from, int64_t count, const int64_t *__restrict__ rp, int width, int is_long,
+                                                     int64_t *lens, int64_t *__restrict__ values, uint64_t capacity) {
+	const int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
+	if (i >= count) return;
+	const int64_t a = rp[i] - rp[0], b = rp[i + 1] - rp[0];
+	const uint64_t pos = ef_get(lab, from + i), end = ef_get(lab, from + i + 1);
+	BitReader r;
+	r.init(lab, pos);
+	for (int64_t j = a; j < b; j++) {
+		const uint64_t n = r.gamma();
+		if (n > 0x7fffffffull || r.tell() + n * (uint64_t)width > end) { raise(lab, ERR_DEGREE); return; }
+		if (!FILL) {
+			lens[j] = (int64_t)n;
+			r.seek(r.tell() + n * (uint64_t)width);
+		} else {
+			const int64_t o = lens[j];
+			if ((uint64_t)o + n > capacity) { raise(lab, ERR_CAPACITY); return; }
+			for (uint64_t t = 0; t < n; t++) {
+				const uint64_t v = width ? r.bits((unsigned)width) : 0;
+				values[o + (int64_t)t] = is_long ? (int64_t)v : (int64_t)(int32_t)(uint32_t)v;  // (the Java fields are long[] / int[])
+			}
+		}
+	}
+	if (r.tell() != end) raise(lab, ERR_DEGREE);
+}
+
+void launch_label_lists(const Launch &L, const GraphDev &lab, bool fill, int width, int is_long, int64_t from, int64_t count, const int64_t *rowptr,
+                        int64_t *lens, int64_t *values, uint64_t capacity) {
+	if (count <= 0) return;
+	if (fill) k_label_lists<true><<<grid_for(count, TPB), TPB, 0, L.stream>>>(lab, from, count, rowptr, width, is_long, lens, values, capacity);
+	else k_label_lists<false><<<grid_for(count, TPB), TPB, 0, L.stream>>>(lab, from, count, rowptr, width, is_long, lens, values, capacity);
+	WGBV_LAUNCHED(L);
 }
 
 }  // namespace wgbv

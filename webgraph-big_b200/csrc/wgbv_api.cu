@@ -1259,8 +1259,9 @@ extern "C" int wgbv_labels_open_mem(int device, int64_t nodes, int kind, int wid
 	clear_error();
 	if (!out || (!labels && labels_bytes) || !labeloffsets || nodes < 0) return fail(WGBV_EARG, "null argument or negative node count");
 	*out = nullptr;
-	if (kind != WGBV_LABEL_FIXED_INT && kind != WGBV_LABEL_GAMMA_INT) return fail(WGBV_EUNSUPPORTED, "unknown label kind %d", kind);
-	if (kind == WGBV_LABEL_FIXED_INT && (width < 0 || width > 32)) return fail(WGBV_EARG, "a fixed-width int label has 0 to 32 bits, not %d", width);
+	if (kind < WGBV_LABEL_FIXED_INT || kind > WGBV_LABEL_FIXED_LONG_LIST) return fail(WGBV_EUNSUPPORTED, "unknown label kind %d", kind);
+	if ((kind == WGBV_LABEL_FIXED_INT || kind == WGBV_LABEL_FIXED_INT_LIST) && (width < 0 || width > 32)) return fail(WGBV_EARG, "a fixed-width int label has 0 to 32 bits, not %d", width);
+	if (kind == WGBV_LABEL_FIXED_LONG_LIST && (width < 0 || width > 64)) return fail(WGBV_EARG, "a fixed-width long label has 0 to 64 bits, not %d", width);
 	wgbv_props p{};
 	p.nodes = nodes;
 	p.window_size = 0;
@@ -1293,6 +1294,7 @@ extern "C" int wgbv_labels_decode(wgbv_stream *s, const wgbv_labels *l, int64_t 
 	if (!s || !l || !d_rowptr || (!d_labels && capacity)) return fail(WGBV_EARG, "null argument");
 	if (from < 0 || to < from || to > l->g->props.nodes) return fail(WGBV_EINDEX, "Node index out of range: [%lld, %lld)", (long long)from, (long long)to);
 	if (l->g->device != s->g->device) return fail(WGBV_EARG, "the labels and the stream live on different devices");
+	if (l->kind >= WGBV_LABEL_FIXED_INT_LIST) return fail(WGBV_EUNSUPPORTED, "list-valued labels are decoded by wgbv_labels_decode_lists");
 	CU(cudaSetDevice(s->g->device));
 	GraphDev lab = l->g->dev;
 	lab.err = s->d_err;
@@ -1300,6 +1302,45 @@ extern "C" int wgbv_labels_decode(wgbv_stream *s, const wgbv_labels *l, int64_t 
 	const uint64_t stream_bits = l->g->dev.bit_end;
 	const uint64_t bound = l->kind == WGBV_LABEL_FIXED_INT && l->width > 0 ? std::min<uint64_t>(capacity, stream_bits / (uint64_t)l->width) : capacity;
 	launch_labels(s->launch(), lab, l->kind, l->width, from, to - from, d_rowptr, d_labels, capacity, bound);
+	const cudaError_t e = cudaGetLastError();
+	if (e != cudaSuccess) return fail(WGBV_ECUDA, "kernel launch failed: %s", cudaGetErrorString(e));
+	return WGBV_OK;
+}
+
+extern "C" int wgbv_labels_decode_lists(wgbv_stream *s, const wgbv_labels *l, int64_t from, int64_t to, const int64_t *d_rowptr,
+                                        int64_t *d_list_ptr, int64_t *d_values, uint64_t capacity, int64_t *values_out) {
+	clear_error();
+	if (!s || !l || !d_rowptr || !d_list_ptr) return fail(WGBV_EARG, "null argument");
+	if (from < 0 || to < from || to > l->g->props.nodes) return fail(WGBV_EINDEX, "Node index out of range: [%lld, %lld)", (long long)from, (long long)to);
+	if (l->g->device != s->g->device) return fail(WGBV_EARG, "the labels and the stream live on different devices");
+	if (l->kind < WGBV_LABEL_FIXED_INT_LIST) return fail(WGBV_EUNSUPPORTED, "scalar labels are decoded by wgbv_labels_decode");
+	CU(cudaSetDevice(s->g->device));
+	GraphDev lab = l->g->dev;
+	lab.err = s->d_err;
+	const Launch L = s->launch();
+	const int is_long = l->kind == WGBV_LABEL_FIXED_LONG_LIST;
+	int rc;
+	PeekArgs pk;
+	pk.add(d_rowptr, 8);
+	pk.add(d_rowptr + (to - from), 8);
+	launch_peek(L, pk, s->d_pin);
+	CU(cudaStreamSynchronize(s->stream));
+	const int64_t arcs = (int64_t)s->h_pin[1] - (int64_t)s->h_pin[0];
+	if (arcs < 0) return fail(WGBV_EARG, "row pointers are not increasing");
+	if ((rc = s->scan_state.ensure((((size_t)arcs + 1) / 2048 + 2) * 8)) || (rc = s->ticket.ensure(64)) || (rc = s->c_arcs.ensure(((size_t)arcs + 1) * 8))) return rc;
+	// lengths of all lists, their prefix sums, then the elements
+	launch_label_lists(L, lab, false, l->width, is_long, from, to - from, d_rowptr, s->c_arcs.as<int64_t>(), nullptr, 0);
+	launch_scan64(L, s->c_arcs.as<unsigned long long>(), d_list_ptr, arcs, s->scan_state.as<uint64_t>(), s->ticket.as<uint32_t>());
+	PeekArgs pt;
+	pt.add(d_list_ptr + arcs, 8);
+	launch_peek(L, pt, s->d_pin);
+	if ((rc = collect_errors(s))) return rc;
+	const int64_t total = (int64_t)s->h_pin[0];
+	if (values_out) *values_out = total;
+	if (d_values) {
+		if ((uint64_t)total > capacity) return fail(WGBV_EARG, "capacity (%llu) is smaller than the %lld label elements of the range", (unsigned long long)capacity, (long long)total);
+		launch_label_lists(L, lab, true, l->width, is_long, from, to - from, d_rowptr, d_list_ptr, d_values, capacity);
+	}
 	const cudaError_t e = cudaGetLastError();
 	if (e != cudaSuccess) return fail(WGBV_ECUDA, "kernel launch failed: %s", cudaGetErrorString(e));
 	return WGBV_OK;
@@ -1320,6 +1361,33 @@ extern "C" int wgbv_labels_decode_host(wgbv_stream *s, const wgbv_labels *l, int
 	CU(cudaMemcpyAsync(s->rowptr.as<int64_t>(), h_rowptr, (size_t)(cnt + 1) * 8, cudaMemcpyHostToDevice, s->stream));
 	if ((rc = wgbv_labels_decode(s, l, from, to, s->rowptr.as<int64_t>(), s->col.as<int64_t>(), (uint64_t)arcs))) return rc;
 	if (arcs) CU(cudaMemcpyAsync(h_labels, s->col.as<int64_t>(), (size_t)arcs * 8, cudaMemcpyDeviceToHost, s->stream));
+	return collect_errors(s);
+}
+
+extern "C" int wgbv_labels_decode_lists_host(wgbv_stream *s, const wgbv_labels *l, int64_t from, int64_t to, const int64_t *h_rowptr,
+                                             int64_t *h_list_ptr, int64_t *h_values, uint64_t capacity, int64_t *values_out) {
+	clear_error();
+	if (!s || !l || !h_rowptr || !h_list_ptr) return fail(WGBV_EARG, "null argument");
+	if (from < 0 || to < from || to > l->g->props.nodes) return fail(WGBV_EINDEX, "Node index out of range: [%lld, %lld)", (long long)from, (long long)to);
+	const int64_t cnt = to - from, arcs = h_rowptr[cnt] - h_rowptr[0];
+	if (arcs < 0) return fail(WGBV_EARG, "row pointers are not increasing");
+	CU(cudaSetDevice(s->g->device));
+	int rc;
+	int64_t total = 0;
+	if ((rc = s->rowptr.ensure((size_t)(cnt + 1) * 8)) || (rc = s->col.ensure((size_t)(arcs + 1) * 8))) return rc;
+	CU(cudaMemcpyAsync(s->rowptr.as<int64_t>(), h_rowptr, (size_t)(cnt + 1) * 8, cudaMemcpyHostToDevice, s->stream));
+	if ((rc = wgbv_labels_decode_lists(s, l, from, to, s->rowptr.as<int64_t>(), s->col.as<int64_t>(), nullptr, 0, &total))) return rc;
+	if (values_out) *values_out = total;
+	CU(cudaMemcpyAsync(h_list_ptr, s->col.as<int64_t>(), (size_t)(arcs + 1) * 8, cudaMemcpyDeviceToHost, s->stream));
+	if (h_values) {
+		if ((uint64_t)total > capacity) return fail(WGBV_EARG, "capacity (%llu) is smaller than the %lld label elements of the range", (unsigned long long)capacity, (long long)total);
+		if ((rc = s->c_soff.ensure((size_t)std::max<int64_t>(total, 1) * 8))) return rc;
+		GraphDev lab = l->g->dev;
+		lab.err = s->d_err;
+		launch_label_lists(s->launch(), lab, true, l->width, l->kind == WGBV_LABEL_FIXED_LONG_LIST, from, cnt, s->rowptr.as<int64_t>(), s->col.as<int64_t>(),
+		                   s->c_soff.as<int64_t>(), (uint64_t)total);
+		if (total) CU(cudaMemcpyAsync(h_values, s->c_soff.as<int64_t>(), (size_t)total * 8, cudaMemcpyDeviceToHost, s->stream));
+	}
 	return collect_errors(s);
 }
 

@@ -217,6 +217,15 @@ public:
 		check(wgbv_labels_decode_host(g.stream(), h_, from, to, rowptr.data(), out.data(), out.size()));
 		return out;
 	}
+	// list-valued labels (FixedWidthIntListLabel / FixedWidthLongListLabel): arc j's list is values[list_ptr[j] .. list_ptr[j + 1])
+	void decodeLists(Graph &g, int64_t from, int64_t to, const std::vector<int64_t> &rowptr, std::vector<int64_t> &list_ptr, std::vector<int64_t> &values) {
+		if ((int64_t)rowptr.size() != to - from + 1) throw IllegalArgumentException("rowptr must have to - from + 1 entries");
+		list_ptr.resize((size_t)(rowptr.back() - rowptr.front()) + 1);
+		int64_t total = 0;
+		check(wgbv_labels_decode_lists_host(g.stream(), h_, from, to, rowptr.data(), list_ptr.data(), nullptr, 0, &total));
+		values.resize((size_t)total);
+		check(wgbv_labels_decode_lists_host(g.stream(), h_, from, to, rowptr.data(), list_ptr.data(), values.data(), values.size(), &total));
+	}
 };
 
 inline NodeIterator::NodeIterator(std::shared_ptr<Graph> g, int64_t from, int64_t upper)

@@ -63,6 +63,8 @@ public class GpuBVGraph extends ImmutableGraph {
 				FunctionDescriptor.of(JAVA_INT, JAVA_INT, JAVA_LONG, JAVA_INT, JAVA_INT, ADDRESS, JAVA_LONG, ADDRESS, JAVA_LONG, ADDRESS));
 		static final MethodHandle LABELS_DECODE_HOST = h("wgbv_labels_decode_host",
 				FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_LONG, JAVA_LONG, ADDRESS, ADDRESS, JAVA_LONG));
+		static final MethodHandle LABELS_DECODE_LISTS_HOST = h("wgbv_labels_decode_lists_host",
+				FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_LONG, JAVA_LONG, ADDRESS, ADDRESS, ADDRESS, JAVA_LONG, ADDRESS));
 		static final MethodHandle LABELS_CLOSE = h("wgbv_labels_close", FunctionDescriptor.ofVoid(ADDRESS));
 
 		/** Status code to the exception the reference throws at the same place (include/wgbv.h). */
@@ -204,6 +206,24 @@ public class GpuBVGraph extends ImmutableGraph {
 	}
 
 	@Override
+	/** List-valued labels (FixedWidthIntListLabel, FixedWidthLongListLabel) of the arcs of [from, to): returns { listPtr
+	 *  (arcs + 1 longs), values }; the list of arc j is values[listPtr[j] .. listPtr[j + 1]). */
+	public MemorySegment[] decodeLabelLists(final MemorySegment labels, final long from, final long to, final MemorySegment rowptr, final Arena a) {
+		final long arcs = rowptr.getAtIndex(JAVA_LONG, to - from) - rowptr.getAtIndex(JAVA_LONG, 0);
+		final MemorySegment listPtr = a.allocate((arcs + 1) * 8, 8), total = a.allocate(8, 8);
+		try {
+			Wgbv.check((int)Wgbv.LABELS_DECODE_LISTS_HOST.invokeExact(stream, labels, from, to, rowptr, listPtr, MemorySegment.NULL, 0L, total));
+			final long count = total.get(JAVA_LONG, 0);
+			final MemorySegment values = a.allocate(Math.max(count, 1) * 8, 8);
+			Wgbv.check((int)Wgbv.LABELS_DECODE_LISTS_HOST.invokeExact(stream, labels, from, to, rowptr, listPtr, values, count, total));
+			return new MemorySegment[] { listPtr, values };
+		} catch (final RuntimeException e) {
+			throw e;
+		} catch (final Throwable t) {
+			throw new RuntimeException(t);
+		}
+	}
+
 	/** Labels of the arcs of [from, to), parallel to the successors that {@link #decodeToCSR} returns for the same range:
 	 *  labels = handle from wgbv_labels_open_mem over the .labels / .labeloffsets of a BitStreamArcLabelledImmutableGraph
 	 *  whose underlying graph is this one; rowptr = first segment returned by decodeToCSR(from, to, a). */
