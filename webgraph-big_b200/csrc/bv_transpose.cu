@@ -14,8 +14,8 @@
 //
 // LSD radix sort, RS_BITS bits per pass over the target half only: ceil(log2(n) / RS_BITS) passes (3 for 10^8 nodes).
 // Ranks are computed without atomics on the data path: a warp owns 512 consecutive words of the tile, finds the lanes
-// that hold the same digit with __match_any_sync (rank in the warp = number of lower lanes with that digit) and keeps
-// one running base per (warp, digit) in shared memory, which is what makes the pass stable.
+// that hold the same digit with one ballot per digit bit (rank in the warp = number of lower lanes with that digit) and
+// keeps one running count per (warp, digit) in shared memory, which is what makes the pass stable.
 #include "bv_block.cuh"
 #include "bv_kernels.cuh"
 
@@ -57,7 +57,13 @@ __global__ void __launch_bounds__(TPB) k_t_pack(GraphDev g, int64_t n, const int
                                                 uint32_t *__restrict__ counts) {
 	__shared__ int64_t s_row[2];
 	__shared__ uint32_t hist[RS_DIGITS];  // digits of radix pass 0 (bits 32 .. 32 + RS_BITS of the packed word)
+	// rowmap[p]: the row of arc j0 + p, relative to the tile's first row.  Every row of the tile marks the position of
+	// its first arc (atomicMax: of several rows starting at one position -- empty ones and the row that follows -- the
+	// last owns the arc), an inclusive max-scan spreads the marks to the right.
+	__shared__ uint32_t rowmap[PACK_TILE];
+	__shared__ uint32_t wmax[TPB / 32];
 	for (int d = threadIdx.x; d < RS_DIGITS; d += TPB) hist[d] = 0;
+	for (int p = threadIdx.x; p < PACK_TILE; p += TPB) rowmap[p] = 0;
 	const uint64_t j0 = (uint64_t)blockIdx.x * PACK_TILE;
 	const uint64_t j1 = j0 + PACK_TILE < arcs ? j0 + PACK_TILE : arcs;
 	const int64_t base = rp[0];
@@ -65,12 +71,40 @@ __global__ void __launch_bounds__(TPB) k_t_pack(GraphDev g, int64_t n, const int
 	if (threadIdx.x == 32) s_row[1] = row_of(rp, 0, n - 1, base + (int64_t)j1 - 1);
 	__syncthreads();
 	const int64_t r0 = s_row[0], r1 = s_row[1];
+	for (int64_t r = r0 + 1 + threadIdx.x; r <= r1; r += TPB) {
+		const int64_t p = rp[r] - base - (int64_t)j0;  // in (0, PACK_TILE): rows after r0 start inside the tile
+		atomicMax(&rowmap[p], (uint32_t)(r - r0));
+	}
+	__syncthreads();
+	{
+		// every warp scans its 512 positions, 32 at a time; the warps' maxima are combined when the map is read
+		const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+		uint32_t carry = 0;
+#pragma unroll 4
+		for (int q = 0; q < PACK_ITEMS; q++) {
+			const int p = (int)warp * (32 * PACK_ITEMS) + q * 32 + (int)lane;
+			uint32_t v = rowmap[p];
+#pragma unroll
+			for (int o = 1; o < 32; o <<= 1) {
+				const uint32_t t = __shfl_up_sync(FULL_MASK_T, v, o);
+				if ((int)lane >= o && t > v) v = t;
+			}
+			if (carry > v) v = carry;
+			rowmap[p] = v;
+			carry = __shfl_sync(FULL_MASK_T, v, 31);
+		}
+		if (lane == 0) wmax[warp] = carry;
+	}
+	__syncthreads();
 #pragma unroll
 	for (int q = 0; q < PACK_ITEMS; q++) {
-		const uint64_t j = j0 + (uint64_t)q * TPB + threadIdx.x;
+		const uint32_t p = (uint32_t)q * TPB + threadIdx.x;
+		const uint64_t j = j0 + p;
 		if (j < j1) {
 			const int64_t y = col[j];
-			const int64_t x = row_of(rp, r0, r1, base + (int64_t)j);
+			uint32_t rel = rowmap[p];
+			for (uint32_t w = 0; w < p / (32 * PACK_ITEMS); w++) rel = wmax[w] > rel ? wmax[w] : rel;
+			const int64_t x = r0 + rel;
 			if (y < 0 || y >= n) {
 				raise(g, ERR_INDEX);
 				pairs[j] = (uint64_t)x;  // keeps the sort well defined; the call fails anyway
@@ -124,16 +158,35 @@ __global__ void __launch_bounds__(TPB, 4) k_rs_scatter(const uint64_t *__restric
 	const uint64_t t0 = (uint64_t)blockIdx.x * RS_TILE;
 	const uint64_t w0 = t0 + (uint64_t)warp * RS_WARP_ITEMS;
 	uint64_t key[RS_ITEMS];
-	// counts per (warp, digit)
+	uint32_t offp[RS_ITEMS / 2];  // per word: its index among the warp's words with the same digit (10 bits), two per register
+	// counts per (warp, digit).  The lanes holding the same digit are found with one ballot per digit bit (match.any
+	// costs the address-divergence unit a step per distinct value: with it this kernel ran at 95 % of that pipe and
+	// nothing else); rank in the warp = number of lower lanes with the digit, and the count so far of the (warp, digit)
+	// pair -- read before the first lane of the group adds the group -- makes the index stable across the rounds.
+#pragma unroll
+	for (int r = 0; r < RS_ITEMS; r++) {
+		const uint64_t j = w0 + (uint64_t)r * 32 + lane;
+		key[r] = j < count ? in[j] : 0;
+	}
 #pragma unroll
 	for (int r = 0; r < RS_ITEMS; r++) {
 		const uint64_t j = w0 + (uint64_t)r * 32 + lane;
 		const bool valid = j < count;
-		key[r] = valid ? in[j] : 0;
-		const uint32_t d = valid ? (uint32_t)(key[r] >> shift) & (RS_DIGITS - 1) : (uint32_t)RS_DIGITS;  // RS_DIGITS: no word
-		const unsigned peers = __match_any_sync(FULL_MASK_T, d);
-		if (valid && (peers & lt) == 0) S.wbase[warp][d] += (uint32_t)__popc(peers);
+		const uint32_t d = (uint32_t)(key[r] >> shift) & (RS_DIGITS - 1);
+		unsigned peers = __ballot_sync(FULL_MASK_T, valid);
+#pragma unroll
+		for (int b = 0; b < RS_BITS; b++) {
+			const bool bit = (d >> b) & 1u;
+			const unsigned bal = __ballot_sync(FULL_MASK_T, bit);
+			peers &= bit ? bal : ~bal;
+		}
+		const uint32_t rank = (uint32_t)__popc(peers & lt);
+		const uint32_t b0 = valid ? S.wbase[warp][d] : 0u;
 		__syncwarp();
+		if (valid && rank == 0) S.wbase[warp][d] = b0 + (uint32_t)__popc(peers);
+		__syncwarp();
+		if (r & 1) offp[r >> 1] |= (b0 + rank) << 16;
+		else offp[r >> 1] = b0 + rank;
 	}
 	__syncthreads();
 	// per digit: bases of the warps inside the digit's run; then the runs' first slots (exclusive scan over the digits,
@@ -170,16 +223,9 @@ __global__ void __launch_bounds__(TPB, 4) k_rs_scatter(const uint64_t *__restric
 #pragma unroll
 	for (int r = 0; r < RS_ITEMS; r++) {
 		const uint64_t j = w0 + (uint64_t)r * 32 + lane;
-		const bool valid = j < count;
-		const uint32_t d = valid ? (uint32_t)(key[r] >> shift) & (RS_DIGITS - 1) : (uint32_t)RS_DIGITS;
-		const unsigned peers = __match_any_sync(FULL_MASK_T, d);
-		const uint32_t rank = (uint32_t)__popc(peers & lt);
-		uint32_t b = 0;
-		if (valid) b = S.wbase[warp][d];
-		__syncwarp();
-		if (valid && rank == 0) S.wbase[warp][d] = b + (uint32_t)__popc(peers);
-		__syncwarp();
-		if (valid) S.sorted[S.dstart[d] + b + rank] = key[r];
+		const uint32_t d = (uint32_t)(key[r] >> shift) & (RS_DIGITS - 1);
+		const uint32_t off = (offp[r >> 1] >> ((r & 1) * 16)) & 0xffffu;
+		if (j < count) S.sorted[S.dstart[d] + S.wbase[warp][d] + off] = key[r];
 	}
 	__syncthreads();
 	const uint32_t here = count - t0 < (uint64_t)RS_TILE ? (uint32_t)(count - t0) : (uint32_t)RS_TILE;
