@@ -397,6 +397,7 @@ struct ExtrasSmem {
 	// kept in `order`, which is not needed before the sort: 256 uint32 -- see hdeg().  Four blocks of this size fit an SM.)
 	uint64_t warp_sum[TPB / 32];
 	uint64_t tile_base;          // arcs before the tile
+	uint64_t tile_total;         // arcs of the tile
 	uint32_t tile;
 };
 
@@ -427,7 +428,7 @@ __device__ __forceinline__ void tile_reader<PosReader>(PosReader &r, const Graph
 // and rp of the tile's rows in global memory, the rows' offsets in S.pos and the outdegrees of the window before the
 // tile in S.hdeg.  Same checks as k_header.
 template <int DEF, class RD>
-__device__ __forceinline__ void tile_front_end(const GraphDev &g, const RangeDev &R, ExtrasSmem &S, int64_t base, int64_t count) {
+__device__ __forceinline__ void tile_front_end(const GraphDev &g, const RangeDev &R, ExtrasSmem &S, int64_t base, int64_t count, uint64_t &rel) {
 	const int64_t tend = base + ETILE < count ? base + ETILE : count;
 	// outdegrees of the rows before the tile: not in the staged bits, a handful of global reads
 	if ((int)threadIdx.x < g.window && (int64_t)threadIdx.x < base && threadIdx.x < 256) {
@@ -486,17 +487,32 @@ __device__ __forceinline__ void tile_front_end(const GraphDev &g, const RangeDev
 		}
 		const uint64_t tile_total = __shfl_sync(FULL_MASK, w, TPB / 32 - 1);
 		if (lane < TPB / 32) S.warp_sum[lane] = w;  // inclusive per warp
+		// the tile's total is published at once; the arcs before the tile are looked up later (tile_finish), when the
+		// heads of the tile have been parsed: nothing before that needs them, and by then the tiles before this one have
+		// published theirs -- a block that waits here waits for the slowest of its 32 predecessors
+		volatile uint64_t *state = R.tile_state;
+		if (lane == 0) {
+			S.tile_total = tile_total;
+			state[S.tile] = (S.tile == 0 ? FLAG_PFX : FLAG_AGG) | tile_total;
+		}
+	}
+	__syncthreads();
+	rel = (warp ? S.warp_sum[warp - 1] : 0) + (inc - sum);
+}
+
+// Second half of the front end: arcs before the tile by decoupled look-back (warp 0; `st` = the states of the 32 tiles
+// before this one, read before the sort so that the latency is spent there), then the row pointers of the tile.
+__device__ __forceinline__ void tile_finish(const RangeDev &R, ExtrasSmem &S, int64_t base, int64_t count, uint64_t rel, uint64_t st) {
+	const int64_t tend = base + ETILE < count ? base + ETILE : count;
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	if (warp == 0) {
 		volatile uint64_t *state = R.tile_state;
 		const uint32_t tile = S.tile;
 		uint64_t exclusive = 0;
-		if (tile == 0) {
-			if (lane == 0) state[0] = FLAG_PFX | tile_total;
-		} else {
-			if (lane == 0) state[tile] = FLAG_AGG | tile_total;
+		if (tile != 0) {
 			int64_t look = (int64_t)tile - 1;
 			for (;;) {
 				const int64_t idx = look - lane;
-				uint64_t st = idx >= 0 ? state[idx] : FLAG_PFX;
 				while (__any_sync(FULL_MASK, (st & FLAG_MASK) == 0))
 					if ((st & FLAG_MASK) == 0) st = state[idx];
 				const unsigned pfx = __ballot_sync(FULL_MASK, (st & FLAG_MASK) == FLAG_PFX);
@@ -507,28 +523,33 @@ __device__ __forceinline__ void tile_front_end(const GraphDev &g, const RangeDev
 				exclusive += contrib;
 				if (pfx) break;
 				look -= 32;
+				st = look - lane >= 0 ? state[look - lane] : FLAG_PFX;
 			}
-			if (lane == 0) state[tile] = FLAG_PFX | (exclusive + tile_total);
+			if (lane == 0) state[tile] = FLAG_PFX | (exclusive + S.tile_total);
 		}
 		if (lane == 0) S.tile_base = exclusive;
 	}
 	__syncthreads();
-	uint64_t run = S.tile_base + (warp ? S.warp_sum[warp - 1] : 0) + (inc - sum);
+	uint64_t run = S.tile_base + rel;
+	const int64_t i0 = base + ERPT * (int64_t)threadIdx.x;
 #pragma unroll
 	for (int j = 0; j < ERPT; j++) {
-		const int64_t i = base + ERPT * threadIdx.x + j;
-		if (i < tend) R.rp_w[i] = (int64_t)run;
-		run += v[j];
+		const int64_t i = i0 + j;
+		if (i < tend) {
+			R.rp_w[i] = (int64_t)run;
+			run += R.deg[i];
+		}
 	}
 	// rp[tend]: the end of the tile's last row (the next tile writes the same value there; for the last tile, the total)
-	if (threadIdx.x == TPB - 1) R.rp_w[tend] = (int64_t)run;
+	if (i0 < tend && i0 + ERPT >= tend) R.rp_w[tend] = (int64_t)run;
 	__syncthreads();
 }
 
 template <int DEF, class RD, bool FUSED>
 __device__ __forceinline__ void extras_tile(const GraphDev &g, const RangeDev &R, const HeavyDev &H, ExtrasSmem &S, int64_t base, int64_t count,
                                             int64_t rp_from) {
-	if (FUSED) tile_front_end<DEF, RD>(g, R, S, base, count);
+	uint64_t rel = 0;
+	if (FUSED) tile_front_end<DEF, RD>(g, R, S, base, count, rel);
 	// heads of my rows (uniform loop: the warp reconverges at the end of every iteration)
 	int bucket[ERPT];
 #pragma unroll 1
@@ -539,7 +560,8 @@ __device__ __forceinline__ void extras_tile(const GraphDev &g, const RangeDev &R
 		// a halo row whose reference lies before the decoded range is never needed (and cannot be decoded): skip it
 		if (i < count && R.deg[i] != 0 && (R.depth ? R.depth[i] < DEPTH_INVALID : (int64_t)R.ref[i] <= i)) {
 			const int64_t x = R.lo + i;
-			if (x >= R.from && (uint64_t)(R.rp[i + 1] - rp_from) > R.col_capacity) raise(g, ERR_CAPACITY);
+			// (front end inside this kernel: the row pointers are not known yet, the rows are checked before they are decoded)
+			if (!FUSED && x >= R.from && (uint64_t)(R.rp[i + 1] - rp_from) > R.col_capacity) raise(g, ERR_CAPACITY);
 			else {
 				RD r;
 				tile_reader<RD>(r, g, S, FUSED ? S.pos[id] : ef_get(g, x));
@@ -578,8 +600,14 @@ __device__ __forceinline__ void extras_tile(const GraphDev &g, const RangeDev &R
 		}
 		__syncwarp();
 	}
+	uint64_t st = FLAG_PFX;
+	if (FUSED && threadIdx.x < 32 && S.tile != 0) {
+		const int64_t idx = (int64_t)S.tile - 1 - (int64_t)threadIdx.x;
+		if (idx >= 0) st = const_cast<volatile uint64_t *>(R.tile_state)[idx];
+	}
 	uint32_t total;
 	block_bin_sort<ERPT>(bucket, S.hist, S.order, &total);
+	if (FUSED) tile_finish(R, S, base, count, rel, st);
 	// after the sort S.hist[b] is the first position of bucket b: rows with intervals in buckets [0, 64), the others in
 	// [64, 128), each half heaviest first; the first fl buckets of either half hold the rows of >= HEAVY extras
 	const int fl = H.rows ? work_bucket(HEAVY - 1) : 0;
@@ -607,9 +635,18 @@ __device__ __forceinline__ void extras_tile(const GraphDev &g, const RangeDev &R
 	for (uint32_t tb = (threadIdx.x & ~31u); tb < nlight; tb += TPB) {
 		const uint32_t t = tb + (threadIdx.x & 31u);
 		const bool active = t < nlight;
-		const unsigned mask = __ballot_sync(FULL_MASK, active);
+		const unsigned amask = __ballot_sync(FULL_MASK, active);
+		int id = 0;
+		bool ok = active;
 		if (active) {
-			const int id = S.order[t < la ? a0 + t : b0 + (t - la)];
+			id = S.order[t < la ? a0 + t : b0 + (t - la)];
+			if (FUSED && (uint64_t)(R.rp[base + id + 1] - rp_from) > R.col_capacity) {
+				raise(g, ERR_CAPACITY);
+				ok = false;
+			}
+		}
+		const unsigned mask = FUSED ? __ballot_sync(FULL_MASK, ok) : amask;
+		if (ok) {
 			const int64_t k = base + id;
 			RD r;
 			tile_reader<RD>(r, g, S, S.pos[id]);
@@ -793,7 +830,16 @@ __global__ void __launch_bounds__(TPB) k_extras_heavy(GraphDev g, RangeDev R, He
 	win.wbase = 0;
 	for (unsigned long long c = (unsigned long long)blockIdx.x * (TPB / 32) + (threadIdx.x >> 5); c * 32 < total; c += warps) {
 		const unsigned long long t = c * 32 + lane;
-		const bool active = t < total;
+		// (a row that does not fit the caller's capacity has been reported already, by k_extras or, with the front end inside
+		// k_extras, right here: it is skipped)
+		bool active = t < total;
+		if (active) {
+			const int64_t ih = H.sorted[t];
+			if (R.lo + ih >= R.from && (uint64_t)(R.rp[ih + 1] - rp_from) > R.col_capacity) {
+				raise(g, ERR_CAPACITY);
+				active = false;
+			}
+		}
 		const unsigned mask = __ballot_sync(FULL_MASK, active);
 		// heads and interval sections straight from global memory (short), then the residuals through the window
 		int64_t i = 0;
