@@ -640,7 +640,7 @@ __device__ __forceinline__ void extras_tile(const GraphDev &g, const RangeDev &R
 		bool ok = active;
 		if (active) {
 			id = S.order[t < la ? a0 + t : b0 + (t - la)];
-			if (FUSED && (uint64_t)(R.rp[base + id + 1] - rp_from) > R.col_capacity) {
+			if (FUSED && R.lo + base + id >= R.from && (uint64_t)(R.rp[base + id + 1] - rp_from) > R.col_capacity) {
 				raise(g, ERR_CAPACITY);
 				ok = false;
 			}
@@ -665,7 +665,7 @@ __global__ void __launch_bounds__(TPB) k_extras(GraphDev g, RangeDev R, HeavyDev
 	}
 	const int64_t base = (int64_t)(FUSED ? S.tile : blockIdx.x) * ETILE;
 	const int64_t count = R.hi - R.lo;
-	const int64_t rp_from = FUSED ? 0 : R.rp[R.from - R.lo];  // (front end inside this kernel: no halo, rp[0] = 0)
+	const int64_t rp_from = FUSED ? R.rp_from_w : R.rp[R.from - R.lo];  // (front end inside this kernel: rp is not written yet)
 	const int64_t tend = base + ETILE < count ? base + ETILE : count;
 	if (threadIdx.x == 0) S.span[0] = ef_get(g, R.lo + base);
 	if (threadIdx.x == 32) S.span[1] = ef_get(g, R.lo + tend);
@@ -769,7 +769,10 @@ __global__ void __launch_bounds__(TPB) k_heavy_scatter(HeavyDev H) {
 static constexpr int HW_WORDS = 32;   // words of stream per lane and refill
 static constexpr int HW_PITCH = 35;   // row pitch in words (odd multiple: the 32 lanes hit 32 banks)
 static constexpr uint32_t HW_LOW = 29;  // refill when a reader's prefetched word index reaches this
-static constexpr uint32_t GIANT_ROW = 4096;   // residuals from which a row is decoded by a whole warp
+#ifndef WGBV_GIANT_ROW
+#define WGBV_GIANT_ROW 4096
+#endif
+static constexpr uint32_t GIANT_ROW = WGBV_GIANT_ROW;   // residuals from which a row is decoded by a whole warp
 static constexpr uint32_t GIANT_ROW2 = 32768;  // ... and from which by GIANT_CHUNKS warps (k_giant_*)
 
 struct HeavyWindow {

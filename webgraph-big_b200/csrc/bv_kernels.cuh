@@ -36,7 +36,7 @@ struct RangeDev {
 	int64_t *halo;          // successors of [lo, from): row x starts at halo + rp[x-lo]
 	uint64_t col_capacity;  // elements available at col
 	RowInfo *info;          // written by k_extras for every row with a reference, read by k_copy_level (may be nullptr)
-	// One-launch front end (no halo, lo == from): k_extras itself reads outdegree and reference of its rows (stage 1),
+	// One-launch front end: k_extras itself reads outdegree and reference of its rows (stage 1),
 	// scans the outdegrees across tiles by decoupled look-back (stage 2) and writes deg_w / ref_w / rp_w -- the very
 	// arrays deg / ref / rp point to -- before it parses the rest.  tile_state: one zeroed word per tile; tile_ticket:
 	// one zeroed word.  All unused when rp_w is nullptr.
@@ -45,6 +45,7 @@ struct RangeDev {
 	int64_t *rp_w = nullptr;
 	uint64_t *tile_state = nullptr;
 	uint32_t *tile_ticket = nullptr;
+	int64_t rp_from_w = 0;  // what rp[from - lo] is going to be (the arcs of the halo rows, which the host has counted)
 };
 
 // One random-access job list: `rows` chain rows, each decoded into its own slot.

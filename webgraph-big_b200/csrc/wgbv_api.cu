@@ -717,6 +717,7 @@ static int decode_rows(wgbv_stream *s, int64_t from, int64_t to, Prepared &P, in
 		R.deg_w = s->deg.as<uint32_t>();
 		R.ref_w = s->ref.as<uint8_t>();
 		R.rp_w = P.front_rp;
+		R.rp_from_w = P.halo_arcs;
 		R.tile_state = s->scan_state.as<uint64_t>();
 		R.tile_ticket = s->ticket.as<uint32_t>();
 	}
@@ -788,22 +789,40 @@ static int decode_general(wgbv_stream *s, int64_t from, int64_t to, int64_t *d_r
 	// Bounded, shallow reference chains and a range that needs no halo run without the separate header and scan
 	// launches and without the read-back of the arc count: k_extras does stages 1 and 2 for its own tiles
 	// (RangeDev::rp_w) and the capacity is checked on the device.  WGBV_SPLIT_FRONT=1 keeps the separate stages.
-	if (trust_maxref && s->front_in_extras && to > from && halo_start(g, from) == from && g->halo_nodes >= 0 && g->props.max_ref_count <= 8 &&
-	    !(g->props.window_size > 0 && g->props.max_ref_count <= 0) && to - from < (int64_t)0xfffffff0ll) {
-		P.lo = from;
-		P.cnt = to - from;
-		P.halo_n = 0;
+	if (trust_maxref && s->front_in_extras && to > from && g->halo_nodes >= 0 && g->props.max_ref_count <= 8 &&
+	    !(g->props.window_size > 0 && g->props.max_ref_count <= 0) && to - halo_start(g, from) < (int64_t)0xfffffff0ll) {
+		const Launch L = s->launch();
+		P.lo = halo_start(g, from);
+		P.cnt = to - P.lo;
+		P.halo_n = from - P.lo;
 		P.halo_arcs = 0;
-		// an upper bound on the arcs of the range: sizes the scratch of the heavy rows (never more than the whole graph has)
-		P.arcs = (int64_t)std::min<uint64_t>(col_capacity, (uint64_t)std::max<int64_t>(g->props.arcs, 0));
-		P.rp = d_rowptr;
-		P.front_rp = d_rowptr;
 		const size_t c = (size_t)P.cnt;
 		if ((rc = s->deg.ensure(c * 4)) || (rc = s->ref.ensure(c)) || (rc = s->scan_state.ensure(((c + 1) / 2048 + (size_t)extras_tiles(P.cnt) + 2) * 8)) ||
 		    (rc = s->ticket.ensure(64)))
 			return rc;
-		for (int i = 0; i < 4; i++) cudaEventRecord(s->ev[i], s->stream);  // (stages 1-2 have no time of their own here)
-		return decode_rows(s, from, to, P, d_col, col_capacity);
+		for (int i = 0; i < 2; i++) cudaEventRecord(s->ev[i], s->stream);
+		if (P.halo_n > 0) {
+			// halo rows (references of the first rows of the range reach back to them): their successors go to a scratch
+			// array whose size must be known before the launch, so their outdegrees are read and added up first -- a few
+			// rows, one read-back.  The row pointers then cover [lo, to) as in the general path and those of [from, to)
+			// are copied out at the end.
+			if ((rc = s->rp.ensure((c + 1) * 8))) return rc;
+			launch_header(L, s->dev, g->def_codes, P.lo, P.halo_n, s->deg.as<uint32_t>(), s->ref.as<uint8_t>());
+			launch_scan(L, s->deg.as<uint32_t>(), s->rp.as<int64_t>(), P.halo_n, s->scan_state.as<uint64_t>(), s->ticket.as<uint32_t>());
+			PeekArgs pk;
+			pk.add(s->rp.as<int64_t>() + P.halo_n, 8);
+			launch_peek(L, pk, s->d_pin);
+			CU(cudaStreamSynchronize(s->stream));
+			P.halo_arcs = (int64_t)s->h_pin[0];
+		}
+		for (int i = 2; i < 4; i++) cudaEventRecord(s->ev[i], s->stream);  // (stages 1-2 have no time of their own here)
+		// an upper bound on the arcs of the range: sizes the scratch of the heavy rows (never more than the whole graph has)
+		P.arcs = (int64_t)std::min<uint64_t>(col_capacity, (uint64_t)std::max<int64_t>(g->props.arcs, 0));
+		P.front_rp = P.halo_n ? s->rp.as<int64_t>() : d_rowptr;
+		P.rp = P.front_rp;
+		if ((rc = decode_rows(s, from, to, P, d_col, col_capacity))) return rc;
+		if (P.halo_n) launch_emit_rowptr(L, P.rp, P.halo_n, to - from, d_rowptr);
+		return WGBV_OK;
 	}
 	if ((rc = prepare(s, from, to, d_rowptr, P, trust_maxref))) return rc;
 	return decode_rows(s, from, to, P, d_col, col_capacity);
