@@ -138,6 +138,45 @@ def test_empty_range_on_a_new_handle_and_upload_exclusivity(cnr_basename, cnr_go
         other.close()
 
 
+def test_device_range_decodes_with_halo_and_exact_capacity():
+    """wgbv_decode_csr (device buffers) on ranges that start in the middle of a compression split: the front end runs
+    inside k_extras after the arcs of the halo rows have been counted.  Every range is decoded into a buffer of exactly
+    its size with a guard behind it; a buffer one element short is refused (IllegalArgumentException, the reference's
+    answer to a too-short array) and nothing is written behind the capacity given.  The graph has rows of hundreds of
+    successors, so the capacity checks of the tile kernel and of the heavy-row kernel both run."""
+    torch = pytest.importorskip("torch")
+    e = bg.copy_model(60000, seed=41, mean_degree=30, max_degree=3000, nsplits=3)
+    deg, col = oracle_of(e).decode_range()
+    rowptr = rowptr_of(deg)
+    n = deg.size
+    GUARD = -1234567
+    with gpu_of(e) as g:
+        rng = np.random.default_rng(8)
+        cuts = [(1, n), (7, 8), (20, 41), (1023, 1025), (1024, 5000), (19999, 20001), (20000, 40000), (20021, 20022), (n - 1, n)]
+        cuts += [tuple(sorted(rng.integers(0, n + 1, 2).tolist())) for _ in range(12)]
+        for a, b in cuts:
+            if a == b:
+                continue
+            arcs = int(rowptr[b] - rowptr[a])
+            d_rp = torch.full((b - a + 1 + 8,), GUARD, dtype=torch.int64, device="cuda")
+            d_col = torch.full((arcs + 64,), GUARD, dtype=torch.int64, device="cuda")
+            g.decodeToCSRDevice(a, b, d_rp.data_ptr(), d_col.data_ptr(), arcs)
+            rp, c = d_rp.cpu().numpy(), d_col.cpu().numpy()
+            assert np.array_equal(rp[: b - a + 1], rowptr[a:b + 1] - rowptr[a]) and np.all(rp[b - a + 1:] == GUARD), (a, b)
+            assert np.array_equal(c[:arcs], col[rowptr[a]:rowptr[b]]) and np.all(c[arcs:] == GUARD), (a, b)
+            if arcs > 1:
+                short = arcs - 1 if arcs < 50 else arcs - int(rng.integers(1, min(arcs, 4000)))
+                d_col.fill_(GUARD)
+                with pytest.raises(wg.IllegalArgumentException):
+                    g.decodeToCSRDevice(a, b, d_rp.data_ptr(), d_col.data_ptr(), short)
+                assert bool((d_col[short:] == GUARD).all()), (a, b, short)
+        # and the handle still works
+        d_rp = torch.empty(n + 1, dtype=torch.int64, device="cuda")
+        d_col = torch.empty(col.size, dtype=torch.int64, device="cuda")
+        g.decodeToCSRDevice(0, n, d_rp.data_ptr(), d_col.data_ptr(), col.size)
+        assert np.array_equal(d_col.cpu().numpy(), col)
+
+
 def test_checksum_kernel_matches_generator_hash(cnr, cnr_golden):
     torch = pytest.importorskip("torch")
     deg, rowptr, col = cnr_golden

@@ -502,7 +502,7 @@ __device__ __forceinline__ void tile_front_end(const GraphDev &g, const RangeDev
 
 // Second half of the front end: arcs before the tile by decoupled look-back (warp 0; `st` = the states of the 32 tiles
 // before this one, read before the sort so that the latency is spent there), then the row pointers of the tile.
-__device__ __forceinline__ void tile_finish(const RangeDev &R, ExtrasSmem &S, int64_t base, int64_t count, uint64_t rel, uint64_t st) {
+__device__ __forceinline__ void tile_finish(const GraphDev &g, const RangeDev &R, ExtrasSmem &S, int64_t base, int64_t count, uint64_t rel, uint64_t st) {
 	const int64_t tend = base + ETILE < count ? base + ETILE : count;
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 	if (warp == 0) {
@@ -541,7 +541,12 @@ __device__ __forceinline__ void tile_finish(const RangeDev &R, ExtrasSmem &S, in
 		}
 	}
 	// rp[tend]: the end of the tile's last row (the next tile writes the same value there; for the last tile, the total)
-	if (i0 < tend && i0 + ERPT >= tend) R.rp_w[tend] = (int64_t)run;
+	if (i0 < tend && i0 + ERPT >= tend) {
+		R.rp_w[tend] = (int64_t)run;
+		// the arcs up to the end of this tile do not fit the caller's array: reported here for the whole tile (rows without
+		// extras never reach the per-row check of the decode loop; no kernel writes behind the capacity)
+		if (R.lo + tend > R.from && (int64_t)run > R.rp_from_w && run - (uint64_t)R.rp_from_w > R.col_capacity) raise(g, ERR_CAPACITY);
+	}
 	__syncthreads();
 }
 
@@ -607,7 +612,7 @@ __device__ __forceinline__ void extras_tile(const GraphDev &g, const RangeDev &R
 	}
 	uint32_t total;
 	block_bin_sort<ERPT>(bucket, S.hist, S.order, &total);
-	if (FUSED) tile_finish(R, S, base, count, rel, st);
+	if (FUSED) tile_finish(g, R, S, base, count, rel, st);
 	// after the sort S.hist[b] is the first position of bucket b: rows with intervals in buckets [0, 64), the others in
 	// [64, 128), each half heaviest first; the first fl buckets of either half hold the rows of >= HEAVY extras
 	const int fl = H.rows ? work_bucket(HEAVY - 1) : 0;
