@@ -346,6 +346,84 @@ void launch_level_lists(const Launch &L, const GraphDev &g, const uint8_t *ref, 
 	WGBV_LAUNCHED(L);
 }
 
+// Deep chains (depths from k_depth, any number of levels): the same lists, eight levels per pass, over the rows that
+// are still to do -- `ids` (increasing row indices; nullptr: all rows of the range).  Bucket l = 1..nlevels takes the rows
+// of depth level0 + l, bucket nlevels + 1 the rows that lie deeper: that list is the `ids` of the next pass, so that a
+// pass costs what its rows cost and not a sweep over the whole range (most rows are within the first eight levels).
+__global__ void __launch_bounds__(TPB) k_deep_block_counts(const uint32_t *__restrict__ depth, const uint32_t *__restrict__ ids, int64_t count,
+                                                           uint32_t level0, uint32_t nlevels, uint32_t nblocks, uint32_t *__restrict__ counts) {
+	__shared__ uint32_t s_cnt[LEVELS_MAX + 2];
+	if (threadIdx.x <= LEVELS_MAX + 1) s_cnt[threadIdx.x] = 0;
+	__syncthreads();
+	const int64_t base = (int64_t)blockIdx.x * LTILE;
+	for (int q = 0; q < 8; q++) {
+		const int64_t t = base + q * TPB + threadIdx.x;
+		uint32_t d = 0;
+		if (t < count) d = depth[ids ? ids[t] : (uint32_t)t];
+		d = (d > level0 && d < DEPTH_INVALID) ? (d - level0 <= nlevels ? d - level0 : nlevels + 1) : 0u;
+		for (uint32_t l = 1; l <= nlevels + 1; l++) {
+			const unsigned m = __ballot_sync(0xffffffffu, d == l);
+			if ((threadIdx.x & 31) == 0 && m) atomicAdd(&s_cnt[l], (uint32_t)__popc(m));
+		}
+	}
+	__syncthreads();
+	if (threadIdx.x >= 1 && threadIdx.x <= nlevels + 1) counts[(size_t)(threadIdx.x - 1) * nblocks + blockIdx.x] = s_cnt[threadIdx.x];
+}
+
+__global__ void __launch_bounds__(TPB) k_deep_fill(const uint32_t *__restrict__ depth, const uint32_t *__restrict__ ids, int64_t count, uint32_t level0,
+                                                   uint32_t nlevels, uint32_t nblocks, const int64_t *__restrict__ pos, uint32_t *__restrict__ list) {
+	__shared__ uint32_t s_cnt[8][TPB / 32][LEVELS_MAX + 2];
+	const int64_t base = (int64_t)blockIdx.x * LTILE;
+	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	uint32_t myd[8], myrank[8], myrow[8];
+	for (int q = 0; q < 8; q++) {
+		const int64_t t = base + q * TPB + threadIdx.x;
+		uint32_t d = 0;
+		myrow[q] = 0;
+		if (t < count) {
+			myrow[q] = ids ? ids[t] : (uint32_t)t;
+			d = depth[myrow[q]];
+		}
+		d = (d > level0 && d < DEPTH_INVALID) ? (d - level0 <= nlevels ? d - level0 : nlevels + 1) : 0u;
+		myd[q] = d;
+		myrank[q] = 0;
+		for (uint32_t l = 1; l <= nlevels + 1; l++) {
+			const unsigned m = __ballot_sync(0xffffffffu, d == l);
+			if (d == l) myrank[q] = (uint32_t)__popc(m & ((1u << lane) - 1));
+			if (lane == 0) s_cnt[q][warp][l] = (uint32_t)__popc(m);
+		}
+	}
+	__syncthreads();
+	if (threadIdx.x >= 1 && threadIdx.x <= nlevels + 1) {
+		const uint32_t l = threadIdx.x;
+		uint32_t run = 0;
+		for (int q = 0; q < 8; q++)
+			for (int w = 0; w < TPB / 32; w++) {
+				const uint32_t c = s_cnt[q][w][l];
+				s_cnt[q][w][l] = run;
+				run += c;
+			}
+	}
+	__syncthreads();
+	for (int q = 0; q < 8; q++) {
+		const uint32_t d = myd[q];
+		if (d >= 1) list[pos[(size_t)(d - 1) * nblocks + blockIdx.x] + s_cnt[q][warp][d] + myrank[q]] = myrow[q];
+	}
+}
+
+// counts: (nlevels + 1) * nblocks words, pos: one more; nblocks = deep_list_blocks(count)
+uint32_t deep_list_blocks(int64_t count) { return grid_for(count, LTILE); }
+void launch_deep_lists(const Launch &L, const uint32_t *depth, const uint32_t *ids, int64_t count, uint32_t level0, uint32_t nlevels, uint32_t *counts,
+                       int64_t *pos, uint32_t *list, uint64_t *scan_state, uint32_t *ticket) {
+	const uint32_t nblocks = deep_list_blocks(count);
+	if (!nblocks) return;
+	k_deep_block_counts<<<nblocks, TPB, 0, L.stream>>>(depth, ids, count, level0, nlevels, nblocks, counts);
+	WGBV_LAUNCHED(L);
+	launch_scan(L, counts, pos, (int64_t)(nlevels + 1) * nblocks, scan_state, ticket);
+	k_deep_fill<<<nblocks, TPB, 0, L.stream>>>(depth, ids, count, level0, nlevels, nblocks, pos, list);
+	WGBV_LAUNCHED(L);
+}
+
 __device__ __forceinline__ int64_t *row_slot(const RangeDev &R, int64_t i, int64_t rp_from) {
 	const int64_t p = R.rp[i];
 	return (R.lo + i >= R.from) ? R.col + (p - rp_from) : R.halo + p;
@@ -1220,10 +1298,51 @@ __global__ void __launch_bounds__(TPB) k_copy_level(GraphDev g, RangeDev R, uint
 	}
 }
 
+// A level of few rows (the deep end of long reference chains): one warp per row and no sorting -- the life of a block of
+// k_copy_level (first pass, sort, two rounds of serial merges: 85 us) is what such a launch costs, whatever its size.
+// Rows with a mask are merged by the warp's first lane, the others by the whole warp.
+static constexpr uint64_t SMALL_LEVEL = 8192;  // (at 40 000 rows the sorted kernel is the faster one: 0.67 vs 0.72 ms for a 250 000-node range)
+
+template <int DEF>
+__global__ void __launch_bounds__(TPB) k_copy_small(GraphDev g, RangeDev R, const uint32_t *__restrict__ list, uint64_t list_count) {
+	const uint64_t w = (uint64_t)blockIdx.x * (TPB / 32) + (threadIdx.x >> 5);
+	if (w >= list_count) return;
+	const unsigned lane = threadIdx.x & 31u;
+	const int64_t rp_from = R.rp[R.from - R.lo];
+	const int64_t i = list[w];
+	const uint32_t d = R.deg[i];
+	if (d == 0 || (R.lo + i >= R.from && (uint64_t)(R.rp[i + 1] - rp_from) > R.col_capacity)) return;
+	const uint32_t rf = R.ref[i], dref = R.deg[i - rf];
+	const RowInfo ri = R.info[i];
+	int64_t *dst = row_slot(R, i, rp_from);
+	const int64_t *src = row_slot(R, i - rf, rp_from);
+	if (row_is_masked(d, dref)) {
+		if (lane == 0 && (ri.a | ri.b) != 0) {
+			const uint32_t ncopied = (uint32_t)(__popcll(ri.a) + __popcll(ri.b));
+			row_copy_masked(g, src, ri.a, ri.b, dst + ncopied, dst, d - ncopied, 1u);
+		}
+	} else if ((uint32_t)ri.b != 0) {
+		const uint32_t ncopied = (uint32_t)ri.b;
+		BitReader r;
+		r.init(g, ri.a);
+		row_copy_warp<DEF>(g, r, src, dref, dst + ncopied, dst, d, (uint32_t)(ri.b >> 32), ncopied);
+	}
+}
+
 void launch_copy_level(const Launch &L, const GraphDev &g, int def, const RangeDev &r, uint32_t level, const uint32_t *list,
                        uint64_t list_count) {
 	const int64_t items = list ? (int64_t)list_count : r.hi - r.lo;
 	if (items <= 0) return;
+	if (list && r.info && list_count < SMALL_LEVEL) {
+		const unsigned grid = grid_for((int64_t)list_count, TPB / 32);
+		switch (def) {
+		case 2: k_copy_small<2><<<grid, TPB, 0, L.stream>>>(g, r, list, list_count); break;
+		case 1: k_copy_small<1><<<grid, TPB, 0, L.stream>>>(g, r, list, list_count); break;
+		default: k_copy_small<0><<<grid, TPB, 0, L.stream>>>(g, r, list, list_count);
+		}
+		WGBV_LAUNCHED(L);
+		return;
+	}
 	const size_t smem = sizeof(CopySmem);
 	const unsigned grid = grid_for(items, CTILE);
 	switch (def) {

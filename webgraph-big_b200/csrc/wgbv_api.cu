@@ -72,7 +72,7 @@ struct wgbv_stream {
 	uint64_t *h_pin = nullptr;  // pinned, mapped host scratch for read-backs (32 words)
 	uint64_t *d_pin = nullptr;  // the device's address of h_pin: kernels write scalars for the host there (launch_peek)
 	uint64_t launches = 0;
-	DevBuf deg, ref, depth, rp, scan_state, ticket, halo, levels, list, col, rowptr, ids, batch;
+	DevBuf deg, ref, depth, rp, scan_state, ticket, halo, levels, list, list2, col, rowptr, ids, batch;
 	DevBuf t_pairs[2], t_indeg, t_counts, t_pos;  // wgbv_transpose_csr
 	DevBuf sym_rowptr, sym_col;                   // wgbv_symmetrize_csr: the transpose
 	DevBuf heavy_rows, heavy_sorted, heavy_cls, heavy_counters, giants, gchunks, level_pos, row_info, tile_done;
@@ -493,7 +493,7 @@ extern "C" void wgbv_stream_destroy(wgbv_stream *s) {
 	cudaSetDevice(s->g->device);
 	if (s->stream) cudaStreamSynchronize(s->stream);
 	for (DevBuf *b : {&s->t_pairs[0], &s->t_pairs[1], &s->t_indeg, &s->t_counts, &s->t_pos, &s->sym_rowptr, &s->sym_col}) b->release();
-	for (DevBuf *b : {&s->deg, &s->ref, &s->depth, &s->rp, &s->scan_state, &s->ticket, &s->halo, &s->levels, &s->list, &s->col,
+	for (DevBuf *b : {&s->deg, &s->ref, &s->depth, &s->rp, &s->scan_state, &s->ticket, &s->halo, &s->levels, &s->list, &s->list2, &s->col,
 	                  &s->rowptr, &s->ids, &s->batch, &s->heavy_rows, &s->heavy_sorted, &s->heavy_cls, &s->heavy_counters, &s->giants, &s->gchunks, &s->tile_done, &s->level_pos, &s->row_info, &s->c_node, &s->c_dst, &s->c_parent, &s->c_deg, &s->c_isq, &s->c_level,
 	                  &s->c_len, &s->c_arcs, &s->c_row0, &s->c_soff, &s->c_store})
 		b->release();
@@ -755,23 +755,32 @@ static int decode_rows(wgbv_stream *s, int64_t from, int64_t to, Prepared &P, in
 	}
 	if (nlev == 0) {
 	} else {
-		// deep chains (depths from k_depth): the same ordered lists, eight levels per pass
-		const size_t nblocks = (size_t)((P.cnt + 2047) / 2048);
-		if ((rc = s->levels.ensure(8 * nblocks * 4)) || (rc = s->level_pos.ensure((8 * nblocks + 1) * 8)) ||
-		    (rc = s->list.ensure((size_t)std::max<int64_t>(P.cnt, 1) * 4)) || (rc = s->scan_state.ensure(((8 * nblocks + 1) / 2048 + 2) * 8)))
-			return rc;
-		for (uint32_t level0 = 0; level0 < P.max_depth; level0 += 8) {
+		// deep chains (depths from k_depth): the same ordered lists, eight levels per pass; every pass also lists the rows
+		// that lie deeper, and the next pass works on that list only (two list buffers take turns)
+		const uint32_t *ids = nullptr;
+		int64_t nids = P.cnt;
+		DevBuf *bufs[2] = {&s->list, &s->list2};
+		int cur = 0;
+		for (uint32_t level0 = 0; level0 < P.max_depth && nids > 0; level0 += 8) {
 			const uint32_t n8 = std::min<uint32_t>(8, P.max_depth - level0);
-			launch_level_lists(L, s->dev, nullptr, s->depth.as<uint32_t>(), P.lo, from, P.cnt, level0, n8, s->levels.as<uint32_t>(),
-			                   s->level_pos.as<int64_t>(), s->list.as<uint32_t>(), s->scan_state.as<uint64_t>(), s->ticket.as<uint32_t>(), s->d_err + 3);
+			const size_t nblocks = (size_t)deep_list_blocks(nids);
+			if ((rc = s->levels.ensure(9 * nblocks * 4)) || (rc = s->level_pos.ensure((9 * nblocks + 1) * 8)) ||
+			    (rc = bufs[cur]->ensure((size_t)std::max<int64_t>(nids, 1) * 4)) || (rc = s->scan_state.ensure(((9 * nblocks + 1) / 2048 + 2) * 8)))
+				return rc;
+			uint32_t *list = bufs[cur]->as<uint32_t>();
+			launch_deep_lists(L, s->depth.as<uint32_t>(), ids, nids, level0, n8, s->levels.as<uint32_t>(), s->level_pos.as<int64_t>(), list,
+			                  s->scan_state.as<uint64_t>(), s->ticket.as<uint32_t>());
 			const int64_t *bounds = (const int64_t *)(s->h_pin + 16);
 			PeekArgs pk;
-			for (uint32_t l = 0; l <= n8; l++) pk.add(s->level_pos.as<int64_t>() + (size_t)l * nblocks, 8);
+			for (uint32_t l = 0; l <= n8 + 1; l++) pk.add(s->level_pos.as<int64_t>() + (size_t)l * nblocks, 8);
 			launch_peek(L, pk, s->d_pin + 16);
 			CU(cudaStreamSynchronize(s->stream));
 			for (uint32_t l = 1; l <= n8; l++)
 				if (bounds[l] > bounds[l - 1])
-					launch_copy_level(L, s->dev, g->def_codes, R, level0 + l, s->list.as<uint32_t>() + bounds[l - 1], (uint64_t)(bounds[l] - bounds[l - 1]));
+					launch_copy_level(L, s->dev, g->def_codes, R, level0 + l, list + bounds[l - 1], (uint64_t)(bounds[l] - bounds[l - 1]));
+			ids = list + bounds[n8];
+			nids = bounds[n8 + 1] - bounds[n8];
+			cur ^= 1;
 		}
 	}
 	cudaEventRecord(s->ev[4], s->stream);
