@@ -99,6 +99,18 @@ WGBV_API int wgbv_open(const char *basename, int device, int shard_index, int sh
 WGBV_API int wgbv_open_mem(const wgbv_props *props, const uint8_t *graph, uint64_t graph_bytes, const uint8_t *offsets,
                   uint64_t offsets_bytes, int device, int shard_index, int shard_count, wgbv_graph **out);
 
+/*
+ * BVGraph.writeOffsets (BVG:2595-2609; the `-o` option of the reference's BVGraph main, BVG:2654ff): the .offsets stream of
+ * a graph that was shipped without one -- nodes + 1 gamma (or delta, per the properties) codes, the first one 0, then the
+ * length in bits of every record.  Host code: a record can only be found by parsing every record before it (how many
+ * codes a record has depends on the outdegree of the row it refers to), which is why the reference, too, walks the file
+ * with a single node iterator.  One pass, lengths only.  *out_bytes receives the size of the stream; nothing is copied
+ * (WGBV_EARG) if out_capacity is smaller -- call with out == NULL to learn the size.  wgbv_open_mem accepts
+ * offsets == NULL and then does the same pass itself.
+ */
+WGBV_API int wgbv_write_offsets(const wgbv_props *props, const uint8_t *graph, uint64_t graph_bytes, uint8_t *out, uint64_t out_capacity,
+                                uint64_t *out_bytes);
+
 /* The shard plan wgbv_open uses, without touching a device (host only): bounds_out[k] is the first node of shard k,
  * bounds_out[shard_count] = nodes; shards are contiguous and balanced by compressed bits (the arc-balancing idea of
  * algo/EliasFanoCumulativeOutdegreeList.java:139-151 applied to bit offsets).  *halo_out = window_size *

@@ -177,6 +177,20 @@ def test_device_range_decodes_with_halo_and_exact_capacity():
         assert np.array_equal(d_col.cpu().numpy(), col)
 
 
+def test_graph_without_offsets_file(cnr_basename, cnr_golden):
+    """A graph shipped without its .offsets (the reference needs `BVGraph -o` first, BVG:2595-2609): wgbv_open_mem with
+    offsets == NULL finds the records itself and the decode equals the golden."""
+    deg, rowptr, col = cnr_golden
+    props = open(cnr_basename + ".properties").read()
+    graph = np.fromfile(cnr_basename + ".graph", dtype=np.uint8)
+    with wg.GpuBVGraph.load_mem(props, graph, None) as g:
+        rp, c = g.decodeToCSR()
+        assert np.array_equal(rp, rowptr) and np.array_equal(c, col)
+        ids = np.array([0, 17, 325556, 100000], dtype=np.int64)
+        _, c2 = g.successorsBatch(ids)
+        assert np.array_equal(c2, np.concatenate([col[rowptr[x]:rowptr[x + 1]] for x in ids]))
+
+
 def test_checksum_kernel_matches_generator_hash(cnr, cnr_golden):
     torch = pytest.importorskip("torch")
     deg, rowptr, col = cnr_golden

@@ -23,6 +23,20 @@ __all__ = ["GpuBVGraph", "NodeIterator", "LazyLongIterator", "Props", "parse_pro
 GRAPH_EXTENSION, OFFSETS_EXTENSION, PROPERTIES_EXTENSION = ".graph", ".offsets", ".properties"
 
 
+def write_offsets(props, graph_bytes):
+    """BVGraph.writeOffsets (BVG:2595-2609): the bytes of the .offsets file of a graph given its properties (a Props or
+    the text of the .properties file) and its .graph bytes.  Host code, one sequential pass over the records."""
+    if isinstance(props, str):
+        props = parse_properties(props)
+    g = np.ascontiguousarray(np.frombuffer(graph_bytes, dtype=np.uint8)) if not isinstance(graph_bytes, np.ndarray) else np.ascontiguousarray(graph_bytes)
+    size = C.c_uint64(0)
+    f = _lib.lib().wgbv_write_offsets
+    _lib.check(f(C.byref(props), g.ctypes.data if g.size else None, g.size, None, 0, C.byref(size)))
+    out = np.zeros(max(size.value, 1), dtype=np.uint8)
+    _lib.check(f(C.byref(props), g.ctypes.data if g.size else None, g.size, out.ctypes.data, out.size, C.byref(size)))
+    return out[: size.value]
+
+
 def parse_properties(text):
     """The .properties checks of BVGraph.loadInternal (BVG:1482-1503) -> Props."""
     p = Props()
@@ -119,14 +133,18 @@ class GpuBVGraph:
 
     @classmethod
     def load_mem(cls, props, graph_bytes, offsets_bytes, device=0, shard_index=0, shard_count=1, cuda_stream=None):
-        """Same from memory: ``props`` is a Props or the text of a .properties file."""
+        """Same from memory: ``props`` is a Props or the text of a .properties file.  offsets_bytes None: the graph came
+        without its .offsets and the records are found by the sequential pass of BVGraph.writeOffsets (see write_offsets)."""
         if isinstance(props, str):
             props = parse_properties(props)
         g = np.ascontiguousarray(np.frombuffer(graph_bytes, dtype=np.uint8)) if not isinstance(graph_bytes, np.ndarray) else np.ascontiguousarray(graph_bytes)
-        o = np.ascontiguousarray(np.frombuffer(offsets_bytes, dtype=np.uint8)) if not isinstance(offsets_bytes, np.ndarray) else np.ascontiguousarray(offsets_bytes)
+        if offsets_bytes is None:
+            o = None
+        else:
+            o = np.ascontiguousarray(np.frombuffer(offsets_bytes, dtype=np.uint8)) if not isinstance(offsets_bytes, np.ndarray) else np.ascontiguousarray(offsets_bytes)
         h = C.c_void_p()
-        _lib.check(_lib.lib().wgbv_open_mem(C.byref(props), g.ctypes.data, g.size, o.ctypes.data, o.size, device,
-                                            shard_index, shard_count, C.byref(h)))
+        _lib.check(_lib.lib().wgbv_open_mem(C.byref(props), g.ctypes.data, g.size, o.ctypes.data if o is not None else None,
+                                            o.size if o is not None else 0, device, shard_index, shard_count, C.byref(h)))
         return cls(_Shared(h, None), cuda_stream)
 
     @classmethod

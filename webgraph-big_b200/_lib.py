@@ -89,6 +89,7 @@ SYMBOLS = [
     ("wgbv_fused_stats", C.c_int, [_P, C.POINTER(C.c_uint64 * 4)]),
     ("wgbv_labels_decode_lists", C.c_int, [_P, _P, C.c_int64, C.c_int64, _P, _P, _P, C.c_uint64, C.POINTER(C.c_int64)]),
     ("wgbv_labels_decode_lists_host", C.c_int, [_P, _P, C.c_int64, C.c_int64, _P, _P, _P, C.c_uint64, C.POINTER(C.c_int64)]),
+    ("wgbv_write_offsets", C.c_int, [_P, _P, C.c_uint64, _P, C.c_uint64, C.POINTER(C.c_uint64)]),
     ("wgbv_union_csr", C.c_int, [_P, C.c_int64, _P, _P, _P, _P, _P, _P, C.c_uint64, C.POINTER(C.c_int64)]),
     ("wgbv_symmetrize_csr", C.c_int, [_P, C.c_int64, _P, _P, _P, _P, C.c_uint64, C.POINTER(C.c_int64)]),
     ("wgbv_encode_csr", C.c_int, [C.c_int, _P, C.c_int64, C.c_int64, _P, _P, C.c_int64, _P, C.c_uint64, C.POINTER(C.c_uint64), _P]),

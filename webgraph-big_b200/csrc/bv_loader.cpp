@@ -227,6 +227,149 @@ int decode_offsets(const wgbv_props &p, const uint8_t *bytes, uint64_t nbytes, i
 	return WGBV_OK;
 }
 
+// ------------------------------------------------------------------------------------------------ writeOffsets
+// BVGraph.writeOffsets (BVG:2595-2609) for a graph that comes without its .offsets file: the position of every record.
+// Sequential by construction -- a record ends where its last code ends, and how many codes it has depends on the
+// outdegree of the row it refers to, which sits at the start of an EARLIER record: no record can be parsed before the
+// ones in front of it (the reference walks the file with one node iterator for the same reason).  So this is host
+// code of the loader, like the parsing of .properties: one pass, lengths only, nothing is decoded into lists.
+// Record layout: BVG:995-1097 (outdegree; reference; block count, blocks; interval count, left/length pairs; residuals).
+namespace {
+struct RecordSkipper : HostBits {
+	uint64_t zeta(int k) {
+		const uint64_t h = unary();
+		if (h * (uint64_t)k + (uint64_t)k > 64) { overrun = true; return 0; }
+		const uint64_t left = 1ull << (h * k);
+		const uint64_t m = bits((unsigned)(h * k + k - 1));
+		if (m < left) return m + left - 1;
+		return ((m << 1) | bits(1)) - 1;
+	}
+	uint64_t nibble() {
+		uint64_t x = 0;
+		uint64_t stop;
+		do {
+			stop = bits(1);
+			x = (x << 3) | bits(3);
+		} while (!stop && !overrun);
+		return x;
+	}
+	uint64_t golomb(int b) {
+		if (b == 0) return 0;
+		const uint64_t q = unary();
+		int log2b = 0;
+		while ((2ull << log2b) <= (uint64_t)b) log2b++;
+		const uint64_t m = (1ull << (log2b + 1)) - (uint64_t)b;
+		uint64_t x = log2b ? bits((unsigned)log2b) : 0;
+		if (x >= m) x = ((x << 1) | bits(1)) - m;
+		return q * (uint64_t)b + x;
+	}
+	uint64_t code(int coding, int k) {
+		switch (coding) {
+		case WGBV_GAMMA: return gamma();
+		case WGBV_DELTA: return delta();
+		case WGBV_UNARY: return unary();
+		case WGBV_ZETA: return zeta(k);
+		case WGBV_NIBBLE: return nibble();
+		case WGBV_GOLOMB: return golomb(k);
+		default: overrun = true; return 0;
+		}
+	}
+};
+}  // namespace
+
+int build_offsets(const wgbv_props &p, const uint8_t *graph, uint64_t graph_bytes, std::vector<uint64_t> &out) {
+	RecordSkipper s;
+	s.p = graph;
+	s.nbits = graph_bytes * 8;
+	s.pos = 0;
+	const int64_t n = p.nodes;
+	const int w = p.window_size > 0 ? p.window_size : 0;
+	std::vector<uint64_t> ring((size_t)w + 1, 0);  // outdegrees of the last w + 1 nodes
+	out.resize((size_t)n + 1);
+	for (int64_t x = 0; x < n; x++) {
+		out[(size_t)x] = s.pos;
+		const uint64_t d = s.code(p.outdegree_coding, 0);
+		ring[(size_t)(x % (w + 1))] = d;
+		if (d == 0) continue;
+		if (d > 0x7fffffffull) return fail(WGBV_ESTATE, "node %lld: outdegree %llu", (long long)x, (unsigned long long)d);
+		uint64_t ref = 0;
+		if (w > 0) {
+			ref = s.code(p.reference_coding, 0);
+			if (ref > (uint64_t)w || (int64_t)ref > x) return fail(WGBV_ESTATE, "The required reference is incompatible with the window size (%d)", w);
+		}
+		uint64_t extra = d;
+		if (ref) {
+			const uint64_t dref = ring[(size_t)((x - (int64_t)ref) % (w + 1))];
+			const uint64_t bc = s.code(p.block_count_coding, 0);
+			uint64_t copied = 0, total = 0;
+			for (uint64_t i = 0; i < bc && !s.overrun; i++) {
+				const uint64_t len = s.code(p.block_coding, 0) + (i ? 1 : 0);
+				total += len;
+				if (!(i & 1)) copied += len;
+			}
+			if (!(bc & 1)) copied += dref > total ? dref - total : 0;  // the implicit last block copies the rest of the list
+			if (copied > d) return fail(WGBV_ESTATE, "node %lld copies more successors than it has", (long long)x);
+			extra = d - copied;
+		}
+		if (extra && p.min_interval_length != 0) {
+			const uint64_t ic = s.gamma();
+			for (uint64_t i = 0; i < ic && !s.overrun; i++) {
+				s.gamma();  // left extreme
+				const uint64_t len = s.gamma() + (uint64_t)p.min_interval_length;
+				if (len > extra) return fail(WGBV_ESTATE, "node %lld: intervals longer than the successor list", (long long)x);
+				extra -= len;
+			}
+		}
+		for (uint64_t i = 0; i < extra && !s.overrun; i++) s.code(p.residual_coding, p.zeta_k);
+		if (s.overrun || s.pos > s.nbits) return fail(WGBV_EIO, "the graph stream ends inside the record of node %lld", (long long)x);
+	}
+	out[(size_t)n] = s.pos;
+	return WGBV_OK;
+}
+
+// the offsets as the .offsets stream codes them (gamma or delta of the differences, n + 1 codes, the first one 0)
+void encode_offsets(const wgbv_props &p, const std::vector<uint64_t> &off, std::vector<uint8_t> &out) {
+	out.clear();
+	uint64_t acc = 0;
+	int fill = 0;  // bits of acc not yet written (< 8 between calls)
+	auto put32 = [&](uint64_t v, int len) {  // len <= 32
+		if (!len) return;
+		acc = (acc << len) | (v & ((1ull << len) - 1));
+		fill += len;
+		while (fill >= 8) {
+			out.push_back((uint8_t)(acc >> (fill - 8)));
+			fill -= 8;
+		}
+		acc &= (1ull << fill) - 1;
+	};
+	auto put = [&](uint64_t v, int len) {  // len <= 64
+		if (len > 32) {
+			put32(v >> 32, len - 32);
+			len = 32;
+		}
+		put32(v, len);
+	};
+	auto put_gamma = [&](uint64_t x) {
+		const uint64_t y = x + 1;
+		const int m = 63 - __builtin_clzll(y);
+		put(0, m);
+		put(1, 1);
+		put(y, m);  // the m bits below the leading one
+	};
+	uint64_t last = 0;
+	for (size_t i = 0; i < off.size(); i++) {
+		const uint64_t d = i ? off[i] - last : off[0];
+		last = off[i];
+		if (p.offset_coding == WGBV_DELTA) {
+			const uint64_t y = d + 1;
+			const int m = 63 - __builtin_clzll(y);
+			put_gamma((uint64_t)m);
+			put(y, m);
+		} else put_gamma(d);
+	}
+	if (fill) out.push_back((uint8_t)(acc << (8 - fill)));
+}
+
 // ------------------------------------------------------------------------------------------------ Elias-Fano
 // l = floor(log2(u / n)) lower bits (the choice of the reference's succinct lists, cf. EFGraph.java:140-142 and
 // algo/EliasFanoCumulativeOutdegreeList.java:95-105); element i sets bit (v_i >> l) + i of the upper array.

@@ -20,6 +20,10 @@ int read_file(const std::string &path, std::vector<uint8_t> &out);
 
 // `count` absolute bit offsets from the gamma/delta coded differences (OffsetsLongIterator, BVG:870-898).
 int decode_offsets(const wgbv_props &p, const uint8_t *bytes, uint64_t nbytes, int64_t count, std::vector<uint64_t> &out);
+// BVGraph.writeOffsets (BVG:2595-2609): the bit position of every record of a .graph stream, nodes + 1 values (host,
+// sequential by construction); and the .offsets stream that codes them
+int build_offsets(const wgbv_props &p, const uint8_t *graph, uint64_t graph_bytes, std::vector<uint64_t> &out);
+void encode_offsets(const wgbv_props &p, const std::vector<uint64_t> &off, std::vector<uint8_t> &out);
 
 // Elias-Fano representation of a monotone list, laid out for the device (see bv_device.cuh: ef_get).
 struct EliasFano {

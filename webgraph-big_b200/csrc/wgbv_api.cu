@@ -335,16 +335,17 @@ static int check_offsets(const std::vector<uint64_t> &off, uint64_t graph_bytes)
 extern "C" int wgbv_open_mem(const wgbv_props *props, const uint8_t *graph, uint64_t graph_bytes, const uint8_t *offsets,
                              uint64_t offsets_bytes, int device, int shard_index, int shard_count, wgbv_graph **out) {
 	clear_error();
-	if (!props || !out || (!graph && graph_bytes) || !offsets) return fail(WGBV_EARG, "null argument");
+	if (!props || !out || (!graph && graph_bytes)) return fail(WGBV_EARG, "null argument");
 	*out = nullptr;
 	if (shard_count < 1 || shard_index < 0 || shard_index >= shard_count) return fail(WGBV_EARG, "bad shard %d of %d", shard_index, shard_count);
 	int rc = check_codings(*props);
 	if (rc) return rc;
 	if ((rc = select_device(device))) return rc;
-	if (shard_count == 1 && offsets_on_device(props, props->nodes + 1))
+	if (offsets && shard_count == 1 && offsets_on_device(props, props->nodes + 1))
 		return open_with_device_offsets(props, graph, graph_bytes, offsets, offsets_bytes, 0, props->nodes + 1, 0, 0, props->nodes, device, out);
 	std::vector<uint64_t> off;
-	if ((rc = decode_offsets(*props, offsets, offsets_bytes, props->nodes + 1, off))) return rc;
+	// (no .offsets: the records are found by the sequential pass of BVGraph.writeOffsets, see wgbv_write_offsets)
+	if ((rc = offsets ? decode_offsets(*props, offsets, offsets_bytes, props->nodes + 1, off) : build_offsets(*props, graph, graph_bytes, off))) return rc;
 	if ((rc = check_offsets(off, graph_bytes))) return rc;
 	const int64_t halo = halo_of(props);
 	if (halo < 0 && shard_count > 1)
@@ -354,6 +355,23 @@ extern "C" int wgbv_open_mem(const wgbv_props *props, const uint8_t *graph, uint
 	const int64_t lo = bounds[(size_t)shard_index], hi = bounds[(size_t)shard_index + 1];
 	const int64_t avail_lo = halo < 0 ? 0 : std::max<int64_t>(0, lo - halo);
 	return build_graph(props, graph, graph_bytes, off, nullptr, 0, avail_lo, lo, hi, halo, device, out);
+}
+
+extern "C" int wgbv_write_offsets(const wgbv_props *props, const uint8_t *graph, uint64_t graph_bytes, uint8_t *out, uint64_t out_capacity,
+                                  uint64_t *out_bytes) {
+	clear_error();
+	if (!props || (!graph && graph_bytes) || !out_bytes) return fail(WGBV_EARG, "null argument");
+	int rc = check_codings(*props);
+	if (rc) return rc;
+	std::vector<uint64_t> off;
+	if ((rc = build_offsets(*props, graph, graph_bytes, off))) return rc;
+	std::vector<uint8_t> stream;
+	encode_offsets(*props, off, stream);
+	*out_bytes = stream.size();
+	if (!out) return WGBV_OK;
+	if (out_capacity < stream.size()) return fail(WGBV_EARG, "out_capacity (%llu) is smaller than the %llu bytes of the offsets stream", (unsigned long long)out_capacity, (unsigned long long)stream.size());
+	if (!stream.empty()) memcpy(out, stream.data(), stream.size());
+	return WGBV_OK;
 }
 
 extern "C" int wgbv_plan_shards(const wgbv_props *props, const uint8_t *offsets, uint64_t offsets_bytes, int shard_count,

@@ -199,6 +199,15 @@ inline std::vector<uint8_t> storeDevice(int device, const wgbv_props &props, int
 	return out;
 }
 
+// BVGraph.writeOffsets (BVG:2595-2609): the .offsets stream of a graph shipped without one (host, one sequential pass).
+inline std::vector<uint8_t> writeOffsets(const wgbv_props &props, const std::vector<uint8_t> &graph) {
+	uint64_t size = 0;
+	check(wgbv_write_offsets(&props, graph.data(), graph.size(), nullptr, 0, &size));
+	std::vector<uint8_t> out((size_t)size);
+	check(wgbv_write_offsets(&props, graph.data(), graph.size(), out.data(), out.size(), &size));
+	return out;
+}
+
 // The labels of a BitStreamArcLabelledImmutableGraph (labelling/BitStreamArcLabelledImmutableGraph.java:65-100) on the
 // device: decode() returns them parallel to the successors that Graph::decodeToCSR returns for the same range.
 class ArcLabels {

@@ -59,6 +59,8 @@ public class GpuBVGraph extends ImmutableGraph {
 		static final MethodHandle ENCODE_CSR = h("wgbv_encode_csr",
 			FunctionDescriptor.of(JAVA_INT, JAVA_INT, ADDRESS, JAVA_LONG, JAVA_LONG, ADDRESS, ADDRESS, JAVA_LONG, ADDRESS, JAVA_LONG, ADDRESS, ADDRESS));
 		// arc labels (labelling/BitStreamArcLabelledImmutableGraph.java:65-100): an array parallel to the successors
+		static final MethodHandle WRITE_OFFSETS = h("wgbv_write_offsets",
+				FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_LONG, ADDRESS, JAVA_LONG, ADDRESS));
 		static final MethodHandle LABELS_OPEN_MEM = h("wgbv_labels_open_mem",
 				FunctionDescriptor.of(JAVA_INT, JAVA_INT, JAVA_LONG, JAVA_INT, JAVA_INT, ADDRESS, JAVA_LONG, ADDRESS, JAVA_LONG, ADDRESS));
 		static final MethodHandle LABELS_DECODE_HOST = h("wgbv_labels_decode_host",
