@@ -852,6 +852,9 @@ __global__ void __launch_bounds__(TPB) k_heavy_scatter(HeavyDev H) {
 static constexpr int HW_WORDS = 32;   // words of stream per lane and refill
 static constexpr int HW_PITCH = 35;   // row pitch in words (odd multiple: the 32 lanes hit 32 banks)
 static constexpr uint32_t HW_LOW = 29;  // refill when a reader's prefetched word index reaches this
+#ifndef WGBV_HEAVY_BLOCKS
+#define WGBV_HEAVY_BLOCKS 1
+#endif
 #ifndef WGBV_GIANT_ROW
 #define WGBV_GIANT_ROW 4096
 #endif
@@ -903,7 +906,7 @@ struct HeavyWindow {
 };
 
 template <int DEF>
-__global__ void __launch_bounds__(TPB) k_extras_heavy(GraphDev g, RangeDev R, HeavyDev H) {
+__global__ void __launch_bounds__(TPB, WGBV_HEAVY_BLOCKS) k_extras_heavy(GraphDev g, RangeDev R, HeavyDev H) {
 	__shared__ uint32_t s_win[TPB / 32][32 * HW_PITCH];
 	const unsigned long long total = H.counters[0];
 	const int64_t rp_from = R.rp[R.from - R.lo];
