@@ -437,9 +437,10 @@ static constexpr int TILE = TPB * RPT;   // rows per block: the sort domain (see
 // by class over the whole range (k_heavy_scatter), and decoded by k_extras_heavy where every warp finds 32 rows of
 // one class.
 #ifndef WGBV_HEAVY
-#define WGBV_HEAVY 128
+#define WGBV_HEAVY 48
 #endif
 static constexpr uint32_t HEAVY = WGBV_HEAVY;
+uint32_t heavy_threshold() { return HEAVY; }
 
 // stage 3a: one block per ETILE consecutive nodes.  Rows without a reference come out complete.
 // The records of consecutive rows are contiguous in the bit stream, so the block first copies the tile's whole span
@@ -853,7 +854,7 @@ static constexpr int HW_WORDS = 32;   // words of stream per lane and refill
 static constexpr int HW_PITCH = 35;   // row pitch in words (odd multiple: the 32 lanes hit 32 banks)
 static constexpr uint32_t HW_LOW = 29;  // refill when a reader's prefetched word index reaches this
 #ifndef WGBV_HEAVY_BLOCKS
-#define WGBV_HEAVY_BLOCKS 1
+#define WGBV_HEAVY_BLOCKS 3
 #endif
 #ifndef WGBV_GIANT_ROW
 #define WGBV_GIANT_ROW 4096

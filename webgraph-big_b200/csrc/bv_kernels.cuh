@@ -138,6 +138,7 @@ void launch_depth(const Launch &L, const GraphDev &g, const uint8_t *ref, uint32
 // the pass lists levels level0+1 .. level0+nlevels; level level0+l (l 1-based) occupies list[pos[(l-1) * nblocks] .. pos[l * nblocks]).  With ref != nullptr the depths are computed
 // on the way (bounded walk, *deep set if a chain is longer than nlevels) and stored to depth[]; with ref == nullptr depth[] is input.
 uint32_t deep_list_blocks(int64_t count);
+uint32_t heavy_threshold();  // rows with at least this many extras go through the global class-sorted list
 void launch_deep_lists(const Launch &L, const uint32_t *depth, const uint32_t *ids, int64_t count, uint32_t level0, uint32_t nlevels, uint32_t *counts,
                        int64_t *pos, uint32_t *list, uint64_t *scan_state, uint32_t *ticket);
 void launch_level_lists(const Launch &L, const GraphDev &g, const uint8_t *ref, uint32_t *depth, int64_t lo, int64_t from, int64_t count,

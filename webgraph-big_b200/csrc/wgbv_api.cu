@@ -716,9 +716,9 @@ static int decode_rows(wgbv_stream *s, int64_t from, int64_t to, Prepared &P, in
 	R.halo = s->halo.as<int64_t>();
 	if ((rc = s->row_info.ensure((size_t)std::max<int64_t>(P.cnt, 1) * sizeof(RowInfo)))) return rc;
 	R.info = s->row_info.as<RowInfo>();
-	// rows with >= 128 extras go through a global, class-sorted list: at most total_arcs / 128 of them (sized for 64)
+	// rows with many extras go through a global, class-sorted list: at most total_arcs / threshold of them
 	HeavyDev H;
-	const size_t hcap = (size_t)((P.arcs + P.halo_arcs) / 64 + 1);
+	const size_t hcap = (size_t)((P.arcs + P.halo_arcs) / heavy_threshold() + 1);
 	if ((rc = s->heavy_rows.ensure(hcap * 4)) || (rc = s->heavy_sorted.ensure(hcap * 4)) || (rc = s->heavy_cls.ensure(hcap)) ||
 	    (rc = s->heavy_counters.ensure(130 * 8)) || (rc = s->giants.ensure(sizeof(GiantRow) * GIANT_MAX)) ||
 	    (rc = s->gchunks.ensure(sizeof(GiantChunk) * (size_t)GIANT_MAX * GIANT_CHUNKS)))
