@@ -862,6 +862,11 @@ static constexpr uint32_t HW_LOW = 29;  // refill when a reader's prefetched wor
 static constexpr uint32_t GIANT_ROW = WGBV_GIANT_ROW;   // residuals from which a row is decoded by a whole warp
 static constexpr uint32_t GIANT_ROW2 = 32768;  // ... and from which by GIANT_CHUNKS warps (k_giant_*)
 
+__device__ __forceinline__ void cp_async4(void *smem_dst, const void *gmem_src) {
+	const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+	asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(gmem_src));
+}
+
 struct HeavyWindow {
 	static constexpr bool enabled = true;
 	uint32_t *win;          // this warp's HW_PITCH * 32 words
@@ -873,12 +878,16 @@ struct HeavyWindow {
 	__device__ __forceinline__ void fill(TileReader &r, uint64_t pos, bool mine) {
 		const unsigned lane = threadIdx.x & 31u;
 		const uint64_t my_w = pos >> 5;
+		// asynchronous copies (LDGSTS): the loads of all 32 rows are in flight together and nothing waits for a register --
+		// with plain loads the stores to shared memory made every group of four wait out a memory latency of its own
 #pragma unroll 4
 		for (int rr = 0; rr < 32; rr++) {
 			const uint64_t w = __shfl_sync(FULL_MASK, my_w, rr);
 			const uint64_t j = w + lane;
-			win[rr * HW_PITCH + lane] = j < nwords32 ? __ldg(words + j) : 0u;
+			if (j < nwords32) cp_async4(&win[rr * HW_PITCH + lane], words + j);
+			else win[rr * HW_PITCH + lane] = 0u;
 		}
+		asm volatile("cp.async.wait_all;" ::: "memory");
 		__syncwarp();
 		if (mine) {
 			wbase = my_w;
@@ -897,9 +906,11 @@ struct HeavyWindow {
 			const uint64_t w = __shfl_sync(mask, my_w, rr);
 			for (unsigned l = (unsigned)__popc(mask & ((1u << lane) - 1u)); l < (unsigned)HW_WORDS; l += (unsigned)__popc(mask)) {
 				const uint64_t j = w + l;
-				win[rr * HW_PITCH + l] = j < nwords32 ? __ldg(words + j) : 0u;
+				if (j < nwords32) cp_async4(&win[rr * HW_PITCH + l], words + j);
+				else win[rr * HW_PITCH + l] = 0u;
 			}
 		}
+		asm volatile("cp.async.wait_all;" ::: "memory");
 		__syncwarp(mask);
 		wbase = my_w;
 		r.init_words(win + lane * HW_PITCH, HW_WORDS, (uint32_t)(pos & 31u));
