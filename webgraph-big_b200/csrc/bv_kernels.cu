@@ -850,11 +850,14 @@ __global__ void __launch_bounds__(TPB) k_heavy_scatter(HeavyDev H) {
 // warp would wait for the slowest lane at every word boundary.  Instead the warp keeps a WINDOW of the next
 // HW_WORDS words of every lane's stream in shared memory, filled by all 32 lanes together with one coalesced
 // 128-byte load per row; the decoders read the window and the warp refills it whenever some lane runs low.
-static constexpr int HW_WORDS = 32;   // words of stream per lane and refill
-static constexpr int HW_PITCH = 35;   // row pitch in words (odd multiple: the 32 lanes hit 32 banks)
-static constexpr uint32_t HW_LOW = 29;  // refill when a reader's prefetched word index reaches this
+#ifndef WGBV_HW_WORDS
+#define WGBV_HW_WORDS 32
+#endif
+static constexpr int HW_WORDS = WGBV_HW_WORDS;   // words of stream per lane and refill (a multiple of 32)
+static constexpr int HW_PITCH = HW_WORDS + 3;    // row pitch in words (odd: the 32 lanes hit 32 banks)
+static constexpr uint32_t HW_LOW = HW_WORDS - 3; // refill when a reader's prefetched word index reaches this
 #ifndef WGBV_HEAVY_BLOCKS
-#define WGBV_HEAVY_BLOCKS 3
+#define WGBV_HEAVY_BLOCKS 2
 #endif
 #ifndef WGBV_GIANT_ROW
 #define WGBV_GIANT_ROW 4096
@@ -883,9 +886,12 @@ struct HeavyWindow {
 #pragma unroll 4
 		for (int rr = 0; rr < 32; rr++) {
 			const uint64_t w = __shfl_sync(FULL_MASK, my_w, rr);
-			const uint64_t j = w + lane;
-			if (j < nwords32) cp_async4(&win[rr * HW_PITCH + lane], words + j);
-			else win[rr * HW_PITCH + lane] = 0u;
+#pragma unroll
+			for (int k = 0; k < HW_WORDS; k += 32) {
+				const uint64_t j = w + k + lane;
+				if (j < nwords32) cp_async4(&win[rr * HW_PITCH + k + lane], words + j);
+				else win[rr * HW_PITCH + k + lane] = 0u;
+			}
 		}
 		asm volatile("cp.async.wait_all;" ::: "memory");
 		__syncwarp();
@@ -919,13 +925,13 @@ struct HeavyWindow {
 
 template <int DEF>
 __global__ void __launch_bounds__(TPB, WGBV_HEAVY_BLOCKS) k_extras_heavy(GraphDev g, RangeDev R, HeavyDev H) {
-	__shared__ uint32_t s_win[TPB / 32][32 * HW_PITCH];
+	extern __shared__ __align__(16) uint32_t s_win[];  // [TPB / 32][32 * HW_PITCH]
 	const unsigned long long total = H.counters[0];
 	const int64_t rp_from = R.rp[R.from - R.lo];
 	const unsigned long long warps = (unsigned long long)gridDim.x * (TPB / 32);
 	const unsigned lane = threadIdx.x & 31;
 	HeavyWindow win;
-	win.win = s_win[threadIdx.x >> 5];
+	win.win = s_win + (threadIdx.x >> 5) * (32 * HW_PITCH);
 	win.words = (const uint32_t *)g.words;
 	win.nwords32 = g.nwords * 2;
 	win.wbase = 0;
@@ -1195,10 +1201,19 @@ void launch_extras(const Launch &L, const GraphDev &g, int def, const RangeDev &
 	const unsigned grid = (unsigned)std::min<int64_t>(grid_for(count / 8 + 1, TILE), 148 * 8);
 	k_heavy_scatter<<<grid, TPB, 0, L.stream>>>(h);
 	WGBV_LAUNCHED(L);
+	const size_t hsmem = (size_t)(TPB / 32) * 32 * HW_PITCH * sizeof(uint32_t);
 	switch (def) {
-	case 2: k_extras_heavy<2><<<148 * 8, TPB, 0, L.stream>>>(g, r, h); break;
-	case 1: k_extras_heavy<1><<<148 * 8, TPB, 0, L.stream>>>(g, r, h); break;
-	default: k_extras_heavy<0><<<148 * 8, TPB, 0, L.stream>>>(g, r, h);
+	case 2:
+		cudaFuncSetAttribute(k_extras_heavy<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hsmem);
+		k_extras_heavy<2><<<148 * 8, TPB, hsmem, L.stream>>>(g, r, h);
+		break;
+	case 1:
+		cudaFuncSetAttribute(k_extras_heavy<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hsmem);
+		k_extras_heavy<1><<<148 * 8, TPB, hsmem, L.stream>>>(g, r, h);
+		break;
+	default:
+		cudaFuncSetAttribute(k_extras_heavy<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hsmem);
+		k_extras_heavy<0><<<148 * 8, TPB, hsmem, L.stream>>>(g, r, h);
 	}
 	WGBV_LAUNCHED(L);
 	if (!h.giants) return;
