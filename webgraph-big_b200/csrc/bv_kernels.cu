@@ -437,7 +437,7 @@ static constexpr int TILE = TPB * RPT;   // rows per block: the sort domain (see
 // by class over the whole range (k_heavy_scatter), and decoded by k_extras_heavy where every warp finds 32 rows of
 // one class.
 #ifndef WGBV_HEAVY
-#define WGBV_HEAVY 48
+#define WGBV_HEAVY 128
 #endif
 static constexpr uint32_t HEAVY = WGBV_HEAVY;
 uint32_t heavy_threshold() { return HEAVY; }
