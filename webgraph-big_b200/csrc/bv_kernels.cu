@@ -1540,56 +1540,138 @@ __device__ __forceinline__ int64_t *chain_slot(const ChainDev &c, uint64_t row) 
 	return (c.is_query[row] ? c.col : c.store) + c.dst_off[row];
 }
 
+// The rows of a batch come in no order and differ wildly in length, so both chain kernels do what the bulk kernels do:
+// a block parses the heads of CHT rows, sorts them by work class in shared memory and only then runs the serial part,
+// 32 rows of one class per warp (unsorted, one row per thread, they ran at 9 and 2-4 active lanes per instruction).
+static constexpr int CHRPT = 4;
+static constexpr int CHT = TPB * CHRPT;
+
+struct ChainSmem {
+	uint64_t a[CHT], b[CHT];  // extras: reader position, (extras, copied); copy: the row's RowInfo
+	uint32_t hist[NBUCKETS + 1];
+	uint16_t order[CHT];
+};
+
 template <int DEF>
 __global__ void __launch_bounds__(TPB) k_chain_extras(GraphDev g, ChainDev c, uint64_t rows) {
-	const uint64_t row = (uint64_t)blockIdx.x * TPB + threadIdx.x;
-	const bool active = row < rows && c.deg[row] != 0;
-	const unsigned mask = __ballot_sync(FULL_MASK, active);
-	if (!active) return;
-	const int64_t x = c.node[row];
-	const int32_t p = c.parent[row];
-	BitReader r;
-	r.init(g, ef_get(g, x));
-	RowHead h;
-	row_head<DEF>(g, r, p >= 0 ? c.deg[p] : 0, h);
-	__syncwarp(mask);
-	row_extras<DEF>(g, r, x, h.d - h.ncopied, chain_slot(c, row) + h.ncopied, mask);
+	__shared__ ChainSmem S;
+	const uint64_t base = (uint64_t)blockIdx.x * CHT;
+	int bucket[CHRPT];
+#pragma unroll 1
+	for (int q = 0; q < CHRPT; q++) {
+		const int id = q * TPB + (int)threadIdx.x;
+		const uint64_t row = base + id;
+		bucket[q] = -1;
+		if (row < rows && c.deg[row] != 0) {
+			const int32_t p = c.parent[row];
+			BitReader r;
+			r.init(g, ef_get(g, c.node[row]));
+			RowHead h;
+			row_head<DEF>(g, r, p >= 0 ? c.deg[p] : 0, h);
+			const uint32_t nextra = h.d - h.ncopied;
+			if (nextra) {
+				bucket[q] = work_bucket(nextra);
+				S.a[id] = r.tell();
+				S.b[id] = (uint64_t)nextra | (uint64_t)h.ncopied << 32;
+			}
+		}
+		__syncwarp();
+	}
+	uint32_t total;
+	block_bin_sort<CHRPT>(bucket, S.hist, S.order, &total);
+#pragma unroll 1
+	for (uint32_t tb = (threadIdx.x & ~31u); tb < total; tb += TPB) {
+		const uint32_t t = tb + (threadIdx.x & 31u);
+		const bool active = t < total;
+		const unsigned mask = __ballot_sync(FULL_MASK, active);
+		if (active) {
+			const int id = S.order[t];
+			const uint64_t row = base + id;
+			BitReader r;
+			r.init(g, S.a[id]);
+			row_extras<DEF>(g, r, c.node[row], (uint32_t)S.b[id], chain_slot(c, row) + (uint32_t)(S.b[id] >> 32), mask);
+		}
+	}
 }
 void launch_chain_extras(const Launch &L, const GraphDev &g, int def, const ChainDev &c, uint64_t rows) {
 	if (!rows) return;
 	switch (def) {
-	case 2: k_chain_extras<2><<<grid_for((int64_t)rows, TPB), TPB, 0, L.stream>>>(g, c, rows); break;
-	case 1: k_chain_extras<1><<<grid_for((int64_t)rows, TPB), TPB, 0, L.stream>>>(g, c, rows); break;
-	default: k_chain_extras<0><<<grid_for((int64_t)rows, TPB), TPB, 0, L.stream>>>(g, c, rows);
+	case 2: k_chain_extras<2><<<grid_for((int64_t)rows, CHT), TPB, 0, L.stream>>>(g, c, rows); break;
+	case 1: k_chain_extras<1><<<grid_for((int64_t)rows, CHT), TPB, 0, L.stream>>>(g, c, rows); break;
+	default: k_chain_extras<0><<<grid_for((int64_t)rows, CHT), TPB, 0, L.stream>>>(g, c, rows);
 	}
 	WGBV_LAUNCHED(L);
 }
 
+// One level of the chains: the rows whose parent (the row holding their reference list) is complete.  As in
+// k_copy_level: rows of fewer than WARP_ROW successors whose parent has at most 128 are merged one lane per row from the
+// mask of copied positions, the others by a whole warp each from the block codes.
 template <int DEF>
 __global__ void __launch_bounds__(TPB) k_chain_copy(GraphDev g, ChainDev c, uint64_t rows, const uint32_t *__restrict__ level,
                                                     uint32_t this_level) {
-	const uint64_t row = (uint64_t)blockIdx.x * TPB + threadIdx.x;
-	const bool active = row < rows && level[row] == this_level && c.deg[row] != 0 && c.parent[row] >= 0;
-	const unsigned mask = __ballot_sync(FULL_MASK, active);
-	if (!active) return;
-	const int32_t p = c.parent[row];
-	const int64_t x = c.node[row];
-	const uint32_t dref = c.deg[p];
-	BitReader r;
-	r.init(g, ef_get(g, x));
-	RowHead h;
-	row_head<DEF>(g, r, dref, h);
-	r.seek(h.blocks_pos);
-	__syncwarp(mask);
-	row_copy<DEF>(g, r, chain_slot(c, (uint64_t)p), dref, chain_slot(c, row) + h.ncopied, chain_slot(c, row), h.d, h.bc, h.ncopied, mask);
+	__shared__ ChainSmem S;
+	const uint64_t base = (uint64_t)blockIdx.x * CHT;
+	int bucket[CHRPT];
+#pragma unroll 1
+	for (int q = 0; q < CHRPT; q++) {
+		const int id = q * TPB + (int)threadIdx.x;
+		const uint64_t row = base + id;
+		bucket[q] = -1;
+		if (row < rows && level[row] == this_level && c.deg[row] != 0 && c.parent[row] >= 0) {
+			const uint32_t d = c.deg[row], dref = c.deg[c.parent[row]];
+			const bool masked = row_is_masked(d, dref);
+			BitReader r;
+			r.init(g, ef_get(g, c.node[row]));
+			RowHead h;
+			row_head<DEF>(g, r, dref, h);
+			const uint64_t ra = masked ? h.cmask[0] : h.blocks_pos;
+			const uint64_t rb = masked ? h.cmask[1] : (uint64_t)h.ncopied | (uint64_t)h.bc << 32;
+			if (masked ? (ra | rb) != 0 : (uint32_t)rb != 0) {
+				bucket[q] = 2 * work_bucket(masked || d >= WARP_ROW ? d : WARP_ROW);
+				S.a[id] = ra;
+				S.b[id] = rb;
+			}
+		}
+		__syncwarp();
+	}
+	uint32_t total;
+	block_bin_sort<CHRPT>(bucket, S.hist, S.order, &total);
+	const unsigned lane = threadIdx.x & 31u;
+	const uint32_t nbig = S.hist[2 * work_bucket(WARP_ROW - 1)];
+#pragma unroll 1
+	for (uint32_t t = threadIdx.x >> 5; t < nbig; t += TPB / 32) {
+		const int id = S.order[t];
+		const uint64_t row = base + id;
+		const uint64_t p = (uint64_t)c.parent[row];
+		const uint32_t ncopied = (uint32_t)S.b[id];
+		int64_t *dst = chain_slot(c, row);
+		BitReader r;
+		r.init(g, S.a[id]);
+		row_copy_warp<DEF>(g, r, chain_slot(c, p), c.deg[p], dst + ncopied, dst, c.deg[row], (uint32_t)(S.b[id] >> 32), ncopied);
+	}
+	__syncwarp();
+#pragma unroll 1
+	for (uint32_t tb = nbig + (threadIdx.x & ~31u); tb < total; tb += TPB) {
+		const uint32_t t = tb + lane;
+		const bool active = t < total;
+		const unsigned mask = __ballot_sync(FULL_MASK, active);
+		if (active) {
+			const int id = S.order[t];
+			const uint64_t row = base + id;
+			const uint64_t m0 = S.a[id], m1 = S.b[id];
+			const uint32_t ncopied = (uint32_t)(__popcll(m0) + __popcll(m1));
+			int64_t *dst = chain_slot(c, row);
+			row_copy_masked(g, chain_slot(c, (uint64_t)c.parent[row]), m0, m1, dst + ncopied, dst, c.deg[row] - ncopied, mask);
+		}
+	}
 }
 void launch_chain_copy(const Launch &L, const GraphDev &g, int def, const ChainDev &c, uint64_t rows, const uint32_t *level,
                        uint32_t this_level) {
 	if (!rows) return;
 	switch (def) {
-	case 2: k_chain_copy<2><<<grid_for((int64_t)rows, TPB), TPB, 0, L.stream>>>(g, c, rows, level, this_level); break;
-	case 1: k_chain_copy<1><<<grid_for((int64_t)rows, TPB), TPB, 0, L.stream>>>(g, c, rows, level, this_level); break;
-	default: k_chain_copy<0><<<grid_for((int64_t)rows, TPB), TPB, 0, L.stream>>>(g, c, rows, level, this_level);
+	case 2: k_chain_copy<2><<<grid_for((int64_t)rows, CHT), TPB, 0, L.stream>>>(g, c, rows, level, this_level); break;
+	case 1: k_chain_copy<1><<<grid_for((int64_t)rows, CHT), TPB, 0, L.stream>>>(g, c, rows, level, this_level); break;
+	default: k_chain_copy<0><<<grid_for((int64_t)rows, CHT), TPB, 0, L.stream>>>(g, c, rows, level, this_level);
 	}
 	WGBV_LAUNCHED(L);
 }
