@@ -1567,7 +1567,16 @@ __global__ void __launch_bounds__(TPB) k_chain_extras(GraphDev g, ChainDev c, ui
 			BitReader r;
 			r.init(g, ef_get(g, c.node[row]));
 			RowHead h;
-			row_head<DEF>(g, r, p >= 0 ? c.deg[p] : 0, h);
+			const uint32_t dref = p >= 0 ? c.deg[p] : 0;
+			row_head<DEF>(g, r, dref, h);
+			if (p >= 0) {
+				// (left for the level that merges this row: it does not parse the head again)
+				const bool masked = row_is_masked(h.d, dref);
+				RowInfo ri;
+				ri.a = masked ? h.cmask[0] : h.blocks_pos;
+				ri.b = masked ? h.cmask[1] : (uint64_t)h.ncopied | (uint64_t)h.bc << 32;
+				c.info[row] = ri;
+			}
 			const uint32_t nextra = h.d - h.ncopied;
 			if (nextra) {
 				bucket[q] = work_bucket(nextra);
@@ -1620,12 +1629,8 @@ __global__ void __launch_bounds__(TPB) k_chain_copy(GraphDev g, ChainDev c, uint
 		if (row < rows && level[row] == this_level && c.deg[row] != 0 && c.parent[row] >= 0) {
 			const uint32_t d = c.deg[row], dref = c.deg[c.parent[row]];
 			const bool masked = row_is_masked(d, dref);
-			BitReader r;
-			r.init(g, ef_get(g, c.node[row]));
-			RowHead h;
-			row_head<DEF>(g, r, dref, h);
-			const uint64_t ra = masked ? h.cmask[0] : h.blocks_pos;
-			const uint64_t rb = masked ? h.cmask[1] : (uint64_t)h.ncopied | (uint64_t)h.bc << 32;
+			const RowInfo ri = c.info[row];  // k_chain_extras left what it parsed
+			const uint64_t ra = ri.a, rb = ri.b;
 			if (masked ? (ra | rb) != 0 : (uint32_t)rb != 0) {
 				bucket[q] = 2 * work_bucket(masked || d >= WARP_ROW ? d : WARP_ROW);
 				S.a[id] = ra;

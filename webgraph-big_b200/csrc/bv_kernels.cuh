@@ -57,6 +57,7 @@ struct ChainDev {
 	const uint8_t *is_query; // 1: the row is a query's own list (goes to col), 0: ancestor (goes to store)
 	int64_t *col;
 	int64_t *store;
+	RowInfo *info;  // per chain row with a parent: what k_chain_extras parsed (mask of copied positions, or where the blocks start), for k_chain_copy
 };
 
 // The global list of rows whose extras are too long to be decoded inside their tile (see bv_kernels.cu).

@@ -89,7 +89,7 @@ struct wgbv_stream {
 	std::vector<FusedCall> fused_pending;
 	uint64_t fused_fallbacks = 0;  // decodes that were rerun
 	uint32_t last_slow_tiles = 0, last_tiles = 0;
-	DevBuf c_node, c_dst, c_parent, c_deg, c_isq, c_level, c_len, c_arcs, c_row0, c_soff, c_store;
+	DevBuf c_node, c_dst, c_parent, c_deg, c_isq, c_level, c_len, c_arcs, c_row0, c_soff, c_store, c_info;
 	cudaEvent_t ev[6]{};
 	bool ev_valid = false;
 	Launch launch() { return Launch{stream, &launches}; }
@@ -513,7 +513,7 @@ extern "C" void wgbv_stream_destroy(wgbv_stream *s) {
 	for (DevBuf *b : {&s->t_pairs[0], &s->t_pairs[1], &s->t_indeg, &s->t_counts, &s->t_pos, &s->sym_rowptr, &s->sym_col}) b->release();
 	for (DevBuf *b : {&s->deg, &s->ref, &s->depth, &s->rp, &s->scan_state, &s->ticket, &s->halo, &s->levels, &s->list, &s->list2, &s->col,
 	                  &s->rowptr, &s->ids, &s->batch, &s->heavy_rows, &s->heavy_sorted, &s->heavy_cls, &s->heavy_counters, &s->giants, &s->gchunks, &s->tile_done, &s->level_pos, &s->row_info, &s->c_node, &s->c_dst, &s->c_parent, &s->c_deg, &s->c_isq, &s->c_level,
-	                  &s->c_len, &s->c_arcs, &s->c_row0, &s->c_soff, &s->c_store})
+	                  &s->c_len, &s->c_arcs, &s->c_row0, &s->c_soff, &s->c_store, &s->c_info})
 		b->release();
 	for (auto &sl : s->slot) {
 		sl.d_rowptr.release();
@@ -1489,7 +1489,7 @@ extern "C" int wgbv_successors_batch(wgbv_stream *s, const int64_t *d_ids, uint6
 	if (rows >= 0x7ffffff0ull) return fail(WGBV_EARG, "the batch expands to too many chain rows; split it");
 	const size_t r = (size_t)std::max<uint64_t>(rows, 1);
 	if ((rc = s->c_node.ensure(r * 8)) || (rc = s->c_dst.ensure(r * 8)) || (rc = s->c_parent.ensure(r * 4)) || (rc = s->c_deg.ensure(r * 4)) ||
-	    (rc = s->c_isq.ensure(r)) || (rc = s->c_level.ensure(r * 4)) || (rc = s->c_store.ensure((size_t)std::max<uint64_t>(store, 1) * 8)))
+	    (rc = s->c_isq.ensure(r)) || (rc = s->c_level.ensure(r * 4)) || (rc = s->c_info.ensure(r * sizeof(RowInfo))) || (rc = s->c_store.ensure((size_t)std::max<uint64_t>(store, 1) * 8)))
 		return rc;
 	launch_chain_fill(L, s->dev, g->def_codes, d_ids, k, s->c_row0.as<int64_t>(), s->c_soff.as<int64_t>(), d_rowptr, s->c_node.as<int64_t>(),
 	                  s->c_dst.as<int64_t>(), s->c_parent.as<int32_t>(), s->c_deg.as<uint32_t>(), s->c_isq.as<uint8_t>(), s->c_level.as<uint32_t>());
@@ -1501,6 +1501,7 @@ extern "C" int wgbv_successors_batch(wgbv_stream *s, const int64_t *d_ids, uint6
 	C.is_query = s->c_isq.as<uint8_t>();
 	C.col = d_col;
 	C.store = s->c_store.as<int64_t>();
+	C.info = s->c_info.as<RowInfo>();
 	launch_chain_extras(L, s->dev, g->def_codes, C, rows);
 	for (uint32_t lev = 1; lev < max_len; lev++) launch_chain_copy(L, s->dev, g->def_codes, C, rows, s->c_level.as<uint32_t>(), lev);
 	const cudaError_t e = cudaGetLastError();
