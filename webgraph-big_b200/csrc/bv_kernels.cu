@@ -448,12 +448,12 @@ uint32_t heavy_threshold() { return HEAVY; }
 // shared-memory latency instead of waiting for L2/DRAM at every word boundary of every lane; a tile whose span does
 // not fit (a very long row in it) reads global memory instead.
 #ifndef WGBV_ERPT
-#define WGBV_ERPT 4
-#define WGBV_EBITS 9216
+#define WGBV_ERPT 3      // 768 rows per tile, five blocks per SM: 28.59 ms per 1e8 nodes against 28.81 with 1024 rows and four
+#define WGBV_EBITS 6912
 #endif
 static constexpr int ERPT = WGBV_ERPT;
 static constexpr int ETILE = TPB * ERPT;
-static constexpr int EBITS = WGBV_EBITS;  // 32-bit words of the stream a tile may stage (36 KiB)
+static constexpr int EBITS = WGBV_EBITS;  // 32-bit words of the stream a tile may stage (27 KiB: 9 words per row)
 
 __device__ __forceinline__ void cp_async16(void *smem_dst, const void *gmem_src) {
 	const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
@@ -473,14 +473,14 @@ struct ExtrasSmem {
 	uint64_t wbase;  // stream word index of bits[0]
 	uint32_t nw;     // words staged
 	// one-launch front end.  (The outdegrees of the rows just before the tile, reference rows of its first rows, are
-	// kept in `order`, which is not needed before the sort: 256 uint32 -- see hdeg().  Four blocks of this size fit an SM.)
+	// kept in `order`, which is not needed before the sort: 256 uint32 -- see hdeg().  Five blocks of this size fit an SM.)
 	uint64_t warp_sum[TPB / 32];
 	uint64_t tile_base;          // arcs before the tile
 	uint64_t tile_total;         // arcs of the tile
 	uint32_t tile;
 };
 
-static_assert(sizeof(ExtrasSmem) <= 56 * 1024, "four blocks of k_extras per SM");
+static_assert(sizeof(ExtrasSmem) <= 44 * 1024, "five blocks of k_extras per SM");
 static_assert(ETILE * sizeof(uint16_t) >= 256 * sizeof(uint32_t), "hdeg() borrows ExtrasSmem::order");
 __device__ __forceinline__ uint32_t *hdeg(ExtrasSmem &S) { return reinterpret_cast<uint32_t *>(S.order); }
 
