@@ -1249,8 +1249,11 @@ struct CopySmem {
 	uint16_t order[CTILE];
 };
 
+#ifndef WGBV_COPY_BLOCKS
+#define WGBV_COPY_BLOCKS 5  // 48 registers, five blocks per SM: 27.9 ms per 1e8 nodes (four blocks 28.6, six 28.3, eight 28.7)
+#endif
 template <int DEF>
-__global__ void __launch_bounds__(TPB) k_copy_level(GraphDev g, RangeDev R, uint32_t level, const uint32_t *__restrict__ list,
+__global__ void __launch_bounds__(TPB, WGBV_COPY_BLOCKS) k_copy_level(GraphDev g, RangeDev R, uint32_t level, const uint32_t *__restrict__ list,
                                                     uint64_t list_count) {
 	extern __shared__ __align__(16) unsigned char smem_raw[];
 	CopySmem &S = *reinterpret_cast<CopySmem *>(smem_raw);
