@@ -72,6 +72,57 @@ __global__ void __launch_bounds__(TPB) k_labels_check(GraphDev lab, int64_t from
 	if (ef_get(lab, from + i + 1) - ef_get(lab, from + i) != (uint64_t)(rp[i + 1] - rp[i]) * (uint64_t)width) raise(lab, ERR_DEGREE);
 }
 
+// Gamma-coded labels, load-balanced: the labels of a node can only be read one after the other, and outdegrees are heavy-
+// tailed, so a warp whose 32 lanes take 32 consecutive nodes runs at the pace of its longest node with most lanes idle.
+// As in the successor kernels a block first looks at LT nodes, sorts them by outdegree class in shared memory and then
+// decodes 32 nodes of one class per warp in lock step.
+static constexpr int LRPT = 4;
+static constexpr int LT = TPB * LRPT;
+
+__global__ void __launch_bounds__(TPB) k_labels_gamma(GraphDev lab, int64_t from, int64_t count, const int64_t *__restrict__ rp,
+                                                      int64_t *__restrict__ out, uint64_t capacity) {
+	__shared__ uint32_t hist[NBUCKETS + 1];
+	__shared__ uint16_t order[LT];
+	const int64_t base = (int64_t)blockIdx.x * LT;
+	const int64_t rp0 = rp[0];
+	int bucket[LRPT];
+#pragma unroll
+	for (int q = 0; q < LRPT; q++) {
+		const int64_t i = base + q * TPB + threadIdx.x;
+		bucket[q] = -1;
+		if (i < count) {
+			const int64_t a = rp[i] - rp0, b = rp[i + 1] - rp0;
+			if ((uint64_t)b > capacity) raise(lab, ERR_CAPACITY);
+			else if (b > a) bucket[q] = work_bucket((uint32_t)(b - a > 0x7fffffff ? 0x7fffffff : b - a));
+			else if (ef_get(lab, from + i + 1) != ef_get(lab, from + i)) raise(lab, ERR_DEGREE);  // no arcs: no label bits
+		}
+	}
+	uint32_t total;
+	block_bin_sort<LRPT>(bucket, hist, order, &total);
+#pragma unroll 1
+	for (uint32_t tb = (threadIdx.x & ~31u); tb < total; tb += TPB) {
+		const uint32_t t = tb + (threadIdx.x & 31u);
+		const bool active = t < total;
+		int64_t j = 0, b = 0;
+		uint64_t end = 0;
+		BitReader r;
+		if (active) {
+			const int64_t i = base + order[t];
+			j = rp[i] - rp0;
+			b = rp[i + 1] - rp0;
+			end = ef_get(lab, from + i + 1);
+			r.init(lab, ef_get(lab, from + i));
+		}
+		while (__any_sync(0xffffffffu, j < b)) {  // (lanes without a node have j == b)
+			if (j < b) {
+				out[j] = (int64_t)(int32_t)(uint32_t)r.gamma();  // the Java field is an int
+				j++;
+			}
+		}
+		if (active && r.tell() != end) raise(lab, ERR_DEGREE);
+	}
+}
+
 void launch_labels(const Launch &L, const GraphDev &lab, int kind, int width, int64_t from, int64_t count, const int64_t *rowptr,
                    int64_t *out, uint64_t capacity, uint64_t arcs_bound) {
 	if (count <= 0) return;
@@ -83,7 +134,7 @@ void launch_labels(const Launch &L, const GraphDev &lab, int kind, int width, in
 			WGBV_LAUNCHED(L);
 		}
 	} else {
-		k_labels<1><<<grid_for(count, TPB), TPB, 0, L.stream>>>(lab, from, count, rowptr, width, out, capacity);
+		k_labels_gamma<<<grid_for(count, LT), TPB, 0, L.stream>>>(lab, from, count, rowptr, out, capacity);
 		WGBV_LAUNCHED(L);
 	}
 }
