@@ -191,6 +191,26 @@ def test_graph_without_offsets_file(cnr_basename, cnr_golden):
         assert np.array_equal(c2, np.concatenate([col[rowptr[x]:rowptr[x + 1]] for x in ids]))
 
 
+def test_properties_that_understate_the_arc_count():
+    """The scratch list of long rows is sized from the arc count the .properties promise.  A file that holds far more arcs
+    than it says (here: 1000 instead of millions, with thousands of rows of hundreds of successors) is reported
+    (IllegalStateException) instead of writing past the list; the same graph with honest properties decodes."""
+    import re
+    torch = pytest.importorskip("torch")
+    e = bg.copy_model(30000, seed=6, mean_degree=300, max_degree=20000, nsplits=2)
+    deg, col = oracle_of(e).decode_range()
+    lying = re.sub(r"(?m)^arcs=\d+$", "arcs=1000", e.properties_text())
+    assert lying != e.properties_text()
+    d_rp = torch.empty(e.n + 1, dtype=torch.int64, device="cuda")
+    d_col = torch.empty(col.size, dtype=torch.int64, device="cuda")
+    with wg.GpuBVGraph.load_mem(lying, e.graph, e.offsets_stream) as g:
+        with pytest.raises(wg.IllegalStateException):
+            g.decodeToCSRDevice(0, e.n, d_rp.data_ptr(), d_col.data_ptr(), col.size)
+    with gpu_of(e) as g:
+        g.decodeToCSRDevice(0, e.n, d_rp.data_ptr(), d_col.data_ptr(), col.size)
+        assert np.array_equal(d_col.cpu().numpy(), col)
+
+
 def test_checksum_kernel_matches_generator_hash(cnr, cnr_golden):
     torch = pytest.importorskip("torch")
     deg, rowptr, col = cnr_golden

@@ -706,10 +706,15 @@ __device__ __forceinline__ void extras_tile(const GraphDev &g, const RangeDev &R
 		if (threadIdx.x == 0) S.gbase = atomicAdd(&H.counters[0], (unsigned long long)nheavy);
 		__syncthreads();
 		if ((int)threadIdx.x < 2 * fl && S.count[threadIdx.x]) atomicAdd(&H.counters[1 + threadIdx.x], (unsigned long long)S.count[threadIdx.x]);
+		// (the list is sized from the arc count of the .properties: a file that holds more than it promises is reported,
+		// never written past the list; the heavy-row kernels then do nothing)
+		if (S.gbase + nheavy > H.capacity && threadIdx.x == 0) raise(g, ERR_DEGREE);
 		for (uint32_t t = threadIdx.x; t < nheavy; t += TPB) {
 			const int id = S.order[t < nheavy_a ? t : a1 + (t - nheavy_a)];
-			H.rows[S.gbase + t] = (uint32_t)(base + id);
-			H.cls[S.gbase + t] = S.cls[id];
+			if (S.gbase + t < H.capacity) {
+				H.rows[S.gbase + t] = (uint32_t)(base + id);
+				H.cls[S.gbase + t] = S.cls[id];
+			}
 		}
 	}
 	// serial part: the lanes of a warp take rows of the same class and run them in lock step (first the light rows with
@@ -822,6 +827,7 @@ __global__ void __launch_bounds__(TPB) k_heavy_scatter(HeavyDev H) {
 	__shared__ uint32_t s_cnt[BIN_CLASSES];
 	__shared__ unsigned long long s_start[BIN_CLASSES];
 	const unsigned long long total = H.counters[0];
+	if (total > H.capacity) return;  // reported by k_extras
 	for (unsigned long long tile = (unsigned long long)blockIdx.x * TILE; tile < total; tile += (unsigned long long)gridDim.x * TILE) {
 		if (threadIdx.x < BIN_CLASSES) s_cnt[threadIdx.x] = 0;
 		__syncthreads();
@@ -927,6 +933,7 @@ template <int DEF>
 __global__ void __launch_bounds__(TPB, WGBV_HEAVY_BLOCKS) k_extras_heavy(GraphDev g, RangeDev R, HeavyDev H) {
 	extern __shared__ __align__(16) uint32_t s_win[];  // [TPB / 32][32 * HW_PITCH]
 	const unsigned long long total = H.counters[0];
+	if (total > H.capacity) return;  // reported by k_extras: the list is incomplete
 	const int64_t rp_from = R.rp[R.from - R.lo];
 	const unsigned long long warps = (unsigned long long)gridDim.x * (TPB / 32);
 	const unsigned lane = threadIdx.x & 31;

@@ -85,6 +85,7 @@ static constexpr uint32_t GIANT_LEAD = 4096;
 
 struct HeavyDev {
 	uint32_t *rows;    // row indices (relative to RangeDev.lo) in arrival order; nullptr disables the heavy path
+	unsigned long long capacity;  // entries the three arrays can hold (sized from the arc count the properties promise)
 	uint8_t *cls;      // class of each entry
 	uint32_t *sorted;  // row indices sorted by class, heaviest first
 	unsigned long long *counters;  // [0] entries, [1..64] per-class counts, [65..128] per-class cursors, [129] giant rows

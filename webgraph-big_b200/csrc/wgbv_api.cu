@@ -724,6 +724,7 @@ static int decode_rows(wgbv_stream *s, int64_t from, int64_t to, Prepared &P, in
 	    (rc = s->gchunks.ensure(sizeof(GiantChunk) * (size_t)GIANT_MAX * GIANT_CHUNKS)))
 		return rc;
 	H.rows = s->heavy_rows.as<uint32_t>();
+	H.capacity = hcap;
 	H.sorted = s->heavy_sorted.as<uint32_t>();
 	H.cls = s->heavy_cls.as<uint8_t>();
 	H.counters = s->heavy_counters.as<unsigned long long>();
